@@ -1,0 +1,93 @@
+/*
+ * sse_oracle.h -- CPU restatement of the reference's per-token hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing in the product (include/, the CUDA library,
+ * the host layer) may include, link or call this.  Only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline / --impl reference legs use it, and only as the checker
+ * or as the timed CPU baseline.
+ *
+ * PARITY STATUS
+ *   decode / filter / encode / frame / bridge subject:  PARITY UNPINNED.
+ *     The arithmetic of this path lives in the Go standard library (encoding/json,
+ *     fmt; toolchain pinned to golang:1.21 by src/sse-adapter/Dockerfile:2), which is
+ *     not vendored in /root/reference and no Go toolchain exists in this image.  The
+ *     reference holds no test or golden vector for the path.  This file restates the
+ *     published algorithm of encoding/json 1.21 (scanner.go, decode.go, encode.go,
+ *     fold.go) and is anchored on the reference's call sites cited per function.
+ *   inspection Set B:  pinned by the reference's three known-answer tests
+ *     (src/spin-functions/nats-subscriber/src/lib.rs:108-124).
+ *   inspection Set A, interest matching:  PARITY UNPINNED (doc snippets / third-party).
+ */
+#ifndef SSE_ORACLE_H
+#define SSE_ORACLE_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* per-record status word; the numeric values are part of the product ABI too
+ * (include/ssegpu.h) and a test asserts that the two headers agree. */
+#define SSEO_OK            0u
+#define SSEO_ERR_SYNTAX    1u   /* json.Unmarshal syntax error  -> message dropped   */
+#define SSEO_ERR_TYPE      2u   /* json.Unmarshal type error    -> message dropped   */
+#define SSEO_FILTERED      3u   /* /stream Last-Event-ID filter -> message skipped   */
+#define SSEO_INSPECT_DROP  4u   /* inline inspection said drop  -> message skipped   */
+#define SSEO_CODE_MASK     0xFu
+#define SSEO_DONE          0x100u /* decoded done==true and the record was emitted    */
+#define SSEO_REDACTED      0x200u /* inline inspection replaced the token text       */
+
+/* TokenMessage (src/sse-adapter/sse_handler.go:46-52) after json.Unmarshal. */
+typedef struct {
+    const uint8_t *cid; uint32_t cid_len;   /* ConversationID, decoded UTF-8 */
+    const uint8_t *tok; uint32_t tok_len;   /* Token, decoded UTF-8          */
+    int64_t seq;                            /* Sequence                      */
+    int64_t ts;                             /* Timestamp                     */
+    int     done;                           /* Done                          */
+} sseo_msg;
+
+/* json.Unmarshal(data, &TokenMessage{})  (sse_handler.go:136-140, :317-321;
+ * redis-nats-bridge/main.go:153-157).  scratch must hold 6*n+16 bytes; the decoded
+ * strings point into it.  Returns SSEO_OK, SSEO_ERR_SYNTAX or SSEO_ERR_TYPE. */
+int sseo_unmarshal(const uint8_t *data, size_t n, sseo_msg *m, uint8_t *scratch);
+
+/* json.Marshal(token) (sse_handler.go:211, :427; bridge main.go:161).
+ * go122!=0 selects the Go>=1.22 spelling of 0x08/0x0C ("\b","\f").  Returns length. */
+size_t sseo_marshal(const sseo_msg *m, uint8_t *dst, int go122);
+size_t sseo_marshal_bound(const sseo_msg *m);
+
+/* The three Fprintf calls (sse_handler.go:212-214, :428-430). Returns frame length. */
+size_t sseo_frame(const sseo_msg *m, uint8_t *dst, int go122);
+
+/* fmt.Sscanf(lastEventID,"%d",&s); s++  (sse_handler.go:92-96).  id==NULL or "" -> 0. */
+int64_t sseo_start_sequence(const char *last_event_id);
+
+/* Whole-batch adapter path: decode -> filter -> encode -> frame, frames packed
+ * back to back.  in_off has n+1 entries; start_seq may be NULL (filter off) and holds
+ * the per-record startSequence (0 = off).  out_off gets n+1 entries.  A dropped or
+ * filtered record has a zero-length slice.  Returns 0, or -1 if out_cap is too small. */
+int sseo_adapter_batch(const uint8_t *in, const uint32_t *in_off, uint32_t n,
+                       const int64_t *start_seq, int go122,
+                       uint8_t *out, uint64_t out_cap, uint64_t *out_off,
+                       uint32_t *status);
+
+/* Whole-batch bridge path (redis-nats-bridge/main.go:153-164): per record the slice is
+ * subject "chat.<cid>.tokens" immediately followed by the re-marshalled JSON;
+ * subj_len[i] gives the split point. */
+int sseo_bridge_batch(const uint8_t *in, const uint32_t *in_off, uint32_t n, int go122,
+                      uint8_t *out, uint64_t out_cap, uint64_t *out_off,
+                      uint32_t *subj_len, uint32_t *status);
+
+/* Timed CPU baseline: runs the adapter path over the batch on `threads` pthreads
+ * (contiguous record ranges, private output arenas), `reps` times; returns the best
+ * wall-clock seconds of one repetition; *frames / *out_bytes are per repetition. */
+double sseo_bench_adapter(const uint8_t *in, const uint32_t *in_off, uint32_t n,
+                          int threads, int reps, uint64_t *frames, uint64_t *out_bytes);
+
+/* fnv1a64 of the conversation id: the shard function. */
+uint64_t sseo_fnv1a64(const uint8_t *p, size_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,95 @@
+"""ctypes binding of oracle/libsse_oracle.so -- test infrastructure only."""
+import ctypes as C
+import gzip
+import json
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+u8p, u32p, u64p, i64p = (C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_int64))
+
+
+def _ptr(a, t):
+    return a.ctypes.data_as(t) if a is not None else None
+
+
+class Oracle:
+    def __init__(self, lib):
+        self.lib = lib
+        lib.sseo_adapter_batch.restype = C.c_int
+        lib.sseo_adapter_batch.argtypes = [u8p, u32p, C.c_uint32, i64p, C.c_int, u8p, C.c_uint64, u64p, u32p]
+        lib.sseo_bridge_batch.restype = C.c_int
+        lib.sseo_bridge_batch.argtypes = [u8p, u32p, C.c_uint32, C.c_int, u8p, C.c_uint64, u64p, u32p, u32p]
+        lib.sseo_bench_adapter.restype = C.c_double
+        lib.sseo_bench_adapter.argtypes = [u8p, u32p, C.c_uint32, C.c_int, C.c_int, u64p, u64p]
+        lib.sseo_start_sequence.restype = C.c_int64
+        lib.sseo_start_sequence.argtypes = [C.c_char_p]
+        lib.sseo_fnv1a64.restype = C.c_uint64
+        lib.sseo_fnv1a64.argtypes = [u8p, C.c_size_t]
+
+    @staticmethod
+    def pack(payloads):
+        """list[bytes] -> (arena u8, offsets u32[n+1])."""
+        off = np.zeros(len(payloads) + 1, dtype=np.uint32)
+        if payloads:
+            off[1:] = np.cumsum([len(p) for p in payloads], dtype=np.uint64).astype(np.uint32)
+        arena = np.frombuffer(b"".join(payloads) + b"\0" * 16, dtype=np.uint8).copy()
+        return arena, off
+
+    def adapter(self, arena, off, start_seq=None, go122=False):
+        n = len(off) - 1
+        cap = int(off[n]) * 6 + 160 * n + 64
+        out = np.empty(cap, dtype=np.uint8)
+        out_off = np.empty(n + 1, dtype=np.uint64)
+        status = np.empty(n, dtype=np.uint32)
+        ss = None if start_seq is None else np.ascontiguousarray(start_seq, dtype=np.int64)
+        rc = self.lib.sseo_adapter_batch(_ptr(arena, u8p), _ptr(off, u32p), n, _ptr(ss, i64p), int(go122),
+                                         _ptr(out, u8p), cap, _ptr(out_off, u64p), _ptr(status, u32p))
+        assert rc == 0
+        return out[: int(out_off[n])], out_off, status
+
+    def bridge(self, arena, off, go122=False):
+        n = len(off) - 1
+        cap = int(off[n]) * 9 + 200 * n + 64
+        out = np.empty(cap, dtype=np.uint8)
+        out_off = np.empty(n + 1, dtype=np.uint64)
+        subj_len = np.empty(n, dtype=np.uint32)
+        status = np.empty(n, dtype=np.uint32)
+        rc = self.lib.sseo_bridge_batch(_ptr(arena, u8p), _ptr(off, u32p), n, int(go122), _ptr(out, u8p), cap,
+                                        _ptr(out_off, u64p), _ptr(subj_len, u32p), _ptr(status, u32p))
+        assert rc == 0
+        return out[: int(out_off[n])], out_off, subj_len, status
+
+    def bench_adapter(self, arena, off, threads, reps=1):
+        n = len(off) - 1
+        frames, nbytes = C.c_uint64(0), C.c_uint64(0)
+        sec = self.lib.sseo_bench_adapter(_ptr(arena, u8p), _ptr(off, u32p), n, threads, reps, C.byref(frames), C.byref(nbytes))
+        return sec, frames.value, nbytes.value
+
+    def start_sequence(self, s):
+        return self.lib.sseo_start_sequence(s.encode() if s is not None else None)
+
+    def fnv1a64(self, b):
+        a = np.frombuffer(bytes(b) + b"\0", dtype=np.uint8)
+        return self.lib.sseo_fnv1a64(_ptr(a, u8p), len(b))
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "libsse_oracle.so"])
+
+
+def load():
+    so = os.path.join(ORACLE_DIR, "libsse_oracle.so")
+    srcs = [os.path.join(ORACLE_DIR, f) for f in os.listdir(ORACLE_DIR) if f.endswith((".c", ".h"))]
+    if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        build()
+    return Oracle(C.CDLL(so))
+
+
+def load_golden():
+    path = os.path.join(ROOT, "tests", "golden", "adapter_vectors.json.gz")
+    with gzip.open(path, "rb") as f:
+        return json.loads(f.read())
