@@ -1,0 +1,13 @@
+"""B200-native SSE hot path: thin ctypes binding of libssegpu.so (include/ssegpu.h).
+
+The package directory name contains hyphens, so it is loaded by file path
+(`__graft_entry__.load_package()`), not by a plain import statement.
+
+There is no CPU fallback anywhere in this package: if libssegpu.so is missing, or no
+sm_100 device is present, construction fails loudly.
+"""
+from .binding import (  # noqa: F401
+    OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, ST_CODE_MASK, ST_DONE, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_OK,
+    Batch, SseGpu, SseGpuError, lib_path, load_library, shard, start_sequence,
+)
+from . import workload  # noqa: F401

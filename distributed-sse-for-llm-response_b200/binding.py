@@ -1,0 +1,193 @@
+"""ctypes binding of the C ABI in include/ssegpu.h.  Mirrors the header one to one."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST = 0, 1, 2, 4
+ST_OK, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_INSPECT_DROP = 0, 1, 2, 3, 4
+ST_CODE_MASK, ST_DONE, ST_REDACTED = 0xF, 0x100, 0x200
+E_OVERFLOW, E_AGAIN = -6, -4
+
+u8p, u32p, u64p, i64p = (C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_int64))
+
+
+class Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("max_records", C.c_uint32), ("max_in_bytes", C.c_uint64),
+                ("max_out_bytes", C.c_uint64), ("ring_slots", C.c_uint32), ("conv_slots", C.c_uint32),
+                ("flags", C.c_uint32)]
+
+
+class Counters(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("records", "frames", "bytes_in", "bytes_out", "err_syntax", "err_type",
+                                          "filtered", "done", "fast_path", "batches")]
+
+    def as_dict(self):
+        return {k: int(getattr(self, k)) for k, _ in self._fields_}
+
+
+class SseGpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("ssegpu error %d: %s" % (code, msg))
+        self.code = code
+
+
+def lib_path():
+    return os.path.join(HERE, "libssegpu.so")
+
+
+_LIB = None
+
+
+def load_library():
+    """Loads libssegpu.so; raises (never falls back) when it has not been built."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if not os.path.exists(path):
+        raise ImportError("libssegpu.so is not built (%s): run `python __graft_entry__.py build`; "
+                          "there is no CPU fallback for this path" % path)
+    lib = C.CDLL(path)
+    vp = C.c_void_p
+    lib.ssegpu_init.restype = C.c_int
+    lib.ssegpu_init.argtypes = [C.POINTER(Config), C.POINTER(vp)]
+    lib.ssegpu_destroy.restype = None
+    lib.ssegpu_destroy.argtypes = [vp]
+    lib.ssegpu_device_count.restype = C.c_int
+    lib.ssegpu_strerror.restype = C.c_char_p
+    lib.ssegpu_strerror.argtypes = [C.c_int]
+    lib.ssegpu_last_cuda_error.restype = C.c_char_p
+    lib.ssegpu_abi_version.restype = C.c_uint32
+    lib.ssegpu_shard.restype = C.c_uint32
+    lib.ssegpu_shard.argtypes = [C.c_char_p, C.c_size_t, C.c_uint32]
+    lib.ssegpu_start_sequence.restype = C.c_int64
+    lib.ssegpu_start_sequence.argtypes = [C.c_char_p]
+    lib.ssegpu_batch_acquire.restype = C.c_int
+    lib.ssegpu_batch_acquire.argtypes = [vp, C.POINTER(vp)]
+    for name, rt in (("ssegpu_in_bytes", u8p), ("ssegpu_in_off", u32p), ("ssegpu_start_seq", i64p), ("ssegpu_conv_slot", u32p),
+                     ("ssegpu_out_bytes", u8p), ("ssegpu_out_off", u64p), ("ssegpu_status", u32p), ("ssegpu_subj_len", u32p)):
+        f = getattr(lib, name)
+        f.restype = rt
+        f.argtypes = [vp]
+    lib.ssegpu_batch_submit.restype = C.c_int
+    lib.ssegpu_batch_submit.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.c_int]
+    lib.ssegpu_batch_wait.restype = C.c_int
+    lib.ssegpu_batch_wait.argtypes = [vp, vp, C.c_uint32]
+    lib.ssegpu_batch_release.restype = C.c_int
+    lib.ssegpu_batch_release.argtypes = [vp, vp]
+    lib.ssegpu_counters_get.restype = C.c_int
+    lib.ssegpu_counters_get.argtypes = [vp, C.POINTER(Counters)]
+    lib.ssegpu_frame_launch.restype = C.c_int
+    lib.ssegpu_frame_launch.argtypes = [vp, vp, vp, vp, C.c_uint32, C.c_uint32, vp, C.c_uint64, vp, vp, vp, vp]
+    lib.ssegpu_frame_launch_result.restype = C.c_int
+    lib.ssegpu_frame_launch_result.argtypes = [vp, C.POINTER(Counters)]
+    lib.ssegpu_launch_count.restype = C.c_uint64
+    lib.ssegpu_launch_count.argtypes = [vp]
+    _LIB = lib
+    return lib
+
+
+def shard(conversation_id: bytes, n_gpus: int) -> int:
+    return load_library().ssegpu_shard(conversation_id, len(conversation_id), n_gpus)
+
+
+def start_sequence(last_event_id):
+    return load_library().ssegpu_start_sequence(None if last_event_id is None else last_event_id.encode())
+
+
+class Batch:
+    """One pinned ring slot.  The numpy arrays are views of library-owned pinned memory."""
+
+    def __init__(self, owner, handle):
+        self.owner, self.h = owner, handle
+        lib, cfg = owner.lib, owner.cfg
+        n = cfg.max_records
+        self.in_bytes = np.ctypeslib.as_array(lib.ssegpu_in_bytes(handle), shape=(cfg.max_in_bytes + 16,))
+        self.in_off = np.ctypeslib.as_array(lib.ssegpu_in_off(handle), shape=(n + 1,))
+        self.start_seq = np.ctypeslib.as_array(lib.ssegpu_start_seq(handle), shape=(n,))
+        self.conv_slot = np.ctypeslib.as_array(lib.ssegpu_conv_slot(handle), shape=(n,))
+        self.n = 0
+
+    def fill(self, arena, off, start_seq=None):
+        n = len(off) - 1
+        total = int(off[n])
+        self.in_bytes[:total] = arena[:total]
+        self.in_off[: n + 1] = off
+        if start_seq is not None:
+            self.start_seq[:n] = start_seq
+        self.n = n
+        return n
+
+    def submit(self, n=None, op=OP_ADAPTER, use_filter=False):
+        n = self.n if n is None else n
+        self.n = n
+        self.owner._check(self.owner.lib.ssegpu_batch_submit(self.owner.ctx, self.h, n, op, int(use_filter)))
+
+    def wait(self, timeout_us=0):
+        self.owner._check(self.owner.lib.ssegpu_batch_wait(self.owner.ctx, self.h, timeout_us))
+        lib, n = self.owner.lib, self.n
+        self.out_off = np.ctypeslib.as_array(lib.ssegpu_out_off(self.h), shape=(n + 1,))
+        self.status = np.ctypeslib.as_array(lib.ssegpu_status(self.h), shape=(max(n, 1),))[:n]
+        self.subj_len = np.ctypeslib.as_array(lib.ssegpu_subj_len(self.h), shape=(max(n, 1),))[:n]
+        total = int(self.out_off[n])
+        self.out = np.ctypeslib.as_array(lib.ssegpu_out_bytes(self.h), shape=(max(total, 1),))[:total]
+        return self
+
+    def release(self):
+        self.owner._check(self.owner.lib.ssegpu_batch_release(self.owner.ctx, self.h))
+
+
+class SseGpu:
+    """One context per GPU (ssegpu_init / ssegpu_destroy)."""
+
+    def __init__(self, device=0, max_records=1 << 16, max_in_bytes=1 << 24, max_out_bytes=0, ring_slots=0):
+        self.lib = load_library()
+        self.cfg = Config(device, max_records, max_in_bytes, max_out_bytes, ring_slots, 0, 0)
+        ctx = C.c_void_p()
+        rc = self.lib.ssegpu_init(C.byref(self.cfg), C.byref(ctx))
+        if rc != 0:
+            raise SseGpuError(rc, "%s [%s]" % (self.lib.ssegpu_strerror(rc).decode(), self.lib.ssegpu_last_cuda_error().decode()))
+        self.ctx = ctx
+
+    def _check(self, rc):
+        if rc != 0:
+            raise SseGpuError(rc, "%s [%s]" % (self.lib.ssegpu_strerror(rc).decode(), self.lib.ssegpu_last_cuda_error().decode()))
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.ssegpu_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def acquire(self):
+        h = C.c_void_p()
+        self._check(self.lib.ssegpu_batch_acquire(self.ctx, C.byref(h)))
+        return Batch(self, h)
+
+    def counters(self):
+        c = Counters()
+        self._check(self.lib.ssegpu_counters_get(self.ctx, C.byref(c)))
+        return c.as_dict()
+
+    def frame_launch(self, d_in, d_in_off, d_start_seq, n, op, d_out, out_cap, d_out_off, d_subj_len, d_status, stream=0):
+        """All pointer arguments are raw device addresses (ints); asynchronous on `stream`."""
+        self._check(self.lib.ssegpu_frame_launch(self.ctx, d_in, d_in_off, d_start_seq or None, n, op, d_out, out_cap, d_out_off,
+                                                 d_subj_len or None, d_status, stream or None))
+
+    def launch_result(self):
+        c = Counters()
+        rc = self.lib.ssegpu_frame_launch_result(self.ctx, C.byref(c))
+        if rc not in (0, E_OVERFLOW):
+            self._check(rc)
+        return rc, c.as_dict()
+
+    def launch_count(self):
+        return int(self.lib.ssegpu_launch_count(self.ctx))

@@ -1,0 +1,52 @@
+// sse_kernels.h -- host-visible launch interface of the fused frame kernel.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace sse {
+
+constexpr int TILE = 128;        // records per tile == threads per CTA
+constexpr int CTR_ROWS = 64;     // counter rows (CTA i adds into row i % CTR_ROWS; the host sums rows)
+constexpr int CTR_COLS = 8;      // ok, syntax, type, filtered, done, fast, bytes_in, bytes_out
+constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32
+
+struct FrameArgs {
+    const uint8_t* in;           // packed payload arena, 16-byte aligned, 16 bytes of padding after the last record
+    const uint32_t* in_off;      // n+1
+    const int64_t* start_seq;    // n or nullptr
+    uint32_t n, op;
+    uint8_t* out;                // packed output arena
+    uint64_t out_cap;
+    uint64_t* out_off;           // n+1
+    uint32_t* subj_len;          // n or nullptr
+    uint32_t* status;            // n
+    // scratch: one device allocation of scratch_bytes(n), zeroed by frame_launch
+    void* scratch_base;
+    uint32_t* ticket;
+    uint32_t* overflow;
+    unsigned long long* counters;
+    uint64_t* tile_state;
+    // filled by frame_launch
+    uint32_t num_tiles, in_cap, out_cap_s;
+    __host__ __device__ uint32_t out_cap_smem() const { return out_cap_s; }
+};
+
+inline size_t scratch_bytes(uint32_t n) {
+    size_t tiles = ((size_t)n + TILE - 1) / TILE;
+    return SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8 + tiles * 8;
+}
+inline size_t scratch_readback_bytes() { return SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8; }
+inline void scratch_carve(void* base, FrameArgs& a) {
+    uint8_t* p = static_cast<uint8_t*>(base);
+    a.scratch_base = base;
+    a.ticket = reinterpret_cast<uint32_t*>(p);
+    a.overflow = reinterpret_cast<uint32_t*>(p + 4);
+    a.counters = reinterpret_cast<unsigned long long*>(p + SCRATCH_HDR);
+    a.tile_state = reinterpret_cast<uint64_t*>(p + SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8);
+}
+
+cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid);
+cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream);
+
+}  // namespace sse

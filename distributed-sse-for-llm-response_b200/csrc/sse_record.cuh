@@ -1,0 +1,723 @@
+// sse_record.cuh -- per-record logic of the SSE hot path (decode -> filter -> encode -> frame).
+//
+// What it replaces in the reference (all Go, CPU, one goroutine hop per token):
+//   json.Unmarshal(msg.Data,&token)           src/sse-adapter/sse_handler.go:136-140, :317-321
+//                                             src/redis-nats-bridge/main.go:153-157
+//   sequence filter                           src/sse-adapter/sse_handler.go:142-145
+//   json.Marshal(token) + 3x fmt.Fprintf      src/sse-adapter/sse_handler.go:211-214, :427-430
+//   "chat."+cid+".tokens" + json.Marshal      src/redis-nats-bridge/main.go:160-161
+//
+// Design (B200-first, not a translation of encoding/json):
+//   * One thread owns one record; the record bytes sit in shared memory (TMA-staged tile)
+//     or, for oversize tiles, in global memory.  Nothing is materialised: the decoder
+//     yields a PLAN (source ranges of the winning string literals + the integers) and
+//     the encoder streams runes from those ranges straight into the output.
+//   * Canonical records -- exactly what Go's own json.Marshal produced, which is what
+//     the proxy and the load generator publish -- satisfy Marshal(Unmarshal(x)) == x.
+//     parse_fast() proves canonicity with word-wide SWAR tests, and the frame is then
+//     header + verbatim payload copy.  Everything else takes parse_general(), a complete
+//     single-pass restatement of the scanner+decoder rules.
+//   * All functions are __host__ __device__ so the very same source is unit-tested on the
+//     CPU build box (tests/hostcheck) before a GPU minute is spent.  That host build is a
+//     test double only; the shipped library contains device code alone.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define SSE_HD __host__ __device__ __forceinline__
+#define SSE_HD_NOINLINE __host__ __device__ __noinline__
+#define SSE_CX __host__ __device__ constexpr
+#else
+#define SSE_CX constexpr
+#define SSE_HD inline
+#define SSE_HD_NOINLINE
+#endif
+
+namespace sse {
+
+// status word (mirrors include/ssegpu.h)
+enum : uint32_t {
+    ST_OK = 0, ST_ERR_SYNTAX = 1, ST_ERR_TYPE = 2, ST_FILTERED = 3, ST_INSPECT_DROP = 4,
+    ST_CODE_MASK = 0xF, ST_DONE = 0x100, ST_REDACTED = 0x200,
+};
+// op flags (mirrors include/ssegpu.h)
+enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u };
+
+constexpr uint32_t MAX_NESTING = 10000;            // encoding/json scanner.go maxNestingDepth
+constexpr uint32_t NEST_WORDS = MAX_NESTING / 32 + 1;
+
+struct Plan {
+    uint32_t cid_b, cid_e;   // content range (between the quotes) of the winning conversation_id literal
+    uint32_t tok_b, tok_e;   // same for token; b==e means ""
+    int64_t  seq, ts;
+    uint32_t done;           // 0/1
+    uint32_t fast;           // 1: payload is canonical, JSON out == payload bytes
+    uint32_t seq_b, seq_n;   // fast only: where the sequence literal sits in the payload (its text IS fmt %d)
+    uint32_t cid_esc;        // fast only: the id literal contains a backslash escape (decoded id != raw bytes)
+};
+
+// ---------------------------------------------------------------- accessors ----
+// A Src gives byte/word reads relative to a 16-byte aligned tile origin; a Dst the
+// matching writes.  Generic-pointer versions work on host and device (global or shared);
+// the kernels add ld.shared/st.shared specialisations.
+struct PtrSrc {
+    const uint8_t* base;
+    SSE_HD uint32_t ld8(uint32_t i) const { return base[i]; }
+    SSE_HD uint32_t ld32a(uint32_t i) const { return *reinterpret_cast<const uint32_t*>(base + i); }
+};
+struct PtrDst {                 // 64-bit positions: the global output arena
+    typedef uint64_t pos_t;
+    uint8_t* base;
+    SSE_HD void st8(uint64_t i, uint32_t v) const { base[i] = (uint8_t)v; }
+    SSE_HD void st32a(uint64_t i, uint32_t v) const { *reinterpret_cast<uint32_t*>(base + i) = v; }
+};
+struct Ptr32Dst {               // 32-bit positions: a shared-memory staging tile
+    typedef uint32_t pos_t;
+    uint8_t* base;
+    SSE_HD void st8(uint32_t i, uint32_t v) const { base[i] = (uint8_t)v; }
+    SSE_HD void st32a(uint32_t i, uint32_t v) const { *reinterpret_cast<uint32_t*>(base + i) = v; }
+};
+
+SSE_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {   // sh in {0,8,16,24}
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(lo, hi, sh);
+#else
+    return sh ? (lo >> sh) | (hi << (32 - sh)) : lo;
+#endif
+}
+
+// little-endian 4 bytes at an arbitrary byte position (may read up to 3 bytes past pos+3's
+// word: tile buffers are padded)
+template <class Src> SSE_HD uint32_t ld32u(const Src& s, uint32_t pos) {
+    uint32_t a = pos & ~3u;
+    uint32_t sh = (pos & 3u) * 8;
+    uint32_t lo = s.ld32a(a);
+    if (sh == 0) return lo;
+    return funnel_r(lo, s.ld32a(a + 4), sh);
+}
+
+SSE_CX uint32_t w4(const char* s) {
+    return (uint32_t)(uint8_t)s[0] | ((uint32_t)(uint8_t)s[1] << 8) | ((uint32_t)(uint8_t)s[2] << 16) |
+           ((uint32_t)(uint8_t)s[3] << 24);
+}
+
+// ---------------------------------------------------------------------- utf8 ----
+// unicode/utf8.DecodeRune over [pos,end): size in the return value, rune in r; invalid -> (U+FFFD,1)
+template <class Src> SSE_HD uint32_t utf8_decode(const Src& s, uint32_t pos, uint32_t end, uint32_t& r) {
+    uint32_t b0 = s.ld8(pos);
+    r = 0xFFFD;
+    if (b0 < 0x80) { r = b0; return 1; }
+    if (b0 < 0xC2 || b0 > 0xF4) return 1;
+    uint32_t need = b0 < 0xE0 ? 1 : (b0 < 0xF0 ? 2 : 3);
+    if (pos + need + 1 > end) return 1;                // truncated
+    uint32_t b1 = s.ld8(pos + 1);
+    uint32_t lo = 0x80, hi = 0xBF;
+    if (b0 == 0xE0) lo = 0xA0; else if (b0 == 0xED) hi = 0x9F; else if (b0 == 0xF0) lo = 0x90; else if (b0 == 0xF4) hi = 0x8F;
+    if (b1 < lo || b1 > hi) return 1;
+    if (need == 1) { r = ((b0 & 0x1F) << 6) | (b1 & 0x3F); return 2; }
+    uint32_t b2 = s.ld8(pos + 2);
+    if ((b2 & 0xC0) != 0x80) return 1;
+    if (need == 2) { r = ((b0 & 0x0F) << 12) | ((b1 & 0x3F) << 6) | (b2 & 0x3F); return 3; }
+    uint32_t b3 = s.ld8(pos + 3);
+    if ((b3 & 0xC0) != 0x80) return 1;
+    r = ((b0 & 0x07) << 18) | ((b1 & 0x3F) << 12) | ((b2 & 0x3F) << 6) | (b3 & 0x3F);
+    return 4;
+}
+
+SSE_HD int hexval(uint32_t c) {
+    if (c >= '0' && c <= '9') return (int)c - '0';
+    c |= 0x20;
+    if (c >= 'a' && c <= 'f') return (int)c - 'a' + 10;
+    return -1;
+}
+
+template <class Src> SSE_HD int hex4(const Src& s, uint32_t pos) {
+    int a = hexval(s.ld8(pos)), b = hexval(s.ld8(pos + 1)), c = hexval(s.ld8(pos + 2)), d = hexval(s.ld8(pos + 3));
+    if ((a | b | c | d) < 0) return -1;
+    return (a << 12) | (b << 8) | (c << 4) | d;
+}
+
+// Next decoded rune of a VALID JSON string literal's content [pos,end)  (decode.go unquoteBytes).
+template <class Src> SSE_HD uint32_t next_rune(const Src& s, uint32_t& pos, uint32_t end) {
+    uint32_t c = s.ld8(pos);
+    if (c == '\\') {
+        uint32_t e = s.ld8(pos + 1);
+        if (e != 'u') {
+            pos += 2;
+            switch (e) {
+            case 'b': return 8;  case 'f': return 12; case 'n': return 10;
+            case 'r': return 13; case 't': return 9;  default: return e;   // " \ /
+            }
+        }
+        uint32_t rr = (uint32_t)hex4(s, pos + 2);
+        pos += 6;
+        if (rr >= 0xD800 && rr < 0xE000) {             // utf16.IsSurrogate
+            if (rr < 0xDC00 && pos + 6 <= end && s.ld8(pos) == '\\' && s.ld8(pos + 1) == 'u') {
+                uint32_t r2 = (uint32_t)hex4(s, pos + 2);
+                if (r2 >= 0xDC00 && r2 < 0xE000) {      // utf16.DecodeRune
+                    pos += 6;
+                    return (((rr - 0xD800) << 10) | (r2 - 0xDC00)) + 0x10000;
+                }
+            }
+            return 0xFFFD;
+        }
+        return rr;
+    }
+    if (c < 0x80) { pos += 1; return c; }
+    uint32_t r;
+    pos += utf8_decode(s, pos, end, r);
+    return r;
+}
+
+// --------------------------------------------------------------- byte writer ----
+// Streams bytes to a Dst at an arbitrary byte position using aligned 32-bit stores for
+// whole words; a leading/trailing partial word is written bytewise because its other
+// bytes belong to the neighbouring record (written by another thread).  With EMIT=false
+// it only counts.
+template <class Dst, bool EMIT> struct Writer {
+    typedef typename Dst::pos_t pos_t;
+    const Dst& d;
+    pos_t pos;          // next byte position
+    uint32_t acc;       // bytes of the current word gathered so far (low bytes first)
+    uint32_t first;     // byte index within the first word where this stream started (0 once flushed whole)
+    SSE_HD Writer(const Dst& dst, pos_t start) : d(dst), pos(start), acc(0), first((uint32_t)start & 3u) {}
+    SSE_HD void flush_word() {                          // pos is word aligned, acc holds bytes [first..3]
+        if (EMIT) {
+            pos_t w = pos - 4;
+            if (first == 0) d.st32a(w, acc);
+            else { for (uint32_t k = first; k < 4; k++) d.st8(w + k, (acc >> (8 * k)) & 0xFF); }
+        }
+        first = 0; acc = 0;
+    }
+    SSE_HD void put(uint32_t b) {
+        if (EMIT) acc |= (b & 0xFF) << (8 * ((uint32_t)pos & 3u));
+        pos++;
+        if (((uint32_t)pos & 3u) == 0) flush_word();
+    }
+    SSE_HD void put32(uint32_t w) {                     // four bytes, little endian
+        if (!EMIT) { pos += 4; return; }
+        uint32_t sh = ((uint32_t)pos & 3u) * 8;
+        if (sh == 0) { acc = w; pos += 4; flush_word(); return; }
+        acc |= w << sh;
+        pos += 4 - (sh >> 3);
+        flush_word();
+        acc = w >> (32 - sh);
+        pos += sh >> 3;
+    }
+    SSE_HD void put_n(uint32_t w, uint32_t n) {         // low n (1..3) bytes of w
+        for (uint32_t k = 0; k < n; k++) put((w >> (8 * k)) & 0xFF);
+    }
+    SSE_HD void finish() {                              // trailing partial word
+        uint32_t k1 = (uint32_t)pos & 3u;
+        if (EMIT && k1) {
+            pos_t w = pos - k1;
+            for (uint32_t k = first; k < k1; k++) d.st8(w + k, (acc >> (8 * k)) & 0xFF);
+        }
+    }
+};
+
+template <class W> SSE_HD void put_lit(W& w, const char* s, uint32_t n) {
+    uint32_t i = 0;
+    for (; i + 4 <= n; i += 4) w.put32(w4(s + i));
+    for (; i < n; i++) w.put((uint8_t)s[i]);
+}
+#define SSE_PUT_LIT(w, lit) put_lit(w, lit, (uint32_t)(sizeof(lit) - 1))
+
+SSE_HD uint32_t dec_digits(uint64_t u) {
+    uint32_t n = 1;
+    while (u >= 10) { u /= 10; n++; }
+    return n;
+}
+SSE_HD uint32_t dec_len(int64_t v) {                   // strconv.AppendInt / fmt %d length
+    uint64_t u = v < 0 ? 0 - (uint64_t)v : (uint64_t)v;
+    return dec_digits(u) + (v < 0 ? 1u : 0u);
+}
+template <class W> SSE_HD void put_int(W& w, int64_t v) {
+    uint64_t u = v < 0 ? 0 - (uint64_t)v : (uint64_t)v;
+    if (v < 0) w.put('-');
+    uint32_t n = dec_digits(u);
+    uint64_t p = 1;
+    for (uint32_t k = 1; k < n; k++) p *= 10;
+    for (uint32_t k = 0; k < n; k++) { uint64_t q = u / p; w.put('0' + (uint32_t)q); u -= q * p; p /= 10; }
+}
+
+SSE_HD uint32_t hexl(uint32_t v) { return v < 10 ? '0' + v : 'a' + (v - 10); }
+
+// encode.go appendString(escapeHTML=true) for one decoded rune.
+template <class W> SSE_HD void put_rune_json(W& w, uint32_t r, bool go122) {
+    if (r < 0x80) {
+        if (r >= 0x20 && r != '"' && r != '\\' && r != '<' && r != '>' && r != '&') { w.put(r); return; }
+        w.put('\\');
+        switch (r) {
+        case '\\': case '"': w.put(r); return;
+        case '\n': w.put('n'); return;
+        case '\r': w.put('r'); return;
+        case '\t': w.put('t'); return;
+        default: break;
+        }
+        if (go122 && r == 8)  { w.put('b'); return; }
+        if (go122 && r == 12) { w.put('f'); return; }
+        w.put('u'); w.put('0'); w.put('0'); w.put(hexl(r >> 4)); w.put(hexl(r & 0xF));
+        return;
+    }
+    if (r == 0x2028 || r == 0x2029) { w.put('\\'); w.put('u'); w.put('2'); w.put('0'); w.put('2'); w.put(hexl(r & 0xF)); return; }
+    if (r < 0x800) { w.put(0xC0 | (r >> 6)); w.put(0x80 | (r & 0x3F)); return; }
+    if (r < 0x10000) { w.put(0xE0 | (r >> 12)); w.put(0x80 | ((r >> 6) & 0x3F)); w.put(0x80 | (r & 0x3F)); return; }
+    w.put(0xF0 | (r >> 18)); w.put(0x80 | ((r >> 12) & 0x3F)); w.put(0x80 | ((r >> 6) & 0x3F)); w.put(0x80 | (r & 0x3F));
+}
+template <class W> SSE_HD void put_rune_raw(W& w, uint32_t r) {   // utf8.EncodeRune
+    if (r < 0x80) { w.put(r); return; }
+    if (r < 0x800) { w.put(0xC0 | (r >> 6)); w.put(0x80 | (r & 0x3F)); return; }
+    if (r < 0x10000) { w.put(0xE0 | (r >> 12)); w.put(0x80 | ((r >> 6) & 0x3F)); w.put(0x80 | (r & 0x3F)); return; }
+    w.put(0xF0 | (r >> 18)); w.put(0x80 | ((r >> 12) & 0x3F)); w.put(0x80 | ((r >> 6) & 0x3F)); w.put(0x80 | (r & 0x3F));
+}
+
+template <class Src, class W> SSE_HD void put_json_string(const Src& s, uint32_t b, uint32_t e, W& w, bool go122) {
+    w.put('"');
+    while (b < e) put_rune_json(w, next_rune(s, b, e), go122);
+    w.put('"');
+}
+
+// verbatim copy of n source bytes starting at byte position sp
+template <class Src, class W> SSE_HD void put_copy(const Src& s, uint32_t sp, uint32_t n, W& w) {
+    while (n && (sp & 3u)) { w.put(s.ld8(sp)); sp++; n--; }
+    for (; n >= 4; n -= 4, sp += 4) w.put32(s.ld32a(sp));
+    for (; n; n--, sp++) w.put(s.ld8(sp));
+}
+
+// ------------------------------------------------------------------ emission ----
+// Writes the record's output (SSE frame, or bridge subject+JSON) at w.pos.  With a counting
+// writer it measures the length.  `o` = record start inside Src.
+template <class Src, class W>
+SSE_HD void emit_record(const Src& s, uint32_t o, uint32_t L, const Plan& pl, uint32_t op, W& w, uint32_t* subj_len) {
+    const bool go122 = (op & OP_GO122) != 0;
+    if (op & OP_BRIDGE) {
+        // redis-nats-bridge/main.go:160  fmt.Sprintf("chat.%s.tokens", token.ConversationID)
+        auto p0 = w.pos;
+        SSE_PUT_LIT(w, "chat.");
+        for (uint32_t b = o + pl.cid_b, e = o + pl.cid_e; b < e;) put_rune_raw(w, next_rune(s, b, e));
+        SSE_PUT_LIT(w, ".tokens");
+        if (subj_len) *subj_len = (uint32_t)(w.pos - p0);
+    } else {
+        SSE_PUT_LIT(w, "event: token\nid: ");            // sse_handler.go:212-213
+        put_int(w, pl.seq);
+        SSE_PUT_LIT(w, "\ndata: ");                      // :214
+    }
+    if (pl.fast) {
+        put_copy(s, o, L, w);                            // Marshal(Unmarshal(x)) == x for canonical x
+    } else {
+        SSE_PUT_LIT(w, "{\"conversation_id\":");
+        put_json_string(s, o + pl.cid_b, o + pl.cid_e, w, go122);
+        SSE_PUT_LIT(w, ",\"token\":");
+        put_json_string(s, o + pl.tok_b, o + pl.tok_e, w, go122);
+        SSE_PUT_LIT(w, ",\"sequence\":");
+        put_int(w, pl.seq);
+        SSE_PUT_LIT(w, ",\"done\":");
+        if (pl.done) SSE_PUT_LIT(w, "true"); else SSE_PUT_LIT(w, "false");
+        SSE_PUT_LIT(w, ",\"timestamp\":");
+        put_int(w, pl.ts);
+        w.put('}');
+    }
+    if (!(op & OP_BRIDGE)) { w.put('\n'); w.put('\n'); }
+    w.finish();
+}
+
+// ------------------------------------------------------------- canonical path ----
+// A byte is "plain" inside a canonical Go-marshalled string when appendString copies it
+// through unchanged and unquoteBytes reads it unchanged: 0x20..0x7F except " \ < > &.
+// Returns a mask with bit 7 of byte k set if byte k MAY be special (exact for the lowest
+// flagged byte, which is the only one used).
+SSE_HD uint32_t special_mask(uint32_t w) {
+    const uint32_t H = 0x80808080u, L1 = 0x01010101u;
+    uint32_t hi = w & H;                                        // >= 0x80
+    uint32_t lt = (w - 0x20202020u) & ~w & H;                   // < 0x20
+    uint32_t a = (w & 0xFBFBFBFBu) ^ 0x22222222u;               // '"' (0x22) or '&' (0x26)
+    uint32_t b = (w & 0xFDFDFDFDu) ^ 0x3C3C3C3Cu;               // '<' (0x3C) or '>' (0x3E)
+    uint32_t c = w ^ 0x5C5C5C5Cu;                               // '\\'
+    uint32_t z = ((a - L1) & ~a) | ((b - L1) & ~b) | ((c - L1) & ~c);
+    return hi | lt | (z & H);
+}
+
+SSE_HD uint32_t first_byte_idx(uint32_t m) {                    // m != 0, flags at bit 7 of each byte
+#if defined(__CUDA_ARCH__)
+    return (uint32_t)(__ffs((int)m) - 1) >> 3;
+#else
+    return (uint32_t)__builtin_ctz(m) >> 3;
+#endif
+}
+
+// Scans a canonical string body starting at pos (just after the opening quote); on success
+// pos is left ON the closing quote.  Fails (false) on anything json.Marshal would not have
+// produced verbatim -- the general path then decides what it really is.
+template <class Src> SSE_HD bool scan_canon_string(const Src& s, uint32_t& pos, uint32_t end, bool go122, bool& has_esc) {
+    for (;;) {
+        if (pos >= end) return false;
+        uint32_t w = ld32u(s, pos);
+        uint32_t m = special_mask(w);
+        if (m == 0) { pos += 4; continue; }
+        uint32_t k = first_byte_idx(m);
+        pos += k;
+        uint32_t c = (w >> (8 * k)) & 0xFF;
+        if (c == '"') return pos < end;
+        if (c == '\\') {
+            has_esc = true;
+            uint32_t e = s.ld8(pos + 1);
+            if (e == '"' || e == '\\' || e == 'n' || e == 'r' || e == 't' || (go122 && (e == 'b' || e == 'f'))) { pos += 2; continue; }
+            if (e != 'u') return false;
+            uint32_t h = ld32u(s, pos + 2);
+            uint32_t h3 = h >> 24;
+            bool ok;
+            uint32_t h012 = h & 0xFFFFFFu;
+            if (h012 == (w4("000\0") & 0xFFFFFFu)) {            // \u000X : control chars without a short form
+                ok = ((h3 >= '0' && h3 <= '8') || h3 == 'b' || h3 == 'c' || h3 == 'e' || h3 == 'f');
+                if (go122 && (h3 == '8' || h3 == 'c')) ok = false;
+            } else if (h012 == (w4("001\0") & 0xFFFFFFu)) {
+                ok = (h3 >= '0' && h3 <= '9') || (h3 >= 'a' && h3 <= 'f');
+            } else if (h012 == (w4("003\0") & 0xFFFFFFu)) {
+                ok = (h3 == 'c' || h3 == 'e');                  // < >
+            } else if (h012 == (w4("002\0") & 0xFFFFFFu)) {
+                ok = (h3 == '6');                               // &
+            } else if (h012 == (w4("202\0") & 0xFFFFFFu)) {
+                ok = (h3 == '8' || h3 == '9');                  // U+2028 / U+2029
+            } else ok = false;
+            if (!ok) return false;
+            pos += 6;
+            continue;
+        }
+        if (c >= 0x80) {                                        // raw multi-byte UTF-8: decoded == raw
+            uint32_t r;
+            uint32_t n = utf8_decode(s, pos, end, r);
+            if (n == 1 || r == 0x2028 || r == 0x2029) return false;
+            pos += n;
+            continue;
+        }
+        return false;                                           // control byte, or < > & raw
+    }
+}
+
+// canonical integer: -?(0|[1-9][0-9]*) within int64, and not "-0"
+template <class Src> SSE_HD bool scan_canon_int(const Src& s, uint32_t& pos, uint32_t end, int64_t& out) {
+    bool neg = false;
+    uint32_t c = s.ld8(pos);
+    if (c == '-') { neg = true; pos++; c = s.ld8(pos); }
+    if (c < '0' || c > '9') return false;
+    uint64_t v = c - '0';
+    pos++;
+    if (v == 0) {
+        if (neg) return false;
+        out = 0;
+        uint32_t d = s.ld8(pos);
+        return !(d >= '0' && d <= '9') || pos >= end;
+    }
+    uint32_t nd = 1;
+    for (;;) {
+        if (pos >= end) break;
+        uint32_t d = s.ld8(pos) - '0';
+        if (d > 9) break;
+        if (++nd > 19) return false;
+        v = v * 10 + d;
+        pos++;
+    }
+    if (neg) { if (v > (1ull << 63)) return false; out = (int64_t)(0 - v); }
+    else     { if (v > 0x7FFFFFFFFFFFFFFFull) return false; out = (int64_t)v; }
+    return true;
+}
+
+// True iff the record is byte-for-byte what json.Marshal(TokenMessage) would emit.
+template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, Plan& pl) {
+    const bool go122 = (op & OP_GO122) != 0;
+    if (L < 72) return false;
+    const uint32_t end = o + L;
+    // {"conversation_id":"   (20 bytes)
+    if (ld32u(s, o) != w4("{\"co") || ld32u(s, o + 4) != w4("nver") || ld32u(s, o + 8) != w4("sati") ||
+        ld32u(s, o + 12) != w4("on_i") || ld32u(s, o + 16) != w4("d\":\"")) return false;
+    uint32_t pos = o + 20;
+    bool cid_esc = false, tok_esc = false;
+    pl.cid_b = 20;
+    if (!scan_canon_string(s, pos, end, go122, cid_esc)) return false;
+    pl.cid_e = pos - o;
+    // ","token":"   (11 bytes)
+    if (pos + 11 > end) return false;
+    if (ld32u(s, pos) != w4("\",\"t") || ld32u(s, pos + 4) != w4("oken") || (ld32u(s, pos + 8) & 0xFFFFFFu) != (w4("\":\"\0") & 0xFFFFFFu)) return false;
+    pos += 11;
+    pl.tok_b = pos - o;
+    if (!scan_canon_string(s, pos, end, go122, tok_esc)) return false;
+    pl.tok_e = pos - o;
+    // ","sequence":   (13 bytes)
+    if (pos + 13 > end) return false;
+    if (ld32u(s, pos) != w4("\",\"s") || ld32u(s, pos + 4) != w4("eque") || ld32u(s, pos + 8) != w4("nce\"") || s.ld8(pos + 12) != ':') return false;
+    pos += 13;
+    pl.seq_b = pos - o;
+    if (pos >= end || !scan_canon_int(s, pos, end, pl.seq)) return false;
+    pl.seq_n = pos - o - pl.seq_b;
+    // ,"done":   (8 bytes)
+    if (pos + 8 > end) return false;
+    if (ld32u(s, pos) != w4(",\"do") || ld32u(s, pos + 4) != w4("ne\":")) return false;
+    pos += 8;
+    if (pos + 5 > end) return false;
+    uint32_t lit = ld32u(s, pos);
+    if (lit == w4("true")) { pl.done = 1; pos += 4; }
+    else if (lit == w4("fals") && s.ld8(pos + 4) == 'e') { pl.done = 0; pos += 5; }
+    else return false;
+    // ,"timestamp":   (13 bytes)
+    if (pos + 13 > end) return false;
+    if (ld32u(s, pos) != w4(",\"ti") || ld32u(s, pos + 4) != w4("mest") || ld32u(s, pos + 8) != w4("amp\"") || s.ld8(pos + 12) != ':') return false;
+    pos += 13;
+    if (pos >= end || !scan_canon_int(s, pos, end, pl.ts)) return false;
+    if (pos + 1 != end || s.ld8(pos) != '}') return false;
+    pl.fast = 1;
+    pl.cid_esc = cid_esc ? 1u : 0u;   // the bridge subject needs the DECODED id
+    (void)tok_esc;
+    return true;
+}
+
+// --------------------------------------------------------------- general path ----
+SSE_HD bool is_ws(uint32_t c) { return c == ' ' || c == '\t' || c == '\r' || c == '\n'; }
+SSE_HD bool is_digit(uint32_t c) { return c - '0' <= 9u; }
+
+// scanner.go stateInString*: pos on the opening quote; returns position past the closing
+// quote or 0 on error.
+template <class Src> SSE_HD uint32_t scan_string(const Src& s, uint32_t pos, uint32_t end) {
+    for (pos++; pos < end; pos++) {
+        uint32_t c = s.ld8(pos);
+        if (c == '"') return pos + 1;
+        if (c < 0x20) return 0;
+        if (c == '\\') {
+            if (++pos >= end) return 0;
+            uint32_t e = s.ld8(pos);
+            if (e == 'u') {
+                if (pos + 4 >= end) return 0;
+                if (hex4(s, pos + 1) < 0) return 0;
+                pos += 4;
+            } else if (!(e == 'b' || e == 'f' || e == 'n' || e == 'r' || e == 't' || e == '\\' || e == '/' || e == '"')) return 0;
+        }
+    }
+    return 0;
+}
+
+// scanner.go number states; returns position past the number or 0.  *plain_int is set when
+// the literal is -?digits (the only shape strconv.ParseInt accepts).
+template <class Src> SSE_HD uint32_t scan_number(const Src& s, uint32_t pos, uint32_t end, bool* plain_int) {
+    *plain_int = true;
+    if (s.ld8(pos) == '-') { if (++pos >= end) return 0; }
+    uint32_t c = s.ld8(pos);
+    if (c == '0') pos++;
+    else if (c >= '1' && c <= '9') { while (pos < end && is_digit(s.ld8(pos))) pos++; }
+    else return 0;
+    if (pos < end && s.ld8(pos) == '.') {
+        *plain_int = false;
+        pos++;
+        if (pos >= end || !is_digit(s.ld8(pos))) return 0;
+        while (pos < end && is_digit(s.ld8(pos))) pos++;
+    }
+    if (pos < end && (s.ld8(pos) | 0x20) == 'e') {
+        *plain_int = false;
+        pos++;
+        if (pos < end && (s.ld8(pos) == '+' || s.ld8(pos) == '-')) pos++;
+        if (pos >= end || !is_digit(s.ld8(pos))) return 0;
+        while (pos < end && is_digit(s.ld8(pos))) pos++;
+    }
+    return pos;
+}
+
+// strconv.ParseInt(lit,10,64) for a literal already known to be -?digits
+template <class Src> SSE_HD bool parse_int64(const Src& s, uint32_t b, uint32_t e, int64_t& out) {
+    bool neg = false;
+    if (s.ld8(b) == '-') { neg = true; b++; }
+    uint64_t v = 0;
+    for (; b < e; b++) {
+        uint64_t d = s.ld8(b) - '0';
+        if (v > (0xFFFFFFFFFFFFFFFFull - d) / 10) return false;
+        v = v * 10 + d;
+    }
+    if (neg) { if (v > (1ull << 63)) return false; out = (int64_t)(0 - v); }
+    else     { if (v > 0x7FFFFFFFFFFFFFFFull) return false; out = (int64_t)v; }
+    return true;
+}
+
+// decode.go object(): field whose name equals the unquoted key exactly, else under simple
+// case folding (fold.go foldName).  Only {K,k,U+212A} and {S,s,U+017F} fold onto ASCII.
+template <class Src> SSE_HD int match_field(const Src& s, uint32_t b, uint32_t e) {
+    uint32_t alive = 0x1F, k = 0;
+    while (b < e && alive) {
+        uint32_t r = next_rune(s, b, e);
+        if (r >= 'a' && r <= 'z') r -= 32;
+        else if (r == 0x212A) r = 'K';
+        else if (r == 0x017F) r = 'S';
+        const char* n0 = "CONVERSATION_ID"; const char* n1 = "TOKEN"; const char* n2 = "SEQUENCE";
+        const char* n3 = "DONE"; const char* n4 = "TIMESTAMP";
+        if (k >= 15 || r != (uint32_t)(uint8_t)n0[k]) alive &= ~1u;
+        if (k >= 5  || r != (uint32_t)(uint8_t)n1[k]) alive &= ~2u;
+        if (k >= 8  || r != (uint32_t)(uint8_t)n2[k]) alive &= ~4u;
+        if (k >= 4  || r != (uint32_t)(uint8_t)n3[k]) alive &= ~8u;
+        if (k >= 9  || r != (uint32_t)(uint8_t)n4[k]) alive &= ~16u;
+        k++;
+    }
+    if (b < e) return -1;
+    if ((alive & 1u) && k == 15) return 0;
+    if ((alive & 2u) && k == 5) return 1;
+    if ((alive & 4u) && k == 8) return 2;
+    if ((alive & 8u) && k == 4) return 3;
+    if ((alive & 16u) && k == 9) return 4;
+    return -1;
+}
+
+// json.Unmarshal(data,&TokenMessage{}) in one pass: whole-document syntax validation
+// (scanner.go) with the depth-1 field assignments of decode.go applied on the way.  A syntax
+// error anywhere wins over any type error, exactly as checkValid-then-decode does.
+// `nest` is a MAX_NESTING-bit stack (1 = object, 0 = array), touched only when nesting.
+template <class Src>
+SSE_HD_NOINLINE uint32_t parse_general(const Src& s, uint32_t o, uint32_t L, Plan& pl, uint32_t* nest) {
+    pl.cid_b = pl.cid_e = pl.tok_b = pl.tok_e = 0;
+    pl.seq = 0; pl.ts = 0; pl.done = 0; pl.fast = 0; pl.seq_b = pl.seq_n = 0; pl.cid_esc = 0;
+    enum { BEGIN_VALUE, BEGIN_VALUE_OR_EMPTY, BEGIN_KEY_OR_EMPTY, BEGIN_KEY, END_VALUE };
+    uint32_t st = BEGIN_VALUE, depth = 0, pos = o;
+    const uint32_t end = o + L;
+    bool type_err = false, top_obj = false;
+    int field = -1;
+    for (;;) {
+        while (pos < end && is_ws(s.ld8(pos))) pos++;
+        if (pos >= end) {
+            if (!(st == END_VALUE && depth == 0)) return ST_ERR_SYNTAX;
+            return type_err ? ST_ERR_TYPE : ST_OK;
+        }
+        uint32_t c = s.ld8(pos);
+        switch (st) {
+        case BEGIN_VALUE_OR_EMPTY:
+            if (c == ']') { depth--; pos++; st = END_VALUE; break; }
+            /* fallthrough */
+        case BEGIN_VALUE: {
+            const bool member = (depth == 1 && top_obj);          // value of a top-level object member
+            const int f = member ? field : -1;
+            if (c == '{' || c == '[') {
+                if (depth + 1 > MAX_NESTING) return ST_ERR_SYNTAX;
+                if (depth == 0) { top_obj = (c == '{'); if (!top_obj) type_err = true; }
+                if (f >= 0) type_err = true;                      // object/array into string/int/bool
+                if (c == '{') nest[depth >> 5] |= 1u << (depth & 31); else nest[depth >> 5] &= ~(1u << (depth & 31));
+                depth++; pos++;
+                st = (c == '{') ? BEGIN_KEY_OR_EMPTY : BEGIN_VALUE_OR_EMPTY;
+                break;
+            }
+            if (c == '"') {
+                uint32_t e = scan_string(s, pos, end);
+                if (!e) return ST_ERR_SYNTAX;
+                if (depth == 0) type_err = true;
+                if (f == 0) { pl.cid_b = pos + 1 - o; pl.cid_e = e - 1 - o; }
+                else if (f == 1) { pl.tok_b = pos + 1 - o; pl.tok_e = e - 1 - o; }
+                else if (f >= 2) type_err = true;
+                pos = e;
+            } else if (c == '-' || is_digit(c)) {
+                bool plain;
+                uint32_t e = scan_number(s, pos, end, &plain);
+                if (!e) return ST_ERR_SYNTAX;
+                if (depth == 0) type_err = true;
+                if (f == 2) { if (!plain || !parse_int64(s, pos, e, pl.seq)) type_err = true; }
+                else if (f == 4) { if (!plain || !parse_int64(s, pos, e, pl.ts)) type_err = true; }
+                else if (f >= 0) type_err = true;
+                pos = e;
+            } else if (c == 't') {
+                if (pos + 4 > end || ld32u(s, pos) != w4("true")) return ST_ERR_SYNTAX;
+                if (depth == 0) type_err = true;
+                if (f == 3) pl.done = 1; else if (f >= 0) type_err = true;
+                pos += 4;
+            } else if (c == 'f') {
+                if (pos + 5 > end || ld32u(s, pos) != w4("fals") || s.ld8(pos + 4) != 'e') return ST_ERR_SYNTAX;
+                if (depth == 0) type_err = true;
+                if (f == 3) pl.done = 0; else if (f >= 0) type_err = true;
+                pos += 5;
+            } else if (c == 'n') {
+                if (pos + 4 > end || ld32u(s, pos) != w4("null")) return ST_ERR_SYNTAX;
+                pos += 4;                                         // null: no-op everywhere, also at top level
+            } else return ST_ERR_SYNTAX;
+            st = END_VALUE;
+            break;
+        }
+        case BEGIN_KEY_OR_EMPTY:
+            if (c == '}') { depth--; pos++; st = END_VALUE; break; }
+            /* fallthrough */
+        case BEGIN_KEY: {
+            if (c != '"') return ST_ERR_SYNTAX;
+            uint32_t e = scan_string(s, pos, end);
+            if (!e) return ST_ERR_SYNTAX;
+            if (depth == 1 && top_obj) field = match_field(s, pos + 1, e - 1);
+            pos = e;
+            while (pos < end && is_ws(s.ld8(pos))) pos++;
+            if (pos >= end || s.ld8(pos) != ':') return ST_ERR_SYNTAX;
+            pos++;
+            st = BEGIN_VALUE;
+            break;
+        }
+        default: /* END_VALUE */
+            if (depth == 0) return ST_ERR_SYNTAX;                 // stateEndTop
+            if (nest[(depth - 1) >> 5] & (1u << ((depth - 1) & 31))) {
+                if (c == ',') st = BEGIN_KEY; else if (c == '}') depth--; else return ST_ERR_SYNTAX;
+            } else {
+                if (c == ',') st = BEGIN_VALUE; else if (c == ']') depth--; else return ST_ERR_SYNTAX;
+            }
+            pos++;
+            break;
+        }
+    }
+}
+
+// -------------------------------------------------------------------- record ----
+// The kernel keeps the canonical path inline (shared-memory loads/stores, ~1k instructions)
+// and reaches everything else through two out-of-line calls, so the hot loop stays small in
+// the instruction cache.  tests/hostcheck runs the same dispatch on the CPU.
+
+// May the record be emitted by emit_record_fast()?
+SSE_HD bool fast_emit_ok(const Plan& pl, uint32_t op) {
+    return pl.fast && !((op & OP_BRIDGE) && pl.cid_esc);
+}
+
+// Pass 1, canonical records only.  false = not canonical (or fast path disabled): call plan_record().
+template <class Src>
+SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, int64_t start_seq,
+                             Plan& pl, uint32_t& st, uint32_t& out_len) {
+    pl.fast = 0;
+    if ((op & OP_NO_FAST) || !parse_fast(s, o, L, op, pl)) return false;
+    if (!fast_emit_ok(pl, op)) return false;
+    out_len = 0;
+    if (!(op & OP_BRIDGE) && start_seq > 0 && pl.seq <= start_seq) { st = ST_FILTERED; return true; }   // sse_handler.go:143
+    out_len = (op & OP_BRIDGE) ? 12 + (pl.cid_e - pl.cid_b) + L : 26 + pl.seq_n + L;
+    st = pl.done ? (ST_OK | ST_DONE) : ST_OK;
+    return true;
+}
+
+// Pass 2 for records accepted by plan_record_fast(): header + verbatim payload (+ trailer).
+template <class Src, class W>
+SSE_HD void emit_record_fast(const Src& s, uint32_t o, uint32_t L, const Plan& pl, uint32_t op, W& w, uint32_t* subj_len) {
+    if (op & OP_BRIDGE) {
+        SSE_PUT_LIT(w, "chat.");                          // redis-nats-bridge/main.go:160
+        put_copy(s, o + pl.cid_b, pl.cid_e - pl.cid_b, w);
+        SSE_PUT_LIT(w, ".tokens");
+        if (subj_len) *subj_len = 12 + (pl.cid_e - pl.cid_b);
+        put_copy(s, o, L, w);                             // main.go:161
+    } else {
+        SSE_PUT_LIT(w, "event: token\nid: ");            // sse_handler.go:212-213
+        put_copy(s, o + pl.seq_b, pl.seq_n, w);           // canonical literal == fmt %d
+        SSE_PUT_LIT(w, "\ndata: ");                      // :214
+        put_copy(s, o, L, w);
+        w.put('\n'); w.put('\n');
+    }
+    w.finish();
+}
+
+// Pass 1, any record: decode + filter; returns the status word and the output length.
+template <class Src>
+SSE_HD uint32_t plan_record(const Src& s, uint32_t o, uint32_t L, uint32_t op, int64_t start_seq,
+                            Plan& pl, uint32_t* nest, uint32_t& out_len) {
+    out_len = 0;
+    uint32_t st = ST_OK;
+    pl.fast = 0;
+    if ((op & OP_NO_FAST) || !parse_fast(s, o, L, op, pl)) st = parse_general(s, o, L, pl, nest);
+    if (st != ST_OK) return st;
+    if (!(op & OP_BRIDGE) && start_seq > 0 && pl.seq <= start_seq) return ST_FILTERED;   // sse_handler.go:143
+    Ptr32Dst nd{nullptr};
+    Writer<Ptr32Dst, false> w(nd, 0);
+    emit_record(s, o, L, pl, op, w, nullptr);
+    out_len = (uint32_t)w.pos;
+    return pl.done ? (ST_OK | ST_DONE) : ST_OK;
+}
+
+}  // namespace sse

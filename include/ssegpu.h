@@ -1,0 +1,152 @@
+/*
+ * ssegpu.h -- C ABI of the B200 SSE hot-path library (libssegpu.so).
+ *
+ * The reference (ccie7599/distributed-sse-for-llm-response) has NO plugin, operator or FFI
+ * interface: both services are built with CGO_ENABLED=0 (src/sse-adapter/Dockerfile:12,
+ * src/redis-nats-bridge/Dockerfile:10).  This ABI is therefore cut at the narrowest seams
+ * of the reference's own hot loops, and each entry point cites the Go code it replaces.
+ * The cgo binding a maintainer adds is shown in INTEGRATION.md (and go/ssegpu/).
+ *
+ * Conventions
+ *   - plain C types only; every function returns 0 on success or a negative ssegpu_err;
+ *   - no callbacks into the host language, no retained host pointers: batch buffers are
+ *     library-owned pinned allocations exposed as raw pointers (cgo: unsafe.Slice);
+ *   - callable from any OS thread (cgo hops threads): every entry point selects its
+ *     device itself and uses the context's own streams;
+ *   - one context per GPU; conversations shard across contexts by
+ *     ssegpu_shard(conversation_id) = fnv1a64(id) % n_gpus, no cross-GPU exchange;
+ *   - there is NO CPU fallback: without a CUDA device ssegpu_init fails with SSEGPU_E_CUDA.
+ *
+ * Record status word (uint32 per record):
+ *   low 4 bits   SSEGPU_ST_* code; a non-OK record has a zero-length output slice, which is
+ *                the reference's "log and drop" (sse_handler.go:137-140, :143-145)
+ *   SSEGPU_ST_DONE      decoded done==true on an emitted record: the adapter closes the
+ *                stream after writing this frame (sse_handler.go:220-226, :436-442)
+ */
+#ifndef SSEGPU_H
+#define SSEGPU_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSEGPU_ABI_VERSION 1
+
+/* ---- error codes ------------------------------------------------------------------ */
+typedef enum {
+    SSEGPU_OK = 0,
+    SSEGPU_E_INVAL = -1,      /* bad argument */
+    SSEGPU_E_CUDA = -2,       /* CUDA runtime error / no device (see ssegpu_last_cuda_error) */
+    SSEGPU_E_NOMEM = -3,      /* allocation failed */
+    SSEGPU_E_AGAIN = -4,      /* ring full: no free batch slot */
+    SSEGPU_E_TOOBIG = -5,     /* n_records / bytes exceed the configured capacity */
+    SSEGPU_E_OVERFLOW = -6,   /* output arena too small for this batch (nothing truncated silently) */
+    SSEGPU_E_STATE = -7,      /* batch used out of order (submit before acquire, ...) */
+    SSEGPU_E_TIMEOUT = -8     /* ssegpu_batch_wait timed out */
+} ssegpu_err;
+
+/* ---- per-record status ------------------------------------------------------------- */
+#define SSEGPU_ST_OK            0u
+#define SSEGPU_ST_ERR_SYNTAX    1u  /* json.Unmarshal syntax error: dropped (sse_handler.go:137-140) */
+#define SSEGPU_ST_ERR_TYPE      2u  /* json.Unmarshal type error: dropped                        */
+#define SSEGPU_ST_FILTERED      3u  /* Last-Event-ID filter (sse_handler.go:142-145)             */
+#define SSEGPU_ST_INSPECT_DROP  4u  /* inline inspection verdict "drop" (sse_handler.go:200-204) */
+#define SSEGPU_ST_CODE_MASK     0xFu
+#define SSEGPU_ST_DONE          0x100u
+#define SSEGPU_ST_REDACTED      0x200u
+
+/* ---- op flags for submit / launch -------------------------------------------------- */
+#define SSEGPU_OP_ADAPTER   0u   /* SSE frame: event/id/data lines (sse_handler.go:211-214, :427-430) */
+#define SSEGPU_OP_BRIDGE    1u   /* subject "chat.<cid>.tokens" + re-marshalled JSON (bridge main.go:160-161) */
+#define SSEGPU_OP_GO122     2u   /* encode 0x08/0x0C as \b \f (Go >= 1.22) instead of Go 1.21's   */
+#define SSEGPU_OP_NO_FAST   4u   /* testing: force every record through the general decoder */
+
+typedef struct ssegpu_ctx ssegpu_ctx;
+typedef struct ssegpu_batch ssegpu_batch;
+
+typedef struct {
+    int32_t  device;          /* CUDA ordinal */
+    uint32_t max_records;     /* records per batch */
+    uint64_t max_in_bytes;    /* payload bytes per batch */
+    uint64_t max_out_bytes;   /* output bytes per batch; 0 = 2*max_in_bytes + 64*max_records */
+    uint32_t ring_slots;      /* batches in flight (pinned host + device buffers each); 0 = none */
+    uint32_t conv_slots;      /* per-conversation inspection state slots; 0 = none */
+    uint32_t flags;           /* reserved, 0 */
+} ssegpu_config;
+
+/* Batch counters; the host sums them over GPUs into the reference's Prometheus metrics
+ * (sse_messages_delivered_total, sse_handler.go:32-35, incremented per frame at :217, :433). */
+typedef struct {
+    uint64_t records, frames, bytes_in, bytes_out;
+    uint64_t err_syntax, err_type, filtered, done;
+    uint64_t fast_path;       /* records proven canonical (JSON out == payload) */
+    uint64_t batches;
+} ssegpu_counters;
+
+/* ---- context ----------------------------------------------------------------------- */
+/* Replaces nothing in the reference (which has no accelerator state); called once per GPU
+ * from the service's main() next to connectNATS (src/sse-adapter/main.go:177-200). */
+int  ssegpu_init(const ssegpu_config *cfg, ssegpu_ctx **out);
+void ssegpu_destroy(ssegpu_ctx *ctx);
+int  ssegpu_device_count(void);
+const char *ssegpu_strerror(int err);
+const char *ssegpu_last_cuda_error(void);
+uint32_t ssegpu_abi_version(void);
+
+/* fnv1a64(conversation_id) % n_gpus: which context owns a conversation (Go: hash/fnv New64a). */
+uint32_t ssegpu_shard(const uint8_t *conversation_id, size_t len, uint32_t n_gpus);
+
+/* fmt.Sscanf(lastEventID,"%d",&s); s++ (sse_handler.go:92-96): the per-connection
+ * startSequence the host stores in ssegpu_start_seq() for every record of that connection. */
+int64_t ssegpu_start_sequence(const char *last_event_id);
+
+/* ---- pinned batch ring (end-to-end path) ------------------------------------------- */
+/* Adapter ingress: the NATS callback (sse_handler.go:135-157, :316-333) appends msg.Data to the
+ * current batch instead of calling json.Unmarshal; bridge ingress: msg.Payload
+ * (redis-nats-bridge/main.go:142-157). */
+int       ssegpu_batch_acquire(ssegpu_ctx *ctx, ssegpu_batch **out);
+uint8_t  *ssegpu_in_bytes(ssegpu_batch *b);     /* max_in_bytes + 16 writable bytes          */
+uint32_t *ssegpu_in_off(ssegpu_batch *b);       /* n+1 offsets into in_bytes, in_off[0] = 0   */
+int64_t  *ssegpu_start_seq(ssegpu_batch *b);    /* n; 0 = filter off (ignored unless use_filter) */
+uint32_t *ssegpu_conv_slot(ssegpu_batch *b);    /* n; inspection state slot of the conversation */
+
+/* Starts H2D copy -> kernels -> D2H copy on the batch's own stream and returns at once. */
+int ssegpu_batch_submit(ssegpu_ctx *ctx, ssegpu_batch *b, uint32_t n_records, uint32_t op_flags,
+                        int use_filter);
+/* Blocks until the results are in host memory.  timeout_us = 0 waits forever. */
+int ssegpu_batch_wait(ssegpu_ctx *ctx, ssegpu_batch *b, uint32_t timeout_us);
+
+/* Adapter egress: the handler goroutine writes out[out_off[i]:out_off[i+1]] with one
+ * w.Write + Flush instead of three Fprintf (sse_handler.go:212-215, :428-431); bridge egress:
+ * nc.Publish(out[off:off+subj_len], out[off+subj_len:next]) (redis-nats-bridge/main.go:164). */
+const uint8_t  *ssegpu_out_bytes(const ssegpu_batch *b);
+const uint64_t *ssegpu_out_off(const ssegpu_batch *b);   /* n+1 */
+const uint32_t *ssegpu_status(const ssegpu_batch *b);    /* n   */
+const uint32_t *ssegpu_subj_len(const ssegpu_batch *b);  /* n, bridge mode only */
+int ssegpu_batch_release(ssegpu_ctx *ctx, ssegpu_batch *b);
+
+/* Counters accumulated over all completed batches of this context (host-side gather). */
+int ssegpu_counters_get(ssegpu_ctx *ctx, ssegpu_counters *out);
+
+/* ---- device-resident launch (kernel-level path, used by the bench and the parity tests) -- */
+/* Same computation as submit, on buffers that already live in this context's GPU memory.
+ * d_in must be 16-byte aligned with 16 readable bytes after the last payload byte.
+ * d_subj_len may be NULL in adapter mode, d_start_seq NULL switches the filter off.
+ * stream is a cudaStream_t (NULL = the context's stream).  Asynchronous. Not re-entrant per
+ * context (the launch scratch is per context). */
+int ssegpu_frame_launch(ssegpu_ctx *ctx, const void *d_in, const uint32_t *d_in_off,
+                        const int64_t *d_start_seq, uint32_t n_records, uint32_t op_flags,
+                        void *d_out, uint64_t out_cap, uint64_t *d_out_off, uint32_t *d_subj_len,
+                        uint32_t *d_status, void *stream);
+/* After the launch's stream has been synchronised: adds the launch's counters into *out and
+ * returns SSEGPU_E_OVERFLOW if out_cap was too small. */
+int ssegpu_frame_launch_result(ssegpu_ctx *ctx, ssegpu_counters *out);
+
+/* Number of kernel launches this context has issued so far (bench.py "gpu_launches"). */
+uint64_t ssegpu_launch_count(ssegpu_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

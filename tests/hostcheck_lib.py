@@ -1,0 +1,43 @@
+"""ctypes binding of tests/hostcheck/libhostcheck.so: the product's per-record device logic
+(csrc/sse_record.cuh) compiled for the CPU as a TEST DOUBLE.  Never used by the product."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HC_DIR = os.path.join(ROOT, "tests", "hostcheck")
+CSRC = os.path.join(ROOT, "distributed-sse-for-llm-response_b200", "csrc")
+u8p, u32p, u64p, i64p = (C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_int64))
+OP_BRIDGE, OP_GO122, OP_NO_FAST = 1, 2, 4
+
+
+def _ptr(a, t):
+    return a.ctypes.data_as(t) if a is not None else None
+
+
+def load():
+    so = os.path.join(HC_DIR, "libhostcheck.so")
+    srcs = [os.path.join(HC_DIR, "hostcheck.cpp"), os.path.join(CSRC, "sse_record.cuh")]
+    if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-fPIC", "-shared", "-I", CSRC, "-o", so, srcs[0]])
+    lib = C.CDLL(so)
+    lib.hc_batch.restype = C.c_int
+    lib.hc_batch.argtypes = [u8p, u32p, C.c_uint32, i64p, C.c_uint32, u8p, C.c_uint64, u64p, u32p, u32p, u32p]
+    return lib
+
+
+def run(lib, arena, off, start_seq=None, op=0):
+    n = len(off) - 1
+    cap = int(off[n]) * 9 + 200 * n + 64
+    out = np.zeros(cap, dtype=np.uint8)
+    out_off = np.empty(n + 1, dtype=np.uint64)
+    subj = np.empty(n, dtype=np.uint32)
+    status = np.empty(n, dtype=np.uint32)
+    nfast = C.c_uint32(0)
+    ss = None if start_seq is None else np.ascontiguousarray(start_seq, dtype=np.int64)
+    rc = lib.hc_batch(_ptr(arena, u8p), _ptr(off, u32p), n, _ptr(ss, i64p), op, _ptr(out, u8p), cap,
+                      _ptr(out_off, u64p), _ptr(subj, u32p), _ptr(status, u32p), C.byref(nfast))
+    assert rc == 0, rc
+    return out[: int(out_off[n])], out_off, subj, status, nfast.value

@@ -1,0 +1,216 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI, against the hand-typed
+vectors, the committed fixtures and the C oracle on the same seeded inputs.  Bit-exact: bytes, offsets, status words."""
+import os
+import random
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+import hand_vectors as hv  # noqa: E402
+import make_golden as mg  # noqa: E402
+from __graft_entry__ import load_package  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    return load_package()
+
+
+@pytest.fixture(scope="module")
+def eng(pkg):
+    e = pkg.SseGpu(device=0, max_records=1 << 20, max_in_bytes=200 << 20, ring_slots=2)
+    yield e
+    e.close()
+
+
+def run_batch(eng, arena, off, start=None, op=0):
+    b = eng.acquire()
+    b.fill(arena, off, start)
+    b.submit(len(off) - 1, op, use_filter=start is not None)
+    b.wait()
+    res = (b.out.copy(), b.out_off.copy(), b.status.copy(), b.subj_len.copy())
+    b.release()
+    return res
+
+
+def slices(out, out_off):
+    raw = out.tobytes()
+    return [raw[int(out_off[i]):int(out_off[i + 1])] for i in range(len(out_off) - 1)]
+
+
+def test_hand_vectors(pkg, eng, oracle):
+    arena, off = oracle.pack([v[1] for v in hv.ADAPTER])
+    start = np.array([v[2] for v in hv.ADAPTER], dtype=np.int64)
+    for op in (0, pkg.OP_NO_FAST):
+        out, out_off, status, _ = run_batch(eng, arena, off, start, op)
+        for (name, _, _, st, frame), g, s in zip(hv.ADAPTER, slices(out, out_off), status):
+            assert int(s) == st, name
+            assert g == frame, name
+    g5 = [v[1] for v in hv.ADAPTER if v[0] == "G5_escapes_go121"]
+    arena, off = oracle.pack(g5)
+    out, out_off, _, _ = run_batch(eng, arena, off, None, pkg.OP_GO122)
+    assert slices(out, out_off)[0] == hv.G5_GO122_FRAME
+    arena, off = oracle.pack([b[0] for b in hv.BRIDGE])
+    out, out_off, status, subj = run_batch(eng, arena, off, None, pkg.OP_BRIDGE)
+    for (payload, st, sj, js), g, sl, s in zip(hv.BRIDGE, slices(out, out_off), subj, status):
+        assert int(s) == st and g[: int(sl)] == sj and g[int(sl):] == js
+
+
+@pytest.mark.parametrize("op", [0, 4, 2, 1, 1 | 4])
+def test_golden_fixtures(pkg, eng, oracle, golden, op):
+    arena, off = oracle.pack([bytes.fromhex(c["in"]) for c in golden])
+    start = np.array([c["start"] for c in golden], dtype=np.int64)
+    out, out_off, status, subj = run_batch(eng, arena, off, None if op & 1 else start, op)
+    for c, g, sl, s in zip(golden, slices(out, out_off), subj, status):
+        if op & pkg.OP_BRIDGE:
+            assert int(s) == c["bstatus"], c["name"]
+            assert g[: int(sl)].hex() == c["subject"] and g[int(sl):].hex() == c["json"], c["name"]
+        else:
+            assert int(s) == c["status"], c["name"]
+            assert g.hex() == (c.get("frame122", c["frame"]) if op & pkg.OP_GO122 else c["frame"]), c["name"]
+
+
+def test_differential_fuzz_vs_oracle(pkg, eng, oracle):
+    rng = random.Random(99)
+    base = mg.canon("7f3c2b1a-1111-4222-8333-944455556666", " hello", 42, False, 1700000000000000000)
+    payloads = []
+    for k in range(30000):
+        r = rng.random()
+        if r < 0.4:
+            payloads.append(mg.canon(mg.rand_text(rng, rng.randrange(0, 40), 0.15), mg.rand_text(rng, rng.randrange(0, 20), 0.3),
+                                     rng.randrange(-5, 5000), rng.random() < 0.05, rng.randrange(-(1 << 63), 1 << 63)))
+        elif r < 0.7:
+            payloads.append(mg.structured(rng))
+        else:
+            payloads.append(mg.mutate(rng, rng.choice([base, payloads[-1] if payloads else base])))
+    arena, off = oracle.pack(payloads)
+    start = np.array([rng.choice([0, 0, 3, 100]) for _ in payloads], dtype=np.int64)
+    for op, go122 in ((0, False), (pkg.OP_GO122, True), (pkg.OP_NO_FAST, False)):
+        want_out, want_off, want_status = oracle.adapter(arena, off, start, go122=go122)
+        out, out_off, status, _ = run_batch(eng, arena, off, start, op)
+        assert np.array_equal(status, want_status)
+        assert np.array_equal(out_off, want_off)
+        assert np.array_equal(out, want_out)
+    want_out, want_off, want_subj, want_status = oracle.bridge(arena, off)
+    out, out_off, status, subj = run_batch(eng, arena, off, None, pkg.OP_BRIDGE)
+    assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off)
+    assert np.array_equal(subj, want_subj) and np.array_equal(out, want_out)
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 127, 128, 129, 255, 256, 257, 1000])
+def test_tile_boundaries(pkg, eng, oracle, n):
+    arena, off = pkg.workload.generate(1, max(n, 1), 1)
+    off = off[: n + 1].copy()
+    want_out, want_off, want_status = oracle.adapter(arena, off)
+    out, out_off, status, _ = run_batch(eng, arena, off)
+    assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
+
+
+def test_empty_and_ragged_records(pkg, eng, oracle):
+    payloads = [b"", b"", b"null", b"", b"x" * 5, b"", mg.canon("c", "t", 1, False, 2), b""] * 40 + [b""] * 300
+    arena, off = oracle.pack(payloads)
+    want_out, want_off, want_status = oracle.adapter(arena, off)
+    out, out_off, status, _ = run_batch(eng, arena, off)
+    assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
+
+
+def test_oversize_tiles_use_global_path(pkg, eng, oracle):
+    """Tiles whose bytes exceed the shared-memory caps (input and/or output side) stay bit-exact."""
+    rng = random.Random(5)
+    payloads = []
+    for k in range(600):
+        r = rng.random()
+        if r < 0.05:
+            payloads.append(mg.canon("c", "x" * rng.randrange(5000, 40000), k, False, 2))
+        elif r < 0.1:
+            payloads.append(mg.canon("c", "<\n&" * rng.randrange(1000, 3000), k, False, 2))      # output 4x input
+        elif r < 0.15:
+            payloads.append(b'{"pad":"' + b"p" * rng.randrange(1000, 30000) + b'","token":"t"}')  # big in, tiny out
+        else:
+            payloads.append(mg.canon("conv-%d" % k, " tok", k, False, 2))
+    arena, off = oracle.pack(payloads)
+    for op in (0, pkg.OP_BRIDGE):
+        if op == 0:
+            want_out, want_off, want_status = oracle.adapter(arena, off)
+        else:
+            want_out, want_off, _, want_status = oracle.bridge(arena, off)
+        out, out_off, status, _ = run_batch(eng, arena, off, None, op)
+        assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
+
+
+@pytest.mark.parametrize("config,n_conv,n_tok", [(0, 1000, 512), (1, 10000, 100)])
+def test_baseline_workloads_bit_exact(pkg, eng, oracle, config, n_conv, n_tok):
+    arena, off = pkg.workload.generate(config, n_conv, n_tok)
+    want_out, want_off, want_status = oracle.adapter(arena, off)
+    before = eng.counters()
+    out, out_off, status, _ = run_batch(eng, arena, off)
+    after = eng.counters()
+    assert np.array_equal(status, want_status)
+    assert np.array_equal(out_off, want_off)
+    assert np.array_equal(out, want_out)
+    n = n_conv * n_tok
+    assert after["frames"] - before["frames"] == n and after["fast_path"] - before["fast_path"] == n
+    assert after["done"] - before["done"] == n_conv
+    assert after["bytes_in"] - before["bytes_in"] == int(off[n]) and after["bytes_out"] - before["bytes_out"] == int(want_off[n])
+
+
+def test_output_overflow_is_reported_not_truncated(pkg, oracle):
+    arena, off = pkg.workload.generate(1, 1000, 4)
+    e = pkg.SseGpu(device=0, max_records=4096, max_in_bytes=1 << 20, max_out_bytes=100000, ring_slots=1)
+    try:
+        b = e.acquire()
+        b.fill(arena, off)
+        b.submit(len(off) - 1, 0)
+        with pytest.raises(pkg.SseGpuError) as err:
+            b.wait()
+        assert err.value.code == -6
+        b.release()
+    finally:
+        e.close()
+
+
+def test_device_resident_launch_full_size_properties(pkg, oracle):
+    """BASELINE config-1 shape at a size the GPU does in milliseconds: checked by size-independent properties
+    (offsets == prefix sum of per-record lengths; every frame == header + payload + trailer) and against the
+    oracle on a sampled window."""
+    import torch
+    n_conv, n_tok = 10000, 200
+    arena, off = pkg.workload.generate(1, n_conv, n_tok)
+    n = n_conv * n_tok
+    eng = pkg.SseGpu(device=0, max_records=n, max_in_bytes=int(off[n]) + 64)
+    try:
+        d_in = torch.from_numpy(arena).cuda()
+        d_off = torch.from_numpy(off.view(np.int32)).cuda()
+        cap = int(off[n]) + 48 * n
+        d_out = torch.zeros(cap, dtype=torch.uint8, device="cuda")
+        d_out_off = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
+        d_status = torch.zeros(n, dtype=torch.int32, device="cuda")
+        st = torch.cuda.current_stream().cuda_stream
+        for _ in range(2):          # second launch reuses the zeroed scratch: must be idempotent
+            eng.frame_launch(d_in.data_ptr(), d_off.data_ptr(), 0, n, 0, d_out.data_ptr(), cap, d_out_off.data_ptr(), 0,
+                             d_status.data_ptr(), st)
+        torch.cuda.synchronize()
+        rc, c = eng.launch_result()
+        assert rc == 0 and c["frames"] == n and c["fast_path"] == n and c["done"] == n_conv
+        out_off = d_out_off.cpu().numpy().astype(np.uint64)
+        status = d_status.cpu().numpy().astype(np.uint32)
+        seq_digits = np.char.str_len((np.arange(n) // n_conv + 1).astype(str))
+        lens = np.diff(off.astype(np.int64)) + 26 + seq_digits
+        assert np.array_equal(np.diff(out_off.astype(np.int64)), lens)
+        assert c["bytes_out"] == int(out_off[n])
+        assert ((status & 0xF) == 0).all() and int((status & 0x100 != 0).sum()) == n_conv
+        out = d_out.cpu().numpy()
+        lo, hi = n // 2 - 5000, n // 2 + 5000
+        sub_off = (off[lo:hi + 1] - off[lo]).astype(np.uint32)
+        sub_arena = np.concatenate([arena[off[lo]:off[hi]], np.zeros(16, np.uint8)])
+        want_out, want_off, _ = oracle.adapter(sub_arena, sub_off)
+        assert np.array_equal(out[int(out_off[lo]):int(out_off[hi])], want_out)
+        # checksum of checksums: the payload bytes survive verbatim inside the frames
+        assert int(out[: int(out_off[n])].astype(np.uint64).sum()) == int(arena[: int(off[n])].astype(np.uint64).sum()) + \
+            sum(b"event: token\nid: \ndata: \n\n") * n + int(sum((ord(ch) for s in (np.arange(n_tok) + 1).astype(str) for ch in s))) * n_conv
+    finally:
+        eng.close()
