@@ -165,7 +165,8 @@ def run_gpu(args):
     d_out = torch.empty(cap, dtype=torch.uint8, device="cuda")
     d_out_off = torch.empty(n + 1, dtype=torch.int64, device="cuda")
     d_status = torch.empty(n, dtype=torch.int32, device="cuda")
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()          # explicit non-default stream: launches and timing events share it
+    torch.cuda.synchronize()
 
     def launch():
         eng.frame_launch(d_in.data_ptr(), d_off.data_ptr(), 0, n, pkg.OP_ADAPTER, d_out.data_ptr(), cap, d_out_off.data_ptr(), 0,

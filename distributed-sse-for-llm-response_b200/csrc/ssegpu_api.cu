@@ -252,7 +252,7 @@ const uint32_t* ssegpu_subj_len(const ssegpu_batch* b) { return b ? b->h_subj : 
 
 int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t op, int use_filter) {
     if (!ctx || !b || b->ctx != ctx) return SSEGPU_E_INVAL;
-    if (b->state != ACQUIRED) return SSEGPU_E_STATE;
+    if (b->state != ACQUIRED && b->state != DONE) return SSEGPU_E_STATE;   // DONE: the owner re-submits the slot
     if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
     const uint64_t in_total = n ? b->h_in_off[n] : 0;
     if (in_total > ctx->cfg.max_in_bytes) return SSEGPU_E_TOOBIG;

@@ -189,7 +189,9 @@ def test_device_resident_launch_full_size_properties(pkg, oracle):
         d_out = torch.zeros(cap, dtype=torch.uint8, device="cuda")
         d_out_off = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
         d_status = torch.zeros(n, dtype=torch.int32, device="cuda")
-        st = torch.cuda.current_stream().cuda_stream
+        stream = torch.cuda.Stream()
+        torch.cuda.synchronize()
+        st = stream.cuda_stream
         for _ in range(2):          # second launch reuses the zeroed scratch: must be idempotent
             eng.frame_launch(d_in.data_ptr(), d_off.data_ptr(), 0, n, 0, d_out.data_ptr(), cap, d_out_off.data_ptr(), 0,
                              d_status.data_ptr(), st)
