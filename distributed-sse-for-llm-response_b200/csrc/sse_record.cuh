@@ -170,48 +170,52 @@ template <class Src> SSE_HD uint32_t next_rune(const Src& s, uint32_t& pos, uint
 }
 
 // --------------------------------------------------------------- byte writer ----
-// Streams bytes to a Dst at an arbitrary byte position using aligned 32-bit stores for
-// whole words; a leading/trailing partial word is written bytewise because its other
-// bytes belong to the neighbouring record (written by another thread).  With EMIT=false
-// it only counts.
+// Streams bytes to a Dst at an arbitrary byte position.  Bytes gather in a 64-bit accumulator
+// and leave as aligned 32-bit stores; only the stream's first and last word, which it shares
+// with the neighbouring records (written by other threads), are written bytewise.  Feeding it
+// is branch-light: put_n() is shift/or plus one predicated flush.  EMIT=false only counts.
 template <class Dst, bool EMIT> struct Writer {
     typedef typename Dst::pos_t pos_t;
     const Dst& d;
-    pos_t pos;          // next byte position
-    uint32_t acc;       // bytes of the current word gathered so far (low bytes first)
-    uint32_t first;     // byte index within the first word where this stream started (0 once flushed whole)
-    SSE_HD Writer(const Dst& dst, pos_t start) : d(dst), pos(start), acc(0), first((uint32_t)start & 3u) {}
-    SSE_HD void flush_word() {                          // pos is word aligned, acc holds bytes [first..3]
+    pos_t wpos;         // aligned position of the word being filled
+    uint64_t acc;       // gathered bytes, bit 0 = byte 0 of the word at wpos
+    uint32_t sh;        // bits of acc in use (8 * bytes), 0..56
+    uint32_t first;     // first byte of the word at wpos that belongs to this stream (0 after the first flush)
+    SSE_HD Writer(const Dst& dst, pos_t start)
+        : d(dst), wpos(start & ~(pos_t)3), acc(0), sh(((uint32_t)start & 3u) * 8), first((uint32_t)start & 3u) {}
+    SSE_HD pos_t pos() const { return wpos + (sh >> 3); }
+    SSE_HD void flush_word() {                          // sh >= 32: the word at wpos is complete
         if (EMIT) {
-            pos_t w = pos - 4;
-            if (first == 0) d.st32a(w, acc);
-            else { for (uint32_t k = first; k < 4; k++) d.st8(w + k, (acc >> (8 * k)) & 0xFF); }
+            uint32_t v = (uint32_t)acc;
+            if (first == 0) d.st32a(wpos, v);
+            else { for (uint32_t k = first; k < 4; k++) d.st8(wpos + k, (v >> (8 * k)) & 0xFF); first = 0; }
         }
-        first = 0; acc = 0;
+        acc >>= 32; sh -= 32; wpos += 4;
     }
-    SSE_HD void put(uint32_t b) {
-        if (EMIT) acc |= (b & 0xFF) << (8 * ((uint32_t)pos & 3u));
-        pos++;
-        if (((uint32_t)pos & 3u) == 0) flush_word();
+    SSE_HD void put_n(uint32_t w, uint32_t n) {         // low n (1..4) bytes of w, little endian
+        if (EMIT) acc |= (uint64_t)(w & (0xFFFFFFFFu >> (32 - 8 * n))) << sh;
+        sh += 8 * n;
+        if (sh >= 32) flush_word();
     }
-    SSE_HD void put32(uint32_t w) {                     // four bytes, little endian
-        if (!EMIT) { pos += 4; return; }
-        uint32_t sh = ((uint32_t)pos & 3u) * 8;
-        if (sh == 0) { acc = w; pos += 4; flush_word(); return; }
-        acc |= w << sh;
-        pos += 4 - (sh >> 3);
+    SSE_HD void put(uint32_t b) { put_n(b, 1); }
+    SSE_HD void put32(uint32_t w) {
+        if (EMIT) acc |= (uint64_t)w << sh;
+        sh += 32;
         flush_word();
-        acc = w >> (32 - sh);
-        pos += sh >> 3;
     }
-    SSE_HD void put_n(uint32_t w, uint32_t n) {         // low n (1..3) bytes of w
-        for (uint32_t k = 0; k < n; k++) put((w >> (8 * k)) & 0xFF);
+    SSE_HD void store_word(uint32_t v) {                // only when sh == 0 and first == 0
+        if (EMIT) d.st32a(wpos, v);
+        wpos += 4;
+    }
+    SSE_HD void skip(uint32_t n) {                      // counting only
+        uint32_t t = (sh >> 3) + n;
+        wpos += t & ~3u; sh = (t & 3u) * 8;
     }
     SSE_HD void finish() {                              // trailing partial word
-        uint32_t k1 = (uint32_t)pos & 3u;
+        uint32_t k1 = sh >> 3;
         if (EMIT && k1) {
-            pos_t w = pos - k1;
-            for (uint32_t k = first; k < k1; k++) d.st8(w + k, (acc >> (8 * k)) & 0xFF);
+            uint32_t v = (uint32_t)acc;
+            for (uint32_t k = first; k < k1; k++) d.st8(wpos + k, (v >> (8 * k)) & 0xFF);
         }
     }
 };
@@ -219,7 +223,11 @@ template <class Dst, bool EMIT> struct Writer {
 template <class W> SSE_HD void put_lit(W& w, const char* s, uint32_t n) {
     uint32_t i = 0;
     for (; i + 4 <= n; i += 4) w.put32(w4(s + i));
-    for (; i < n; i++) w.put((uint8_t)s[i]);
+    if (i < n) {
+        uint32_t v = 0;
+        for (uint32_t k = 0; i + k < n; k++) v |= (uint32_t)(uint8_t)s[i + k] << (8 * k);
+        w.put_n(v, n - i);
+    }
 }
 #define SSE_PUT_LIT(w, lit) put_lit(w, lit, (uint32_t)(sizeof(lit) - 1))
 
@@ -278,11 +286,27 @@ template <class Src, class W> SSE_HD void put_json_string(const Src& s, uint32_t
     w.put('"');
 }
 
-// verbatim copy of n source bytes starting at byte position sp
+// verbatim copy of n source bytes starting at byte position sp: bytes until the destination is
+// word aligned, then one aligned load + funnel shift + aligned store per word (the relative
+// alignment of source and destination is constant), then the tail bytes.
 template <class Src, class W> SSE_HD void put_copy(const Src& s, uint32_t sp, uint32_t n, W& w) {
-    while (n && (sp & 3u)) { w.put(s.ld8(sp)); sp++; n--; }
-    for (; n >= 4; n -= 4, sp += 4) w.put32(s.ld32a(sp));
-    for (; n; n--, sp++) w.put(s.ld8(sp));
+    uint32_t k = (4u - (w.sh >> 3)) & 3u;
+    if (k > n) k = n;
+    if (k) { w.put_n(ld32u(s, sp), k); sp += k; n -= k; }
+    uint32_t nw = n >> 2;
+    if (nw) {
+        uint32_t a = sp & ~3u;
+        const uint32_t shb = (sp & 3u) * 8;
+        uint32_t lo = s.ld32a(a);
+        for (uint32_t i = 0; i < nw; i++) {
+            a += 4;
+            uint32_t hi = s.ld32a(a);
+            w.store_word(funnel_r(lo, hi, shb));
+            lo = hi;
+        }
+        sp += nw * 4; n -= nw * 4;
+    }
+    if (n) w.put_n(ld32u(s, sp), n);
 }
 
 // ------------------------------------------------------------------ emission ----
@@ -293,11 +317,11 @@ SSE_HD void emit_record(const Src& s, uint32_t o, uint32_t L, const Plan& pl, ui
     const bool go122 = (op & OP_GO122) != 0;
     if (op & OP_BRIDGE) {
         // redis-nats-bridge/main.go:160  fmt.Sprintf("chat.%s.tokens", token.ConversationID)
-        auto p0 = w.pos;
+        auto p0 = w.pos();
         SSE_PUT_LIT(w, "chat.");
         for (uint32_t b = o + pl.cid_b, e = o + pl.cid_e; b < e;) put_rune_raw(w, next_rune(s, b, e));
         SSE_PUT_LIT(w, ".tokens");
-        if (subj_len) *subj_len = (uint32_t)(w.pos - p0);
+        if (subj_len) *subj_len = (uint32_t)(w.pos() - p0);
     } else {
         SSE_PUT_LIT(w, "event: token\nid: ");            // sse_handler.go:212-213
         put_int(w, pl.seq);
@@ -329,13 +353,17 @@ SSE_HD void emit_record(const Src& s, uint32_t o, uint32_t L, const Plan& pl, ui
 // flagged byte, which is the only one used).
 SSE_HD uint32_t special_mask(uint32_t w) {
     const uint32_t H = 0x80808080u, L1 = 0x01010101u;
-    uint32_t hi = w & H;                                        // >= 0x80
-    uint32_t lt = (w - 0x20202020u) & ~w & H;                   // < 0x20
+    uint32_t lt = (w - 0x20202020u) & ~w;                       // < 0x20
     uint32_t a = (w & 0xFBFBFBFBu) ^ 0x22222222u;               // '"' (0x22) or '&' (0x26)
     uint32_t b = (w & 0xFDFDFDFDu) ^ 0x3C3C3C3Cu;               // '<' (0x3C) or '>' (0x3E)
     uint32_t c = w ^ 0x5C5C5C5Cu;                               // '\\'
     uint32_t z = ((a - L1) & ~a) | ((b - L1) & ~b) | ((c - L1) & ~c);
-    return hi | lt | (z & H);
+    return (w | lt | z) & H;                                    // w & H: >= 0x80
+}
+// bit 7 of byte k set iff byte k is not an ASCII digit (exact for every byte)
+SSE_HD uint32_t nondigit_mask(uint32_t w) {
+    uint32_t x = w ^ 0x30303030u;                               // digits -> 0x00..0x09
+    return (((x & 0x7F7F7F7Fu) + 0x76767676u) | x) & 0x80808080u;
 }
 
 SSE_HD uint32_t first_byte_idx(uint32_t m) {                    // m != 0, flags at bit 7 of each byte
@@ -346,41 +374,48 @@ SSE_HD uint32_t first_byte_idx(uint32_t m) {                    // m != 0, flags
 #endif
 }
 
+// \uXXXX spellings json.Marshal itself produces (so that they survive decode->encode verbatim)
+SSE_HD bool canon_u_escape(uint32_t h, bool go122) {           // h = the four hex bytes, little endian
+    const uint32_t h3 = h >> 24, h012 = h & 0xFFFFFFu;
+    if (h012 == (w4("000\0") & 0xFFFFFFu)) {                    // \u000X: controls without a short form
+        if (go122 && (h3 == '8' || h3 == 'c')) return false;
+        return (h3 >= '0' && h3 <= '8') || h3 == 'b' || h3 == 'c' || h3 == 'e' || h3 == 'f';
+    }
+    if (h012 == (w4("001\0") & 0xFFFFFFu)) return (h3 >= '0' && h3 <= '9') || (h3 >= 'a' && h3 <= 'f');
+    if (h012 == (w4("003\0") & 0xFFFFFFu)) return h3 == 'c' || h3 == 'e';                  // < >
+    if (h012 == (w4("002\0") & 0xFFFFFFu)) return h3 == '6';                               // &
+    if (h012 == (w4("202\0") & 0xFFFFFFu)) return h3 == '8' || h3 == '9';                  // U+2028 / U+2029
+    return false;
+}
+
 // Scans a canonical string body starting at pos (just after the opening quote); on success
 // pos is left ON the closing quote.  Fails (false) on anything json.Marshal would not have
 // produced verbatim -- the general path then decides what it really is.
 template <class Src> SSE_HD bool scan_canon_string(const Src& s, uint32_t& pos, uint32_t end, bool go122, bool& has_esc) {
     for (;;) {
-        if (pos >= end) return false;
-        uint32_t w = ld32u(s, pos);
-        uint32_t m = special_mask(w);
-        if (m == 0) { pos += 4; continue; }
-        uint32_t k = first_byte_idx(m);
+        // word loop: one aligned load per 4 bytes, the previous word is carried
+        uint32_t a = pos & ~3u;
+        const uint32_t shb = (pos & 3u) * 8;
+        uint32_t lo = s.ld32a(a), w, m;
+        for (;;) {
+            if (pos >= end) return false;
+            a += 4;
+            uint32_t hi = s.ld32a(a);
+            w = funnel_r(lo, hi, shb);
+            m = special_mask(w);
+            if (m) break;
+            lo = hi;
+            pos += 4;
+        }
+        const uint32_t k = first_byte_idx(m);
         pos += k;
-        uint32_t c = (w >> (8 * k)) & 0xFF;
+        const uint32_t c = (w >> (8 * k)) & 0xFF;
         if (c == '"') return pos < end;
         if (c == '\\') {
             has_esc = true;
             uint32_t e = s.ld8(pos + 1);
             if (e == '"' || e == '\\' || e == 'n' || e == 'r' || e == 't' || (go122 && (e == 'b' || e == 'f'))) { pos += 2; continue; }
-            if (e != 'u') return false;
-            uint32_t h = ld32u(s, pos + 2);
-            uint32_t h3 = h >> 24;
-            bool ok;
-            uint32_t h012 = h & 0xFFFFFFu;
-            if (h012 == (w4("000\0") & 0xFFFFFFu)) {            // \u000X : control chars without a short form
-                ok = ((h3 >= '0' && h3 <= '8') || h3 == 'b' || h3 == 'c' || h3 == 'e' || h3 == 'f');
-                if (go122 && (h3 == '8' || h3 == 'c')) ok = false;
-            } else if (h012 == (w4("001\0") & 0xFFFFFFu)) {
-                ok = (h3 >= '0' && h3 <= '9') || (h3 >= 'a' && h3 <= 'f');
-            } else if (h012 == (w4("003\0") & 0xFFFFFFu)) {
-                ok = (h3 == 'c' || h3 == 'e');                  // < >
-            } else if (h012 == (w4("002\0") & 0xFFFFFFu)) {
-                ok = (h3 == '6');                               // &
-            } else if (h012 == (w4("202\0") & 0xFFFFFFu)) {
-                ok = (h3 == '8' || h3 == '9');                  // U+2028 / U+2029
-            } else ok = false;
-            if (!ok) return false;
+            if (e != 'u' || !canon_u_escape(ld32u(s, pos + 2), go122)) return false;
             pos += 6;
             continue;
         }
@@ -395,32 +430,43 @@ template <class Src> SSE_HD bool scan_canon_string(const Src& s, uint32_t& pos, 
     }
 }
 
-// canonical integer: -?(0|[1-9][0-9]*) within int64, and not "-0"
-template <class Src> SSE_HD bool scan_canon_int(const Src& s, uint32_t& pos, uint32_t end, int64_t& out) {
-    bool neg = false;
-    uint32_t c = s.ld8(pos);
-    if (c == '-') { neg = true; pos++; c = s.ld8(pos); }
-    if (c < '0' || c > '9') return false;
-    uint64_t v = c - '0';
-    pos++;
-    if (v == 0) {
-        if (neg) return false;
-        out = 0;
-        uint32_t d = s.ld8(pos);
-        return !(d >= '0' && d <= '9') || pos >= end;
+// canonical integer literal: -?(0|[1-9][0-9]*), at most 19 digits and certainly inside int64
+// (a 19-digit literal starting with '9' is left to the general path, which does the exact
+// range check).  Leaves pos just past the literal.  The VALUE is produced only when
+// want_value (sequence: needed by the filter and the slow emitter) and then only for <= 9
+// digits; longer sequences also go to the general path.  Word-at-a-time digit test.
+template <class Src> SSE_HD bool scan_canon_int(const Src& s, uint32_t& pos, uint32_t end, bool want_value, int64_t& out) {
+    const uint32_t c0 = s.ld8(pos);
+    const uint32_t neg = (c0 == '-') ? 1u : 0u;
+    const uint32_t start = pos + neg;
+    uint32_t nd = 0;
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+    for (uint32_t i = 0; i < 5; i++) {
+        uint32_t m = nondigit_mask(ld32u(s, start + 4 * i));
+        if (m) { nd += first_byte_idx(m); break; }
+        nd += 4;
     }
-    uint32_t nd = 1;
-    for (;;) {
-        if (pos >= end) break;
-        uint32_t d = s.ld8(pos) - '0';
-        if (d > 9) break;
-        if (++nd > 19) return false;
-        v = v * 10 + d;
-        pos++;
+    if (nd == 0 || nd > 19 || start + nd > end) return false;
+    const uint32_t d0 = s.ld8(start);
+    if (d0 == '0' && (nd != 1 || neg)) return false;            // leading zero, "-0"
+    if (nd == 19 && d0 == '9') return false;                    // might overflow: exact check in the general path
+    pos = start + nd;
+    if (want_value) {
+        if (nd > 9) return false;
+        uint32_t v = 0;
+        for (uint32_t i = 0; i < nd; i++) v = v * 10 + (s.ld8(start + i) - '0');
+        out = neg ? -(int64_t)v : (int64_t)v;
     }
-    if (neg) { if (v > (1ull << 63)) return false; out = (int64_t)(0 - v); }
-    else     { if (v > 0x7FFFFFFFFFFFFFFFull) return false; out = (int64_t)v; }
     return true;
+}
+
+// three unaligned words at pos with four aligned loads
+template <class Src> SSE_HD void ld3u(const Src& s, uint32_t pos, uint32_t& w0, uint32_t& w1, uint32_t& w2) {
+    const uint32_t a = pos & ~3u, shb = (pos & 3u) * 8;
+    uint32_t x0 = s.ld32a(a), x1 = s.ld32a(a + 4), x2 = s.ld32a(a + 8), x3 = s.ld32a(a + 12);
+    w0 = funnel_r(x0, x1, shb); w1 = funnel_r(x1, x2, shb); w2 = funnel_r(x2, x3, shb);
 }
 
 // True iff the record is byte-for-byte what json.Marshal(TokenMessage) would emit.
@@ -428,42 +474,51 @@ template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L
     const bool go122 = (op & OP_GO122) != 0;
     if (L < 72) return false;
     const uint32_t end = o + L;
+    uint32_t w0, w1, w2, d;
     // {"conversation_id":"   (20 bytes)
-    if (ld32u(s, o) != w4("{\"co") || ld32u(s, o + 4) != w4("nver") || ld32u(s, o + 8) != w4("sati") ||
-        ld32u(s, o + 12) != w4("on_i") || ld32u(s, o + 16) != w4("d\":\"")) return false;
+    {
+        const uint32_t a = o & ~3u, shb = (o & 3u) * 8;
+        uint32_t x0 = s.ld32a(a), x1 = s.ld32a(a + 4), x2 = s.ld32a(a + 8), x3 = s.ld32a(a + 12), x4 = s.ld32a(a + 16), x5 = s.ld32a(a + 20);
+        d = (funnel_r(x0, x1, shb) ^ w4("{\"co")) | (funnel_r(x1, x2, shb) ^ w4("nver")) | (funnel_r(x2, x3, shb) ^ w4("sati")) |
+            (funnel_r(x3, x4, shb) ^ w4("on_i")) | (funnel_r(x4, x5, shb) ^ w4("d\":\""));
+        if (d) return false;
+    }
     uint32_t pos = o + 20;
     bool cid_esc = false, tok_esc = false;
     pl.cid_b = 20;
     if (!scan_canon_string(s, pos, end, go122, cid_esc)) return false;
     pl.cid_e = pos - o;
     // ","token":"   (11 bytes)
-    if (pos + 11 > end) return false;
-    if (ld32u(s, pos) != w4("\",\"t") || ld32u(s, pos + 4) != w4("oken") || (ld32u(s, pos + 8) & 0xFFFFFFu) != (w4("\":\"\0") & 0xFFFFFFu)) return false;
+    ld3u(s, pos, w0, w1, w2);
+    d = (w0 ^ w4("\",\"t")) | (w1 ^ w4("oken")) | ((w2 ^ w4("\":\"\0")) & 0xFFFFFFu);
+    if (d || pos + 11 > end) return false;
     pos += 11;
     pl.tok_b = pos - o;
     if (!scan_canon_string(s, pos, end, go122, tok_esc)) return false;
     pl.tok_e = pos - o;
     // ","sequence":   (13 bytes)
-    if (pos + 13 > end) return false;
-    if (ld32u(s, pos) != w4("\",\"s") || ld32u(s, pos + 4) != w4("eque") || ld32u(s, pos + 8) != w4("nce\"") || s.ld8(pos + 12) != ':') return false;
+    ld3u(s, pos, w0, w1, w2);
+    d = (w0 ^ w4("\",\"s")) | (w1 ^ w4("eque")) | (w2 ^ w4("nce\"")) | (s.ld8(pos + 12) ^ ':');
+    if (d || pos + 14 > end) return false;
     pos += 13;
     pl.seq_b = pos - o;
-    if (pos >= end || !scan_canon_int(s, pos, end, pl.seq)) return false;
+    if (!scan_canon_int(s, pos, end, true, pl.seq)) return false;
     pl.seq_n = pos - o - pl.seq_b;
-    // ,"done":   (8 bytes)
-    if (pos + 8 > end) return false;
-    if (ld32u(s, pos) != w4(",\"do") || ld32u(s, pos + 4) != w4("ne\":")) return false;
+    // ,"done":   (8 bytes) + true|false
+    ld3u(s, pos, w0, w1, w2);
+    d = (w0 ^ w4(",\"do")) | (w1 ^ w4("ne\":"));
+    if (d || pos + 13 > end) return false;
     pos += 8;
-    if (pos + 5 > end) return false;
-    uint32_t lit = ld32u(s, pos);
-    if (lit == w4("true")) { pl.done = 1; pos += 4; }
-    else if (lit == w4("fals") && s.ld8(pos + 4) == 'e') { pl.done = 0; pos += 5; }
+    if (w2 == w4("true")) { pl.done = 1; pos += 4; }
+    else if (w2 == w4("fals") && s.ld8(pos + 4) == 'e') { pl.done = 0; pos += 5; }
     else return false;
     // ,"timestamp":   (13 bytes)
-    if (pos + 13 > end) return false;
-    if (ld32u(s, pos) != w4(",\"ti") || ld32u(s, pos + 4) != w4("mest") || ld32u(s, pos + 8) != w4("amp\"") || s.ld8(pos + 12) != ':') return false;
+    ld3u(s, pos, w0, w1, w2);
+    d = (w0 ^ w4(",\"ti")) | (w1 ^ w4("mest")) | (w2 ^ w4("amp\"")) | (s.ld8(pos + 12) ^ ':');
+    if (d || pos + 14 > end) return false;
     pos += 13;
-    if (pos >= end || !scan_canon_int(s, pos, end, pl.ts)) return false;
+    pl.ts = 0;
+    if (!scan_canon_int(s, pos, end, false, pl.ts)) return false;
     if (pos + 1 != end || s.ld8(pos) != '}') return false;
     pl.fast = 1;
     pl.cid_esc = cid_esc ? 1u : 0u;   // the bridge subject needs the DECODED id
@@ -716,7 +771,7 @@ SSE_HD uint32_t plan_record(const Src& s, uint32_t o, uint32_t L, uint32_t op, i
     Ptr32Dst nd{nullptr};
     Writer<Ptr32Dst, false> w(nd, 0);
     emit_record(s, o, L, pl, op, w, nullptr);
-    out_len = (uint32_t)w.pos;
+    out_len = (uint32_t)w.pos();
     return pl.done ? (ST_OK | ST_DONE) : ST_OK;
 }
 

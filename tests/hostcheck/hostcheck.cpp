@@ -35,7 +35,7 @@ extern "C" int hc_batch(const uint8_t* in, const uint32_t* in_off, uint32_t n, c
             Writer<PtrDst, true> wr(dst, w);
             if (fastp) emit_record_fast(src, o, L, pl, op, wr, subj_len ? &subj_len[i] : nullptr);
             else emit_record(src, o, L, pl, op, wr, subj_len ? &subj_len[i] : nullptr);
-            if (wr.pos != w + len) return -2;   // measured and emitted lengths must agree
+            if (wr.pos() != w + len) return -2;   // measured and emitted lengths must agree
             w += len;
         }
     }

@@ -1,0 +1,73 @@
+#!/usr/bin/env python3
+"""Per-source-line instruction and stall-sample totals for the frame kernel.
+
+usage: tools/ncu_lines.py <report.ncu-rep> [libssegpu.so] [--top N] [--func regex]
+Joins `ncu --page source --csv` (SASS rows, in order) with `nvdisasm -g` line info of the kernel cubin
+extracted from the library that was profiled (must be the same build)."""
+import csv
+import os
+import re
+import subprocess
+import sys
+import tempfile
+
+rep = sys.argv[1]
+lib = sys.argv[2] if len(sys.argv) > 2 and not sys.argv[2].startswith("--") else os.path.join(
+    os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "distributed-sse-for-llm-response_b200", "libssegpu.so")
+top = int(sys.argv[sys.argv.index("--top") + 1]) if "--top" in sys.argv else 45
+
+tmp = tempfile.mkdtemp()
+subprocess.check_call(["cuobjdump", "-xelf", "all", lib], cwd=tmp, stdout=subprocess.DEVNULL)
+cubin = [f for f in os.listdir(tmp) if f.startswith("sse_kernels.")][0]
+dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
+
+# instruction order -> (file:line, inlined-at chain)
+lines = []
+cur = None
+in_kernel = False
+for ln in dis.splitlines():
+    if ln.startswith(".text."):
+        in_kernel = "k_frame_tiles" in ln
+    m = re.search(r'//## File "([^"]+)", line (\d+)(.*)', ln)
+    if m:
+        cur = (os.path.basename(m.group(1)), int(m.group(2)))
+        continue
+    if in_kernel and re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+\S", ln):
+        lines.append((cur, ln.split("*/", 1)[1].strip()[:60]))
+
+rows = list(csv.reader(subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout.splitlines()))
+hi = [i for i, r in enumerate(rows) if "Instructions Executed" in r][0]
+hdr = rows[hi]
+ie, smp, srcc = hdr.index("Instructions Executed"), hdr.index("# Samples"), hdr.index("Source")
+body = [r for r in rows[hi + 1:] if len(r) > ie and r[ie].isdigit()]
+print("sass rows: ncu %d, nvdisasm %d" % (len(body), len(lines)))
+n = min(len(body), len(lines))
+agg = {}
+tot_i = tot_s = 0
+for k in range(n):
+    key = lines[k][0]
+    a = agg.setdefault(key, [0, 0])
+    a[0] += int(body[k][ie])
+    a[1] += int(body[k][smp])
+    tot_i += int(body[k][ie])
+    tot_s += int(body[k][smp])
+print("total warp-instructions %d, samples %d" % (tot_i, tot_s))
+src_cache = {}
+
+
+def src_line(key):
+    if key is None:
+        return ""
+    f, l = key
+    for d in ("distributed-sse-for-llm-response_b200/csrc",):
+        p = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), d, f)
+        if os.path.exists(p):
+            if p not in src_cache:
+                src_cache[p] = open(p).read().splitlines()
+            if l - 1 < len(src_cache[p]):
+                return src_cache[p][l - 1].strip()[:100]
+    return ""
+
+
+for key, (i, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+    print("%5.1f%% inst %5.1f%% smp  %-28s %s" % (100.0 * i / tot_i, 100.0 * s / max(tot_s, 1), "%s:%d" % key if key else "?", src_line(key)))
