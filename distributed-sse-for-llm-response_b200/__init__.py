@@ -7,7 +7,7 @@ There is no CPU fallback anywhere in this package: if libssegpu.so is missing, o
 sm_100 device is present, construction fails loudly.
 """
 from .binding import (  # noqa: F401
-    OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, ST_CODE_MASK, ST_DONE, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_OK,
+    OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_ORDERED, ST_CODE_MASK, ST_DONE, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_OK,
     Batch, SseGpu, SseGpuError, lib_path, load_library, shard, start_sequence,
 )
 from . import workload  # noqa: F401

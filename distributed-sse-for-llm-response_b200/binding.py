@@ -6,7 +6,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
-OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST = 0, 1, 2, 4
+OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_ORDERED = 0, 1, 2, 4, 8
 ST_OK, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_INSPECT_DROP = 0, 1, 2, 3, 4
 ST_CODE_MASK, ST_DONE, ST_REDACTED = 0xF, 0x100, 0x200
 E_OVERFLOW, E_AGAIN = -6, -4
@@ -68,7 +68,7 @@ def load_library():
     lib.ssegpu_batch_acquire.restype = C.c_int
     lib.ssegpu_batch_acquire.argtypes = [vp, C.POINTER(vp)]
     for name, rt in (("ssegpu_in_bytes", u8p), ("ssegpu_in_off", u32p), ("ssegpu_start_seq", i64p), ("ssegpu_conv_slot", u32p),
-                     ("ssegpu_out_bytes", u8p), ("ssegpu_out_off", u64p), ("ssegpu_status", u32p), ("ssegpu_subj_len", u32p)):
+                     ("ssegpu_out_bytes", u8p), ("ssegpu_out_off", u64p), ("ssegpu_out_len", u32p), ("ssegpu_status", u32p), ("ssegpu_subj_len", u32p)):
         f = getattr(lib, name)
         f.restype = rt
         f.argtypes = [vp]
@@ -81,7 +81,7 @@ def load_library():
     lib.ssegpu_counters_get.restype = C.c_int
     lib.ssegpu_counters_get.argtypes = [vp, C.POINTER(Counters)]
     lib.ssegpu_frame_launch.restype = C.c_int
-    lib.ssegpu_frame_launch.argtypes = [vp, vp, vp, vp, C.c_uint32, C.c_uint32, vp, C.c_uint64, vp, vp, vp, vp]
+    lib.ssegpu_frame_launch.argtypes = [vp, vp, vp, vp, C.c_uint32, C.c_uint32, vp, C.c_uint64, vp, vp, vp, vp, vp]
     lib.ssegpu_frame_launch_result.restype = C.c_int
     lib.ssegpu_frame_launch_result.argtypes = [vp, C.POINTER(Counters)]
     lib.ssegpu_launch_count.restype = C.c_uint64
@@ -130,6 +130,7 @@ class Batch:
         self.owner._check(self.owner.lib.ssegpu_batch_wait(self.owner.ctx, self.h, timeout_us))
         lib, n = self.owner.lib, self.n
         self.out_off = np.ctypeslib.as_array(lib.ssegpu_out_off(self.h), shape=(n + 1,))
+        self.out_len = np.ctypeslib.as_array(lib.ssegpu_out_len(self.h), shape=(max(n, 1),))[:n]
         self.status = np.ctypeslib.as_array(lib.ssegpu_status(self.h), shape=(max(n, 1),))[:n]
         self.subj_len = np.ctypeslib.as_array(lib.ssegpu_subj_len(self.h), shape=(max(n, 1),))[:n]
         total = int(self.out_off[n])
@@ -177,10 +178,11 @@ class SseGpu:
         self._check(self.lib.ssegpu_counters_get(self.ctx, C.byref(c)))
         return c.as_dict()
 
-    def frame_launch(self, d_in, d_in_off, d_start_seq, n, op, d_out, out_cap, d_out_off, d_subj_len, d_status, stream=0):
+    def frame_launch(self, d_in, d_in_off, d_start_seq, n, op, d_out, out_cap, d_out_off, d_out_len, d_subj_len, d_status,
+                     stream=0):
         """All pointer arguments are raw device addresses (ints); asynchronous on `stream`."""
         self._check(self.lib.ssegpu_frame_launch(self.ctx, d_in, d_in_off, d_start_seq or None, n, op, d_out, out_cap, d_out_off,
-                                                 d_subj_len or None, d_status, stream or None))
+                                                 d_out_len, d_subj_len or None, d_status, stream or None))
 
     def launch_result(self):
         c = Counters()

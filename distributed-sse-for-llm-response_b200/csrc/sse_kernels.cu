@@ -14,10 +14,12 @@
 //     (cp.async.bulk ... mbarrier::complete_tx), 16-byte aligned, no register staging;
 //   * one thread per record runs sse_record.cuh (SWAR canonical check / general decoder);
 //   * frame lengths: warp-shuffle scan -> CTA scan -> single-pass decoupled look-back
-//     (64-bit {flag,prefix} words) for the tile's global byte offset;
-//   * frames are assembled in a shared-memory staging tile laid out congruent (mod 16) to the
-//     output arena, then leave as ONE TMA bulk store (cp.async.bulk.global.shared::cta) plus
-//     at most 15 head and 15 tail bytes, so HBM sees only full-line traffic.
+//     (64-bit {flag,prefix} words, 256 predecessors inspected per L2 round trip) for the
+//     tile's global byte offset;
+//   * frames are assembled in a shared-memory staging tile BEFORE the tile's global offset is
+//     known (so the look-back latency hides behind the emission and the next tile's TMA load),
+//     then leave as coalesced 16-byte vector stores, byte-shifted on the fly to the arena's
+//     alignment, plus at most 15 head and 15 tail bytes: HBM sees only full-line traffic.
 //   No tensor cores: nothing here is a contraction.
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -51,15 +53,6 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gsrc, ui
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
-// shared -> global bulk copy (TMA, 1-D)
-__device__ __forceinline__ void tma_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
 __device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t* p) {
     uint64_t v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -74,29 +67,46 @@ constexpr uint64_t FLAG_AGG = 1ull << 62;      // value = this tile's own byte c
 constexpr uint64_t FLAG_PFX = 2ull << 62;      // value = inclusive prefix up to and including this tile
 constexpr uint64_t VAL_MASK = (1ull << 62) - 1;
 
-// Single-pass decoupled look-back, run by warp 0.  Returns the exclusive prefix of `tile`.
+// Single-pass decoupled look-back, run by warp 0 AFTER the tile's aggregate was published.
+// With hundreds of phase-locked persistent CTAs the nearest tile that already owns a prefix
+// is typically hundreds of tiles back, so every L2 round trip inspects LB_WIN*32 predecessors
+// (all loads in flight together) instead of 32.  Returns the exclusive prefix of `tile`.
+constexpr int LB_WIN = 8;
+__device__ __forceinline__ void publish_aggregate(uint64_t* tile_state, uint32_t tile, uint64_t total) {
+    st_relaxed_u64(&tile_state[tile], (tile == 0 ? FLAG_PFX : FLAG_AGG) | total);
+}
 __device__ __forceinline__ uint64_t lookback(uint64_t* tile_state, uint32_t tile, uint64_t total, uint32_t lane) {
-    if (tile == 0) {
-        if (lane == 0) st_relaxed_u64(&tile_state[0], FLAG_PFX | total);
-        return 0;
-    }
-    if (lane == 0) st_relaxed_u64(&tile_state[tile], FLAG_AGG | total);
+    if (tile == 0) return 0;
     uint64_t excl = 0;
-    int64_t j = (int64_t)tile - 1;             // window covers tiles j, j-1, ..., j-31
+    int64_t j = (int64_t)tile - 1;             // nearest predecessor not yet accounted for
     for (;;) {
-        int64_t idx = j - (int64_t)lane;
-        uint64_t v;
+        uint64_t v[LB_WIN];
+        bool pending;
         do {
-            v = idx >= 0 ? ld_relaxed_u64(&tile_state[idx]) : FLAG_PFX;   // before tile 0: prefix 0
-        } while (__any_sync(0xFFFFFFFFu, (v >> 62) == 0));
-        uint32_t pfx_mask = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 2);
-        uint32_t first_pfx = pfx_mask ? (uint32_t)(__ffs((int)pfx_mask) - 1) : 32u;   // nearest tile holding a prefix
-        uint64_t contrib = lane <= first_pfx ? (v & VAL_MASK) : 0;
+            pending = false;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xFFFFFFFFu, contrib, o);
-        excl += contrib;
-        if (pfx_mask) break;
-        j -= 32;
+            for (int k = 0; k < LB_WIN; k++) {
+                int64_t idx = j - (int64_t)(k * 32 + lane);
+                v[k] = idx >= 0 ? ld_relaxed_u64(&tile_state[idx]) : FLAG_PFX;   // before tile 0: prefix 0
+                pending |= (v[k] >> 62) == 0;
+            }
+        } while (__any_sync(0xFFFFFFFFu, pending));
+        uint64_t part = 0;
+        bool found = false;
+#pragma unroll
+        for (int k = 0; k < LB_WIN; k++) {
+            if (!found) {
+                uint32_t pfx_mask = __ballot_sync(0xFFFFFFFFu, (v[k] >> 62) == 2);
+                uint32_t first_pfx = pfx_mask ? (uint32_t)(__ffs((int)pfx_mask) - 1) : 32u;   // nearest tile holding a prefix
+                if (lane <= first_pfx) part += v[k] & VAL_MASK;
+                found = pfx_mask != 0;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
+        excl += part;
+        if (found) break;
+        j -= 32 * LB_WIN;
     }
     if (lane == 0) st_relaxed_u64(&tile_state[tile], FLAG_PFX | (excl + total));
     return excl;
@@ -132,42 +142,84 @@ __device__ __noinline__ uint32_t emit_slow(const uint8_t* src_base, uint32_t o, 
     return subj;
 }
 
-__global__ void __launch_bounds__(TILE) k_frame_tiles(const FrameArgs a) {
+// tid 0: claim bookkeeping for tile t -- tile byte range + TMA load into s_in
+__device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t t, uint64_t& c_in) {
+    ts->tile = t;
+    if (t < a.num_tiles) {
+        const uint32_t r0 = t * TILE;
+        const uint32_t nrec = min((uint32_t)TILE, a.n - r0);
+        const uint32_t tb = a.in_off[r0], te = a.in_off[r0 + nrec];
+        ts->tb = tb; ts->te = te;
+        const uint32_t abase = tb & ~15u;
+        const uint32_t bytes = (te - abase + 15u) & ~15u;
+        if (bytes != 0 && bytes <= a.in_cap) {
+            mbar_expect_tx(&ts->mbar, bytes);
+            tma_load_1d(s_in, a.in + abase, bytes, &ts->mbar);
+        }
+        c_in += te - tb;
+    }
+}
+
+__device__ __forceinline__ uint4 lds128(const uint8_t* p) { return *reinterpret_cast<const uint4*>(p); }
+
+// Staging tile (bytes [0,total) of s_out) -> out[g0, g0+total): coalesced 16-byte stores for the
+// 16-byte aligned interior, byte-shifted by r = (-g0) mod 16 on the fly (r is tile-uniform, so
+// the word part of the shift is a template parameter chosen once per tile).
+template <int Q>
+__device__ __forceinline__ void copy_chunks(uint4* __restrict__ dst, const uint8_t* s_out, uint32_t nchunk, uint32_t b, uint32_t tid) {
+    for (uint32_t i = tid; i < nchunk; i += TILE) {
+        const uint4 A = lds128(s_out + 16 * i), B = lds128(s_out + 16 * i + 16);
+        uint4 y;
+        if (Q == 0) { y.x = __funnelshift_r(A.x, A.y, b); y.y = __funnelshift_r(A.y, A.z, b); y.z = __funnelshift_r(A.z, A.w, b); y.w = __funnelshift_r(A.w, B.x, b); }
+        if (Q == 1) { y.x = __funnelshift_r(A.y, A.z, b); y.y = __funnelshift_r(A.z, A.w, b); y.z = __funnelshift_r(A.w, B.x, b); y.w = __funnelshift_r(B.x, B.y, b); }
+        if (Q == 2) { y.x = __funnelshift_r(A.z, A.w, b); y.y = __funnelshift_r(A.w, B.x, b); y.z = __funnelshift_r(B.x, B.y, b); y.w = __funnelshift_r(B.y, B.z, b); }
+        if (Q == 3) { y.x = __funnelshift_r(A.w, B.x, b); y.y = __funnelshift_r(B.x, B.y, b); y.z = __funnelshift_r(B.y, B.z, b); y.w = __funnelshift_r(B.z, B.w, b); }
+        dst[i] = y;
+    }
+}
+__device__ __forceinline__ void copy_out(uint8_t* __restrict__ out, const uint8_t* s_out, uint64_t g0, uint32_t total, uint32_t tid) {
+    const uint64_t g1 = g0 + total;
+    const uint64_t ga = (g0 + 15) & ~15ull, gb = g1 & ~15ull;
+    if (ga >= gb) {
+        for (uint32_t i = tid; i < total; i += TILE) out[g0 + i] = s_out[i];
+        return;
+    }
+    const uint32_t r = (uint32_t)(ga - g0), b = (r & 3u) * 8;
+    const uint32_t nchunk = (uint32_t)((gb - ga) >> 4);
+    uint4* dst = reinterpret_cast<uint4*>(out + ga);
+    switch (r >> 2) {                          // tile-uniform: no divergence
+    case 0:  copy_chunks<0>(dst, s_out, nchunk, b, tid); break;
+    case 1:  copy_chunks<1>(dst, s_out, nchunk, b, tid); break;
+    case 2:  copy_chunks<2>(dst, s_out, nchunk, b, tid); break;
+    default: copy_chunks<3>(dst, s_out, nchunk, b, tid); break;
+    }
+    const uint32_t tail = (uint32_t)(g1 - gb);
+    if (tid < r) out[g0 + tid] = s_out[tid];
+    if (tid >= 32 && tid - 32 < tail) out[gb + (tid - 32)] = s_out[total - tail + (tid - 32)];
+}
+
+__global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* s_in = smem;                                   // in_cap + 16
-    uint8_t* s_out = smem + a.in_cap + 16;                  // out_cap_s + 16
-    TileSmem* ts = reinterpret_cast<TileSmem*>(s_out + a.out_cap_s + 16);
+    uint8_t* s_out = smem + a.in_cap + 16;                  // out_cap_s + 48
+    TileSmem* ts = reinterpret_cast<TileSmem*>(s_out + a.out_cap_s + 48);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint32_t c_ok = 0, c_syn = 0, c_typ = 0, c_fil = 0, c_done = 0, c_fast = 0;
     uint64_t c_in = 0, c_out = 0;
     uint32_t parity = 0;
 
-    if (tid == 0) mbar_init(&ts->mbar, 1);
-    __syncthreads();
+    if (tid == 0) {
+        mbar_init(&ts->mbar, 1);
+        setup_tile(a, ts, s_in, atomicAdd(a.ticket, 1u), c_in);
+    }
 
     for (;;) {
-        // ---- S0: claim a tile, start its TMA load --------------------------------
-        if (tid == 0) {
-            uint32_t t = atomicAdd(a.ticket, 1u);
-            ts->tile = t;
-            if (t < a.num_tiles) {
-                uint32_t r0 = t * TILE;
-                uint32_t nrec = min((uint32_t)TILE, a.n - r0);
-                uint32_t tb = a.in_off[r0], te = a.in_off[r0 + nrec];
-                ts->tb = tb; ts->te = te;
-                uint32_t abase = tb & ~15u;
-                uint32_t bytes = (te - abase + 15u) & ~15u;
-                if (bytes != 0 && bytes <= a.in_cap) {
-                    mbar_expect_tx(&ts->mbar, bytes);
-                    tma_load_1d(s_in, a.in + abase, bytes, &ts->mbar);
-                }
-                c_in += te - tb;
-            }
-        }
-        __syncthreads();                                                      // (A)
+        __syncthreads();                                                      // (A) tile info visible; s_out free
         const uint32_t tile = ts->tile;
         if (tile >= a.num_tiles) break;
+        uint32_t next_t = 0;
+        if (tid == 0) next_t = atomicAdd(a.ticket, 1u);                       // claimed early, used after (D)
         const uint32_t r0 = tile * TILE;
         const uint32_t nrec = min((uint32_t)TILE, a.n - r0);
         const uint32_t tb = ts->tb, te = ts->te;
@@ -192,7 +244,11 @@ __global__ void __launch_bounds__(TILE) k_frame_tiles(const FrameArgs a) {
         bool fastp = false;
         if (active) {
             if (smem_in) { PtrSrc src{s_in}; fastp = plan_record_fast(src, o, L, a.op, my_start, pl, st, len); }
-            if (!fastp) st = plan_slow(smem_in ? s_in : a.in + abase, o, L, a.op, my_start, &pl, &len);
+            if (!fastp) {            // separate Plan object: taking pl's address would push the hot path's plan into local memory
+                Plan sp;
+                st = plan_slow(smem_in ? s_in : a.in + abase, o, L, a.op, my_start, &sp, &len);
+                pl = sp;
+            }
         }
 
         // ---- CTA exclusive scan of lengths --------------------------------------------
@@ -207,70 +263,70 @@ __global__ void __launch_bounds__(TILE) k_frame_tiles(const FrameArgs a) {
         uint32_t wpre = 0, total = 0;
 #pragma unroll
         for (int w = 0; w < TILE / 32; w++) { uint32_t v = ts->wsum[w]; if (w < (int)warp) wpre += v; total += v; }
-        if (warp == 0) {
-            uint64_t excl = lookback(a.tile_state, tile, total, lane);
-            if (lane == 0) {
-                ts->base = excl;
-                c_out += total;
-                if (tile == a.num_tiles - 1) a.out_off[a.n] = excl + total;
-                bulk_wait_read0();            // previous tile's TMA store has finished reading s_out
-            }
+        const bool ordered = (a.op & OP_ORDERED) != 0;                        // launch-uniform
+        const bool smem_out = total <= a.out_cap_smem();                      // tile-uniform
+        if (tid == 0) {
+            c_out += total;
+            if (ordered) publish_aggregate(a.tile_state, tile, total);
+            else ts->base = atomicAdd(a.cursor, (unsigned long long)total);   // arrival-order placement: nothing to wait for
         }
-        __syncthreads();                                                      // (C)
-        const uint64_t base = ts->base;
         const uint32_t local = wpre + incl - len;
-        const uint32_t shift = (uint32_t)base & 15u;
-        const bool fits = base + total <= a.out_cap;
-        const bool smem_out = shift + total <= a.out_cap_smem();
-
+        const uint32_t code = st & ST_CODE_MASK;
         uint32_t subj = 0;
-        if (active) {
-            const uint32_t code = st & ST_CODE_MASK;
-            if (code == ST_OK) {
-                c_ok++; c_fast += fastp ? 1u : 0u; if (st & ST_DONE) c_done++;
-                if (fits) {
-                    if (fastp && smem_out) {
-                        PtrSrc src{s_in};
-                        Ptr32Dst d{s_out};
-                        Writer<Ptr32Dst, true> w(d, shift + local);
-                        emit_record_fast(src, o, L, pl, a.op, w, &subj);
-                    } else {
-                        subj = emit_slow(smem_in ? s_in : a.in + abase, o, L, &pl, a.op, smem_out ? s_out : a.out,
-                                         smem_out ? (uint64_t)(shift + local) : base + local);
-                    }
+
+        if (smem_out) {
+            // ---- pass 2 into the staging tile; the global offset is not needed yet ------
+            if (active && code == ST_OK) {
+                if (fastp) {
+                    PtrSrc src{s_in};
+                    Ptr32Dst d{s_out};
+                    Writer<Ptr32Dst, true> w(d, local);
+                    emit_record_fast(src, o, L, pl, a.op, w, &subj);
+                } else {
+                    Plan sp = pl;
+                    subj = emit_slow(smem_in ? s_in : a.in + abase, o, L, &sp, a.op, s_out, (uint64_t)local);
                 }
-            } else if (code == ST_ERR_SYNTAX) c_syn++;
+            }
+            __syncthreads();                                                  // (D) s_in free, staging tile complete, base visible
+            if (warp == 0) {
+                if (lane == 0) setup_tile(a, ts, s_in, next_t, c_in);         // next tile's TMA load flies during the copy-out
+                if (ordered) {
+                    uint64_t excl = lookback(a.tile_state, tile, total, lane);
+                    if (lane == 0) ts->base = excl;
+                }
+            }
+            if (ordered) __syncthreads();                                     // (E)
+        } else {
+            // ---- oversize tile: emit straight into the arena ---------------------------
+            if (ordered && warp == 0) {
+                uint64_t excl = lookback(a.tile_state, tile, total, lane);
+                if (lane == 0) ts->base = excl;
+            }
+            __syncthreads();                                                  // (D')
+        }
+        const uint64_t base = ts->base;
+        const bool fits = base + total <= a.out_cap;
+        if (!smem_out) {
+            if (active && code == ST_OK && fits) {
+                Plan sp = pl;
+                subj = emit_slow(smem_in ? s_in : a.in + abase, o, L, &sp, a.op, a.out, base + local);
+            }
+            __syncthreads();                                                  // (E') s_in free
+            if (tid == 0) setup_tile(a, ts, s_in, next_t, c_in);
+        }
+        if (active) {
+            if (code == ST_OK) { c_ok++; c_fast += fastp ? 1u : 0u; if (st & ST_DONE) c_done++; }
+            else if (code == ST_ERR_SYNTAX) c_syn++;
             else if (code == ST_ERR_TYPE) c_typ++;
             else if (code == ST_FILTERED) c_fil++;
             a.out_off[r0 + tid] = base + local;
+            a.out_len[r0 + tid] = len;
             a.status[r0 + tid] = st;
             if (a.subj_len) a.subj_len[r0 + tid] = subj;
         }
-        if (!fits && tid == 0) atomicExch(a.overflow, 1u);
-
-        // ---- staging tile -> output arena ----------------------------------------------
-        if (smem_out && fits && total != 0) {
-            fence_proxy_async_smem();
-            __syncthreads();                                                  // (D)
-            const uint64_t g0 = base, g1 = base + total;
-            const uint64_t ga = (g0 + 15) & ~15ull, gb = g1 & ~15ull;         // 16-byte aligned interior
-            if (ga < gb) {
-                if (tid == 0) {
-                    tma_store_1d(a.out + ga, s_out + (uint32_t)(ga - (g0 - shift)), (uint32_t)(gb - ga));
-                    bulk_commit();
-                }
-                const uint32_t head = (uint32_t)(ga - g0), tail = (uint32_t)(g1 - gb);
-                if (tid < head) a.out[g0 + tid] = s_out[shift + tid];
-                if (tid >= 32 && tid - 32 < tail) a.out[gb + (tid - 32)] = s_out[(uint32_t)(gb - (g0 - shift)) + (tid - 32)];
-            } else {
-                for (uint32_t i = tid; i < total; i += TILE) a.out[g0 + i] = s_out[shift + i];
-            }
-        } else {
-            __syncthreads();                                                  // (D')
-        }
+        if (tid == 0 && !fits) atomicExch(a.overflow, 1u);
+        if (smem_out && fits && total != 0) copy_out(a.out, s_out, base, total, tid);
     }
-
-    if (tid == 0) bulk_wait0();
 
     // ---- counters: one row per CTA slot, summed by the host --------------------------
     unsigned long long* row = a.counters + (size_t)(blockIdx.x % CTR_ROWS) * CTR_COLS;
@@ -285,6 +341,13 @@ __global__ void __launch_bounds__(TILE) k_frame_tiles(const FrameArgs a) {
     if (tid == 0) {
         if (c_in) atomicAdd(&row[6], (unsigned long long)c_in);
         if (c_out) atomicAdd(&row[7], (unsigned long long)c_out);
+        // the CTA that finishes last publishes the arena's total size as out_off[n]
+        __threadfence();
+        if (atomicAdd(a.done_ctas, 1u) == gridDim.x - 1) {
+            __threadfence();
+            a.out_off[a.n] = (a.op & OP_ORDERED) ? (ld_relaxed_u64(&a.tile_state[a.num_tiles - 1]) & VAL_MASK)
+                                                 : (uint64_t)atomicAdd(a.cursor, 0ull);
+        }
     }
 }
 
@@ -297,7 +360,7 @@ cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uin
     // BASELINE workload; caps leave ~15% slack.  Tiles that exceed them take the direct
     // global-memory path inside the same kernel.
     const uint32_t ic = 20 * 1024, oc = 24 * 1024;
-    const uint32_t sm = ic + 16 + oc + 16 + (uint32_t)sizeof(TileSmem);
+    const uint32_t sm = ic + 16 + oc + 48 + (uint32_t)sizeof(TileSmem);
     cudaError_t e = cudaFuncSetAttribute(k_frame_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     if (e != cudaSuccess) return e;
     if (g_num_sms[device] == 0) {

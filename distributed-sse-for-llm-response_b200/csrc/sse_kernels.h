@@ -9,7 +9,7 @@ namespace sse {
 constexpr int TILE = 128;        // records per tile == threads per CTA
 constexpr int CTR_ROWS = 64;     // counter rows (CTA i adds into row i % CTR_ROWS; the host sums rows)
 constexpr int CTR_COLS = 8;      // ok, syntax, type, filtered, done, fast, bytes_in, bytes_out
-constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32
+constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32
 
 struct FrameArgs {
     const uint8_t* in;           // packed payload arena, 16-byte aligned, 16 bytes of padding after the last record
@@ -18,13 +18,16 @@ struct FrameArgs {
     uint32_t n, op;
     uint8_t* out;                // packed output arena
     uint64_t out_cap;
-    uint64_t* out_off;           // n+1
+    uint64_t* out_off;           // n+1 (entry n = total output bytes)
+    uint32_t* out_len;           // n
     uint32_t* subj_len;          // n or nullptr
     uint32_t* status;            // n
     // scratch: one device allocation of scratch_bytes(n), zeroed by frame_launch
     void* scratch_base;
     uint32_t* ticket;
     uint32_t* overflow;
+    unsigned long long* cursor;  // arrival-order placement: next free output byte
+    uint32_t* done_ctas;
     unsigned long long* counters;
     uint64_t* tile_state;
     // filled by frame_launch
@@ -42,6 +45,8 @@ inline void scratch_carve(void* base, FrameArgs& a) {
     a.scratch_base = base;
     a.ticket = reinterpret_cast<uint32_t*>(p);
     a.overflow = reinterpret_cast<uint32_t*>(p + 4);
+    a.cursor = reinterpret_cast<unsigned long long*>(p + 8);
+    a.done_ctas = reinterpret_cast<uint32_t*>(p + 16);
     a.counters = reinterpret_cast<unsigned long long*>(p + SCRATCH_HDR);
     a.tile_state = reinterpret_cast<uint64_t*>(p + SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8);
 }

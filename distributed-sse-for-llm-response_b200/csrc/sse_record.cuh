@@ -41,7 +41,7 @@ enum : uint32_t {
     ST_CODE_MASK = 0xF, ST_DONE = 0x100, ST_REDACTED = 0x200,
 };
 // op flags (mirrors include/ssegpu.h)
-enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u };
+enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u, OP_ORDERED = 8u };
 
 constexpr uint32_t MAX_NESTING = 10000;            // encoding/json scanner.go maxNestingDepth
 constexpr uint32_t NEST_WORDS = MAX_NESTING / 32 + 1;
@@ -89,11 +89,8 @@ SSE_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {   // sh in {0,
 // little-endian 4 bytes at an arbitrary byte position (may read up to 3 bytes past pos+3's
 // word: tile buffers are padded)
 template <class Src> SSE_HD uint32_t ld32u(const Src& s, uint32_t pos) {
-    uint32_t a = pos & ~3u;
-    uint32_t sh = (pos & 3u) * 8;
-    uint32_t lo = s.ld32a(a);
-    if (sh == 0) return lo;
-    return funnel_r(lo, s.ld32a(a + 4), sh);
+    const uint32_t a = pos & ~3u;
+    return funnel_r(s.ld32a(a), s.ld32a(a + 4), (pos & 3u) * 8);   // branch-free: lanes differ in alignment
 }
 
 SSE_CX uint32_t w4(const char* s) {
@@ -203,6 +200,16 @@ template <class Dst, bool EMIT> struct Writer {
         sh += 32;
         flush_word();
     }
+    // put32 for streams whose first partial word is already out (first == 0): no first-word test
+    SSE_HD void put32_nf(uint32_t w) {
+        if (EMIT) { acc |= (uint64_t)w << sh; d.st32a(wpos, (uint32_t)acc); }
+        acc >>= 32; wpos += 4;
+    }
+    SSE_HD void put_n_nf(uint32_t w, uint32_t n) {
+        if (EMIT) acc |= (uint64_t)(w & (0xFFFFFFFFu >> (32 - 8 * n))) << sh;
+        sh += 8 * n;
+        if (sh >= 32) { if (EMIT) d.st32a(wpos, (uint32_t)acc); acc >>= 32; sh -= 32; wpos += 4; }
+    }
     SSE_HD void store_word(uint32_t v) {                // only when sh == 0 and first == 0
         if (EMIT) d.st32a(wpos, v);
         wpos += 4;
@@ -220,6 +227,15 @@ template <class Dst, bool EMIT> struct Writer {
     }
 };
 
+template <class W> SSE_HD void put_lit_nf(W& w, const char* s, uint32_t n) {     // after the first flush
+    uint32_t i = 0;
+    for (; i + 4 <= n; i += 4) w.put32_nf(w4(s + i));
+    if (i < n) {
+        uint32_t v = 0;
+        for (uint32_t k = 0; i + k < n; k++) v |= (uint32_t)(uint8_t)s[i + k] << (8 * k);
+        w.put_n_nf(v, n - i);
+    }
+}
 template <class W> SSE_HD void put_lit(W& w, const char* s, uint32_t n) {
     uint32_t i = 0;
     for (; i + 4 <= n; i += 4) w.put32(w4(s + i));
@@ -230,6 +246,7 @@ template <class W> SSE_HD void put_lit(W& w, const char* s, uint32_t n) {
     }
 }
 #define SSE_PUT_LIT(w, lit) put_lit(w, lit, (uint32_t)(sizeof(lit) - 1))
+#define SSE_PUT_LIT_NF(w, lit) put_lit_nf(w, lit, (uint32_t)(sizeof(lit) - 1))
 
 SSE_HD uint32_t dec_digits(uint64_t u) {
     uint32_t n = 1;
@@ -288,17 +305,25 @@ template <class Src, class W> SSE_HD void put_json_string(const Src& s, uint32_t
 
 // verbatim copy of n source bytes starting at byte position sp: bytes until the destination is
 // word aligned, then one aligned load + funnel shift + aligned store per word (the relative
-// alignment of source and destination is constant), then the tail bytes.
-template <class Src, class W> SSE_HD void put_copy(const Src& s, uint32_t sp, uint32_t n, W& w) {
+// alignment of source and destination is constant), then the tail bytes.  NF: the writer's
+// first partial word has already been flushed (true whenever a header went out before).
+template <bool NF, class Src, class W> SSE_HD void put_copy_t(const Src& s, uint32_t sp, uint32_t n, W& w) {
     uint32_t k = (4u - (w.sh >> 3)) & 3u;
     if (k > n) k = n;
-    if (k) { w.put_n(ld32u(s, sp), k); sp += k; n -= k; }
+    if (k) { if (NF) w.put_n_nf(ld32u(s, sp), k); else w.put_n(ld32u(s, sp), k); sp += k; n -= k; }
     uint32_t nw = n >> 2;
     if (nw) {
         uint32_t a = sp & ~3u;
         const uint32_t shb = (sp & 3u) * 8;
         uint32_t lo = s.ld32a(a);
-        for (uint32_t i = 0; i < nw; i++) {
+        uint32_t i = 0;
+        for (; i + 4 <= nw; i += 4) {
+            uint32_t h0 = s.ld32a(a + 4), h1 = s.ld32a(a + 8), h2 = s.ld32a(a + 12), h3 = s.ld32a(a + 16);
+            w.store_word(funnel_r(lo, h0, shb)); w.store_word(funnel_r(h0, h1, shb));
+            w.store_word(funnel_r(h1, h2, shb)); w.store_word(funnel_r(h2, h3, shb));
+            lo = h3; a += 16;
+        }
+        for (; i < nw; i++) {
             a += 4;
             uint32_t hi = s.ld32a(a);
             w.store_word(funnel_r(lo, hi, shb));
@@ -306,8 +331,9 @@ template <class Src, class W> SSE_HD void put_copy(const Src& s, uint32_t sp, ui
         }
         sp += nw * 4; n -= nw * 4;
     }
-    if (n) w.put_n(ld32u(s, sp), n);
+    if (n) { if (NF) w.put_n_nf(ld32u(s, sp), n); else w.put_n(ld32u(s, sp), n); }
 }
+template <class Src, class W> SSE_HD void put_copy(const Src& s, uint32_t sp, uint32_t n, W& w) { put_copy_t<false>(s, sp, n, w); }
 
 // ------------------------------------------------------------------ emission ----
 // Writes the record's output (SSE frame, or bridge subject+JSON) at w.pos.  With a counting
@@ -397,15 +423,14 @@ template <class Src> SSE_HD bool scan_canon_string(const Src& s, uint32_t& pos, 
         uint32_t a = pos & ~3u;
         const uint32_t shb = (pos & 3u) * 8;
         uint32_t lo = s.ld32a(a), w, m;
-        for (;;) {
+        for (;;) {                                              // 8 bytes per trip
             if (pos >= end) return false;
-            a += 4;
-            uint32_t hi = s.ld32a(a);
-            w = funnel_r(lo, hi, shb);
-            m = special_mask(w);
-            if (m) break;
-            lo = hi;
-            pos += 4;
+            const uint32_t h1 = s.ld32a(a + 4), h2 = s.ld32a(a + 8);
+            const uint32_t wa = funnel_r(lo, h1, shb), wb = funnel_r(h1, h2, shb);
+            const uint32_t ma = special_mask(wa), mb = special_mask(wb);
+            if ((ma | mb) == 0) { lo = h2; a += 8; pos += 8; continue; }
+            if (ma) { w = wa; m = ma; } else { w = wb; m = mb; pos += 4; }
+            break;
         }
         const uint32_t k = first_byte_idx(m);
         pos += k;
@@ -430,33 +455,64 @@ template <class Src> SSE_HD bool scan_canon_string(const Src& s, uint32_t& pos, 
     }
 }
 
+// four ASCII digits (first digit in the low byte) -> value
+SSE_HD uint32_t digits4(uint32_t w) {
+    uint32_t t = w & 0x0F0F0F0Fu;
+    t = t * 10 + (t >> 8);                                      // byte0 = d0*10+d1, byte2 = d2*10+d3
+    return (t & 0xFF) * 100 + ((t >> 16) & 0xFF);
+}
+
 // canonical integer literal: -?(0|[1-9][0-9]*), at most 19 digits and certainly inside int64
 // (a 19-digit literal starting with '9' is left to the general path, which does the exact
 // range check).  Leaves pos just past the literal.  The VALUE is produced only when
-// want_value (sequence: needed by the filter and the slow emitter) and then only for <= 9
-// digits; longer sequences also go to the general path.  Word-at-a-time digit test.
+// want_value (sequence: needed by the filter and the slow emitter) and then only for <= 8
+// digits; longer sequences also go to the general path.  Word-at-a-time digit test on
+// aligned loads.
 template <class Src> SSE_HD bool scan_canon_int(const Src& s, uint32_t& pos, uint32_t end, bool want_value, int64_t& out) {
-    const uint32_t c0 = s.ld8(pos);
-    const uint32_t neg = (c0 == '-') ? 1u : 0u;
+    const uint32_t a = pos & ~3u, shb = (pos & 3u) * 8;
+    uint32_t x0 = s.ld32a(a), x1 = s.ld32a(a + 4), x2 = s.ld32a(a + 8);
+    uint32_t w0 = funnel_r(x0, x1, shb), w1 = funnel_r(x1, x2, shb);
+    const uint32_t neg = ((w0 & 0xFF) == '-') ? 1u : 0u;
+    if (neg) {                                                  // drop the sign byte (rare)
+        uint32_t x3 = s.ld32a(a + 12);
+        w0 = funnel_r(w0, w1, 8); w1 = funnel_r(w1, funnel_r(x2, x3, shb), 8);
+    }
     const uint32_t start = pos + neg;
-    uint32_t nd = 0;
+    uint32_t nd;
+    uint32_t m = nondigit_mask(w0);
+    if (m) nd = first_byte_idx(m);
+    else {
+        m = nondigit_mask(w1);
+        if (m) nd = 4 + first_byte_idx(m);
+        else {                                                  // 8+ digits: timestamps
+            nd = 8;
+            uint32_t p = start + 8;
 #if defined(__CUDACC__)
 #pragma unroll 1
 #endif
-    for (uint32_t i = 0; i < 5; i++) {
-        uint32_t m = nondigit_mask(ld32u(s, start + 4 * i));
-        if (m) { nd += first_byte_idx(m); break; }
-        nd += 4;
+            for (uint32_t i = 0; i < 3; i++, p += 4) {
+                m = nondigit_mask(ld32u(s, p));
+                if (m) { nd += first_byte_idx(m); break; }
+                nd += 4;
+            }
+        }
     }
     if (nd == 0 || nd > 19 || start + nd > end) return false;
-    const uint32_t d0 = s.ld8(start);
+    const uint32_t d0 = w0 & 0xFF;
     if (d0 == '0' && (nd != 1 || neg)) return false;            // leading zero, "-0"
     if (nd == 19 && d0 == '9') return false;                    // might overflow: exact check in the general path
     pos = start + nd;
     if (want_value) {
-        if (nd > 9) return false;
-        uint32_t v = 0;
-        for (uint32_t i = 0; i < nd; i++) v = v * 10 + (s.ld8(start + i) - '0');
+        if (nd > 8) return false;
+        uint32_t v;
+        // right-align the digits inside 4-digit groups: missing leading digits become zeros
+        if (nd <= 4) v = digits4(w0 << (8 * (4 - nd)));
+        else {
+            const uint32_t k = nd - 4;                          // 1..4 digits in the leading group
+            const uint32_t hi = digits4(w0 << (8 * (4 - k)));   // first k digits
+            const uint32_t lo4 = funnel_r(w0, w1, 8 * k);       // next four digits (k = 4: shift 32 == w1)
+            v = hi * 10000 + digits4(k == 4 ? w1 : lo4);
+        }
         out = neg ? -(int64_t)v : (int64_t)v;
     }
     return true;
@@ -743,17 +799,19 @@ SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, 
 template <class Src, class W>
 SSE_HD void emit_record_fast(const Src& s, uint32_t o, uint32_t L, const Plan& pl, uint32_t op, W& w, uint32_t* subj_len) {
     if (op & OP_BRIDGE) {
-        SSE_PUT_LIT(w, "chat.");                          // redis-nats-bridge/main.go:160
-        put_copy(s, o + pl.cid_b, pl.cid_e - pl.cid_b, w);
-        SSE_PUT_LIT(w, ".tokens");
+        w.put32(w4("chat"));                              // redis-nats-bridge/main.go:160 (first word: bytewise if shared)
+        w.put_n_nf('.', 1);
+        put_copy_t<true>(s, o + pl.cid_b, pl.cid_e - pl.cid_b, w);
+        SSE_PUT_LIT_NF(w, ".tokens");
         if (subj_len) *subj_len = 12 + (pl.cid_e - pl.cid_b);
-        put_copy(s, o, L, w);                             // main.go:161
+        put_copy_t<true>(s, o, L, w);                     // main.go:161
     } else {
-        SSE_PUT_LIT(w, "event: token\nid: ");            // sse_handler.go:212-213
-        put_copy(s, o + pl.seq_b, pl.seq_n, w);           // canonical literal == fmt %d
-        SSE_PUT_LIT(w, "\ndata: ");                      // :214
-        put_copy(s, o, L, w);
-        w.put('\n'); w.put('\n');
+        w.put32(w4("even"));                              // sse_handler.go:212-213
+        SSE_PUT_LIT_NF(w, "t: token\nid: ");
+        put_copy_t<true>(s, o + pl.seq_b, pl.seq_n, w);   // canonical literal == fmt %d
+        SSE_PUT_LIT_NF(w, "\ndata: ");                    // :214
+        put_copy_t<true>(s, o, L, w);
+        w.put_n_nf(w4("\n\n\0\0"), 2);
     }
     w.finish();
 }

@@ -41,11 +41,11 @@ struct ssegpu_batch {
     uint64_t total_out = 0;
     // pinned host
     uint8_t* h_in = nullptr; uint32_t* h_in_off = nullptr; int64_t* h_start = nullptr; uint32_t* h_conv = nullptr;
-    uint8_t* h_out = nullptr; uint64_t* h_out_off = nullptr; uint32_t* h_status = nullptr; uint32_t* h_subj = nullptr;
+    uint8_t* h_out = nullptr; uint64_t* h_out_off = nullptr; uint32_t* h_out_len = nullptr; uint32_t* h_status = nullptr; uint32_t* h_subj = nullptr;
     uint8_t* h_hdr = nullptr;    // scratch header + counter rows read back
     // device
     uint8_t* d_in = nullptr; uint32_t* d_in_off = nullptr; int64_t* d_start = nullptr;
-    uint8_t* d_out = nullptr; uint64_t* d_out_off = nullptr; uint32_t* d_status = nullptr; uint32_t* d_subj = nullptr;
+    uint8_t* d_out = nullptr; uint64_t* d_out_off = nullptr; uint32_t* d_out_len = nullptr; uint32_t* d_status = nullptr; uint32_t* d_subj = nullptr;
     void* d_scratch = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_done = nullptr;
@@ -79,10 +79,10 @@ void add_rows(const uint8_t* hdr, ssegpu_counters* c, uint32_t n_records) {
 void free_batch(ssegpu_batch* b) {
     if (!b) return;
     cudaFreeHost(b->h_in); cudaFreeHost(b->h_in_off); cudaFreeHost(b->h_start); cudaFreeHost(b->h_conv);
-    cudaFreeHost(b->h_out); cudaFreeHost(b->h_out_off); cudaFreeHost(b->h_status); cudaFreeHost(b->h_subj);
+    cudaFreeHost(b->h_out); cudaFreeHost(b->h_out_off); cudaFreeHost(b->h_out_len); cudaFreeHost(b->h_status); cudaFreeHost(b->h_subj);
     cudaFreeHost(b->h_hdr);
     cudaFree(b->d_in); cudaFree(b->d_in_off); cudaFree(b->d_start);
-    cudaFree(b->d_out); cudaFree(b->d_out_off); cudaFree(b->d_status); cudaFree(b->d_subj);
+    cudaFree(b->d_out); cudaFree(b->d_out_off); cudaFree(b->d_out_len); cudaFree(b->d_status); cudaFree(b->d_subj);
     cudaFree(b->d_scratch);
     if (b->ev_done) cudaEventDestroy(b->ev_done);
     if (b->stream) cudaStreamDestroy(b->stream);
@@ -102,6 +102,7 @@ int alloc_batch(ssegpu_ctx* ctx, ssegpu_batch** out) {
     CU(cudaHostAlloc(&b->h_conv, n * 4 + 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_out, ctx->out_cap + 64, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_out_off, (n + 1) * 8, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&b->h_out_len, n * 4 + 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_status, n * 4 + 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_subj, n * 4 + 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_hdr, sse::scratch_readback_bytes(), cudaHostAllocDefault));
@@ -114,6 +115,7 @@ int alloc_batch(ssegpu_ctx* ctx, ssegpu_batch** out) {
     CU(cudaMalloc(&b->d_start, n * 8 + 8));
     CU(cudaMalloc(&b->d_out, ctx->out_cap + 64));
     CU(cudaMalloc(&b->d_out_off, (n + 1) * 8));
+    CU(cudaMalloc(&b->d_out_len, n * 4 + 4));
     CU(cudaMalloc(&b->d_status, n * 4 + 4));
     CU(cudaMalloc(&b->d_subj, n * 4 + 4));
     CU(cudaMalloc(&b->d_scratch, sse::scratch_bytes((uint32_t)n)));
@@ -247,6 +249,7 @@ int64_t* ssegpu_start_seq(ssegpu_batch* b) { return b ? b->h_start : nullptr; }
 uint32_t* ssegpu_conv_slot(ssegpu_batch* b) { return b ? b->h_conv : nullptr; }
 const uint8_t* ssegpu_out_bytes(const ssegpu_batch* b) { return b ? b->h_out : nullptr; }
 const uint64_t* ssegpu_out_off(const ssegpu_batch* b) { return b ? b->h_out_off : nullptr; }
+const uint32_t* ssegpu_out_len(const ssegpu_batch* b) { return b ? b->h_out_len : nullptr; }
 const uint32_t* ssegpu_status(const ssegpu_batch* b) { return b ? b->h_status : nullptr; }
 const uint32_t* ssegpu_subj_len(const ssegpu_batch* b) { return b ? b->h_subj : nullptr; }
 
@@ -268,13 +271,14 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     sse::FrameArgs a{};
     a.in = b->d_in; a.in_off = b->d_in_off; a.start_seq = use_filter ? b->d_start : nullptr;
     a.n = n; a.op = op;
-    a.out = b->d_out; a.out_cap = ctx->out_cap; a.out_off = b->d_out_off;
+    a.out = b->d_out; a.out_cap = ctx->out_cap; a.out_off = b->d_out_off; a.out_len = b->d_out_len;
     a.subj_len = (op & SSEGPU_OP_BRIDGE) ? b->d_subj : nullptr;
     a.status = b->d_status;
     sse::scratch_carve(b->d_scratch, a);
     CU(sse::frame_launch(ctx->cfg.device, a, st));
 
     CU(cudaMemcpyAsync(b->h_out_off, b->d_out_off, ((size_t)n + 1) * 8, cudaMemcpyDeviceToHost, st));
+    if (n) CU(cudaMemcpyAsync(b->h_out_len, b->d_out_len, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
     if (n) CU(cudaMemcpyAsync(b->h_status, b->d_status, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
     if ((op & SSEGPU_OP_BRIDGE) && n) CU(cudaMemcpyAsync(b->h_subj, b->d_subj, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(b->h_hdr, b->d_scratch, sse::scratch_readback_bytes(), cudaMemcpyDeviceToHost, st));
@@ -341,15 +345,15 @@ int ssegpu_counters_get(ssegpu_ctx* ctx, ssegpu_counters* out) {
 
 int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_off, const int64_t* d_start_seq,
                         uint32_t n, uint32_t op, void* d_out, uint64_t out_cap, uint64_t* d_out_off,
-                        uint32_t* d_subj_len, uint32_t* d_status, void* stream) {
-    if (!ctx || !d_in_off || !d_out_off || (n && (!d_in || !d_out || !d_status))) return SSEGPU_E_INVAL;
+                        uint32_t* d_out_len, uint32_t* d_subj_len, uint32_t* d_status, void* stream) {
+    if (!ctx || !d_in_off || !d_out_off || (n && (!d_in || !d_out || !d_status || !d_out_len))) return SSEGPU_E_INVAL;
     if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
     if (reinterpret_cast<uintptr_t>(d_in) & 15) return SSEGPU_E_INVAL;
     CU(cudaSetDevice(ctx->cfg.device));
     sse::FrameArgs a{};
     a.in = static_cast<const uint8_t*>(d_in); a.in_off = d_in_off; a.start_seq = d_start_seq;
     a.n = n; a.op = op;
-    a.out = static_cast<uint8_t*>(d_out); a.out_cap = out_cap; a.out_off = d_out_off;
+    a.out = static_cast<uint8_t*>(d_out); a.out_cap = out_cap; a.out_off = d_out_off; a.out_len = d_out_len;
     a.subj_len = d_subj_len; a.status = d_status;
     sse::scratch_carve(ctx->d_launch_scratch, a);
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;

@@ -61,6 +61,9 @@ typedef enum {
 #define SSEGPU_OP_BRIDGE    1u   /* subject "chat.<cid>.tokens" + re-marshalled JSON (bridge main.go:160-161) */
 #define SSEGPU_OP_GO122     2u   /* encode 0x08/0x0C as \b \f (Go >= 1.22) instead of Go 1.21's   */
 #define SSEGPU_OP_NO_FAST   4u   /* testing: force every record through the general decoder */
+#define SSEGPU_OP_ORDERED   8u   /* lay tiles out in record order (the arena then equals the sequential Go output
+                                    byte for byte); default: tiles land in completion order, every frame still at
+                                    out[out_off[i] .. out_off[i]+out_len[i]) and the arena still dense */
 
 typedef struct ssegpu_ctx ssegpu_ctx;
 typedef struct ssegpu_batch ssegpu_batch;
@@ -117,11 +120,13 @@ int ssegpu_batch_submit(ssegpu_ctx *ctx, ssegpu_batch *b, uint32_t n_records, ui
 /* Blocks until the results are in host memory.  timeout_us = 0 waits forever. */
 int ssegpu_batch_wait(ssegpu_ctx *ctx, ssegpu_batch *b, uint32_t timeout_us);
 
-/* Adapter egress: the handler goroutine writes out[out_off[i]:out_off[i+1]] with one
+/* Adapter egress: the handler goroutine writes out[out_off[i] : out_off[i]+out_len[i]] with one
  * w.Write + Flush instead of three Fprintf (sse_handler.go:212-215, :428-431); bridge egress:
- * nc.Publish(out[off:off+subj_len], out[off+subj_len:next]) (redis-nats-bridge/main.go:164). */
+ * nc.Publish(out[off:off+subj_len], out[off+subj_len:off+out_len]) (redis-nats-bridge/main.go:164).
+ * out_off[n] is the total number of output bytes of the batch. */
 const uint8_t  *ssegpu_out_bytes(const ssegpu_batch *b);
 const uint64_t *ssegpu_out_off(const ssegpu_batch *b);   /* n+1 */
+const uint32_t *ssegpu_out_len(const ssegpu_batch *b);   /* n   */
 const uint32_t *ssegpu_status(const ssegpu_batch *b);    /* n   */
 const uint32_t *ssegpu_subj_len(const ssegpu_batch *b);  /* n, bridge mode only */
 int ssegpu_batch_release(ssegpu_ctx *ctx, ssegpu_batch *b);
@@ -137,8 +142,8 @@ int ssegpu_counters_get(ssegpu_ctx *ctx, ssegpu_counters *out);
  * context (the launch scratch is per context). */
 int ssegpu_frame_launch(ssegpu_ctx *ctx, const void *d_in, const uint32_t *d_in_off,
                         const int64_t *d_start_seq, uint32_t n_records, uint32_t op_flags,
-                        void *d_out, uint64_t out_cap, uint64_t *d_out_off, uint32_t *d_subj_len,
-                        uint32_t *d_status, void *stream);
+                        void *d_out, uint64_t out_cap, uint64_t *d_out_off, uint32_t *d_out_len,
+                        uint32_t *d_subj_len, uint32_t *d_status, void *stream);
 /* After the launch's stream has been synchronised: adds the launch's counters into *out and
  * returns SSEGPU_E_OVERFLOW if out_cap was too small. */
 int ssegpu_frame_launch_result(ssegpu_ctx *ctx, ssegpu_counters *out);

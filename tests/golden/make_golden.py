@@ -172,6 +172,13 @@ def build():
         add("canon_rand_%d" % k, canon(rand_text(rng, rng.randrange(0, 40), 0.1), rand_text(rng, rng.randrange(0, 24), rng.choice([0, 0.2, 0.6])),
                                      rng.choice([0, 1, 9, 10, 99, 100, 999, 1000, -1, rng.randrange(-(1 << 63), 1 << 63)]),
                                      rng.random() < 0.1, rng.choice([0, T, -T, (1 << 63) - 1, -(1 << 63)])))
+    # every digit count of the two integers (the CUDA canonical path parses them word-wise)
+    for k in range(1, 20):
+        for v in (10 ** (k - 1), 10 ** k - 1, int("1234567890123456789"[:k]), int("9876543210987654321"[:k])):
+            for sign in (1, -1):
+                if abs(v) < (1 << 63):
+                    add("digits_seq_%d_%d" % (k, sign * v), canon("c", "t", sign * v, False, 7))
+                    add("digits_ts_%d_%d" % (k, sign * v), canon("c", "t", 7, False, sign * v))
     # near-canonical: one byte changed / inserted / removed
     base = canon("7f3c2b1a-1111-4222-8333-944455556666", " hello", 42, False, T)
     for i in range(len(base)):

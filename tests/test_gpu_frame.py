@@ -27,19 +27,7 @@ def eng(pkg):
     e.close()
 
 
-def run_batch(eng, arena, off, start=None, op=0):
-    b = eng.acquire()
-    b.fill(arena, off, start)
-    b.submit(len(off) - 1, op, use_filter=start is not None)
-    b.wait()
-    res = (b.out.copy(), b.out_off.copy(), b.status.copy(), b.subj_len.copy())
-    b.release()
-    return res
-
-
-def slices(out, out_off):
-    raw = out.tobytes()
-    return [raw[int(out_off[i]):int(out_off[i + 1])] for i in range(len(out_off) - 1)]
+from gpu_util import run_batch, slices, normalise  # noqa: E402
 
 
 def test_hand_vectors(pkg, eng, oracle):
@@ -60,7 +48,7 @@ def test_hand_vectors(pkg, eng, oracle):
         assert int(s) == st and g[: int(sl)] == sj and g[int(sl):] == js
 
 
-@pytest.mark.parametrize("op", [0, 4, 2, 1, 1 | 4])
+@pytest.mark.parametrize("op", [0, 4, 2, 1, 1 | 4, 8, 8 | 1])
 def test_golden_fixtures(pkg, eng, oracle, golden, op):
     arena, off = oracle.pack([bytes.fromhex(c["in"]) for c in golden])
     start = np.array([c["start"] for c in golden], dtype=np.int64)
@@ -89,7 +77,7 @@ def test_differential_fuzz_vs_oracle(pkg, eng, oracle):
             payloads.append(mg.mutate(rng, rng.choice([base, payloads[-1] if payloads else base])))
     arena, off = oracle.pack(payloads)
     start = np.array([rng.choice([0, 0, 3, 100]) for _ in payloads], dtype=np.int64)
-    for op, go122 in ((0, False), (pkg.OP_GO122, True), (pkg.OP_NO_FAST, False)):
+    for op, go122 in ((0, False), (pkg.OP_GO122, True), (pkg.OP_NO_FAST, False), (pkg.OP_ORDERED, False)):
         want_out, want_off, want_status = oracle.adapter(arena, off, start, go122=go122)
         out, out_off, status, _ = run_batch(eng, arena, off, start, op)
         assert np.array_equal(status, want_status)
@@ -101,12 +89,13 @@ def test_differential_fuzz_vs_oracle(pkg, eng, oracle):
     assert np.array_equal(subj, want_subj) and np.array_equal(out, want_out)
 
 
+@pytest.mark.parametrize("op", [0, 8])
 @pytest.mark.parametrize("n", [0, 1, 2, 127, 128, 129, 255, 256, 257, 1000])
-def test_tile_boundaries(pkg, eng, oracle, n):
+def test_tile_boundaries(pkg, eng, oracle, n, op):
     arena, off = pkg.workload.generate(1, max(n, 1), 1)
     off = off[: n + 1].copy()
     want_out, want_off, want_status = oracle.adapter(arena, off)
-    out, out_off, status, _ = run_batch(eng, arena, off)
+    out, out_off, status, _ = run_batch(eng, arena, off, None, op)
     assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
 
 
@@ -133,8 +122,8 @@ def test_oversize_tiles_use_global_path(pkg, eng, oracle):
         else:
             payloads.append(mg.canon("conv-%d" % k, " tok", k, False, 2))
     arena, off = oracle.pack(payloads)
-    for op in (0, pkg.OP_BRIDGE):
-        if op == 0:
+    for op in (0, pkg.OP_BRIDGE, pkg.OP_ORDERED):
+        if not op & pkg.OP_BRIDGE:
             want_out, want_off, want_status = oracle.adapter(arena, off)
         else:
             want_out, want_off, _, want_status = oracle.bridge(arena, off)
@@ -142,12 +131,13 @@ def test_oversize_tiles_use_global_path(pkg, eng, oracle):
         assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
 
 
+@pytest.mark.parametrize("op", [0, 8])
 @pytest.mark.parametrize("config,n_conv,n_tok", [(0, 1000, 512), (1, 10000, 100)])
-def test_baseline_workloads_bit_exact(pkg, eng, oracle, config, n_conv, n_tok):
+def test_baseline_workloads_bit_exact(pkg, eng, oracle, config, n_conv, n_tok, op):
     arena, off = pkg.workload.generate(config, n_conv, n_tok)
     want_out, want_off, want_status = oracle.adapter(arena, off)
     before = eng.counters()
-    out, out_off, status, _ = run_batch(eng, arena, off)
+    out, out_off, status, _ = run_batch(eng, arena, off, None, op)
     after = eng.counters()
     assert np.array_equal(status, want_status)
     assert np.array_equal(out_off, want_off)
@@ -173,7 +163,8 @@ def test_output_overflow_is_reported_not_truncated(pkg, oracle):
         e.close()
 
 
-def test_device_resident_launch_full_size_properties(pkg, oracle):
+@pytest.mark.parametrize("op", [0, 8])
+def test_device_resident_launch_full_size_properties(pkg, oracle, op):
     """BASELINE config-1 shape at a size the GPU does in milliseconds: checked by size-independent properties
     (offsets == prefix sum of per-record lengths; every frame == header + payload + trailer) and against the
     oracle on a sampled window."""
@@ -188,24 +179,25 @@ def test_device_resident_launch_full_size_properties(pkg, oracle):
         cap = int(off[n]) + 48 * n
         d_out = torch.zeros(cap, dtype=torch.uint8, device="cuda")
         d_out_off = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
+        d_out_len = torch.zeros(n, dtype=torch.int32, device="cuda")
         d_status = torch.zeros(n, dtype=torch.int32, device="cuda")
         stream = torch.cuda.Stream()
         torch.cuda.synchronize()
         st = stream.cuda_stream
         for _ in range(2):          # second launch reuses the zeroed scratch: must be idempotent
-            eng.frame_launch(d_in.data_ptr(), d_off.data_ptr(), 0, n, 0, d_out.data_ptr(), cap, d_out_off.data_ptr(), 0,
-                             d_status.data_ptr(), st)
+            eng.frame_launch(d_in.data_ptr(), d_off.data_ptr(), 0, n, op, d_out.data_ptr(), cap, d_out_off.data_ptr(),
+                             d_out_len.data_ptr(), 0, d_status.data_ptr(), st)
         torch.cuda.synchronize()
         rc, c = eng.launch_result()
         assert rc == 0 and c["frames"] == n and c["fast_path"] == n and c["done"] == n_conv
-        out_off = d_out_off.cpu().numpy().astype(np.uint64)
         status = d_status.cpu().numpy().astype(np.uint32)
         seq_digits = np.char.str_len((np.arange(n) // n_conv + 1).astype(str))
         lens = np.diff(off.astype(np.int64)) + 26 + seq_digits
-        assert np.array_equal(np.diff(out_off.astype(np.int64)), lens)
+        assert np.array_equal(d_out_len.cpu().numpy().astype(np.int64), lens)
+        out, out_off = normalise(d_out.cpu().numpy(), d_out_off.cpu().numpy().astype(np.uint64),
+                                 d_out_len.cpu().numpy().astype(np.uint32), bool(op & 8))
         assert c["bytes_out"] == int(out_off[n])
         assert ((status & 0xF) == 0).all() and int((status & 0x100 != 0).sum()) == n_conv
-        out = d_out.cpu().numpy()
         lo, hi = n // 2 - 5000, n // 2 + 5000
         sub_off = (off[lo:hi + 1] - off[lo]).astype(np.uint32)
         sub_arena = np.concatenate([arena[off[lo]:off[hi]], np.zeros(16, np.uint8)])

@@ -19,21 +19,28 @@ top = int(sys.argv[sys.argv.index("--top") + 1]) if "--top" in sys.argv else 45
 tmp = tempfile.mkdtemp()
 subprocess.check_call(["cuobjdump", "-xelf", "all", lib], cwd=tmp, stdout=subprocess.DEVNULL)
 cubin = [f for f in os.listdir(tmp) if f.startswith("sse_kernels.")][0]
-dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
+dis = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
 
-# instruction order -> (file:line, inlined-at chain)
+# instruction order -> (innermost file:line, chain of frames innermost..outermost)
 lines = []
-cur = None
+chains = []
+cur_chain = []
+pending = []
 in_kernel = False
 for ln in dis.splitlines():
     if ln.startswith(".text."):
         in_kernel = "k_frame_tiles" in ln
-    m = re.search(r'//## File "([^"]+)", line (\d+)(.*)', ln)
+    m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
     if m:
-        cur = (os.path.basename(m.group(1)), int(m.group(2)))
+        pending.append((os.path.basename(m.group(1)), int(m.group(2))))
         continue
-    if in_kernel and re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+\S", ln):
-        lines.append((cur, ln.split("*/", 1)[1].strip()[:60]))
+    if re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+\S", ln):
+        if pending:
+            cur_chain = pending
+            pending = []
+        if in_kernel:
+            lines.append((cur_chain[0] if cur_chain else None, ln.split("*/", 1)[1].strip()[:60]))
+            chains.append(cur_chain)
 
 rows = list(csv.reader(subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout.splitlines()))
 hi = [i for i, r in enumerate(rows) if "Instructions Executed" in r][0]
@@ -69,5 +76,49 @@ def src_line(key):
     return ""
 
 
+# ---- per function (any frame of the inline chain), and per kernel-level call site ----
+CS = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "distributed-sse-for-llm-response_b200", "csrc")
+fn_cache = {}
+
+
+def func_of(key):
+    f, l = key
+    p = os.path.join(CS, f)
+    if not os.path.exists(p):
+        return f
+    if p not in fn_cache:
+        fn_cache[p] = open(p).read().splitlines()
+    src = fn_cache[p]
+    for k in range(min(l, len(src)) - 1, -1, -1):
+        t = src[k]
+        m = re.match(r"^(?:    )?(?:template\s*<[^>]*>\s*)?(?:SSE_HD(?:_NOINLINE)?|__device__|__global__|static|inline)\b.*?(\w+)\s*\(", t)
+        if m and not t.strip().startswith("//"):
+            return m.group(1)
+    return f
+
+
+fn_incl, site = {}, {}
+for k in range(n):
+    ie_k, s_k = int(body[k][ie]), int(body[k][smp])
+    seen = set()
+    for fr in chains[k]:
+        fn = func_of(fr)
+        if fn not in seen:
+            seen.add(fn)
+            a = fn_incl.setdefault(fn, [0, 0])
+            a[0] += ie_k
+            a[1] += s_k
+    if chains[k]:
+        outer = chains[k][-1]
+        a = site.setdefault(outer, [0, 0])
+        a[0] += ie_k
+        a[1] += s_k
+print("---- inclusive per function ----")
+for fn, (i, s_) in sorted(fn_incl.items(), key=lambda kv: -kv[1][0])[:28]:
+    print("%5.1f%% inst %5.1f%% smp  %s" % (100.0 * i / tot_i, 100.0 * s_ / max(tot_s, 1), fn))
+print("---- per kernel-level line (outermost frame) ----")
+for key, (i, s_) in sorted(site.items(), key=lambda kv: -kv[1][0])[:22]:
+    print("%5.1f%% inst %5.1f%% smp  %-22s %s" % (100.0 * i / tot_i, 100.0 * s_ / max(tot_s, 1), "%s:%d" % key, src_line(key)))
+print("---- per innermost line ----")
 for key, (i, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
     print("%5.1f%% inst %5.1f%% smp  %-28s %s" % (100.0 * i / tot_i, 100.0 * s / max(tot_s, 1), "%s:%d" % key if key else "?", src_line(key)))
