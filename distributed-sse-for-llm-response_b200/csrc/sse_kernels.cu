@@ -53,6 +53,15 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gsrc, ui
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// shared -> global bulk copy (TMA, 1-D).  16-byte aligned on both sides, bytes a multiple of 16.
+__device__ __forceinline__ void tma_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 __device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t* p) {
     uint64_t v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -200,8 +209,8 @@ __device__ __forceinline__ void copy_out(uint8_t* __restrict__ out, const uint8_
 
 __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t* s_in = smem;                                   // in_cap + 16
-    uint8_t* s_out = smem + a.in_cap + 16;                  // out_cap_s + 48
+    uint8_t* s_in = smem;                                   // in_cap + 32 (word reads run up to 24 bytes past a record)
+    uint8_t* s_out = smem + a.in_cap + 32;                  // out_cap_s + 48
     TileSmem* ts = reinterpret_cast<TileSmem*>(s_out + a.out_cap_s + 48);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -259,16 +268,22 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
             if (lane >= d) incl += v;
         }
         if (lane == 31) ts->wsum[warp] = incl;
+        if (tid == 0) bulk_wait_read0();                                      // previous tile's bulk store has finished reading s_out
         __syncthreads();                                                      // (B)
         uint32_t wpre = 0, total = 0;
 #pragma unroll
         for (int w = 0; w < TILE / 32; w++) { uint32_t v = ts->wsum[w]; if (w < (int)warp) wpre += v; total += v; }
         const bool ordered = (a.op & OP_ORDERED) != 0;                        // launch-uniform
         const bool smem_out = total <= a.out_cap_smem();                      // tile-uniform
+        // arrival-order placement: every tile owns a 16-byte aligned slice of the arena, so its staging
+        // tile leaves as ONE TMA bulk store; the <=15 pad bytes after its last frame are zeroed.
+        const uint32_t alloc = ordered ? total : ((total + 15u) & ~15u);
         if (tid == 0) {
             c_out += total;
             if (ordered) publish_aggregate(a.tile_state, tile, total);
-            else ts->base = atomicAdd(a.cursor, (unsigned long long)total);   // arrival-order placement: nothing to wait for
+            else {
+                ts->base = atomicAdd(a.cursor, (unsigned long long)alloc);    // nothing to wait for
+            }
         }
         const uint32_t local = wpre + incl - len;
         const uint32_t code = st & ST_CODE_MASK;
@@ -286,6 +301,10 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
                     Plan sp = pl;
                     subj = emit_slow(smem_in ? s_in : a.in + abase, o, L, &sp, a.op, s_out, (uint64_t)local);
                 }
+            }
+            if (!ordered) {
+                if (tid < alloc - total) s_out[total + tid] = 0;
+                fence_proxy_async_smem();                                     // staging writes -> visible to the TMA store
             }
             __syncthreads();                                                  // (D) s_in free, staging tile complete, base visible
             if (warp == 0) {
@@ -305,12 +324,13 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
             __syncthreads();                                                  // (D')
         }
         const uint64_t base = ts->base;
-        const bool fits = base + total <= a.out_cap;
+        const bool fits = base + alloc <= a.out_cap;
         if (!smem_out) {
             if (active && code == ST_OK && fits) {
                 Plan sp = pl;
                 subj = emit_slow(smem_in ? s_in : a.in + abase, o, L, &sp, a.op, a.out, base + local);
             }
+            if (fits && tid < alloc - total) a.out[base + total + tid] = 0;       // pad of an aligned tile
             __syncthreads();                                                  // (E') s_in free
             if (tid == 0) setup_tile(a, ts, s_in, next_t, c_in);
         }
@@ -325,8 +345,13 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
             if (a.subj_len) a.subj_len[r0 + tid] = subj;
         }
         if (tid == 0 && !fits) atomicExch(a.overflow, 1u);
-        if (smem_out && fits && total != 0) copy_out(a.out, s_out, base, total, tid);
+        if (smem_out && fits && total != 0) {
+            if (ordered) copy_out(a.out, s_out, base, total, tid);
+            else if (tid == 0) { tma_store_1d(a.out + base, s_out, alloc); bulk_commit(); }
+        }
     }
+
+    if (tid == 0) bulk_wait0();
 
     // ---- counters: one row per CTA slot, summed by the host --------------------------
     unsigned long long* row = a.counters + (size_t)(blockIdx.x % CTR_ROWS) * CTR_COLS;
@@ -360,7 +385,7 @@ cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uin
     // BASELINE workload; caps leave ~15% slack.  Tiles that exceed them take the direct
     // global-memory path inside the same kernel.
     const uint32_t ic = 20 * 1024, oc = 24 * 1024;
-    const uint32_t sm = ic + 16 + oc + 48 + (uint32_t)sizeof(TileSmem);
+    const uint32_t sm = ic + 32 + oc + 48 + (uint32_t)sizeof(TileSmem);
     cudaError_t e = cudaFuncSetAttribute(k_frame_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     if (e != cudaSuccess) return e;
     if (g_num_sms[device] == 0) {

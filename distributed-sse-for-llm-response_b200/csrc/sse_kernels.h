@@ -12,7 +12,7 @@ constexpr int CTR_COLS = 8;      // ok, syntax, type, filtered, done, fast, byte
 constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32
 
 struct FrameArgs {
-    const uint8_t* in;           // packed payload arena, 16-byte aligned, 16 bytes of padding after the last record
+    const uint8_t* in;           // packed payload arena, 16-byte aligned, 32 readable bytes after the last record
     const uint32_t* in_off;      // n+1
     const int64_t* start_seq;    // n or nullptr
     uint32_t n, op;

@@ -422,13 +422,13 @@ template <class Src> SSE_HD bool scan_canon_string(const Src& s, uint32_t& pos, 
         // word loop: one aligned load per 4 bytes, the previous word is carried
         uint32_t a = pos & ~3u;
         const uint32_t shb = (pos & 3u) * 8;
-        uint32_t lo = s.ld32a(a), w, m;
-        for (;;) {                                              // 8 bytes per trip
+        uint32_t lo = s.ld32a(a), h1 = s.ld32a(a + 4), h2 = s.ld32a(a + 8), w, m;
+        for (;;) {                                              // 8 bytes per trip, next trip's words already in flight
             if (pos >= end) return false;
-            const uint32_t h1 = s.ld32a(a + 4), h2 = s.ld32a(a + 8);
+            const uint32_t n1 = s.ld32a(a + 12), n2 = s.ld32a(a + 16);
             const uint32_t wa = funnel_r(lo, h1, shb), wb = funnel_r(h1, h2, shb);
             const uint32_t ma = special_mask(wa), mb = special_mask(wb);
-            if ((ma | mb) == 0) { lo = h2; a += 8; pos += 8; continue; }
+            if ((ma | mb) == 0) { lo = h2; h1 = n1; h2 = n2; a += 8; pos += 8; continue; }
             if (ma) { w = wa; m = ma; } else { w = wb; m = mb; pos += 4; }
             break;
         }
@@ -518,6 +518,35 @@ template <class Src> SSE_HD bool scan_canon_int(const Src& s, uint32_t& pos, uin
     return true;
 }
 
+// The timestamp literal is the record's tail: it occupies [pos, end-1) and '}' sits at end-1.
+// Its value is not needed on the canonical path, only that it IS canonical: six independent
+// aligned loads, five funnel shifts, digit masks -- straight-line, no search loop.
+template <class Src> SSE_HD bool check_canon_tail_int(const Src& s, uint32_t pos, uint32_t end) {
+    const uint32_t neg = (s.ld8(pos) == '-') ? 1u : 0u;
+    const uint32_t start = pos + neg, lim = end - 1;
+    if (start >= lim) return false;
+    const uint32_t nd = lim - start;
+    if (nd > 19) return false;
+    const uint32_t a = start & ~3u, shb = (start & 3u) * 8;
+    const uint32_t x0 = s.ld32a(a), x1 = s.ld32a(a + 4), x2 = s.ld32a(a + 8), x3 = s.ld32a(a + 12), x4 = s.ld32a(a + 16),
+                   x5 = s.ld32a(a + 20);
+    const uint32_t w0 = funnel_r(x0, x1, shb);
+    const uint32_t d0 = w0 & 0xFF;
+    if (d0 == '0' && (nd != 1 || neg)) return false;            // leading zero, "-0"
+    if (nd == 19 && d0 == '9') return false;                    // might overflow: exact check in the general path
+    uint32_t bad = 0;
+    const uint32_t ws[5] = {w0, funnel_r(x1, x2, shb), funnel_r(x2, x3, shb), funnel_r(x3, x4, shb), funnel_r(x4, x5, shb)};
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+    for (int k = 0; k < 5; k++) {
+        const int c = (int)nd - 4 * k;                          // digits expected in word k
+        const uint32_t keep = c >= 4 ? 0x80808080u : (c > 0 ? (0x80808080u >> (8 * (4 - c))) : 0u);
+        bad |= nondigit_mask(ws[k]) & keep;
+    }
+    return bad == 0 && s.ld8(lim) == '}';
+}
+
 // three unaligned words at pos with four aligned loads
 template <class Src> SSE_HD void ld3u(const Src& s, uint32_t pos, uint32_t& w0, uint32_t& w1, uint32_t& w2) {
     const uint32_t a = pos & ~3u, shb = (pos & 3u) * 8;
@@ -573,9 +602,8 @@ template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L
     d = (w0 ^ w4(",\"ti")) | (w1 ^ w4("mest")) | (w2 ^ w4("amp\"")) | (s.ld8(pos + 12) ^ ':');
     if (d || pos + 14 > end) return false;
     pos += 13;
-    pl.ts = 0;
-    if (!scan_canon_int(s, pos, end, false, pl.ts)) return false;
-    if (pos + 1 != end || s.ld8(pos) != '}') return false;
+    pl.ts = 0;                                                  // never read for canonical records
+    if (!check_canon_tail_int(s, pos, end)) return false;
     pl.fast = 1;
     pl.cid_esc = cid_esc ? 1u : 0u;   // the bridge subject needs the DECODED id
     (void)tok_esc;

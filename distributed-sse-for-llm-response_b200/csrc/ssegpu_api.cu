@@ -262,9 +262,9 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     CU(cudaSetDevice(ctx->cfg.device));
     cudaStream_t st = b->stream;
     b->n = n; b->op = op;
-    // 16 readable bytes after the last payload byte (TMA tiles are 16-byte granular)
-    memset(b->h_in + in_total, 0, 32);
-    CU(cudaMemcpyAsync(b->d_in, b->h_in, ((in_total + 15) & ~15ull) + 16, cudaMemcpyHostToDevice, st));
+    // 32 readable bytes after the last payload byte (TMA tiles are 16-byte granular, word reads overrun a little)
+    memset(b->h_in + in_total, 0, 48);
+    CU(cudaMemcpyAsync(b->d_in, b->h_in, ((in_total + 15) & ~15ull) + 32, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(b->d_in_off, b->h_in_off, ((size_t)n + 1) * 4, cudaMemcpyHostToDevice, st));
     if (use_filter && n) CU(cudaMemcpyAsync(b->d_start, b->h_start, (size_t)n * 8, cudaMemcpyHostToDevice, st));
 
@@ -284,7 +284,7 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     CU(cudaMemcpyAsync(b->h_hdr, b->d_scratch, sse::scratch_readback_bytes(), cudaMemcpyDeviceToHost, st));
     // Speculative copy of the frames: a canonical record grows by 26 + digits(seq) bytes
     // (28 + len("chat..tokens")=40ish in bridge mode); anything beyond is fetched in wait().
-    uint64_t spec = in_total + (uint64_t)n * ((op & SSEGPU_OP_BRIDGE) ? 80 : 32);
+    uint64_t spec = in_total + (uint64_t)n * ((op & SSEGPU_OP_BRIDGE) ? 80 : 32) + 16ull * ((n + sse::TILE - 1) / sse::TILE);
     if (spec > ctx->out_cap) spec = ctx->out_cap;
     b->spec_out = spec;
     if (spec) CU(cudaMemcpyAsync(b->h_out, b->d_out, spec, cudaMemcpyDeviceToHost, st));

@@ -41,7 +41,7 @@ def shard_members(config, n_total, rank, world, seed_ids=SEED_IDS):
 
 def generate(config, n_conv, n_tok, conv_first=0, seed_ids=SEED_IDS, seed_tok=SEED_TOK, threads=None, arena=None,
              conv_map=None):
-    """-> (arena uint8[total+16], off uint32[n+1]).  `arena` may be a preallocated uint8 array (e.g. a pinned view);
+    """-> (arena uint8[total+64], off uint32[n+1]).  `arena` may be a preallocated uint8 array (e.g. a pinned view);
     `conv_map` (uint32 indices, e.g. from shard_members) replaces the contiguous range [conv_first, conv_first+n_conv)."""
     lib = _lib()
     cm = None
@@ -56,7 +56,7 @@ def generate(config, n_conv, n_tok, conv_first=0, seed_ids=SEED_IDS, seed_tok=SE
     if total == 0 and n:
         raise ValueError("workload exceeds the 4 GiB arena limit")
     if arena is None:
-        arena = np.empty(total + 16, dtype=np.uint8)
+        arena = np.zeros(total + 64, dtype=np.uint8)
     assert arena.size >= total + 16
     got = lib.sseload_generate(config, n_conv, n_tok, conv_first, cm, seed_ids, seed_tok, arena.ctypes.data, arena.size,
                                off.ctypes.data, threads)

@@ -61,9 +61,10 @@ typedef enum {
 #define SSEGPU_OP_BRIDGE    1u   /* subject "chat.<cid>.tokens" + re-marshalled JSON (bridge main.go:160-161) */
 #define SSEGPU_OP_GO122     2u   /* encode 0x08/0x0C as \b \f (Go >= 1.22) instead of Go 1.21's   */
 #define SSEGPU_OP_NO_FAST   4u   /* testing: force every record through the general decoder */
-#define SSEGPU_OP_ORDERED   8u   /* lay tiles out in record order (the arena then equals the sequential Go output
-                                    byte for byte); default: tiles land in completion order, every frame still at
-                                    out[out_off[i] .. out_off[i]+out_len[i]) and the arena still dense */
+#define SSEGPU_OP_ORDERED   8u   /* lay the frames out back to back in record order (the arena then equals the
+                                    sequential Go output byte for byte).  Default: each tile of 128 consecutive
+                                    records lands 16-byte aligned in completion order (<=15 zero bytes between
+                                    tiles); every frame is still out[out_off[i] .. out_off[i]+out_len[i]) */
 
 typedef struct ssegpu_ctx ssegpu_ctx;
 typedef struct ssegpu_batch ssegpu_batch;
@@ -109,7 +110,7 @@ int64_t ssegpu_start_sequence(const char *last_event_id);
  * current batch instead of calling json.Unmarshal; bridge ingress: msg.Payload
  * (redis-nats-bridge/main.go:142-157). */
 int       ssegpu_batch_acquire(ssegpu_ctx *ctx, ssegpu_batch **out);
-uint8_t  *ssegpu_in_bytes(ssegpu_batch *b);     /* max_in_bytes + 16 writable bytes          */
+uint8_t  *ssegpu_in_bytes(ssegpu_batch *b);     /* max_in_bytes + 48 writable bytes          */
 uint32_t *ssegpu_in_off(ssegpu_batch *b);       /* n+1 offsets into in_bytes, in_off[0] = 0   */
 int64_t  *ssegpu_start_seq(ssegpu_batch *b);    /* n; 0 = filter off (ignored unless use_filter) */
 uint32_t *ssegpu_conv_slot(ssegpu_batch *b);    /* n; inspection state slot of the conversation */
@@ -136,7 +137,7 @@ int ssegpu_counters_get(ssegpu_ctx *ctx, ssegpu_counters *out);
 
 /* ---- device-resident launch (kernel-level path, used by the bench and the parity tests) -- */
 /* Same computation as submit, on buffers that already live in this context's GPU memory.
- * d_in must be 16-byte aligned with 16 readable bytes after the last payload byte.
+ * d_in must be 16-byte aligned with 32 readable bytes after the last payload byte.
  * d_subj_len may be NULL in adapter mode, d_start_seq NULL switches the filter off.
  * stream is a cudaStream_t (NULL = the context's stream).  Asynchronous. Not re-entrant per
  * context (the launch scratch is per context). */

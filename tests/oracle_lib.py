@@ -36,7 +36,7 @@ class Oracle:
         off = np.zeros(len(payloads) + 1, dtype=np.uint32)
         if payloads:
             off[1:] = np.cumsum([len(p) for p in payloads], dtype=np.uint64).astype(np.uint32)
-        arena = np.frombuffer(b"".join(payloads) + b"\0" * 16, dtype=np.uint8).copy()
+        arena = np.frombuffer(b"".join(payloads) + b"\0" * 64, dtype=np.uint8).copy()
         return arena, off
 
     def adapter(self, arena, off, start_seq=None, go122=False):
