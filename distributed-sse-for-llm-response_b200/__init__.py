@@ -8,6 +8,6 @@ sm_100 device is present, construction fails loudly.
 """
 from .binding import (  # noqa: F401
     OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_ORDERED, ST_CODE_MASK, ST_DONE, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_OK,
-    Batch, SseGpu, SseGpuError, lib_path, load_library, shard, start_sequence,
+    STATIC_MAX_RECORDS, Batch, SseGpu, SseGpuError, frame_launch_static, lib_path, load_library, shard, start_sequence,
 )
 from . import workload  # noqa: F401

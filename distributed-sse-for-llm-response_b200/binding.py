@@ -86,6 +86,9 @@ def load_library():
     lib.ssegpu_frame_launch_result.argtypes = [vp, C.POINTER(Counters)]
     lib.ssegpu_launch_count.restype = C.c_uint64
     lib.ssegpu_launch_count.argtypes = [vp]
+    lib.ssegpu_frame_launch_static.restype = C.c_int
+    lib.ssegpu_frame_launch_static.argtypes = [C.c_int, vp, vp, vp, C.c_uint32, C.c_uint32, vp, C.c_uint64, vp, vp, vp, vp, vp]
+    lib.ssegpu_static_last_error.restype = C.c_char_p
     _LIB = lib
     return lib
 
@@ -96,6 +99,20 @@ def shard(conversation_id: bytes, n_gpus: int) -> int:
 
 def start_sequence(last_event_id):
     return load_library().ssegpu_start_sequence(None if last_event_id is None else last_event_id.encode())
+
+
+STATIC_MAX_RECORDS = 1 << 20
+
+
+def frame_launch_static(device, d_in, d_in_off, d_start_seq, n, op, d_out, out_cap, d_out_off, d_out_len, d_subj_len,
+                        d_status, stream=0):
+    """ssegpu_frame_launch_static: context-free launch that allocates nothing (built-in scratch array, at most
+    STATIC_MAX_RECORDS records).  Pointer arguments are raw device addresses.  Overflow shows as out_off[n] > out_cap."""
+    lib = load_library()
+    rc = lib.ssegpu_frame_launch_static(device, d_in, d_in_off, d_start_seq or None, n, op, d_out, out_cap, d_out_off,
+                                        d_out_len, d_subj_len or None, d_status, stream or None)
+    if rc != 0:
+        raise SseGpuError(rc, "%s [%s]" % (lib.ssegpu_strerror(rc).decode(), lib.ssegpu_static_last_error().decode()))
 
 
 class Batch:

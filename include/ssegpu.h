@@ -152,6 +152,31 @@ int ssegpu_frame_launch_result(ssegpu_ctx *ctx, ssegpu_counters *out);
 /* Number of kernel launches this context has issued so far (bench.py "gpu_launches"). */
 uint64_t ssegpu_launch_count(ssegpu_ctx *ctx);
 
+/* ---- launch without any allocation ------------------------------------------------- */
+/* No counterpart in the reference (which has no accelerator code at all); added for callers that cannot
+ * allocate GPU memory: a service sharing its GPU with an inference server that has already reserved nearly
+ * all of HBM, or a latency-critical loop that cannot take the device-wide synchronisation of cudaMalloc.
+ * Same computation as ssegpu_frame_launch, but context-free: the kernel's scratch (tile ticket, arena
+ * cursor, counter rows, one look-back word per tile) lives in a fixed array inside the library image
+ * (SSEGPU_STATIC_SCRATCH_BYTES per GPU that loads the library, held until the process exits) and the call
+ * performs no cudaMalloc / cudaFree / pinned allocation.  The caller supplies every input and output
+ * buffer (same requirements as ssegpu_frame_launch).
+ *   - n_records above SSEGPU_STATIC_MAX_RECORDS is refused with SSEGPU_E_TOOBIG (see ssegpu_static_last_error);
+ *   - the first call on a device resolves the array's device address; make that first call outside any
+ *     stream capture;
+ *   - all calls on one device share the one array: it is cleared on `stream` at the start of every call, and
+ *     two calls whose GPU work overlaps (different streams, or different threads) race on it -- serialise them;
+ *   - there is no result call: out_off[n_records] holds the arena bytes needed, so the batch overflowed the
+ *     output arena exactly when out_off[n_records] > out_cap after the stream has been synchronised.
+ * stream is a cudaStream_t (NULL = the legacy default stream).  Asynchronous. */
+#define SSEGPU_STATIC_MAX_RECORDS   (1u << 20)
+#define SSEGPU_STATIC_SCRATCH_BYTES (72u * 1024u)
+int ssegpu_frame_launch_static(int device, const void *d_in, const uint32_t *d_in_off,
+                               const int64_t *d_start_seq, uint32_t n_records, uint32_t op_flags,
+                               void *d_out, uint64_t out_cap, uint64_t *d_out_off, uint32_t *d_out_len,
+                               uint32_t *d_subj_len, uint32_t *d_status, void *stream);
+const char *ssegpu_static_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif
