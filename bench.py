@@ -80,6 +80,17 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def measured_traffic(n_records):
+    """dram__bytes_read.sum + dram__bytes_write.sum of k_frame_tiles from the committed ncu --set full capture,
+    scaled to this launch's record count (the capture is one launch of the N=1 workload)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return (t["dram_bytes_read"] + t["dram_bytes_write"]) * n_records / t["records_per_launch"]
+    except Exception:
+        return None
+
+
 def dist_env():
     return int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
 
@@ -281,7 +292,7 @@ def run_gpu(args):
                     "bytes_per_sec": (in_all + out_all) * args.steps / mx[2]},
             "gpu_launches": int(launches), "gpu_launches_e2e": int(e2e_launches),
             "roofline": {"bound": "hbm", "kernel": "k_frame_tiles", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "peak_source": which, "frac_of_8000_datasheet": achieved / 8000.0, "traffic": None,
+                         "peak_source": which, "frac_of_8000_datasheet": achieved / 8000.0, "traffic": measured_traffic(n),
                          "alg_bytes_per_launch": int(alg_bytes), "kernel_ms": kern_ms,
                          "note": "kernel_ms = CUDA events around memset(scratch)+k_frame_tiles on the launching stream, mean of %d" % args.steps},
             "cpu_baseline": cpu,
