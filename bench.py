@@ -96,10 +96,7 @@ def dist_env():
 
 
 def make_workload(pkg, rank, world):
-    if world == 1:
-        return pkg.workload.generate(1, N_CONV, N_TOK)
-    members = pkg.workload.shard_members(1, N_CONV * world, rank, world)
-    return pkg.workload.generate(1, 0, N_TOK, conv_map=members)
+    return pkg.sharding.rank_workload(1, N_CONV * world, N_TOK, rank, world)
 
 
 def cpu_baseline(arena, off, threads, budget_s=12.0):

@@ -11,3 +11,4 @@ from .binding import (  # noqa: F401
     STATIC_MAX_RECORDS, Batch, SseGpu, SseGpuError, frame_launch_static, lib_path, load_library, shard, start_sequence,
 )
 from . import workload  # noqa: F401
+from . import sharding  # noqa: F401
