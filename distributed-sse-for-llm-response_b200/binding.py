@@ -6,10 +6,14 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
-OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_ORDERED = 0, 1, 2, 4, 8
+OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_ORDERED, OP_INSPECT, OP_INSPECT_INLINE = 0, 1, 2, 4, 8, 16, 32
+INSPECT_PER_TOKEN, INSPECT_STREAMING = 0, 1
+KIND_LITERAL, KIND_REGEX = 0, 1
+ACT_ALLOW, ACT_REDACT, ACT_DROP, ACT_ALERT = 0, 1, 2, 3
+VERDICT_BEGIN_UNKNOWN = 0x10000
 ST_OK, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_INSPECT_DROP = 0, 1, 2, 3, 4
 ST_CODE_MASK, ST_DONE, ST_REDACTED = 0xF, 0x100, 0x200
-E_OVERFLOW, E_AGAIN = -6, -4
+E_OVERFLOW, E_AGAIN, E_DUPCONV, E_PATTERN = -6, -4, -9, -10
 
 u8p, u32p, u64p, i64p = (C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_int64))
 
@@ -18,6 +22,10 @@ class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_records", C.c_uint32), ("max_in_bytes", C.c_uint64),
                 ("max_out_bytes", C.c_uint64), ("ring_slots", C.c_uint32), ("conv_slots", C.c_uint32),
                 ("flags", C.c_uint32)]
+
+
+class Pattern(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("action", C.c_uint32), ("text", C.c_char_p)]
 
 
 class Counters(C.Structure):
@@ -86,6 +94,16 @@ def load_library():
     lib.ssegpu_frame_launch_result.argtypes = [vp, C.POINTER(Counters)]
     lib.ssegpu_launch_count.restype = C.c_uint64
     lib.ssegpu_launch_count.argtypes = [vp]
+    lib.ssegpu_patterns_load.restype = C.c_int
+    lib.ssegpu_patterns_load.argtypes = [vp, C.POINTER(Pattern), C.c_uint32, C.c_uint32]
+    lib.ssegpu_conv_reset.restype = C.c_int
+    lib.ssegpu_conv_reset.argtypes = [vp]
+    lib.ssegpu_inspect_bind.restype = C.c_int
+    lib.ssegpu_inspect_bind.argtypes = [vp, vp, vp, vp]
+    lib.ssegpu_verdict.restype = u32p
+    lib.ssegpu_verdict.argtypes = [vp]
+    lib.ssegpu_match.restype = C.POINTER(C.c_int32)
+    lib.ssegpu_match.argtypes = [vp]
     lib.ssegpu_frame_launch_static.restype = C.c_int
     lib.ssegpu_frame_launch_static.argtypes = [C.c_int, vp, vp, vp, C.c_uint32, C.c_uint32, vp, C.c_uint64, vp, vp, vp, vp, vp]
     lib.ssegpu_static_last_error.restype = C.c_char_p
@@ -128,13 +146,15 @@ class Batch:
         self.conv_slot = np.ctypeslib.as_array(lib.ssegpu_conv_slot(handle), shape=(n,))
         self.n = 0
 
-    def fill(self, arena, off, start_seq=None):
+    def fill(self, arena, off, start_seq=None, conv_slot=None):
         n = len(off) - 1
         total = int(off[n])
         self.in_bytes[:total] = arena[:total]
         self.in_off[: n + 1] = off
         if start_seq is not None:
             self.start_seq[:n] = start_seq
+        if conv_slot is not None:
+            self.conv_slot[:n] = conv_slot
         self.n = n
         return n
 
@@ -150,6 +170,8 @@ class Batch:
         self.out_len = np.ctypeslib.as_array(lib.ssegpu_out_len(self.h), shape=(max(n, 1),))[:n]
         self.status = np.ctypeslib.as_array(lib.ssegpu_status(self.h), shape=(max(n, 1),))[:n]
         self.subj_len = np.ctypeslib.as_array(lib.ssegpu_subj_len(self.h), shape=(max(n, 1),))[:n]
+        self.verdict = np.ctypeslib.as_array(lib.ssegpu_verdict(self.h), shape=(max(n, 1),))[:n]
+        self.match = np.ctypeslib.as_array(lib.ssegpu_match(self.h), shape=(2 * max(n, 1),))[:2 * n].reshape(n, 2)
         total = int(self.out_off[n])
         self.out = np.ctypeslib.as_array(lib.ssegpu_out_bytes(self.h), shape=(max(total, 1),))[:total]
         return self
@@ -161,9 +183,9 @@ class Batch:
 class SseGpu:
     """One context per GPU (ssegpu_init / ssegpu_destroy)."""
 
-    def __init__(self, device=0, max_records=1 << 16, max_in_bytes=1 << 24, max_out_bytes=0, ring_slots=0):
+    def __init__(self, device=0, max_records=1 << 16, max_in_bytes=1 << 24, max_out_bytes=0, ring_slots=0, conv_slots=0):
         self.lib = load_library()
-        self.cfg = Config(device, max_records, max_in_bytes, max_out_bytes, ring_slots, 0, 0)
+        self.cfg = Config(device, max_records, max_in_bytes, max_out_bytes, ring_slots, conv_slots, 0)
         ctx = C.c_void_p()
         rc = self.lib.ssegpu_init(C.byref(self.cfg), C.byref(ctx))
         if rc != 0:
@@ -184,6 +206,17 @@ class SseGpu:
             self.close()
         except Exception:
             pass
+
+    def load_patterns(self, patterns, mode=INSPECT_PER_TOKEN):
+        """patterns: list of (kind, action, text-bytes) -- ssegpu_patterns_load."""
+        arr = (Pattern * len(patterns))(*[Pattern(k, a, t) for k, a, t in patterns])
+        self._check(self.lib.ssegpu_patterns_load(self.ctx, arr, len(patterns), mode))
+
+    def conv_reset(self):
+        self._check(self.lib.ssegpu_conv_reset(self.ctx))
+
+    def inspect_bind(self, d_conv_slot, d_verdict, d_match):
+        self._check(self.lib.ssegpu_inspect_bind(self.ctx, d_conv_slot or None, d_verdict, d_match))
 
     def acquire(self):
         h = C.c_void_p()

@@ -25,6 +25,7 @@
 #include <stdint.h>
 #include "sse_kernels.h"
 #include "sse_record.cuh"
+#include "sse_inspect.cuh"
 
 namespace sse {
 
@@ -169,6 +170,31 @@ __device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uin
     }
 }
 
+// Inspection of one record's token text (out of line, generic pointers).  Streaming mode carries the DFA
+// state of the record's conversation slot; a slot may be touched once per launch (stamped with the launch epoch).
+struct InspectOut { uint32_t verdict; int32_t begin, end; };
+__device__ __noinline__ InspectOut inspect_slow(const FrameArgs& a, const uint8_t* src_base, uint32_t o, uint32_t tok_b, uint32_t tok_e,
+                                                bool done, uint32_t rec) {
+    const InspectDev& t = *a.insp;
+    PtrSrc src{src_base};
+    InspectOut out{0, 0, 0};
+    if (t.mode == INSPECT_STREAMING) {
+        const uint32_t slot = a.conv_slot[rec];
+        if (slot >= a.conv_slots || atomicExch(&a.conv_epoch[slot], a.epoch) == a.epoch) { atomicExch(a.dup_conv, 1u); return out; }
+        InspectResult r = inspect_token(t, src, o + tok_b, o + tok_e, a.conv_state[slot], done);
+        a.conv_state[slot] = r.state;
+        out.verdict = r.verdict; out.begin = r.begin; out.end = r.end;
+    } else {
+        InspectResult r = inspect_token(t, src, o + tok_b, o + tok_e, 0, true);
+        out.verdict = r.verdict; out.begin = r.begin; out.end = r.end;
+    }
+    return out;
+}
+__device__ __noinline__ uint32_t measure_slow(const uint8_t* src_base, uint32_t o, uint32_t L, const Plan* pl, uint32_t op) {
+    PtrSrc src{src_base};
+    return measure_record(src, o, L, *pl, op);
+}
+
 __device__ __forceinline__ uint4 lds128(const uint8_t* p) { return *reinterpret_cast<const uint4*>(p); }
 
 // Staging tile (bytes [0,total) of s_out) -> out[g0, g0+total): coalesced 16-byte stores for the
@@ -207,6 +233,8 @@ __device__ __forceinline__ void copy_out(uint8_t* __restrict__ out, const uint8_
     if (tid >= 32 && tid - 32 < tail) out[gb + (tid - 32)] = s_out[total - tail + (tid - 32)];
 }
 
+// INSPECT is a compile-time switch so that the plain framing kernel carries none of the inspection code's registers.
+template <bool INSPECT>
 __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* s_in = smem;                                   // in_cap + 32 (word reads run up to 24 bytes past a record)
@@ -257,6 +285,35 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
                 Plan sp;
                 st = plan_slow(smem_in ? s_in : a.in + abase, o, L, a.op, my_start, &sp, &len);
                 pl = sp;
+            }
+        }
+
+        // ---- content inspection of the decoded token text (optional) ------------------------
+        if (INSPECT) {
+            InspectOut io{0, 0, 0};
+            if (active && (st & ST_CODE_MASK) == ST_OK) {
+                const uint8_t* sb = smem_in ? s_in : a.in + abase;
+                io = inspect_slow(a, sb, o, pl.tok_b, pl.tok_e, (st & ST_DONE) != 0, r0 + tid);
+                if (a.op & OP_INSPECT_INLINE) {                               // sse_handler.go:200-207
+                    const uint32_t act = io.verdict & 0xFF;
+                    if (act == ACT_DROP) { st = ST_INSPECT_DROP; len = 0; }
+                    else if (act == ACT_REDACT) {
+                        Plan sp = pl;
+                        if (fastp) {                                          // the canonical path skipped values the encoder now needs
+                            uint32_t unused;
+                            plan_slow(sb, o, L, a.op | OP_NO_FAST, my_start, &sp, &unused);
+                        }
+                        sp.tok_redacted = 1; sp.fast = 0; fastp = false;
+                        pl = sp;
+                        len = measure_slow(sb, o, L, &sp, a.op);
+                        st |= ST_REDACTED;
+                    }
+                }
+            }
+            if (active) {
+                a.verdict[r0 + tid] = io.verdict;
+                a.match[2 * (size_t)(r0 + tid)] = io.begin;
+                a.match[2 * (size_t)(r0 + tid) + 1] = io.end;
             }
         }
 
@@ -386,13 +443,15 @@ cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uin
     // global-memory path inside the same kernel.
     const uint32_t ic = 20 * 1024, oc = 24 * 1024;
     const uint32_t sm = ic + 32 + oc + 48 + (uint32_t)sizeof(TileSmem);
-    cudaError_t e = cudaFuncSetAttribute(k_frame_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    cudaError_t e = cudaFuncSetAttribute(k_frame_tiles<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_frame_tiles<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     if (e != cudaSuccess) return e;
     if (g_num_sms[device] == 0) {
         int sms = 0, per = 0;
         e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles, TILE, sm);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<false>, TILE, sm);
         if (e != cudaSuccess) return e;
         if (per < 1) per = 1;
         g_num_sms[device] = sms;
@@ -414,7 +473,8 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
     if ((int)a.num_tiles < grid) grid = (int)a.num_tiles;
-    k_frame_tiles<<<grid, TILE, smem_bytes, stream>>>(a);
+    if (a.insp != nullptr) k_frame_tiles<true><<<grid, TILE, smem_bytes, stream>>>(a);
+    else k_frame_tiles<false><<<grid, TILE, smem_bytes, stream>>>(a);
     return cudaGetLastError();
 }
 

@@ -6,10 +6,12 @@
 
 namespace sse {
 
+struct InspectDev;               // sse_inspect.cuh
+
 constexpr int TILE = 128;        // records per tile == threads per CTA
 constexpr int CTR_ROWS = 64;     // counter rows (CTA i adds into row i % CTR_ROWS; the host sums rows)
 constexpr int CTR_COLS = 8;      // ok, syntax, type, filtered, done, fast, bytes_in, bytes_out
-constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32
+constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32, [20] duplicate-conversation flag u32
 
 struct FrameArgs {
     const uint8_t* in;           // packed payload arena, 16-byte aligned, 32 readable bytes after the last record
@@ -22,12 +24,22 @@ struct FrameArgs {
     uint32_t* out_len;           // n
     uint32_t* subj_len;          // n or nullptr
     uint32_t* status;            // n
+    // content inspection (nullptr insp = off): tables, per-record conversation slot, carried DFA state per slot,
+    // per-slot launch stamp (a conversation may appear once per streaming batch), outputs
+    const InspectDev* insp;
+    const uint32_t* conv_slot;   // n (streaming mode)
+    uint32_t* conv_state;        // [conv_slots]
+    uint32_t* conv_epoch;        // [conv_slots]
+    uint32_t conv_slots, epoch;
+    uint32_t* verdict;           // n
+    int32_t* match;              // 2n: begin, end (byte offsets into the decoded token text)
     // scratch: one device allocation of scratch_bytes(n), zeroed by frame_launch
     void* scratch_base;
     uint32_t* ticket;
     uint32_t* overflow;
     unsigned long long* cursor;  // arrival-order placement: next free output byte
     uint32_t* done_ctas;
+    uint32_t* dup_conv;
     unsigned long long* counters;
     uint64_t* tile_state;
     // filled by frame_launch
@@ -47,6 +59,7 @@ inline void scratch_carve(void* base, FrameArgs& a) {
     a.overflow = reinterpret_cast<uint32_t*>(p + 4);
     a.cursor = reinterpret_cast<unsigned long long*>(p + 8);
     a.done_ctas = reinterpret_cast<uint32_t*>(p + 16);
+    a.dup_conv = reinterpret_cast<uint32_t*>(p + 20);
     a.counters = reinterpret_cast<unsigned long long*>(p + SCRATCH_HDR);
     a.tile_state = reinterpret_cast<uint64_t*>(p + SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8);
 }

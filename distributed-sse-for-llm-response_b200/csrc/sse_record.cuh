@@ -41,7 +41,7 @@ enum : uint32_t {
     ST_CODE_MASK = 0xF, ST_DONE = 0x100, ST_REDACTED = 0x200,
 };
 // op flags (mirrors include/ssegpu.h)
-enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u, OP_ORDERED = 8u };
+enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u, OP_ORDERED = 8u, OP_INSPECT = 16u, OP_INSPECT_INLINE = 32u };
 
 constexpr uint32_t MAX_NESTING = 10000;            // encoding/json scanner.go maxNestingDepth
 constexpr uint32_t NEST_WORDS = MAX_NESTING / 32 + 1;
@@ -54,6 +54,7 @@ struct Plan {
     uint32_t fast;           // 1: payload is canonical, JSON out == payload bytes
     uint32_t seq_b, seq_n;   // fast only: where the sequence literal sits in the payload (its text IS fmt %d)
     uint32_t cid_esc;        // fast only: the id literal contains a backslash escape (decoded id != raw bytes)
+    uint32_t tok_redacted;   // inline inspection replaced the token text with "[REDACTED]" (sse_handler.go:205-207)
 };
 
 // ---------------------------------------------------------------- accessors ----
@@ -359,7 +360,8 @@ SSE_HD void emit_record(const Src& s, uint32_t o, uint32_t L, const Plan& pl, ui
         SSE_PUT_LIT(w, "{\"conversation_id\":");
         put_json_string(s, o + pl.cid_b, o + pl.cid_e, w, go122);
         SSE_PUT_LIT(w, ",\"token\":");
-        put_json_string(s, o + pl.tok_b, o + pl.tok_e, w, go122);
+        if (pl.tok_redacted) SSE_PUT_LIT(w, "\"[REDACTED]\"");   // RedactedContent of the Spin inspector (lib.rs:73)
+        else put_json_string(s, o + pl.tok_b, o + pl.tok_e, w, go122);
         SSE_PUT_LIT(w, ",\"sequence\":");
         put_int(w, pl.seq);
         SSE_PUT_LIT(w, ",\"done\":");
@@ -605,6 +607,7 @@ template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L
     pl.ts = 0;                                                  // never read for canonical records
     if (!check_canon_tail_int(s, pos, end)) return false;
     pl.fast = 1;
+    pl.tok_redacted = 0;
     pl.cid_esc = cid_esc ? 1u : 0u;   // the bridge subject needs the DECODED id
     (void)tok_esc;
     return true;
@@ -708,7 +711,7 @@ template <class Src> SSE_HD int match_field(const Src& s, uint32_t b, uint32_t e
 template <class Src>
 SSE_HD_NOINLINE uint32_t parse_general(const Src& s, uint32_t o, uint32_t L, Plan& pl, uint32_t* nest) {
     pl.cid_b = pl.cid_e = pl.tok_b = pl.tok_e = 0;
-    pl.seq = 0; pl.ts = 0; pl.done = 0; pl.fast = 0; pl.seq_b = pl.seq_n = 0; pl.cid_esc = 0;
+    pl.seq = 0; pl.ts = 0; pl.done = 0; pl.fast = 0; pl.seq_b = pl.seq_n = 0; pl.cid_esc = 0; pl.tok_redacted = 0;
     enum { BEGIN_VALUE, BEGIN_VALUE_OR_EMPTY, BEGIN_KEY_OR_EMPTY, BEGIN_KEY, END_VALUE };
     uint32_t st = BEGIN_VALUE, depth = 0, pos = o;
     const uint32_t end = o + L;
@@ -842,6 +845,15 @@ SSE_HD void emit_record_fast(const Src& s, uint32_t o, uint32_t L, const Plan& p
         w.put_n_nf(w4("\n\n\0\0"), 2);
     }
     w.finish();
+}
+
+// Output length of an already decoded record (after inline inspection changed the plan).
+template <class Src>
+SSE_HD uint32_t measure_record(const Src& s, uint32_t o, uint32_t L, const Plan& pl, uint32_t op) {
+    Ptr32Dst nd{nullptr};
+    Writer<Ptr32Dst, false> w(nd, 0);
+    emit_record(s, o, L, pl, op, w, nullptr);
+    return (uint32_t)w.pos();
 }
 
 // Pass 1, any record: decode + filter; returns the status word and the output length.

@@ -13,6 +13,8 @@
 #include <vector>
 
 #include "../../include/ssegpu.h"
+#include "inspect_compile.hpp"
+#include "sse_inspect.cuh"
 #include "sse_kernels.h"
 
 namespace {
@@ -42,10 +44,12 @@ struct ssegpu_batch {
     // pinned host
     uint8_t* h_in = nullptr; uint32_t* h_in_off = nullptr; int64_t* h_start = nullptr; uint32_t* h_conv = nullptr;
     uint8_t* h_out = nullptr; uint64_t* h_out_off = nullptr; uint32_t* h_out_len = nullptr; uint32_t* h_status = nullptr; uint32_t* h_subj = nullptr;
+    uint32_t* h_verdict = nullptr; int32_t* h_match = nullptr;
     uint8_t* h_hdr = nullptr;    // scratch header + counter rows read back
     // device
     uint8_t* d_in = nullptr; uint32_t* d_in_off = nullptr; int64_t* d_start = nullptr;
     uint8_t* d_out = nullptr; uint64_t* d_out_off = nullptr; uint32_t* d_out_len = nullptr; uint32_t* d_status = nullptr; uint32_t* d_subj = nullptr;
+    uint32_t* d_conv = nullptr; uint32_t* d_verdict = nullptr; int32_t* d_match = nullptr;
     void* d_scratch = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_done = nullptr;
@@ -61,6 +65,13 @@ struct ssegpu_ctx {
     std::mutex mu;
     ssegpu_counters totals{};
     uint64_t launches = 0;
+    // content inspection
+    void* d_insp_blob = nullptr;          // DFA tables
+    sse::InspectDev* d_insp = nullptr;    // descriptor with device pointers into the blob
+    uint32_t insp_mode = 0, insp_start_state = 0;
+    uint32_t* d_conv_state = nullptr; uint32_t* d_conv_epoch = nullptr;
+    uint32_t epoch = 0;
+    const uint32_t* bound_conv = nullptr; uint32_t* bound_verdict = nullptr; int32_t* bound_match = nullptr;   // ssegpu_inspect_bind
 };
 
 namespace {
@@ -80,7 +91,8 @@ void free_batch(ssegpu_batch* b) {
     if (!b) return;
     cudaFreeHost(b->h_in); cudaFreeHost(b->h_in_off); cudaFreeHost(b->h_start); cudaFreeHost(b->h_conv);
     cudaFreeHost(b->h_out); cudaFreeHost(b->h_out_off); cudaFreeHost(b->h_out_len); cudaFreeHost(b->h_status); cudaFreeHost(b->h_subj);
-    cudaFreeHost(b->h_hdr);
+    cudaFreeHost(b->h_hdr); cudaFreeHost(b->h_verdict); cudaFreeHost(b->h_match);
+    cudaFree(b->d_conv); cudaFree(b->d_verdict); cudaFree(b->d_match);
     cudaFree(b->d_in); cudaFree(b->d_in_off); cudaFree(b->d_start);
     cudaFree(b->d_out); cudaFree(b->d_out_off); cudaFree(b->d_out_len); cudaFree(b->d_status); cudaFree(b->d_subj);
     cudaFree(b->d_scratch);
@@ -106,6 +118,11 @@ int alloc_batch(ssegpu_ctx* ctx, ssegpu_batch** out) {
     CU(cudaHostAlloc(&b->h_status, n * 4 + 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_subj, n * 4 + 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_hdr, sse::scratch_readback_bytes(), cudaHostAllocDefault));
+    CU(cudaHostAlloc(&b->h_verdict, n * 4 + 4, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&b->h_match, n * 8 + 8, cudaHostAllocDefault));
+    CU(cudaMalloc(&b->d_conv, n * 4 + 4));
+    CU(cudaMalloc(&b->d_verdict, n * 4 + 4));
+    CU(cudaMalloc(&b->d_match, n * 8 + 8));
     memset(b->h_in, 0, in_bytes);
     memset(b->h_start, 0, n * 8 + 8);
     memset(b->h_conv, 0, n * 4 + 4);
@@ -143,6 +160,8 @@ const char* ssegpu_strerror(int err) {
     case SSEGPU_E_OVERFLOW: return "output arena too small for this batch";
     case SSEGPU_E_STATE: return "batch used out of order";
     case SSEGPU_E_TIMEOUT: return "timed out";
+    case SSEGPU_E_DUPCONV: return "a conversation slot appears twice in one streaming-inspection batch (or is out of range)";
+    case SSEGPU_E_PATTERN: return "unsupported or malformed inspection pattern (see ssegpu_last_cuda_error for the reason)";
     default: return "unknown error";
     }
 }
@@ -229,6 +248,7 @@ void ssegpu_destroy(ssegpu_ctx* ctx) {
     cudaDeviceSynchronize();
     for (ssegpu_batch* b : ctx->slots) free_batch(b);
     cudaFree(ctx->d_launch_scratch);
+    cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp); cudaFree(ctx->d_conv_state); cudaFree(ctx->d_conv_epoch);
     cudaFreeHost(ctx->h_launch_hdr);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -252,6 +272,8 @@ const uint64_t* ssegpu_out_off(const ssegpu_batch* b) { return b ? b->h_out_off 
 const uint32_t* ssegpu_out_len(const ssegpu_batch* b) { return b ? b->h_out_len : nullptr; }
 const uint32_t* ssegpu_status(const ssegpu_batch* b) { return b ? b->h_status : nullptr; }
 const uint32_t* ssegpu_subj_len(const ssegpu_batch* b) { return b ? b->h_subj : nullptr; }
+const uint32_t* ssegpu_verdict(const ssegpu_batch* b) { return b ? b->h_verdict : nullptr; }
+const int32_t* ssegpu_match(const ssegpu_batch* b) { return b ? b->h_match : nullptr; }
 
 int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t op, int use_filter) {
     if (!ctx || !b || b->ctx != ctx) return SSEGPU_E_INVAL;
@@ -275,7 +297,23 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     a.subj_len = (op & SSEGPU_OP_BRIDGE) ? b->d_subj : nullptr;
     a.status = b->d_status;
     sse::scratch_carve(b->d_scratch, a);
+    const bool inspect = (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) != 0;
+    if (inspect) {
+        if (!ctx->d_insp) return SSEGPU_E_STATE;                  // ssegpu_patterns_load first
+        if (ctx->insp_mode == sse::INSPECT_STREAMING) {
+            if (!ctx->d_conv_state) return SSEGPU_E_STATE;        // conv_slots was 0 at init
+            if (n) CU(cudaMemcpyAsync(b->d_conv, b->h_conv, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+        }
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        a.insp = ctx->d_insp; a.conv_slot = b->d_conv; a.conv_state = ctx->d_conv_state; a.conv_epoch = ctx->d_conv_epoch;
+        a.conv_slots = ctx->cfg.conv_slots; a.epoch = ++ctx->epoch;
+        a.verdict = b->d_verdict; a.match = b->d_match;
+    }
     CU(sse::frame_launch(ctx->cfg.device, a, st));
+    if (inspect && n) {
+        CU(cudaMemcpyAsync(b->h_verdict, b->d_verdict, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(b->h_match, b->d_match, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    }
 
     CU(cudaMemcpyAsync(b->h_out_off, b->d_out_off, ((size_t)n + 1) * 8, cudaMemcpyDeviceToHost, st));
     if (n) CU(cudaMemcpyAsync(b->h_out_len, b->d_out_len, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
@@ -317,7 +355,8 @@ int ssegpu_batch_wait(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t timeout_us) {
     const uint32_t overflow = reinterpret_cast<const uint32_t*>(b->h_hdr)[1];
     b->total_out = b->h_out_off[b->n];
     int rc = SSEGPU_OK;
-    if (overflow) rc = SSEGPU_E_OVERFLOW;
+    if (reinterpret_cast<const uint32_t*>(b->h_hdr)[5]) rc = SSEGPU_E_DUPCONV;
+    else if (overflow) rc = SSEGPU_E_OVERFLOW;
     else if (b->total_out > b->spec_out) {
         CU(cudaMemcpyAsync(b->h_out + b->spec_out, b->d_out + b->spec_out, b->total_out - b->spec_out, cudaMemcpyDeviceToHost, b->stream));
         CU(cudaStreamSynchronize(b->stream));
@@ -356,6 +395,14 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
     a.out = static_cast<uint8_t*>(d_out); a.out_cap = out_cap; a.out_off = d_out_off; a.out_len = d_out_len;
     a.subj_len = d_subj_len; a.status = d_status;
     sse::scratch_carve(ctx->d_launch_scratch, a);
+    if (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) {
+        if (!ctx->d_insp || !ctx->bound_verdict || !ctx->bound_match) return SSEGPU_E_STATE;
+        if (ctx->insp_mode == sse::INSPECT_STREAMING && (!ctx->bound_conv || !ctx->d_conv_state)) return SSEGPU_E_STATE;
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        a.insp = ctx->d_insp; a.conv_slot = ctx->bound_conv; a.conv_state = ctx->d_conv_state; a.conv_epoch = ctx->d_conv_epoch;
+        a.conv_slots = ctx->cfg.conv_slots; a.epoch = ++ctx->epoch;
+        a.verdict = ctx->bound_verdict; a.match = ctx->bound_match;
+    }
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
     CU(sse::frame_launch(ctx->cfg.device, a, st));
     std::lock_guard<std::mutex> lk(ctx->mu);
@@ -368,7 +415,85 @@ int ssegpu_frame_launch_result(ssegpu_ctx* ctx, ssegpu_counters* out) {
     CU(cudaSetDevice(ctx->cfg.device));
     CU(cudaMemcpy(ctx->h_launch_hdr, ctx->d_launch_scratch, sse::scratch_readback_bytes(), cudaMemcpyDeviceToHost));
     if (out) add_rows(ctx->h_launch_hdr, out, 0);
+    if (reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[5]) return SSEGPU_E_DUPCONV;
     return reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[1] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
+}
+
+// ---- content inspection --------------------------------------------------------------------
+int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n, uint32_t mode) {
+    if (!ctx || !pats || mode > 1) return SSEGPU_E_INVAL;
+    CU(cudaSetDevice(ctx->cfg.device));
+    std::vector<sse_inspect::PatternSpec> specs;
+    for (uint32_t i = 0; i < n; i++) specs.push_back({pats[i].kind, pats[i].action, pats[i].text ? pats[i].text : ""});
+    sse_inspect::Compiled c;
+    std::string err;
+    if (!sse_inspect::compile(specs, c, err)) { snprintf(g_cuda_err, sizeof g_cuda_err, "%s", err.c_str()); return SSEGPU_E_PATTERN; }
+    if (c.anchored.size() > sse::INSPECT_MAX_ANCHORED) { snprintf(g_cuda_err, sizeof g_cuda_err, "more than %u variable-length patterns", sse::INSPECT_MAX_ANCHORED); return SSEGPU_E_PATTERN; }
+    // flatten every DFA into one blob: cls[256] | next u16[] | acc_imm | acc_del | acc_eot, 16-byte aligned pieces
+    std::vector<uint8_t> blob;
+    auto put = [&](const void* p, size_t bytes) { size_t off = (blob.size() + 15) & ~(size_t)15; blob.resize(off + bytes); memcpy(blob.data() + off, p, bytes); return off; };
+    struct Off { size_t cls, next, imm, del, eot; };
+    std::vector<const sse_inspect::Dfa*> dfas{&c.forward};
+    for (auto& d : c.anchored) dfas.push_back(&d);
+    std::vector<Off> offs;
+    for (const sse_inspect::Dfa* d : dfas)
+        offs.push_back({put(d->cls, 256), put(d->next.data(), d->next.size() * 2), put(d->acc_imm.data(), d->acc_imm.size() * 4),
+                        put(d->acc_del.data(), d->acc_del.size() * 4), put(d->acc_eot.data(), d->acc_eot.size() * 4)});
+    void* d_blob = nullptr;
+    sse::InspectDev* d_desc = nullptr;
+    CU(cudaMalloc(&d_blob, blob.size()));
+    CU(cudaMemcpy(d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+    sse::InspectDev h{};
+    auto fill = [&](sse::DfaDev& dd, const sse_inspect::Dfa& d, const Off& o) {
+        const uint8_t* base = static_cast<const uint8_t*>(d_blob);
+        dd.cls = base + o.cls; dd.next = reinterpret_cast<const uint16_t*>(base + o.next);
+        dd.acc_imm = reinterpret_cast<const uint32_t*>(base + o.imm); dd.acc_del = reinterpret_cast<const uint32_t*>(base + o.del);
+        dd.acc_eot = reinterpret_cast<const uint32_t*>(base + o.eot);
+        dd.n_classes = d.n_classes; dd.start0 = d.start[0]; dd.start1 = d.start[1];
+    };
+    fill(h.fwd, c.forward, offs[0]);
+    for (size_t k = 0; k < c.anchored.size(); k++) fill(h.anchored[k], c.anchored[k], offs[k + 1]);
+    h.n_patterns = n; h.mode = mode;
+    for (uint32_t i = 0; i < 32; i++) { h.action[i] = 0; h.fixed_len[i] = 0; h.anchored_of[i] = -1; }
+    for (uint32_t i = 0; i < n; i++) {
+        h.action[i] = c.patterns[i].action;
+        h.fixed_len[i] = c.patterns[i].min_len == c.patterns[i].max_len ? c.patterns[i].min_len : 0;
+        h.anchored_of[i] = c.anchored_of[i];
+    }
+    CU(cudaMalloc(&d_desc, sizeof h));
+    CU(cudaMemcpy(d_desc, &h, sizeof h, cudaMemcpyHostToDevice));
+    CU(cudaDeviceSynchronize());                                    // no batch may still be using the old tables
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp);
+    ctx->d_insp_blob = d_blob; ctx->d_insp = d_desc; ctx->insp_mode = mode; ctx->insp_start_state = c.forward.start[0];
+    if (ctx->cfg.conv_slots) {
+        if (!ctx->d_conv_state) {
+            CU(cudaMalloc(&ctx->d_conv_state, (size_t)ctx->cfg.conv_slots * 4));
+            CU(cudaMalloc(&ctx->d_conv_epoch, (size_t)ctx->cfg.conv_slots * 4));
+        }
+        std::vector<uint32_t> init(ctx->cfg.conv_slots, ctx->insp_start_state);
+        CU(cudaMemcpy(ctx->d_conv_state, init.data(), init.size() * 4, cudaMemcpyHostToDevice));
+        CU(cudaMemset(ctx->d_conv_epoch, 0, (size_t)ctx->cfg.conv_slots * 4));
+        ctx->epoch = 0;
+    }
+    return SSEGPU_OK;
+}
+
+int ssegpu_conv_reset(ssegpu_ctx* ctx) {
+    if (!ctx) return SSEGPU_E_INVAL;
+    if (!ctx->d_conv_state) return SSEGPU_OK;
+    CU(cudaSetDevice(ctx->cfg.device));
+    CU(cudaDeviceSynchronize());
+    std::vector<uint32_t> init(ctx->cfg.conv_slots, ctx->insp_start_state);
+    CU(cudaMemcpy(ctx->d_conv_state, init.data(), init.size() * 4, cudaMemcpyHostToDevice));
+    return SSEGPU_OK;
+}
+
+int ssegpu_inspect_bind(ssegpu_ctx* ctx, const uint32_t* d_conv_slot, uint32_t* d_verdict, int32_t* d_match) {
+    if (!ctx) return SSEGPU_E_INVAL;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->bound_conv = d_conv_slot; ctx->bound_verdict = d_verdict; ctx->bound_match = d_match;
+    return SSEGPU_OK;
 }
 
 uint64_t ssegpu_launch_count(ssegpu_ctx* ctx) {

@@ -43,7 +43,9 @@ typedef enum {
     SSEGPU_E_TOOBIG = -5,     /* n_records / bytes exceed the configured capacity */
     SSEGPU_E_OVERFLOW = -6,   /* output arena too small for this batch (nothing truncated silently) */
     SSEGPU_E_STATE = -7,      /* batch used out of order (submit before acquire, ...) */
-    SSEGPU_E_TIMEOUT = -8     /* ssegpu_batch_wait timed out */
+    SSEGPU_E_TIMEOUT = -8,    /* ssegpu_batch_wait timed out */
+    SSEGPU_E_DUPCONV = -9,    /* streaming inspection: a conversation slot occurs twice in one batch / out of range */
+    SSEGPU_E_PATTERN = -10    /* unsupported or malformed inspection pattern */
 } ssegpu_err;
 
 /* ---- per-record status ------------------------------------------------------------- */
@@ -61,6 +63,11 @@ typedef enum {
 #define SSEGPU_OP_BRIDGE    1u   /* subject "chat.<cid>.tokens" + re-marshalled JSON (bridge main.go:160-161) */
 #define SSEGPU_OP_GO122     2u   /* encode 0x08/0x0C as \b \f (Go >= 1.22) instead of Go 1.21's   */
 #define SSEGPU_OP_NO_FAST   4u   /* testing: force every record through the general decoder */
+#define SSEGPU_OP_INSPECT   16u  /* scan the decoded token text with the loaded pattern set; verdicts only (the
+                                    reference's "async" placement, docs/security-inspection-patterns.md:84-140) */
+#define SSEGPU_OP_INSPECT_INLINE 32u /* ... and act on them before framing (sse_handler.go:200-207): verdict drop
+                                    suppresses the frame (status SSEGPU_ST_INSPECT_DROP), redact replaces the token
+                                    text by "[REDACTED]" (status bit SSEGPU_ST_REDACTED), alert changes nothing */
 #define SSEGPU_OP_ORDERED   8u   /* lay the frames out back to back in record order (the arena then equals the
                                     sequential Go output byte for byte).  Default: each tile of 128 consecutive
                                     records lands 16-byte aligned in completion order (<=15 zero bytes between
@@ -134,6 +141,29 @@ int ssegpu_batch_release(ssegpu_ctx *ctx, ssegpu_batch *b);
 
 /* Counters accumulated over all completed batches of this context (host-side gather). */
 int ssegpu_counters_get(ssegpu_ctx *ctx, ssegpu_counters *out);
+
+/* ---- content inspection ------------------------------------------------------------ */
+/* The reference's inspection hook is a comment (sse_handler.go:193-208: callInspector(endpoint, token) ->
+ * {Action, RedactedContent}); its pattern sets are snippets: docs/security-inspection-patterns.md:205-209, :229-234
+ * ("Set A": 3 regexes -> redact, 4 literals -> alert) and src/spin-functions/nats-subscriber/src/lib.rs:59-64,
+ * :79-84 ("Set B": 8 literals -> redact / drop).  Semantics (defined by this project): the DECODED
+ * token text is scanned bytewise; \d [0-9], \w [0-9A-Za-z_], \b on ASCII word bytes; literals fold ASCII case.
+ * kind 0 = literal, 1 = regex subset (atoms, classes, + * ? {n,m}, \b; no groups/alternation).  Up to 32 patterns.
+ * mode 0 = per_token: every token is scanned on its own; the lowest-numbered matching pattern wins.
+ * mode 1 = streaming: the DFA state is carried per conversation slot (ssegpu_conv_slot) across tokens, so patterns
+ *          split over token boundaries are found; the first match to become decidable wins; a conversation may
+ *          occur at most once per batch (SSEGPU_E_DUPCONV otherwise); the done token resets the slot.
+ * verdict word: action (0 allow, 1 redact, 2 drop, 3 alert) | pattern index << 8 | SSEGPU_VERDICT_BEGIN_UNKNOWN.
+ * match[2i], match[2i+1]: begin / end byte offsets into the decoded token text (begin may be negative in streaming
+ * mode; INT32_MIN with SSEGPU_VERDICT_BEGIN_UNKNOWN for variable-length patterns whose start is not recoverable). */
+typedef struct { uint32_t kind; uint32_t action; const char *text; } ssegpu_pattern;
+#define SSEGPU_VERDICT_BEGIN_UNKNOWN 0x10000u
+int ssegpu_patterns_load(ssegpu_ctx *ctx, const ssegpu_pattern *patterns, uint32_t n, uint32_t mode);
+int ssegpu_conv_reset(ssegpu_ctx *ctx);                        /* every conversation slot back to the start state */
+const uint32_t *ssegpu_verdict(const ssegpu_batch *b);         /* n  */
+const int32_t  *ssegpu_match(const ssegpu_batch *b);           /* 2n */
+/* device buffers used by ssegpu_frame_launch when op_flags has SSEGPU_OP_INSPECT[_INLINE] */
+int ssegpu_inspect_bind(ssegpu_ctx *ctx, const uint32_t *d_conv_slot, uint32_t *d_verdict, int32_t *d_match);
 
 /* ---- device-resident launch (kernel-level path, used by the bench and the parity tests) -- */
 /* Same computation as submit, on buffers that already live in this context's GPU memory.

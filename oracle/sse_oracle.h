@@ -84,6 +84,19 @@ int sseo_bridge_batch(const uint8_t *in, const uint32_t *in_off, uint32_t n, int
 double sseo_bench_adapter(const uint8_t *in, const uint32_t *in_off, uint32_t n,
                           int threads, int reps, uint64_t *frames, uint64_t *out_bytes);
 
+/* ---- content inspection (oracle/sse_inspect_oracle.c; semantics in its header comment) ---- */
+typedef struct { uint32_t kind;   /* 0 literal, ASCII case-insensitive; 1 regex subset */
+                 uint32_t action; /* 1 redact, 2 drop, 3 alert */
+                 const char *text; } sseo_pattern;
+typedef struct sseo_inspector sseo_inspector;
+sseo_inspector *sseo_inspect_new(const sseo_pattern *pats, uint32_t n);   /* NULL: unsupported pattern */
+void sseo_inspect_free(sseo_inspector *I);
+/* verdict = action | pattern_id<<8 | (begin unknown ? 1<<16 : 0); 0 = allow */
+void sseo_inspect_token(const sseo_inspector *I, const uint8_t *text, uint32_t len,
+                        uint32_t *verdict, int32_t *begin, int32_t *end);
+void sseo_inspect_stream(const sseo_inspector *I, const uint8_t *stream, uint32_t s, uint32_t t, int done,
+                         uint32_t *verdict, int32_t *begin, int32_t *end);
+
 /* fnv1a64 of the conversation id: the shard function. */
 uint64_t sseo_fnv1a64(const uint8_t *p, size_t n);
 

@@ -43,3 +43,57 @@ extern "C" int hc_batch(const uint8_t* in, const uint32_t* in_off, uint32_t n, c
     if (n_fast) *n_fast = fast;
     return 0;
 }
+
+// ---- inspection: the product's pattern compiler + DFA walk on the CPU (test double, see top of file) ----
+#include "inspect_compile.hpp"
+#include "sse_inspect.cuh"
+
+struct hc_pattern { uint32_t kind, action; const char* text; };
+
+extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode, const uint8_t* in, const uint32_t* in_off,
+                          uint32_t n, const uint32_t* conv_slot, uint32_t conv_slots, uint32_t* verdict, int32_t* match,
+                          uint32_t* status, uint32_t* n_states) {
+    std::vector<sse_inspect::PatternSpec> specs;
+    for (uint32_t i = 0; i < n_pats; i++) specs.push_back({pats[i].kind, pats[i].action, pats[i].text});
+    sse_inspect::Compiled c;
+    std::string err;
+    if (!sse_inspect::compile(specs, c, err)) return -1;
+    InspectDev t{};
+    auto fill = [](DfaDev& dd, const sse_inspect::Dfa& d) {
+        dd.cls = d.cls; dd.next = d.next.data(); dd.acc_imm = d.acc_imm.data(); dd.acc_del = d.acc_del.data();
+        dd.acc_eot = d.acc_eot.data(); dd.n_classes = d.n_classes; dd.start0 = d.start[0]; dd.start1 = d.start[1];
+    };
+    fill(t.fwd, c.forward);
+    if (c.anchored.size() > INSPECT_MAX_ANCHORED) return -2;
+    for (size_t k = 0; k < c.anchored.size(); k++) fill(t.anchored[k], c.anchored[k]);
+    t.n_patterns = n_pats; t.mode = mode;
+    for (uint32_t i = 0; i < 32; i++) { t.action[i] = 0; t.fixed_len[i] = 0; t.anchored_of[i] = -1; }
+    for (uint32_t i = 0; i < n_pats; i++) {
+        t.action[i] = c.patterns[i].action;
+        t.fixed_len[i] = c.patterns[i].min_len == c.patterns[i].max_len ? c.patterns[i].min_len : 0;
+        t.anchored_of[i] = c.anchored_of[i];
+    }
+    if (n_states) *n_states = c.forward.n_states;
+    std::vector<uint32_t> state(conv_slots ? conv_slots : 1, c.forward.start[0]);
+    std::vector<uint32_t> nest(NEST_WORDS);
+    PtrSrc src{in};
+    for (uint32_t i = 0; i < n; i++) {
+        Plan pl;
+        uint32_t len = 0;
+        const uint32_t o = in_off[i], L = in_off[i + 1] - in_off[i];
+        uint32_t st = plan_record(src, o, L, 0, 0, pl, nest.data(), len);
+        status[i] = st;
+        verdict[i] = 0; match[2 * i] = 0; match[2 * i + 1] = 0;
+        if ((st & ST_CODE_MASK) != ST_OK) continue;
+        InspectResult r;
+        if (mode == INSPECT_STREAMING) {
+            uint32_t slot = conv_slot[i];
+            r = inspect_token(t, src, o + pl.tok_b, o + pl.tok_e, state[slot], (st & ST_DONE) != 0);
+            state[slot] = r.state;
+        } else {
+            r = inspect_token(t, src, o + pl.tok_b, o + pl.tok_e, 0, true);
+        }
+        verdict[i] = r.verdict; match[2 * i] = r.begin; match[2 * i + 1] = r.end;
+    }
+    return 0;
+}

@@ -19,13 +19,36 @@ def _ptr(a, t):
 
 def load():
     so = os.path.join(HC_DIR, "libhostcheck.so")
-    srcs = [os.path.join(HC_DIR, "hostcheck.cpp"), os.path.join(CSRC, "sse_record.cuh")]
+    srcs = [os.path.join(HC_DIR, "hostcheck.cpp"), os.path.join(CSRC, "sse_record.cuh"), os.path.join(CSRC, "sse_inspect.cuh"),
+            os.path.join(CSRC, "inspect_compile.hpp")]
     if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-fPIC", "-shared", "-I", CSRC, "-o", so, srcs[0]])
     lib = C.CDLL(so)
     lib.hc_batch.restype = C.c_int
     lib.hc_batch.argtypes = [u8p, u32p, C.c_uint32, i64p, C.c_uint32, u8p, C.c_uint64, u64p, u32p, u32p, u32p]
+    lib.hc_inspect.restype = C.c_int
+    lib.hc_inspect.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, u8p, u32p, C.c_uint32, u32p, C.c_uint32, u32p,
+                               C.POINTER(C.c_int32), u32p, u32p]
     return lib
+
+
+class HcPattern(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("action", C.c_uint32), ("text", C.c_char_p)]
+
+
+def inspect(lib, patterns, mode, arena, off, conv_slot=None, conv_slots=0):
+    """patterns: list of (kind, action, text-bytes).  -> (verdict, match[n,2], status, n_states)"""
+    n = len(off) - 1
+    arr = (HcPattern * len(patterns))(*[HcPattern(k, a, t) for k, a, t in patterns])
+    verdict = np.zeros(n, dtype=np.uint32)
+    match = np.zeros(2 * n, dtype=np.int32)
+    status = np.zeros(n, dtype=np.uint32)
+    ns = C.c_uint32(0)
+    cs = None if conv_slot is None else np.ascontiguousarray(conv_slot, dtype=np.uint32)
+    rc = lib.hc_inspect(arr, len(patterns), mode, _ptr(arena, u8p), _ptr(off, u32p), n, _ptr(cs, u32p), conv_slots,
+                        _ptr(verdict, u32p), match.ctypes.data_as(C.POINTER(C.c_int32)), _ptr(status, u32p), C.byref(ns))
+    assert rc == 0, rc
+    return verdict, match.reshape(n, 2), status, ns.value
 
 
 def run(lib, arena, off, start_seq=None, op=0):

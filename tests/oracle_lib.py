@@ -30,6 +30,10 @@ class Oracle:
         lib.sseo_fnv1a64.restype = C.c_uint64
         lib.sseo_fnv1a64.argtypes = [u8p, C.c_size_t]
 
+    def inspector(self, patterns):
+        """patterns: list of (kind, action, text-bytes) -> OracleInspector"""
+        return OracleInspector(self.lib, patterns)
+
     @staticmethod
     def pack(payloads):
         """list[bytes] -> (arena u8, offsets u32[n+1])."""
@@ -75,6 +79,42 @@ class Oracle:
     def fnv1a64(self, b):
         a = np.frombuffer(bytes(b) + b"\0", dtype=np.uint8)
         return self.lib.sseo_fnv1a64(_ptr(a, u8p), len(b))
+
+
+class _Pat(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("action", C.c_uint32), ("text", C.c_char_p)]
+
+
+class OracleInspector:
+    """Brute-force matcher of oracle/sse_inspect_oracle.c."""
+
+    def __init__(self, lib, patterns):
+        self.lib = lib
+        lib.sseo_inspect_new.restype = C.c_void_p
+        lib.sseo_inspect_new.argtypes = [C.c_void_p, C.c_uint32]
+        lib.sseo_inspect_free.argtypes = [C.c_void_p]
+        i32p = C.POINTER(C.c_int32)
+        lib.sseo_inspect_token.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, u32p, i32p, i32p]
+        lib.sseo_inspect_stream.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, u32p, i32p, i32p]
+        self._keep = (_Pat * len(patterns))(*[_Pat(k, a, t) for k, a, t in patterns])
+        self.h = lib.sseo_inspect_new(self._keep, len(patterns))
+        assert self.h, "oracle rejected the pattern set"
+
+    def token(self, text):
+        v, b, e = C.c_uint32(0), C.c_int32(0), C.c_int32(0)
+        self.lib.sseo_inspect_token(self.h, text, len(text), C.byref(v), C.byref(b), C.byref(e))
+        return v.value, b.value, e.value
+
+    def stream(self, text, s, t, done):
+        v, b, e = C.c_uint32(0), C.c_int32(0), C.c_int32(0)
+        self.lib.sseo_inspect_stream(self.h, text, s, t, int(done), C.byref(v), C.byref(b), C.byref(e))
+        return v.value, b.value, e.value
+
+    def __del__(self):
+        try:
+            self.lib.sseo_inspect_free(self.h)
+        except Exception:
+            pass
 
 
 def build():

@@ -29,7 +29,7 @@ pending = []
 in_kernel = False
 for ln in dis.splitlines():
     if ln.startswith(".text."):
-        in_kernel = "k_frame_tiles" in ln
+        in_kernel = "k_frame_tiles" in ln and ("Lb0" in ln or "ILb0" in ln)
     m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
     if m:
         pending.append((os.path.basename(m.group(1)), int(m.group(2))))
