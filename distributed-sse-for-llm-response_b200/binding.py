@@ -6,7 +6,8 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
-OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_ORDERED, OP_INSPECT, OP_INSPECT_INLINE = 0, 1, 2, 4, 8, 16, 32
+OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_ORDERED, OP_INSPECT, OP_INSPECT_INLINE, OP_MATCH = 0, 1, 2, 4, 8, 16, 32, 64
+ST_NO_INTEREST = 5
 INSPECT_PER_TOKEN, INSPECT_STREAMING = 0, 1
 KIND_LITERAL, KIND_REGEX = 0, 1
 ACT_ALLOW, ACT_REDACT, ACT_DROP, ACT_ALERT = 0, 1, 2, 3
@@ -26,6 +27,10 @@ class Config(C.Structure):
 
 class Pattern(C.Structure):
     _fields_ = [("kind", C.c_uint32), ("action", C.c_uint32), ("text", C.c_char_p)]
+
+
+class SubDelta(C.Structure):
+    _fields_ = [("op", C.c_uint32), ("sub_id", C.c_uint32), ("subject", C.c_char_p), ("subject_len", C.c_uint32)]
 
 
 class Counters(C.Structure):
@@ -94,6 +99,16 @@ def load_library():
     lib.ssegpu_frame_launch_result.argtypes = [vp, C.POINTER(Counters)]
     lib.ssegpu_launch_count.restype = C.c_uint64
     lib.ssegpu_launch_count.argtypes = [vp]
+    lib.ssegpu_interest_apply.restype = C.c_int
+    lib.ssegpu_interest_apply.argtypes = [vp, C.POINTER(SubDelta), C.c_uint32]
+    lib.ssegpu_interest_subs.restype = u32p
+    lib.ssegpu_interest_subs.argtypes = [vp, u32p]
+    lib.ssegpu_interest_wild_ids.restype = u32p
+    lib.ssegpu_interest_wild_ids.argtypes = [vp, u32p]
+    lib.ssegpu_sub_span.restype = u32p
+    lib.ssegpu_sub_span.argtypes = [vp]
+    lib.ssegpu_interest_bind.restype = C.c_int
+    lib.ssegpu_interest_bind.argtypes = [vp, vp]
     lib.ssegpu_patterns_load.restype = C.c_int
     lib.ssegpu_patterns_load.argtypes = [vp, C.POINTER(Pattern), C.c_uint32, C.c_uint32]
     lib.ssegpu_conv_reset.restype = C.c_int
@@ -170,6 +185,7 @@ class Batch:
         self.out_len = np.ctypeslib.as_array(lib.ssegpu_out_len(self.h), shape=(max(n, 1),))[:n]
         self.status = np.ctypeslib.as_array(lib.ssegpu_status(self.h), shape=(max(n, 1),))[:n]
         self.subj_len = np.ctypeslib.as_array(lib.ssegpu_subj_len(self.h), shape=(max(n, 1),))[:n]
+        self.sub_span = np.ctypeslib.as_array(lib.ssegpu_sub_span(self.h), shape=(3 * max(n, 1),))[:3 * n].reshape(n, 3)
         self.verdict = np.ctypeslib.as_array(lib.ssegpu_verdict(self.h), shape=(max(n, 1),))[:n]
         self.match = np.ctypeslib.as_array(lib.ssegpu_match(self.h), shape=(2 * max(n, 1),))[:2 * n].reshape(n, 2)
         total = int(self.out_off[n])
@@ -211,6 +227,25 @@ class SseGpu:
         """patterns: list of (kind, action, text-bytes) -- ssegpu_patterns_load."""
         arr = (Pattern * len(patterns))(*[Pattern(k, a, t) for k, a, t in patterns])
         self._check(self.lib.ssegpu_patterns_load(self.ctx, arr, len(patterns), mode))
+
+    def interest_apply(self, deltas):
+        """deltas: list of (op 0 add / 1 del, subscriber id, subject bytes) -- ssegpu_interest_apply."""
+        arr = (SubDelta * max(len(deltas), 1))(*[SubDelta(o, i, s, len(s)) for o, i, s in deltas])
+        self._keep_deltas = arr
+        self._check(self.lib.ssegpu_interest_apply(self.ctx, arr, len(deltas)))
+
+    def interest_subs(self):
+        n = C.c_uint32(0)
+        p = self.lib.ssegpu_interest_subs(self.ctx, C.byref(n))
+        return np.ctypeslib.as_array(p, shape=(max(n.value, 1),))[: n.value].copy()
+
+    def interest_wild_ids(self):
+        n = C.c_uint32(0)
+        p = self.lib.ssegpu_interest_wild_ids(self.ctx, C.byref(n))
+        return np.ctypeslib.as_array(p, shape=(max(n.value, 1),))[: n.value].copy() if n.value else np.zeros(0, np.uint32)
+
+    def interest_bind(self, d_sub_span):
+        self._check(self.lib.ssegpu_interest_bind(self.ctx, d_sub_span))
 
     def conv_reset(self):
         self._check(self.lib.ssegpu_conv_reset(self.ctx))

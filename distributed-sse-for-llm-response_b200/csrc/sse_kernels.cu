@@ -26,6 +26,7 @@
 #include "sse_kernels.h"
 #include "sse_record.cuh"
 #include "sse_inspect.cuh"
+#include "sse_interest.cuh"
 
 namespace sse {
 
@@ -190,6 +191,10 @@ __device__ __noinline__ InspectOut inspect_slow(const FrameArgs& a, const uint8_
     }
     return out;
 }
+__device__ __noinline__ InterestHit interest_slow(const FrameArgs& a, const uint8_t* src_base, uint32_t o, uint32_t cid_b, uint32_t cid_e) {
+    PtrSrc src{src_base};
+    return interest_lookup(*a.interest, src, o + cid_b, o + cid_e);
+}
 __device__ __noinline__ uint32_t measure_slow(const uint8_t* src_base, uint32_t o, uint32_t L, const Plan* pl, uint32_t op) {
     PtrSrc src{src_base};
     return measure_record(src, o, L, *pl, op);
@@ -233,8 +238,9 @@ __device__ __forceinline__ void copy_out(uint8_t* __restrict__ out, const uint8_
     if (tid >= 32 && tid - 32 < tail) out[gb + (tid - 32)] = s_out[total - tail + (tid - 32)];
 }
 
-// INSPECT is a compile-time switch so that the plain framing kernel carries none of the inspection code's registers.
-template <bool INSPECT>
+// EXT is a compile-time switch so that the plain framing kernel carries none of the registers of the optional
+// stages (content inspection, interest lookup).
+template <bool EXT>
 __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* s_in = smem;                                   // in_cap + 32 (word reads run up to 24 bytes past a record)
@@ -289,7 +295,7 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
         }
 
         // ---- content inspection of the decoded token text (optional) ------------------------
-        if (INSPECT) {
+        if (EXT && a.insp != nullptr) {                                       // launch-uniform
             InspectOut io{0, 0, 0};
             if (active && (st & ST_CODE_MASK) == ST_OK) {
                 const uint8_t* sb = smem_in ? s_in : a.in + abase;
@@ -314,6 +320,19 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
                 a.verdict[r0 + tid] = io.verdict;
                 a.match[2 * (size_t)(r0 + tid)] = io.begin;
                 a.match[2 * (size_t)(r0 + tid) + 1] = io.end;
+            }
+        }
+
+        // ---- subject -> subscriber/interest table (optional) ---------------------------------
+        if (EXT && a.interest != nullptr) {                                   // launch-uniform
+            InterestHit h{0, 0, 0};
+            if (active && (st & ST_CODE_MASK) == ST_OK) {
+                h = interest_slow(a, smem_in ? s_in : a.in + abase, o, pl.cid_b, pl.cid_e);
+                if (h.list_cnt == 0 && h.wild_mask == 0) { st = ST_NO_INTEREST; len = 0; }   // nobody subscribed: nothing to frame
+            }
+            if (active) {
+                const size_t k = 3 * (size_t)(r0 + tid);
+                a.hit[k] = h.list_off; a.hit[k + 1] = h.list_cnt; a.hit[k + 2] = h.wild_mask;
             }
         }
 
@@ -473,7 +492,7 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
     if ((int)a.num_tiles < grid) grid = (int)a.num_tiles;
-    if (a.insp != nullptr) k_frame_tiles<true><<<grid, TILE, smem_bytes, stream>>>(a);
+    if (a.insp != nullptr || a.interest != nullptr) k_frame_tiles<true><<<grid, TILE, smem_bytes, stream>>>(a);
     else k_frame_tiles<false><<<grid, TILE, smem_bytes, stream>>>(a);
     return cudaGetLastError();
 }

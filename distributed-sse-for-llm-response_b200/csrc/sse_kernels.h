@@ -7,6 +7,7 @@
 namespace sse {
 
 struct InspectDev;               // sse_inspect.cuh
+struct InterestDev;              // sse_interest.cuh
 
 constexpr int TILE = 128;        // records per tile == threads per CTA
 constexpr int CTR_ROWS = 64;     // counter rows (CTA i adds into row i % CTR_ROWS; the host sums rows)
@@ -33,6 +34,9 @@ struct FrameArgs {
     uint32_t conv_slots, epoch;
     uint32_t* verdict;           // n
     int32_t* match;              // 2n: begin, end (byte offsets into the decoded token text)
+    // subscriber/interest table (nullptr = off): per record (CSR offset, count, wildcard mask)
+    const InterestDev* interest;
+    uint32_t* hit;               // 3n
     // scratch: one device allocation of scratch_bytes(n), zeroed by frame_launch
     void* scratch_base;
     uint32_t* ticket;

@@ -37,11 +37,11 @@ namespace sse {
 
 // status word (mirrors include/ssegpu.h)
 enum : uint32_t {
-    ST_OK = 0, ST_ERR_SYNTAX = 1, ST_ERR_TYPE = 2, ST_FILTERED = 3, ST_INSPECT_DROP = 4,
+    ST_OK = 0, ST_ERR_SYNTAX = 1, ST_ERR_TYPE = 2, ST_FILTERED = 3, ST_INSPECT_DROP = 4, ST_NO_INTEREST = 5,
     ST_CODE_MASK = 0xF, ST_DONE = 0x100, ST_REDACTED = 0x200,
 };
 // op flags (mirrors include/ssegpu.h)
-enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u, OP_ORDERED = 8u, OP_INSPECT = 16u, OP_INSPECT_INLINE = 32u };
+enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u, OP_ORDERED = 8u, OP_INSPECT = 16u, OP_INSPECT_INLINE = 32u, OP_MATCH = 64u };
 
 constexpr uint32_t MAX_NESTING = 10000;            // encoding/json scanner.go maxNestingDepth
 constexpr uint32_t NEST_WORDS = MAX_NESTING / 32 + 1;

@@ -14,6 +14,7 @@
 
 #include "../../include/ssegpu.h"
 #include "inspect_compile.hpp"
+#include "interest_table.hpp"
 #include "sse_inspect.cuh"
 #include "sse_kernels.h"
 
@@ -44,7 +45,7 @@ struct ssegpu_batch {
     // pinned host
     uint8_t* h_in = nullptr; uint32_t* h_in_off = nullptr; int64_t* h_start = nullptr; uint32_t* h_conv = nullptr;
     uint8_t* h_out = nullptr; uint64_t* h_out_off = nullptr; uint32_t* h_out_len = nullptr; uint32_t* h_status = nullptr; uint32_t* h_subj = nullptr;
-    uint32_t* h_verdict = nullptr; int32_t* h_match = nullptr;
+    uint32_t* h_verdict = nullptr; int32_t* h_match = nullptr; uint32_t* h_hit = nullptr; uint32_t* d_hit = nullptr;
     uint8_t* h_hdr = nullptr;    // scratch header + counter rows read back
     // device
     uint8_t* d_in = nullptr; uint32_t* d_in_off = nullptr; int64_t* d_start = nullptr;
@@ -71,6 +72,10 @@ struct ssegpu_ctx {
     uint32_t insp_mode = 0, insp_start_state = 0;
     uint32_t* d_conv_state = nullptr; uint32_t* d_conv_epoch = nullptr;
     uint32_t epoch = 0;
+    // interest table
+    sse_interest::HostTable interest;
+    void* d_int_slots = nullptr; void* d_int_keys = nullptr; void* d_int_wild = nullptr; sse::InterestDev* d_interest = nullptr;
+    uint32_t* bound_hit = nullptr;
     const uint32_t* bound_conv = nullptr; uint32_t* bound_verdict = nullptr; int32_t* bound_match = nullptr;   // ssegpu_inspect_bind
 };
 
@@ -91,7 +96,7 @@ void free_batch(ssegpu_batch* b) {
     if (!b) return;
     cudaFreeHost(b->h_in); cudaFreeHost(b->h_in_off); cudaFreeHost(b->h_start); cudaFreeHost(b->h_conv);
     cudaFreeHost(b->h_out); cudaFreeHost(b->h_out_off); cudaFreeHost(b->h_out_len); cudaFreeHost(b->h_status); cudaFreeHost(b->h_subj);
-    cudaFreeHost(b->h_hdr); cudaFreeHost(b->h_verdict); cudaFreeHost(b->h_match);
+    cudaFreeHost(b->h_hdr); cudaFreeHost(b->h_verdict); cudaFreeHost(b->h_match); cudaFreeHost(b->h_hit); cudaFree(b->d_hit);
     cudaFree(b->d_conv); cudaFree(b->d_verdict); cudaFree(b->d_match);
     cudaFree(b->d_in); cudaFree(b->d_in_off); cudaFree(b->d_start);
     cudaFree(b->d_out); cudaFree(b->d_out_off); cudaFree(b->d_out_len); cudaFree(b->d_status); cudaFree(b->d_subj);
@@ -123,6 +128,8 @@ int alloc_batch(ssegpu_ctx* ctx, ssegpu_batch** out) {
     CU(cudaMalloc(&b->d_conv, n * 4 + 4));
     CU(cudaMalloc(&b->d_verdict, n * 4 + 4));
     CU(cudaMalloc(&b->d_match, n * 8 + 8));
+    CU(cudaHostAlloc(&b->h_hit, n * 12 + 12, cudaHostAllocDefault));
+    CU(cudaMalloc(&b->d_hit, n * 12 + 12));
     memset(b->h_in, 0, in_bytes);
     memset(b->h_start, 0, n * 8 + 8);
     memset(b->h_conv, 0, n * 4 + 4);
@@ -248,6 +255,7 @@ void ssegpu_destroy(ssegpu_ctx* ctx) {
     cudaDeviceSynchronize();
     for (ssegpu_batch* b : ctx->slots) free_batch(b);
     cudaFree(ctx->d_launch_scratch);
+    cudaFree(ctx->d_int_slots); cudaFree(ctx->d_int_keys); cudaFree(ctx->d_int_wild); cudaFree(ctx->d_interest);
     cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp); cudaFree(ctx->d_conv_state); cudaFree(ctx->d_conv_epoch);
     cudaFreeHost(ctx->h_launch_hdr);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -274,6 +282,7 @@ const uint32_t* ssegpu_status(const ssegpu_batch* b) { return b ? b->h_status : 
 const uint32_t* ssegpu_subj_len(const ssegpu_batch* b) { return b ? b->h_subj : nullptr; }
 const uint32_t* ssegpu_verdict(const ssegpu_batch* b) { return b ? b->h_verdict : nullptr; }
 const int32_t* ssegpu_match(const ssegpu_batch* b) { return b ? b->h_match : nullptr; }
+const uint32_t* ssegpu_sub_span(const ssegpu_batch* b) { return b ? b->h_hit : nullptr; }
 
 int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t op, int use_filter) {
     if (!ctx || !b || b->ctx != ctx) return SSEGPU_E_INVAL;
@@ -309,7 +318,13 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
         a.conv_slots = ctx->cfg.conv_slots; a.epoch = ++ctx->epoch;
         a.verdict = b->d_verdict; a.match = b->d_match;
     }
+    const bool match = (op & SSEGPU_OP_MATCH) != 0;
+    if (match) {
+        if (!ctx->d_interest) return SSEGPU_E_STATE;                  // ssegpu_interest_apply first
+        a.interest = ctx->d_interest; a.hit = b->d_hit;
+    }
     CU(sse::frame_launch(ctx->cfg.device, a, st));
+    if (match && n) CU(cudaMemcpyAsync(b->h_hit, b->d_hit, (size_t)n * 12, cudaMemcpyDeviceToHost, st));
     if (inspect && n) {
         CU(cudaMemcpyAsync(b->h_verdict, b->d_verdict, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
         CU(cudaMemcpyAsync(b->h_match, b->d_match, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
@@ -403,6 +418,10 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
         a.conv_slots = ctx->cfg.conv_slots; a.epoch = ++ctx->epoch;
         a.verdict = ctx->bound_verdict; a.match = ctx->bound_match;
     }
+    if (op & SSEGPU_OP_MATCH) {
+        if (!ctx->d_interest || !ctx->bound_hit) return SSEGPU_E_STATE;
+        a.interest = ctx->d_interest; a.hit = ctx->bound_hit;
+    }
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
     CU(sse::frame_launch(ctx->cfg.device, a, st));
     std::lock_guard<std::mutex> lk(ctx->mu);
@@ -493,6 +512,61 @@ int ssegpu_inspect_bind(ssegpu_ctx* ctx, const uint32_t* d_conv_slot, uint32_t* 
     if (!ctx) return SSEGPU_E_INVAL;
     std::lock_guard<std::mutex> lk(ctx->mu);
     ctx->bound_conv = d_conv_slot; ctx->bound_verdict = d_verdict; ctx->bound_match = d_match;
+    return SSEGPU_OK;
+}
+
+// ---- subscriber / interest table ---------------------------------------------------------------
+int ssegpu_interest_apply(ssegpu_ctx* ctx, const ssegpu_sub_delta* d, uint32_t n) {
+    if (!ctx || (n && !d)) return SSEGPU_E_INVAL;
+    CU(cudaSetDevice(ctx->cfg.device));
+    std::string err;
+    for (uint32_t i = 0; i < n; i++) {
+        if (!d[i].subject) return SSEGPU_E_INVAL;
+        std::string subj(d[i].subject, d[i].subject_len);
+        if (d[i].op == 0) { if (!ctx->interest.add(subj, d[i].sub_id, err)) { snprintf(g_cuda_err, sizeof g_cuda_err, "%s", err.c_str()); return SSEGPU_E_TOOBIG; } }
+        else if (d[i].op == 1) ctx->interest.del(subj, d[i].sub_id);
+        else return SSEGPU_E_INVAL;
+    }
+    sse_interest::HostTable& t = ctx->interest;
+    t.flatten();
+    void *ds = nullptr, *dk = nullptr, *dw = nullptr;
+    sse::InterestDev* dd = nullptr;
+    CU(cudaMalloc(&ds, t.slots.size() * sizeof(sse::InterestSlot)));
+    CU(cudaMalloc(&dk, t.keys.size()));
+    CU(cudaMalloc(&dw, t.wild_bytes.size()));
+    CU(cudaMalloc(&dd, sizeof(sse::InterestDev)));
+    CU(cudaMemcpy(ds, t.slots.data(), t.slots.size() * sizeof(sse::InterestSlot), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dk, t.keys.data(), t.keys.size(), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dw, t.wild_bytes.data(), t.wild_bytes.size(), cudaMemcpyHostToDevice));
+    sse::InterestDev h{};
+    h.slots = static_cast<const sse::InterestSlot*>(ds); h.keys = static_cast<const uint8_t*>(dk);
+    h.mask = (uint32_t)t.slots.size() - 1; h.n_wild = (uint32_t)t.wild_ids.size();
+    h.wild_bytes = static_cast<const uint8_t*>(dw);
+    for (size_t i = 0; i < t.wild_off.size(); i++) h.wild_off[i] = t.wild_off[i];
+    CU(cudaMemcpy(dd, &h, sizeof h, cudaMemcpyHostToDevice));
+    CU(cudaDeviceSynchronize());                                   // versioned swap: no batch may still read the old table
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaFree(ctx->d_int_slots); cudaFree(ctx->d_int_keys); cudaFree(ctx->d_int_wild); cudaFree(ctx->d_interest);
+    ctx->d_int_slots = ds; ctx->d_int_keys = dk; ctx->d_int_wild = dw; ctx->d_interest = dd;
+    return SSEGPU_OK;
+}
+
+const uint32_t* ssegpu_interest_subs(ssegpu_ctx* ctx, uint32_t* count) {
+    if (!ctx) return nullptr;
+    if (count) *count = (uint32_t)ctx->interest.subs.size();
+    return ctx->interest.subs.data();
+}
+
+const uint32_t* ssegpu_interest_wild_ids(ssegpu_ctx* ctx, uint32_t* count) {
+    if (!ctx) return nullptr;
+    if (count) *count = (uint32_t)ctx->interest.wild_ids.size();
+    return ctx->interest.wild_ids.data();
+}
+
+int ssegpu_interest_bind(ssegpu_ctx* ctx, uint32_t* d_sub_span) {
+    if (!ctx) return SSEGPU_E_INVAL;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->bound_hit = d_sub_span;
     return SSEGPU_OK;
 }
 

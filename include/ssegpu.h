@@ -54,6 +54,7 @@ typedef enum {
 #define SSEGPU_ST_ERR_TYPE      2u  /* json.Unmarshal type error: dropped                        */
 #define SSEGPU_ST_FILTERED      3u  /* Last-Event-ID filter (sse_handler.go:142-145)             */
 #define SSEGPU_ST_INSPECT_DROP  4u  /* inline inspection verdict "drop" (sse_handler.go:200-204) */
+#define SSEGPU_ST_NO_INTEREST   5u  /* SSEGPU_OP_MATCH: no subscription matches the record's subject    */
 #define SSEGPU_ST_CODE_MASK     0xFu
 #define SSEGPU_ST_DONE          0x100u
 #define SSEGPU_ST_REDACTED      0x200u
@@ -68,6 +69,9 @@ typedef enum {
 #define SSEGPU_OP_INSPECT_INLINE 32u /* ... and act on them before framing (sse_handler.go:200-207): verdict drop
                                     suppresses the frame (status SSEGPU_ST_INSPECT_DROP), redact replaces the token
                                     text by "[REDACTED]" (status bit SSEGPU_ST_REDACTED), alert changes nothing */
+#define SSEGPU_OP_MATCH     64u  /* look the record's subject chat.<cid>.tokens up in the interest table: per record a span of
+                                    subscriber ids (ssegpu_sub_span); records nobody subscribed to are not framed
+                                    (status SSEGPU_ST_NO_INTEREST) */
 #define SSEGPU_OP_ORDERED   8u   /* lay the frames out back to back in record order (the arena then equals the
                                     sequential Go output byte for byte).  Default: each tile of 128 consecutive
                                     records lands 16-byte aligned in completion order (<=15 zero bytes between
@@ -164,6 +168,21 @@ const uint32_t *ssegpu_verdict(const ssegpu_batch *b);         /* n  */
 const int32_t  *ssegpu_match(const ssegpu_batch *b);           /* 2n */
 /* device buffers used by ssegpu_frame_launch when op_flags has SSEGPU_OP_INSPECT[_INLINE] */
 int ssegpu_inspect_bind(ssegpu_ctx *ctx, const uint32_t *d_conv_slot, uint32_t *d_verdict, int32_t *d_match);
+
+/* ---- subscriber / interest table ---------------------------------------------------- */
+/* Replaces, for this path, the subscription matching that the reference delegates to nats.go / nats-server:
+ * nc.Subscribe("chat.<id>.tokens", cb) per connection (sse_handler.go:133-135, :314-316), wildcard consumers such
+ * as chat.*.tokens (docs/security-inspection-patterns.md:110,268).  NATS subject rules: '.'-separated tokens, '*' = one
+ * token, '>' = the rest.  ssegpu_interest_apply adds (op 0) / removes (op 1) (subject, subscriber id) pairs and swaps
+ * the device table in (synchronous).  With SSEGPU_OP_MATCH every record gets three words in ssegpu_sub_span():
+ * [3i] offset and [3i+1] count of its subscriber ids inside ssegpu_interest_subs(), [3i+2] bit mask over
+ * ssegpu_interest_wild_ids() of the wildcard subscriptions that match.  At most 32 wildcard subscriptions. */
+typedef struct { uint32_t op; uint32_t sub_id; const char *subject; uint32_t subject_len; } ssegpu_sub_delta;
+int ssegpu_interest_apply(ssegpu_ctx *ctx, const ssegpu_sub_delta *deltas, uint32_t n);
+const uint32_t *ssegpu_interest_subs(ssegpu_ctx *ctx, uint32_t *count);      /* host copy, valid until the next apply */
+const uint32_t *ssegpu_interest_wild_ids(ssegpu_ctx *ctx, uint32_t *count);
+const uint32_t *ssegpu_sub_span(const ssegpu_batch *b);                      /* 3n */
+int ssegpu_interest_bind(ssegpu_ctx *ctx, uint32_t *d_sub_span);             /* buffer used by ssegpu_frame_launch */
 
 /* ---- device-resident launch (kernel-level path, used by the bench and the parity tests) -- */
 /* Same computation as submit, on buffers that already live in this context's GPU memory.

@@ -33,6 +33,7 @@ extern "C" {
 #define SSEO_ERR_TYPE      2u   /* json.Unmarshal type error    -> message dropped   */
 #define SSEO_FILTERED      3u   /* /stream Last-Event-ID filter -> message skipped   */
 #define SSEO_INSPECT_DROP  4u   /* inline inspection said drop  -> message skipped   */
+#define SSEO_NO_INTEREST   5u   /* no subscription matches the subject               */
 #define SSEO_CODE_MASK     0xFu
 #define SSEO_DONE          0x100u /* decoded done==true and the record was emitted    */
 #define SSEO_REDACTED      0x200u /* inline inspection replaced the token text       */

@@ -97,3 +97,44 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
     }
     return 0;
 }
+
+// ---- interest table: host builder + HD lookup on the CPU (test double) ----
+#include "interest_table.hpp"
+
+struct hc_delta { uint32_t op, sub_id; const char* subject; uint32_t subject_len; };
+
+extern "C" int hc_interest(const hc_delta* d, uint32_t nd, const uint8_t* in, const uint32_t* in_off, uint32_t n, uint32_t* hit,
+                           uint32_t* status, uint32_t* subs_out, uint32_t subs_cap, uint32_t* n_subs, uint32_t* wild_ids_out, uint32_t* n_wild) {
+    sse_interest::HostTable t;
+    std::string err;
+    for (uint32_t i = 0; i < nd; i++) {
+        std::string s(d[i].subject, d[i].subject_len);
+        if (d[i].op == 0) { if (!t.add(s, d[i].sub_id, err)) return -1; } else t.del(s, d[i].sub_id);
+    }
+    t.flatten();
+    if (t.subs.size() > subs_cap) return -2;
+    memcpy(subs_out, t.subs.data(), t.subs.size() * 4);
+    *n_subs = (uint32_t)t.subs.size();
+    memcpy(wild_ids_out, t.wild_ids.data(), t.wild_ids.size() * 4);
+    *n_wild = (uint32_t)t.wild_ids.size();
+    InterestDev dev{};
+    dev.slots = t.slots.data(); dev.keys = t.keys.data(); dev.mask = (uint32_t)t.slots.size() - 1;
+    dev.n_wild = (uint32_t)t.wild_ids.size(); dev.wild_bytes = t.wild_bytes.data();
+    for (size_t i = 0; i < t.wild_off.size(); i++) dev.wild_off[i] = t.wild_off[i];
+    std::vector<uint32_t> nest(NEST_WORDS);
+    PtrSrc src{in};
+    for (uint32_t i = 0; i < n; i++) {
+        Plan pl;
+        uint32_t len = 0;
+        const uint32_t o = in_off[i], L = in_off[i + 1] - in_off[i];
+        uint32_t st = plan_record(src, o, L, OP_BRIDGE, 0, pl, nest.data(), len);
+        hit[3 * i] = hit[3 * i + 1] = hit[3 * i + 2] = 0;
+        if ((st & ST_CODE_MASK) == ST_OK) {
+            InterestHit h = interest_lookup(dev, src, o + pl.cid_b, o + pl.cid_e);
+            hit[3 * i] = h.list_off; hit[3 * i + 1] = h.list_cnt; hit[3 * i + 2] = h.wild_mask;
+            if (h.list_cnt == 0 && h.wild_mask == 0) st = ST_NO_INTEREST;
+        }
+        status[i] = st;
+    }
+    return 0;
+}

@@ -20,7 +20,7 @@ def _ptr(a, t):
 def load():
     so = os.path.join(HC_DIR, "libhostcheck.so")
     srcs = [os.path.join(HC_DIR, "hostcheck.cpp"), os.path.join(CSRC, "sse_record.cuh"), os.path.join(CSRC, "sse_inspect.cuh"),
-            os.path.join(CSRC, "inspect_compile.hpp")]
+            os.path.join(CSRC, "inspect_compile.hpp"), os.path.join(CSRC, "sse_interest.cuh"), os.path.join(CSRC, "interest_table.hpp")]
     if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-fPIC", "-shared", "-I", CSRC, "-o", so, srcs[0]])
     lib = C.CDLL(so)
@@ -30,6 +30,27 @@ def load():
     lib.hc_inspect.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, u8p, u32p, C.c_uint32, u32p, C.c_uint32, u32p,
                                C.POINTER(C.c_int32), u32p, u32p]
     return lib
+
+
+class HcDelta(C.Structure):
+    _fields_ = [("op", C.c_uint32), ("sub_id", C.c_uint32), ("subject", C.c_char_p), ("subject_len", C.c_uint32)]
+
+
+def interest(lib, deltas, arena, off):
+    """deltas: list of (op, sub_id, subject bytes) -> (hit[n,3], status, subs, wild_ids)"""
+    lib.hc_interest.restype = C.c_int
+    lib.hc_interest.argtypes = [C.c_void_p, C.c_uint32, u8p, u32p, C.c_uint32, u32p, u32p, u32p, C.c_uint32, u32p, u32p, u32p]
+    n = len(off) - 1
+    arr = (HcDelta * len(deltas))(*[HcDelta(o, i, s, len(s)) for o, i, s in deltas])
+    hit = np.zeros(3 * n, dtype=np.uint32)
+    status = np.zeros(n, dtype=np.uint32)
+    subs = np.zeros(len(deltas) + 1, dtype=np.uint32)
+    wild = np.zeros(64, dtype=np.uint32)
+    ns, nw = C.c_uint32(0), C.c_uint32(0)
+    rc = lib.hc_interest(arr, len(deltas), _ptr(arena, u8p), _ptr(off, u32p), n, _ptr(hit, u32p), _ptr(status, u32p),
+                         _ptr(subs, u32p), len(subs), C.byref(ns), _ptr(wild, u32p), C.byref(nw))
+    assert rc == 0, rc
+    return hit.reshape(n, 3), status, subs[: ns.value], wild[: nw.value]
 
 
 class HcPattern(C.Structure):

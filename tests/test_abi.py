@@ -31,7 +31,7 @@ def test_every_declared_symbol_is_exported(pkg):
 def test_status_constants_match_oracle_header(pkg):
     h = _header()
     o = open(os.path.join(ROOT, "oracle", "sse_oracle.h")).read()
-    for name in ("OK", "ERR_SYNTAX", "ERR_TYPE", "FILTERED", "INSPECT_DROP", "CODE_MASK", "DONE", "REDACTED"):
+    for name in ("OK", "ERR_SYNTAX", "ERR_TYPE", "FILTERED", "INSPECT_DROP", "NO_INTEREST", "CODE_MASK", "DONE", "REDACTED"):
         a = re.search(r"#define SSEGPU_ST_%s\s+(\w+)" % name, h).group(1)
         b = re.search(r"#define SSEO_%s\s+(\w+)" % name, o).group(1)
         assert int(a.rstrip("u"), 0) == int(b.rstrip("u"), 0), name
