@@ -183,10 +183,13 @@ template <class Dst, bool EMIT> struct Writer {
         : d(dst), wpos(start & ~(pos_t)3), acc(0), sh(((uint32_t)start & 3u) * 8), first((uint32_t)start & 3u) {}
     SSE_HD pos_t pos() const { return wpos + (sh >> 3); }
     SSE_HD void flush_word() {                          // sh >= 32: the word at wpos is complete
-        if (EMIT) {
-            uint32_t v = (uint32_t)acc;
+        if (EMIT) {                                     // straight-line predicated stores: lanes differ in `first`
+            const uint32_t v = (uint32_t)acc;
             if (first == 0) d.st32a(wpos, v);
-            else { for (uint32_t k = first; k < 4; k++) d.st8(wpos + k, (v >> (8 * k)) & 0xFF); first = 0; }
+            if (first != 0 && first <= 1) d.st8(wpos + 1, (v >> 8) & 0xFF);
+            if (first != 0 && first <= 2) d.st8(wpos + 2, (v >> 16) & 0xFF);
+            if (first != 0) d.st8(wpos + 3, v >> 24);
+            first = 0;
         }
         acc >>= 32; sh -= 32; wpos += 4;
     }
@@ -219,11 +222,12 @@ template <class Dst, bool EMIT> struct Writer {
         uint32_t t = (sh >> 3) + n;
         wpos += t & ~3u; sh = (t & 3u) * 8;
     }
-    SSE_HD void finish() {                              // trailing partial word
-        uint32_t k1 = sh >> 3;
-        if (EMIT && k1) {
-            uint32_t v = (uint32_t)acc;
-            for (uint32_t k = first; k < k1; k++) d.st8(wpos + k, (v >> (8 * k)) & 0xFF);
+    SSE_HD void finish() {                              // trailing partial word: bytes [first, sh/8)
+        if (EMIT) {
+            const uint32_t k1 = sh >> 3, v = (uint32_t)acc;
+            if (first == 0 && k1 >= 1) d.st8(wpos, v & 0xFF);
+            if (first <= 1 && k1 >= 2) d.st8(wpos + 1, (v >> 8) & 0xFF);
+            if (first <= 2 && k1 >= 3) d.st8(wpos + 2, (v >> 16) & 0xFF);
         }
     }
 };
@@ -416,45 +420,55 @@ SSE_HD bool canon_u_escape(uint32_t h, bool go122) {           // h = the four h
     return false;
 }
 
-// Scans a canonical string body starting at pos (just after the opening quote); on success
-// pos is left ON the closing quote.  Fails (false) on anything json.Marshal would not have
-// produced verbatim -- the general path then decides what it really is.
+// The canonical path is written SINGLE-EXIT: no early returns, failures only clear an `ok` flag and the code
+// runs on (positions clamped to the record end, so every read stays inside the padded tile).  With early
+// returns the lanes of a warp that leave a variable-length loop at different trips never reconverge (the
+// only common post-dominator is the end of the function) and everything after the first string -- literal
+// compares, both integers, the emission set-up -- ran at half the lanes (ncu r01: 16.0 active threads).
+
+// Scans a canonical string body starting at pos (just after the opening quote); on success pos is left ON
+// the closing quote.  Fails on anything json.Marshal would not have produced verbatim -- the general path
+// then decides what it really is.
 template <class Src> SSE_HD bool scan_canon_string(const Src& s, uint32_t& pos, uint32_t end, bool go122, bool& has_esc) {
-    for (;;) {
-        // word loop: one aligned load per 4 bytes, the previous word is carried
+    bool ok = true, fin = false;
+    while (!fin) {
+        // word loop: one aligned load per 4 bytes, the previous words are carried, the next trip's are in flight
         uint32_t a = pos & ~3u;
         const uint32_t shb = (pos & 3u) * 8;
-        uint32_t lo = s.ld32a(a), h1 = s.ld32a(a + 4), h2 = s.ld32a(a + 8), w, m;
-        for (;;) {                                              // 8 bytes per trip, next trip's words already in flight
-            if (pos >= end) return false;
+        uint32_t lo = s.ld32a(a), h1 = s.ld32a(a + 4), h2 = s.ld32a(a + 8), w = 0, m = 0;
+        while (pos < end) {                                     // 8 bytes per trip
             const uint32_t n1 = s.ld32a(a + 12), n2 = s.ld32a(a + 16);
             const uint32_t wa = funnel_r(lo, h1, shb), wb = funnel_r(h1, h2, shb);
             const uint32_t ma = special_mask(wa), mb = special_mask(wb);
-            if ((ma | mb) == 0) { lo = h2; h1 = n1; h2 = n2; a += 8; pos += 8; continue; }
-            if (ma) { w = wa; m = ma; } else { w = wb; m = mb; pos += 4; }
-            break;
+            if (ma | mb) {
+                const bool first = ma != 0;
+                w = first ? wa : wb; m = first ? ma : mb; pos += first ? 0u : 4u;
+                break;
+            }
+            lo = h2; h1 = n1; h2 = n2; a += 8; pos += 8;
         }
-        const uint32_t k = first_byte_idx(m);
-        pos += k;
-        const uint32_t c = (w >> (8 * k)) & 0xFF;
-        if (c == '"') return pos < end;
-        if (c == '\\') {
-            has_esc = true;
-            uint32_t e = s.ld8(pos + 1);
-            if (e == '"' || e == '\\' || e == 'n' || e == 'r' || e == 't' || (go122 && (e == 'b' || e == 'f'))) { pos += 2; continue; }
-            if (e != 'u' || !canon_u_escape(ld32u(s, pos + 2), go122)) return false;
-            pos += 6;
-            continue;
+        if (m == 0) { ok = false; fin = true; }                 // ran off the record without a closing quote
+        else {
+            const uint32_t k = first_byte_idx(m);
+            pos += k;
+            const uint32_t c = (w >> (8 * k)) & 0xFF;
+            if (c == '"') { ok = pos < end; fin = true; }
+            else if (c == '\\') {
+                has_esc = true;
+                const uint32_t e = s.ld8(pos + 1);
+                if (e == '"' || e == '\\' || e == 'n' || e == 'r' || e == 't' || (go122 && (e == 'b' || e == 'f'))) pos += 2;
+                else if (e == 'u' && canon_u_escape(ld32u(s, pos + 2), go122)) pos += 6;
+                else { ok = false; fin = true; }
+            } else if (c >= 0x80) {                             // raw multi-byte UTF-8: decoded == raw
+                uint32_t r;
+                const uint32_t n = utf8_decode(s, pos, end, r);
+                if (n == 1 || r == 0x2028 || r == 0x2029) { ok = false; fin = true; }
+                else pos += n;
+            } else { ok = false; fin = true; }                  // control byte, or < > & raw
         }
-        if (c >= 0x80) {                                        // raw multi-byte UTF-8: decoded == raw
-            uint32_t r;
-            uint32_t n = utf8_decode(s, pos, end, r);
-            if (n == 1 || r == 0x2028 || r == 0x2029) return false;
-            pos += n;
-            continue;
-        }
-        return false;                                           // control byte, or < > & raw
     }
+    if (pos > end) pos = end;
+    return ok;
 }
 
 // four ASCII digits (first digit in the low byte) -> value
@@ -464,80 +478,56 @@ SSE_HD uint32_t digits4(uint32_t w) {
     return (t & 0xFF) * 100 + ((t >> 16) & 0xFF);
 }
 
-// canonical integer literal: -?(0|[1-9][0-9]*), at most 19 digits and certainly inside int64
-// (a 19-digit literal starting with '9' is left to the general path, which does the exact
-// range check).  Leaves pos just past the literal.  The VALUE is produced only when
-// want_value (sequence: needed by the filter and the slow emitter) and then only for <= 8
-// digits; longer sequences also go to the general path.  Word-at-a-time digit test on
-// aligned loads.
-template <class Src> SSE_HD bool scan_canon_int(const Src& s, uint32_t& pos, uint32_t end, bool want_value, int64_t& out) {
+// canonical integer literal with a value: -?(0|[1-9][0-9]*) of at most 8 digits (sequence numbers; longer
+// ones go to the general path, which parses any int64).  Leaves pos just past the literal.
+template <class Src> SSE_HD bool scan_canon_int(const Src& s, uint32_t& pos, uint32_t end, int64_t& out) {
     const uint32_t a = pos & ~3u, shb = (pos & 3u) * 8;
-    uint32_t x0 = s.ld32a(a), x1 = s.ld32a(a + 4), x2 = s.ld32a(a + 8);
+    const uint32_t x0 = s.ld32a(a), x1 = s.ld32a(a + 4), x2 = s.ld32a(a + 8), x3 = s.ld32a(a + 12);
     uint32_t w0 = funnel_r(x0, x1, shb), w1 = funnel_r(x1, x2, shb);
+    const uint32_t w2 = funnel_r(x2, x3, shb);
     const uint32_t neg = ((w0 & 0xFF) == '-') ? 1u : 0u;
-    if (neg) {                                                  // drop the sign byte (rare)
-        uint32_t x3 = s.ld32a(a + 12);
-        w0 = funnel_r(w0, w1, 8); w1 = funnel_r(w1, funnel_r(x2, x3, shb), 8);
-    }
+    if (neg) { w0 = funnel_r(w0, w1, 8); w1 = funnel_r(w1, w2, 8); }             // drop the sign byte
     const uint32_t start = pos + neg;
-    uint32_t nd;
-    uint32_t m = nondigit_mask(w0);
-    if (m) nd = first_byte_idx(m);
-    else {
-        m = nondigit_mask(w1);
-        if (m) nd = 4 + first_byte_idx(m);
-        else {                                                  // 8+ digits: timestamps
-            nd = 8;
-            uint32_t p = start + 8;
-#if defined(__CUDACC__)
-#pragma unroll 1
-#endif
-            for (uint32_t i = 0; i < 3; i++, p += 4) {
-                m = nondigit_mask(ld32u(s, p));
-                if (m) { nd += first_byte_idx(m); break; }
-                nd += 4;
-            }
-        }
-    }
-    if (nd == 0 || nd > 19 || start + nd > end) return false;
+    const uint32_t m0 = nondigit_mask(w0), m1 = nondigit_mask(w1);
+    const uint32_t nd = m0 ? first_byte_idx(m0) : (m1 ? 4 + first_byte_idx(m1) : 9);   // 9 = "more than 8"
     const uint32_t d0 = w0 & 0xFF;
-    if (d0 == '0' && (nd != 1 || neg)) return false;            // leading zero, "-0"
-    if (nd == 19 && d0 == '9') return false;                    // might overflow: exact check in the general path
-    pos = start + nd;
-    if (want_value) {
-        if (nd > 8) return false;
-        uint32_t v;
-        // right-align the digits inside 4-digit groups: missing leading digits become zeros
-        if (nd <= 4) v = digits4(w0 << (8 * (4 - nd)));
-        else {
-            const uint32_t k = nd - 4;                          // 1..4 digits in the leading group
-            const uint32_t hi = digits4(w0 << (8 * (4 - k)));   // first k digits
-            const uint32_t lo4 = funnel_r(w0, w1, 8 * k);       // next four digits (k = 4: shift 32 == w1)
-            v = hi * 10000 + digits4(k == 4 ? w1 : lo4);
-        }
-        out = neg ? -(int64_t)v : (int64_t)v;
-    }
-    return true;
+    bool ok = nd >= 1 && nd <= 8 && start + nd <= end;
+    ok = ok && !(d0 == '0' && (nd != 1 || neg));                // leading zero, "-0"
+    const uint32_t ndc = nd > 8 ? 8 : (nd < 1 ? 1 : nd);
+    // right-align the digits inside 4-digit groups: missing leading digits become zeros
+    const uint32_t k = ndc > 4 ? ndc - 4 : ndc;                 // digits in the leading group (1..4)
+    const uint32_t hi = digits4(w0 << (8 * (4 - k)));
+    const uint32_t lo4 = k == 4 ? w1 : funnel_r(w0, w1, 8 * k);
+    const uint32_t v = ndc > 4 ? hi * 10000 + digits4(lo4) : hi;
+    out = neg ? -(int64_t)v : (int64_t)v;
+    pos = start + ndc;
+    if (pos > end) pos = end;
+    return ok;
 }
 
 // The timestamp literal is the record's tail: it occupies [pos, end-1) and '}' sits at end-1.
 // Its value is not needed on the canonical path, only that it IS canonical: six independent
 // aligned loads, five funnel shifts, digit masks -- straight-line, no search loop.
 template <class Src> SSE_HD bool check_canon_tail_int(const Src& s, uint32_t pos, uint32_t end) {
-    const uint32_t neg = (s.ld8(pos) == '-') ? 1u : 0u;
-    const uint32_t start = pos + neg, lim = end - 1;
-    if (start >= lim) return false;
-    const uint32_t nd = lim - start;
-    if (nd > 19) return false;
-    const uint32_t a = start & ~3u, shb = (start & 3u) * 8;
+    const uint32_t lim = end - 1;
+    const uint32_t a = pos & ~3u, shb = (pos & 3u) * 8;
     const uint32_t x0 = s.ld32a(a), x1 = s.ld32a(a + 4), x2 = s.ld32a(a + 8), x3 = s.ld32a(a + 12), x4 = s.ld32a(a + 16),
                    x5 = s.ld32a(a + 20);
-    const uint32_t w0 = funnel_r(x0, x1, shb);
-    const uint32_t d0 = w0 & 0xFF;
-    if (d0 == '0' && (nd != 1 || neg)) return false;            // leading zero, "-0"
-    if (nd == 19 && d0 == '9') return false;                    // might overflow: exact check in the general path
+    uint32_t ws[6] = {funnel_r(x0, x1, shb), funnel_r(x1, x2, shb), funnel_r(x2, x3, shb), funnel_r(x3, x4, shb), funnel_r(x4, x5, shb), x5 >> shb};
+    const uint32_t neg = ((ws[0] & 0xFF) == '-') ? 1u : 0u;
+    if (neg) {                                                  // drop the sign byte (timestamps are positive in practice)
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+        for (int k = 0; k < 5; k++) ws[k] = funnel_r(ws[k], ws[k + 1], 8);
+    }
+    const uint32_t start = pos + neg;
+    const uint32_t nd = lim > start ? lim - start : 0;
+    const uint32_t d0 = ws[0] & 0xFF;
+    bool ok = nd >= 1 && nd <= 19;
+    ok = ok && !(d0 == '0' && (nd != 1 || neg));                // leading zero, "-0"
+    ok = ok && !(nd == 19 && d0 == '9');                        // might overflow: exact check in the general path
     uint32_t bad = 0;
-    const uint32_t ws[5] = {w0, funnel_r(x1, x2, shb), funnel_r(x2, x3, shb), funnel_r(x3, x4, shb), funnel_r(x4, x5, shb)};
 #if defined(__CUDACC__)
 #pragma unroll
 #endif
@@ -546,7 +536,7 @@ template <class Src> SSE_HD bool check_canon_tail_int(const Src& s, uint32_t pos
         const uint32_t keep = c >= 4 ? 0x80808080u : (c > 0 ? (0x80808080u >> (8 * (4 - c))) : 0u);
         bad |= nondigit_mask(ws[k]) & keep;
     }
-    return bad == 0 && s.ld8(lim) == '}';
+    return ok && bad == 0 && s.ld8(lim) == '}';
 }
 
 // three unaligned words at pos with four aligned loads
@@ -559,8 +549,8 @@ template <class Src> SSE_HD void ld3u(const Src& s, uint32_t pos, uint32_t& w0, 
 // True iff the record is byte-for-byte what json.Marshal(TokenMessage) would emit.
 template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, Plan& pl) {
     const bool go122 = (op & OP_GO122) != 0;
-    if (L < 72) return false;
-    const uint32_t end = o + L;
+    bool ok = L >= 72;
+    const uint32_t end = o + (ok ? L : 0u);                     // a too-short record runs through with an empty range
     uint32_t w0, w1, w2, d;
     // {"conversation_id":"   (20 bytes)
     {
@@ -568,49 +558,49 @@ template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L
         uint32_t x0 = s.ld32a(a), x1 = s.ld32a(a + 4), x2 = s.ld32a(a + 8), x3 = s.ld32a(a + 12), x4 = s.ld32a(a + 16), x5 = s.ld32a(a + 20);
         d = (funnel_r(x0, x1, shb) ^ w4("{\"co")) | (funnel_r(x1, x2, shb) ^ w4("nver")) | (funnel_r(x2, x3, shb) ^ w4("sati")) |
             (funnel_r(x3, x4, shb) ^ w4("on_i")) | (funnel_r(x4, x5, shb) ^ w4("d\":\""));
-        if (d) return false;
+        ok = ok && d == 0;
     }
-    uint32_t pos = o + 20;
+    uint32_t pos = ok ? o + 20 : end;
     bool cid_esc = false, tok_esc = false;
     pl.cid_b = 20;
-    if (!scan_canon_string(s, pos, end, go122, cid_esc)) return false;
+    ok = scan_canon_string(s, pos, end, go122, cid_esc) && ok;
     pl.cid_e = pos - o;
     // ","token":"   (11 bytes)
     ld3u(s, pos, w0, w1, w2);
     d = (w0 ^ w4("\",\"t")) | (w1 ^ w4("oken")) | ((w2 ^ w4("\":\"\0")) & 0xFFFFFFu);
-    if (d || pos + 11 > end) return false;
-    pos += 11;
+    ok = ok && d == 0 && pos + 11 <= end;
+    pos = ok ? pos + 11 : end;
     pl.tok_b = pos - o;
-    if (!scan_canon_string(s, pos, end, go122, tok_esc)) return false;
+    ok = scan_canon_string(s, pos, end, go122, tok_esc) && ok;
     pl.tok_e = pos - o;
     // ","sequence":   (13 bytes)
     ld3u(s, pos, w0, w1, w2);
     d = (w0 ^ w4("\",\"s")) | (w1 ^ w4("eque")) | (w2 ^ w4("nce\"")) | (s.ld8(pos + 12) ^ ':');
-    if (d || pos + 14 > end) return false;
-    pos += 13;
+    ok = ok && d == 0 && pos + 14 <= end;
+    pos = ok ? pos + 13 : end;
     pl.seq_b = pos - o;
-    if (!scan_canon_int(s, pos, end, true, pl.seq)) return false;
+    ok = scan_canon_int(s, pos, end, pl.seq) && ok;
     pl.seq_n = pos - o - pl.seq_b;
     // ,"done":   (8 bytes) + true|false
     ld3u(s, pos, w0, w1, w2);
     d = (w0 ^ w4(",\"do")) | (w1 ^ w4("ne\":"));
-    if (d || pos + 13 > end) return false;
-    pos += 8;
-    if (w2 == w4("true")) { pl.done = 1; pos += 4; }
-    else if (w2 == w4("fals") && s.ld8(pos + 4) == 'e') { pl.done = 0; pos += 5; }
-    else return false;
+    const bool is_true = w2 == w4("true");
+    const bool is_false = w2 == w4("fals") && s.ld8(pos + 12) == 'e';
+    ok = ok && d == 0 && pos + 13 <= end && (is_true || is_false);
+    pl.done = is_true ? 1u : 0u;
+    pos = ok ? pos + (is_true ? 12u : 13u) : end;
     // ,"timestamp":   (13 bytes)
     ld3u(s, pos, w0, w1, w2);
     d = (w0 ^ w4(",\"ti")) | (w1 ^ w4("mest")) | (w2 ^ w4("amp\"")) | (s.ld8(pos + 12) ^ ':');
-    if (d || pos + 14 > end) return false;
-    pos += 13;
+    ok = ok && d == 0 && pos + 14 <= end;
+    pos = ok ? pos + 13 : end;
     pl.ts = 0;                                                  // never read for canonical records
-    if (!check_canon_tail_int(s, pos, end)) return false;
-    pl.fast = 1;
+    ok = check_canon_tail_int(s, pos, ok ? end : pos + 1) && ok;
+    pl.fast = ok ? 1u : 0u;
     pl.tok_redacted = 0;
     pl.cid_esc = cid_esc ? 1u : 0u;   // the bridge subject needs the DECODED id
     (void)tok_esc;
-    return true;
+    return ok;
 }
 
 // --------------------------------------------------------------- general path ----

@@ -119,6 +119,29 @@ for fn, (i, s_) in sorted(fn_incl.items(), key=lambda kv: -kv[1][0])[:28]:
 print("---- per kernel-level line (outermost frame) ----")
 for key, (i, s_) in sorted(site.items(), key=lambda kv: -kv[1][0])[:22]:
     print("%5.1f%% inst %5.1f%% smp  %-22s %s" % (100.0 * i / tot_i, 100.0 * s_ / max(tot_s, 1), "%s:%d" % key, src_line(key)))
+if "--lost" in sys.argv:
+    te = hdr.index("Thread Instructions Executed")
+    fn_eff, line_eff = {}, {}
+    for k in range(n):
+        i_k, t_k = int(body[k][ie]), int(body[k][te])
+        seen = set()
+        for fr in chains[k]:
+            fn = func_of(fr)
+            if fn not in seen:
+                seen.add(fn)
+                a = fn_eff.setdefault(fn, [0, 0])
+                a[0] += i_k
+                a[1] += t_k
+        a = line_eff.setdefault(lines[k][0], [0, 0])
+        a[0] += i_k
+        a[1] += t_k
+    tot_lost = sum(32 * a[0] - a[1] for a in line_eff.values())
+    print("---- divergence: share of warp-instructions, average active threads, share of all lost lane-slots ----")
+    for fn, (i, t) in sorted(fn_eff.items(), key=lambda kv: -(32 * kv[1][0] - kv[1][1]))[:16]:
+        print("%-24s %5.1f%% inst  %4.1f thr  %5.1f%% of lost" % (fn, 100.0 * i / tot_i, t / max(i, 1), 100.0 * (32 * i - t) / tot_lost))
+    for key, (i, t) in sorted(line_eff.items(), key=lambda kv: -(32 * kv[1][0] - kv[1][1]))[:24]:
+        print("%-26s %5.1f%% inst  %4.1f thr  %5.1f%% of lost  %s" % ("%s:%d" % key if key else "?", 100.0 * i / tot_i, t / max(i, 1),
+                                                                     100.0 * (32 * i - t) / tot_lost, src_line(key)[:70]))
 print("---- per innermost line ----")
 for key, (i, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
     print("%5.1f%% inst %5.1f%% smp  %-28s %s" % (100.0 * i / tot_i, 100.0 * s / max(tot_s, 1), "%s:%d" % key if key else "?", src_line(key)))
