@@ -92,16 +92,23 @@ __device__ __forceinline__ uint64_t lookback(uint64_t* tile_state, uint32_t tile
     int64_t j = (int64_t)tile - 1;             // nearest predecessor not yet accounted for
     for (;;) {
         uint64_t v[LB_WIN];
+#pragma unroll
+        for (int k = 0; k < LB_WIN; k++) v[k] = 0;
         bool pending;
-        do {
-            pending = false;
+        uint32_t spins = 0;
+        do {                                       // re-poll only the words that were still empty, and back off: hundreds
+            pending = false;                       // of CTAs poll the same few L2 lines
 #pragma unroll
             for (int k = 0; k < LB_WIN; k++) {
-                int64_t idx = j - (int64_t)(k * 32 + lane);
-                v[k] = idx >= 0 ? ld_relaxed_u64(&tile_state[idx]) : FLAG_PFX;   // before tile 0: prefix 0
-                pending |= (v[k] >> 62) == 0;
+                if ((v[k] >> 62) == 0) {
+                    int64_t idx = j - (int64_t)(k * 32 + lane);
+                    v[k] = idx >= 0 ? ld_relaxed_u64(&tile_state[idx]) : FLAG_PFX;   // before tile 0: prefix 0
+                    pending |= (v[k] >> 62) == 0;
+                }
             }
-        } while (__any_sync(0xFFFFFFFFu, pending));
+            pending = __any_sync(0xFFFFFFFFu, pending);
+            if (pending && ++spins > 1) __nanosleep(spins < 8 ? 100 : 400);
+        } while (pending);
         uint64_t part = 0;
         bool found = false;
 #pragma unroll

@@ -316,23 +316,20 @@ template <bool NF, class Src, class W> SSE_HD void put_copy_t(const Src& s, uint
     uint32_t k = (4u - (w.sh >> 3)) & 3u;
     if (k > n) k = n;
     if (k) { if (NF) w.put_n_nf(ld32u(s, sp), k); else w.put_n(ld32u(s, sp), k); sp += k; n -= k; }
-    uint32_t nw = n >> 2;
+    const uint32_t nw = n >> 2;
     if (nw) {
+        // one loop, four words per trip, the last trip predicated per word: every lane of the warp runs the
+        // same trips (no divergent remainder loop); loads past the last word stay inside the padded tile
         uint32_t a = sp & ~3u;
         const uint32_t shb = (sp & 3u) * 8;
         uint32_t lo = s.ld32a(a);
-        uint32_t i = 0;
-        for (; i + 4 <= nw; i += 4) {
-            uint32_t h0 = s.ld32a(a + 4), h1 = s.ld32a(a + 8), h2 = s.ld32a(a + 12), h3 = s.ld32a(a + 16);
-            w.store_word(funnel_r(lo, h0, shb)); w.store_word(funnel_r(h0, h1, shb));
-            w.store_word(funnel_r(h1, h2, shb)); w.store_word(funnel_r(h2, h3, shb));
+        for (uint32_t i = 0; i < nw; i += 4) {
+            const uint32_t h0 = s.ld32a(a + 4), h1 = s.ld32a(a + 8), h2 = s.ld32a(a + 12), h3 = s.ld32a(a + 16);
+            w.store_word(funnel_r(lo, h0, shb));
+            if (i + 1 < nw) w.store_word(funnel_r(h0, h1, shb));
+            if (i + 2 < nw) w.store_word(funnel_r(h1, h2, shb));
+            if (i + 3 < nw) w.store_word(funnel_r(h2, h3, shb));
             lo = h3; a += 16;
-        }
-        for (; i < nw; i++) {
-            a += 4;
-            uint32_t hi = s.ld32a(a);
-            w.store_word(funnel_r(lo, hi, shb));
-            lo = hi;
         }
         sp += nw * 4; n -= nw * 4;
     }
