@@ -206,7 +206,7 @@ struct Dfa {
     uint32_t n_states = 0, n_classes = 0;
     uint32_t start[2] = {0, 0};                 // start state when the byte before the text is a non-word / word byte
     uint8_t cls[256];                           // byte -> class
-    std::vector<uint16_t> next;                 // [state][class]; 0xFFFF = dead
+    std::vector<uint16_t> next;                 // [state][class]; 0xFFFF = dead; bit 15 = target state reports a match
     std::vector<uint32_t> acc_imm, acc_del, acc_eot;
 };
 
@@ -300,6 +300,11 @@ inline bool build_dfa(const Nfa& nfa, const std::vector<uint32_t>& starts, bool 
     }
     out.n_states = (uint32_t)states.size();
     out.next.resize((size_t)out.n_states * out.n_classes, 0xFFFF);
+    if (out.n_states >= 0x7FFF) { err = "too many DFA states"; return false; }
+    // bit 15 of a transition says "the target state reports a match" (acc_imm | acc_del non-zero), so the walk
+    // loads the accept masks only when something fired
+    for (uint16_t& nx : out.next)
+        if (nx != 0xFFFF && (out.acc_imm[nx] | out.acc_del[nx])) nx |= 0x8000;
     return true;
 }
 

@@ -5,14 +5,17 @@
 // a published subject (src/redis-nats-bridge/main.go:160-164) against those subscriptions happens inside
 // nats.go v1.31.0 / nats-server 2.10 (third-party, not vendored).  Semantics restated here are the NATS
 // subject rules: subjects are '.'-separated tokens; a subscription matches literally, '*' matches exactly
-// one token, '>' (last token only) matches one or more trailing tokens; empty tokens never match a wildcard.
+// one token, '>' (last token only) matches one or more trailing tokens; empty tokens never match anything.
 // Only literal chat.<id>.tokens and the wildcards chat.*.tokens / chat.*.control occur in the reference
 // (docs/security-inspection-patterns.md:110,268; kubernetes/base/nats-core/core-cluster.yaml:234,248).
 //
 // Layout: literal subscriptions of the form chat.<id>.tokens live in an open-addressing hash table keyed
-// by the id bytes (fnv1a64, linear probing, <= 50% load), values are CSR spans of subscriber ids; the few
-// wildcard subscriptions are a side list matched token by token.  At 100 k subjects the table is ~4 MB
-// (slots) + keys: far beyond one SM's shared memory, so it is read through L2 (126 MB holds it entirely).
+// by the DECODED id bytes (the bridge builds the subject from the decoded id, main.go:160): 32-byte slots
+// (one L2 sector each), linear probing, <= 50% load, a word-wise multiplicative hash, keys stored as
+// zero-padded 32-bit words so that the compare is word-wise too; values are CSR spans of subscriber ids.
+// The few wildcard subscriptions are a side list; the common shapes are pre-classified by the host so that
+// an id without dots never needs the token-by-token matcher.  At 100 k subjects the table is ~8 MB: far beyond
+// one SM's shared memory, so it is read through L2 (126 MB holds it entirely).
 #pragma once
 #include <stdint.h>
 #include "sse_inspect.cuh"
@@ -20,30 +23,59 @@
 namespace sse {
 
 struct InterestSlot {
-    uint64_t hash;               // 0 = empty
-    uint32_t key_off, key_len;   // id bytes in keys[]
+    uint32_t hash;               // 0 = empty
+    uint32_t key_off;            // first word of the key in keys[]
+    uint32_t key_len;            // bytes
     uint32_t list_off, list_cnt; // span in the CSR subscriber array
+    uint32_t pad[3];
 };
 
 constexpr uint32_t INTEREST_MAX_WILD = 32;
+constexpr uint32_t INTEREST_MAX_ID = 1024;      // longer ids cannot be subscribed to literally
 
 struct InterestDev {
     const InterestSlot* slots;
-    const uint8_t* keys;
+    const uint32_t* keys;        // zero-padded little-endian words
     uint32_t mask;               // capacity - 1 (capacity is a power of two)
     uint32_t n_wild;
+    uint32_t wild_single;        // wildcards that match every valid single-token id   (chat.*.tokens, chat.>, >, ...)
+    uint32_t wild_generic;       // wildcards that need the token-by-token matcher for single-token ids too
     const uint8_t* wild_bytes;   // wildcard subscription subjects, back to back
     uint32_t wild_off[INTEREST_MAX_WILD + 1];
 };
 
 struct InterestHit { uint32_t list_off, list_cnt, wild_mask; };
 
-// NATS subject match of pattern pat[0,pn) against the subject "chat." + id + ".tokens" given by byte accessor sub(i), length sn.
+SSE_HD uint32_t key_hash_init(uint32_t len) { return 0x9E3779B9u ^ len; }
+SSE_HD uint32_t key_hash_step(uint32_t h, uint32_t w) { h = (h ^ w) * 0x85EBCA6Bu; return (h << 13) | (h >> 19); }
+SSE_HD uint32_t key_hash_fin(uint32_t h) { h ^= h >> 16; h *= 0xC2B2AE35u; h ^= h >> 13; return h ? h : 1u; }
+
+// Probe for the key given by word(k), k < ceil(len/4) (last word zero-padded).
+template <class WordFn>
+SSE_HD void lookup_literal(const InterestDev& t, WordFn&& word, uint32_t len, InterestHit& h) {
+    if (!t.slots) return;
+    const uint32_t nw = (len + 3) >> 2;
+    uint32_t hash = key_hash_init(len);
+    for (uint32_t k = 0; k < nw; k++) hash = key_hash_step(hash, word(k));
+    hash = key_hash_fin(hash);
+    for (uint32_t p = hash & t.mask;; p = (p + 1) & t.mask) {
+        const InterestSlot& e = t.slots[p];
+        const uint32_t eh = e.hash;
+        if (eh == 0) return;
+        if (eh == hash && e.key_len == len) {
+            const uint32_t* key = t.keys + e.key_off;
+            bool same = true;
+            for (uint32_t k = 0; k < nw; k++) same = same && key[k] == word(k);
+            if (same) { h.list_off = e.list_off; h.list_cnt = e.list_cnt; return; }
+        }
+    }
+}
+
+// NATS subject match of pattern pat[0,pn) against the subject given by byte accessor sub(i), length sn.
 template <class SubFn>
 SSE_HD bool nats_match(const uint8_t* pat, uint32_t pn, SubFn&& sub, uint32_t sn) {
     uint32_t pi = 0, si = 0;
     for (;;) {
-        // one token of each
         uint32_t pe = pi;
         while (pe < pn && pat[pe] != '.') pe++;
         uint32_t se = si;
@@ -60,45 +92,34 @@ SSE_HD bool nats_match(const uint8_t* pat, uint32_t pn, SubFn&& sub, uint32_t sn
     }
 }
 
+// General case (out of line in the kernel): ids with escapes, with dots, longer than the fast lane handles, or
+// wildcard shapes that need the matcher.  Decodes the id into a local buffer first.
 template <class Src>
 SSE_HD_NOINLINE InterestHit interest_lookup(const InterestDev& t, const Src& s, uint32_t cid_b, uint32_t cid_e) {
     InterestHit h{0, 0, 0};
-    // fnv1a64 over the DECODED id (the bridge builds the subject from the decoded id, main.go:160)
-    uint64_t hash = 0xcbf29ce484222325ull;
-    uint32_t len = 0;
-    uint32_t prev = '.';
+    uint32_t idw[INTEREST_MAX_ID / 4];                               // decoded id, zero-padded words
+    uint8_t* id = reinterpret_cast<uint8_t*>(idw);
+    uint32_t len = 0, prev = '.';
     bool empty_token = false;                                        // "chat..tokens", "chat.a..b.tokens": not a valid NATS subject
     for_each_decoded_byte(s, cid_b, cid_e, [&](uint32_t c) {
-        hash ^= c; hash *= 0x100000001b3ull; len++;
+        if (len < INTEREST_MAX_ID) id[len] = (uint8_t)c;
+        len++;
         if (c == '.' && prev == '.') empty_token = true;
         prev = c;
     });
     if (prev == '.' || empty_token) return h;                        // covers the empty id too
-    if (hash == 0) hash = 1;
-    if (t.slots) {
-        for (uint32_t p = (uint32_t)hash & t.mask;; p = (p + 1) & t.mask) {
-            const InterestSlot e = t.slots[p];
-            if (e.hash == 0) break;
-            if (e.hash == hash && e.key_len == len) {
-                uint32_t k = 0;
-                bool same = true;
-                for_each_decoded_byte(s, cid_b, cid_e, [&](uint32_t c) { same = same && t.keys[e.key_off + k] == c; k++; });
-                if (same) { h.list_off = e.list_off; h.list_cnt = e.list_cnt; break; }
-            }
-        }
+    const bool fits = len <= INTEREST_MAX_ID;
+    if (fits) {
+        for (uint32_t k = len; k < ((len + 3) & ~3u); k++) id[k] = 0;
+        lookup_literal(t, [&](uint32_t k) { return idw[k]; }, len, h);
     }
     if (t.n_wild) {
-        // subject bytes: "chat." + id + ".tokens"; the id is materialised only up to 128 bytes, which
-        // covers every wildcard decision except for ids longer than that (then compared by the slow accessor)
-        uint8_t idbuf[128];
-        uint32_t k = 0;
-        for_each_decoded_byte(s, cid_b, cid_e, [&](uint32_t c) { if (k < 128) idbuf[k] = (uint8_t)c; k++; });
         const uint32_t sn = 5 + len + 7;
         auto sub = [&](uint32_t i) -> uint32_t {
             if (i < 5) return (uint32_t)(uint8_t)"chat."[i];
             if (i < 5 + len) {
-                uint32_t j = i - 5;
-                if (j < 128) return idbuf[j];
+                const uint32_t j = i - 5;
+                if (j < INTEREST_MAX_ID) return id[j];
                 uint32_t q = 0, r = 0;                                 // rare: re-decode up to byte j
                 for_each_decoded_byte(s, cid_b, cid_e, [&](uint32_t c) { if (q == j) r = c; q++; });
                 return r;
@@ -109,6 +130,29 @@ SSE_HD_NOINLINE InterestHit interest_lookup(const InterestDev& t, const Src& s, 
             if (nats_match(t.wild_bytes + t.wild_off[w], t.wild_off[w + 1] - t.wild_off[w], sub, sn)) h.wild_mask |= 1u << w;
     }
     return h;
+}
+
+// Fast lane: the id's decoded text IS its raw bytes (canonical record, no backslash escape in the id) and it has
+// no dot (one NATS token) and no wildcard needs the general matcher.  Word loads from the tile.  Returns false
+// when the general routine must take over.
+template <class Src>
+SSE_HD bool interest_lookup_raw(const InterestDev& t, const Src& s, uint32_t cid_b, uint32_t cid_e, InterestHit& h) {
+    const uint32_t len = cid_e - cid_b;
+    if (len == 0 || len > 64 || t.wild_generic) return false;
+    uint32_t dots = 0;
+    for (uint32_t i = 0; i < len; i += 4) {
+        const uint32_t w = ld32u(s, cid_b + i);
+        const uint32_t keep = len - i >= 4 ? 0xFFFFFFFFu : (0xFFFFFFFFu >> (8 * (4 - (len - i))));
+        const uint32_t x = (w ^ 0x2E2E2E2Eu) | ~keep;                // bytes past the id can never look like '.'
+        dots |= (x - 0x01010101u) & ~x & 0x80808080u;
+    }
+    if (dots) return false;
+    h.list_off = 0; h.list_cnt = 0; h.wild_mask = t.wild_single;
+    lookup_literal(t, [&](uint32_t k) {
+        const uint32_t w = ld32u(s, cid_b + 4 * k), rem = len - 4 * k;
+        return rem >= 4 ? w : (w & (0xFFFFFFFFu >> (8 * (4 - rem))));
+    }, len, h);
+    return true;
 }
 
 }  // namespace sse

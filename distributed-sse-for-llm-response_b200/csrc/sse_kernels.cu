@@ -178,25 +178,12 @@ __device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uin
     }
 }
 
-// Inspection of one record's token text (out of line, generic pointers).  Streaming mode carries the DFA
-// state of the record's conversation slot; a slot may be touched once per launch (stamped with the launch epoch).
-struct InspectOut { uint32_t verdict; int32_t begin, end; };
-__device__ __noinline__ InspectOut inspect_slow(const FrameArgs& a, const uint8_t* src_base, uint32_t o, uint32_t tok_b, uint32_t tok_e,
-                                                bool done, uint32_t rec) {
-    const InspectDev& t = *a.insp;
+// Inspection of one record's token text, general case (out of line, generic pointers): escapes in the token,
+// non-canonical records, or the leftmost-start search of a variable-length match.
+__device__ __noinline__ InspectResult inspect_slow(const InspectDev* t, const uint8_t* src_base, uint32_t tok_b, uint32_t tok_e,
+                                                   uint32_t state_in, bool eot) {
     PtrSrc src{src_base};
-    InspectOut out{0, 0, 0};
-    if (t.mode == INSPECT_STREAMING) {
-        const uint32_t slot = a.conv_slot[rec];
-        if (slot >= a.conv_slots || atomicExch(&a.conv_epoch[slot], a.epoch) == a.epoch) { atomicExch(a.dup_conv, 1u); return out; }
-        InspectResult r = inspect_token(t, src, o + tok_b, o + tok_e, a.conv_state[slot], done);
-        a.conv_state[slot] = r.state;
-        out.verdict = r.verdict; out.begin = r.begin; out.end = r.end;
-    } else {
-        InspectResult r = inspect_token(t, src, o + tok_b, o + tok_e, 0, true);
-        out.verdict = r.verdict; out.begin = r.begin; out.end = r.end;
-    }
-    return out;
+    return inspect_token(*t, src, tok_b, tok_e, state_in, eot);
 }
 __device__ __noinline__ InterestHit interest_slow(const FrameArgs& a, const uint8_t* src_base, uint32_t o, uint32_t cid_b, uint32_t cid_e) {
     PtrSrc src{src_base};
@@ -259,6 +246,17 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
     uint64_t c_in = 0, c_out = 0;
     uint32_t parity = 0;
 
+    // EXT: on-chip copy of the inspection DFA's byte-class map and hottest transition rows
+    DfaCache dcache{nullptr, nullptr, 0};
+    if (EXT && a.insp != nullptr) {
+        uint8_t* s_cls = reinterpret_cast<uint8_t*>(ts + 1);
+        uint16_t* s_rows = reinterpret_cast<uint16_t*>(s_cls + 256);
+        const DfaDev& d = a.insp->fwd;
+        const uint32_t nc = min(d.n_states, DFA_CACHE_ENTRIES / d.n_classes);
+        for (uint32_t i = tid; i < 256; i += TILE) s_cls[i] = d.cls[i];
+        for (uint32_t i = tid; i < nc * d.n_classes; i += TILE) s_rows[i] = d.next[i];
+        dcache.cls = s_cls; dcache.rows = s_rows; dcache.n_cached = nc;
+    }
     if (tid == 0) {
         mbar_init(&ts->mbar, 1);
         setup_tile(a, ts, s_in, atomicAdd(a.ticket, 1u), c_in);
@@ -303,10 +301,25 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
 
         // ---- content inspection of the decoded token text (optional) ------------------------
         if (EXT && a.insp != nullptr) {                                       // launch-uniform
-            InspectOut io{0, 0, 0};
+            InspectResult io{0, 0, 0, 0};
             if (active && (st & ST_CODE_MASK) == ST_OK) {
+                const InspectDev& t = *a.insp;
                 const uint8_t* sb = smem_in ? s_in : a.in + abase;
-                io = inspect_slow(a, sb, o, pl.tok_b, pl.tok_e, (st & ST_DONE) != 0, r0 + tid);
+                const bool streaming = t.mode == INSPECT_STREAMING;
+                const bool eot = !streaming || (st & ST_DONE) != 0;
+                uint32_t slot = 0, state_in = 0;
+                bool valid = true;
+                if (streaming) {          // a conversation slot may be touched once per launch: stamp it with the launch epoch
+                    slot = a.conv_slot[r0 + tid];
+                    valid = slot < a.conv_slots && atomicExch(&a.conv_epoch[slot], a.epoch) != a.epoch;
+                    if (valid) state_in = a.conv_state[slot]; else atomicExch(a.dup_conv, 1u);
+                }
+                if (valid) {
+                    bool done_fast = false;
+                    if (fastp && !pl.tok_esc) { PtrSrc src{s_in}; done_fast = inspect_raw(t, dcache, src, o + pl.tok_b, o + pl.tok_e, state_in, eot, io); }
+                    if (!done_fast) io = inspect_slow(a.insp, sb, o + pl.tok_b, o + pl.tok_e, state_in, eot);
+                    if (streaming) a.conv_state[slot] = io.state;
+                }
                 if (a.op & OP_INSPECT_INLINE) {                               // sse_handler.go:200-207
                     const uint32_t act = io.verdict & 0xFF;
                     if (act == ACT_DROP) { st = ST_INSPECT_DROP; len = 0; }
@@ -334,7 +347,9 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
         if (EXT && a.interest != nullptr) {                                   // launch-uniform
             InterestHit h{0, 0, 0};
             if (active && (st & ST_CODE_MASK) == ST_OK) {
-                h = interest_slow(a, smem_in ? s_in : a.in + abase, o, pl.cid_b, pl.cid_e);
+                bool done_fast = false;
+                if (fastp && !pl.cid_esc) { PtrSrc src{s_in}; done_fast = interest_lookup_raw(*a.interest, src, o + pl.cid_b, o + pl.cid_e, h); }
+                if (!done_fast) h = interest_slow(a, smem_in ? s_in : a.in + abase, o, pl.cid_b, pl.cid_e);
                 if (h.list_cnt == 0 && h.wild_mask == 0) { st = ST_NO_INTEREST; len = 0; }   // nobody subscribed: nothing to frame
             }
             if (active) {
@@ -461,37 +476,44 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
 
 // ---------------------------------------------------------------------- launch ----
 static int g_num_sms[64];
-static int g_ctas_per_sm[64];
+static int g_ctas_per_sm[64][2];
 
-cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
-    // Shared memory per CTA: a tile of TILE records is ~17 KB in / ~21 KB out at the
-    // BASELINE workload; caps leave ~15% slack.  Tiles that exceed them take the direct
-    // global-memory path inside the same kernel.
+// Shared memory per CTA: a tile of TILE records is ~17 KB in / ~21 KB out at the BASELINE workload; the caps leave
+// ~15% slack.  Tiles that exceed them take the direct global-memory path inside the same kernel.  The EXT kernel
+// (inspection / interest lookup) adds the on-chip DFA cache.
+static cudaError_t configure_variant(int device, bool ext, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
     const uint32_t ic = 20 * 1024, oc = 24 * 1024;
-    const uint32_t sm = ic + 32 + oc + 48 + (uint32_t)sizeof(TileSmem);
-    cudaError_t e = cudaFuncSetAttribute(k_frame_tiles<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    const uint32_t sm = ic + 32 + oc + 48 + (uint32_t)sizeof(TileSmem) + (ext ? DFA_CACHE_BYTES : 0u);
+    cudaError_t e = ext ? cudaFuncSetAttribute(k_frame_tiles<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)
+                        : cudaFuncSetAttribute(k_frame_tiles<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_frame_tiles<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    if (e != cudaSuccess) return e;
-    if (g_num_sms[device] == 0) {
+    if (g_ctas_per_sm[device][ext] == 0) {
         int sms = 0, per = 0;
         e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<false>, TILE, sm);
+        e = ext ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<true>, TILE, sm)
+                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<false>, TILE, sm);
         if (e != cudaSuccess) return e;
         if (per < 1) per = 1;
         g_num_sms[device] = sms;
-        g_ctas_per_sm[device] = per;
+        g_ctas_per_sm[device][ext] = per;
     }
     *in_cap = ic; *out_cap = oc; *smem_bytes = sm;
-    *grid = g_num_sms[device] * g_ctas_per_sm[device];
+    *grid = g_num_sms[device] * g_ctas_per_sm[device][ext];
     return cudaSuccess;
+}
+
+cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
+    cudaError_t e = configure_variant(device, true, in_cap, out_cap, smem_bytes, grid);
+    if (e != cudaSuccess) return e;
+    return configure_variant(device, false, in_cap, out_cap, smem_bytes, grid);
 }
 
 cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     uint32_t smem_bytes;
     int grid;
-    cudaError_t e = frame_configure(device, &a.in_cap, &a.out_cap_s, &smem_bytes, &grid);
+    const bool ext = a.insp != nullptr || a.interest != nullptr;
+    cudaError_t e = configure_variant(device, ext, &a.in_cap, &a.out_cap_s, &smem_bytes, &grid);
     if (e != cudaSuccess) return e;
     a.num_tiles = (a.n + TILE - 1) / TILE;
     // scratch: ticket + overflow flag + counters + tile status words, zeroed per launch
@@ -499,7 +521,7 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
     if ((int)a.num_tiles < grid) grid = (int)a.num_tiles;
-    if (a.insp != nullptr || a.interest != nullptr) k_frame_tiles<true><<<grid, TILE, smem_bytes, stream>>>(a);
+    if (ext) k_frame_tiles<true><<<grid, TILE, smem_bytes, stream>>>(a);
     else k_frame_tiles<false><<<grid, TILE, smem_bytes, stream>>>(a);
     return cudaGetLastError();
 }

@@ -54,6 +54,7 @@ struct Plan {
     uint32_t fast;           // 1: payload is canonical, JSON out == payload bytes
     uint32_t seq_b, seq_n;   // fast only: where the sequence literal sits in the payload (its text IS fmt %d)
     uint32_t cid_esc;        // fast only: the id literal contains a backslash escape (decoded id != raw bytes)
+    uint32_t tok_esc;        // fast only: the token literal contains a backslash escape (decoded text != raw bytes)
     uint32_t tok_redacted;   // inline inspection replaced the token text with "[REDACTED]" (sse_handler.go:205-207)
 };
 
@@ -596,7 +597,7 @@ template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L
     pl.fast = ok ? 1u : 0u;
     pl.tok_redacted = 0;
     pl.cid_esc = cid_esc ? 1u : 0u;   // the bridge subject needs the DECODED id
-    (void)tok_esc;
+    pl.tok_esc = tok_esc ? 1u : 0u;
     return ok;
 }
 
@@ -698,7 +699,7 @@ template <class Src> SSE_HD int match_field(const Src& s, uint32_t b, uint32_t e
 template <class Src>
 SSE_HD_NOINLINE uint32_t parse_general(const Src& s, uint32_t o, uint32_t L, Plan& pl, uint32_t* nest) {
     pl.cid_b = pl.cid_e = pl.tok_b = pl.tok_e = 0;
-    pl.seq = 0; pl.ts = 0; pl.done = 0; pl.fast = 0; pl.seq_b = pl.seq_n = 0; pl.cid_esc = 0; pl.tok_redacted = 0;
+    pl.seq = 0; pl.ts = 0; pl.done = 0; pl.fast = 0; pl.seq_b = pl.seq_n = 0; pl.cid_esc = 0; pl.tok_esc = 0; pl.tok_redacted = 0;
     enum { BEGIN_VALUE, BEGIN_VALUE_OR_EMPTY, BEGIN_KEY_OR_EMPTY, BEGIN_KEY, END_VALUE };
     uint32_t st = BEGIN_VALUE, depth = 0, pos = o;
     const uint32_t end = o + L;

@@ -468,7 +468,7 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
         dd.cls = base + o.cls; dd.next = reinterpret_cast<const uint16_t*>(base + o.next);
         dd.acc_imm = reinterpret_cast<const uint32_t*>(base + o.imm); dd.acc_del = reinterpret_cast<const uint32_t*>(base + o.del);
         dd.acc_eot = reinterpret_cast<const uint32_t*>(base + o.eot);
-        dd.n_classes = d.n_classes; dd.start0 = d.start[0]; dd.start1 = d.start[1];
+        dd.n_classes = d.n_classes; dd.start0 = d.start[0]; dd.start1 = d.start[1]; dd.n_states = d.n_states;
     };
     fill(h.fwd, c.forward, offs[0]);
     for (size_t k = 0; k < c.anchored.size(); k++) fill(h.anchored[k], c.anchored[k], offs[k + 1]);
@@ -532,14 +532,15 @@ int ssegpu_interest_apply(ssegpu_ctx* ctx, const ssegpu_sub_delta* d, uint32_t n
     void *ds = nullptr, *dk = nullptr, *dw = nullptr;
     sse::InterestDev* dd = nullptr;
     CU(cudaMalloc(&ds, t.slots.size() * sizeof(sse::InterestSlot)));
-    CU(cudaMalloc(&dk, t.keys.size()));
+    CU(cudaMalloc(&dk, t.keys.size() * 4));
     CU(cudaMalloc(&dw, t.wild_bytes.size()));
     CU(cudaMalloc(&dd, sizeof(sse::InterestDev)));
     CU(cudaMemcpy(ds, t.slots.data(), t.slots.size() * sizeof(sse::InterestSlot), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dk, t.keys.data(), t.keys.size(), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dk, t.keys.data(), t.keys.size() * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(dw, t.wild_bytes.data(), t.wild_bytes.size(), cudaMemcpyHostToDevice));
     sse::InterestDev h{};
-    h.slots = static_cast<const sse::InterestSlot*>(ds); h.keys = static_cast<const uint8_t*>(dk);
+    h.slots = static_cast<const sse::InterestSlot*>(ds); h.keys = static_cast<const uint32_t*>(dk);
+    h.wild_single = t.wild_single; h.wild_generic = t.wild_generic;
     h.mask = (uint32_t)t.slots.size() - 1; h.n_wild = (uint32_t)t.wild_ids.size();
     h.wild_bytes = static_cast<const uint8_t*>(dw);
     for (size_t i = 0; i < t.wild_off.size(); i++) h.wild_off[i] = t.wild_off[i];

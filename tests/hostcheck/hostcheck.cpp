@@ -61,7 +61,7 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
     InspectDev t{};
     auto fill = [](DfaDev& dd, const sse_inspect::Dfa& d) {
         dd.cls = d.cls; dd.next = d.next.data(); dd.acc_imm = d.acc_imm.data(); dd.acc_del = d.acc_del.data();
-        dd.acc_eot = d.acc_eot.data(); dd.n_classes = d.n_classes; dd.start0 = d.start[0]; dd.start1 = d.start[1];
+        dd.acc_eot = d.acc_eot.data(); dd.n_classes = d.n_classes; dd.start0 = d.start[0]; dd.start1 = d.start[1]; dd.n_states = d.n_states;
     };
     fill(t.fwd, c.forward);
     if (c.anchored.size() > INSPECT_MAX_ANCHORED) return -2;
@@ -77,22 +77,27 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
     std::vector<uint32_t> state(conv_slots ? conv_slots : 1, c.forward.start[0]);
     std::vector<uint32_t> nest(NEST_WORDS);
     PtrSrc src{in};
+    // the kernel keeps the first few states' rows on chip; here the "cache" aliases the full table but is
+    // deliberately small so that both the cached and the uncached branch of dfa_step run
+    DfaCache cache{c.forward.cls, c.forward.next.data(), c.forward.n_states < 20 ? c.forward.n_states : 20};
     for (uint32_t i = 0; i < n; i++) {
         Plan pl;
-        uint32_t len = 0;
+        uint32_t len = 0, st = ST_OK;
         const uint32_t o = in_off[i], L = in_off[i + 1] - in_off[i];
-        uint32_t st = plan_record(src, o, L, 0, 0, pl, nest.data(), len);
+        const bool fastp = plan_record_fast(src, o, L, 0, 0, pl, st, len);
+        if (!fastp) st = plan_record(src, o, L, 0, 0, pl, nest.data(), len);
         status[i] = st;
         verdict[i] = 0; match[2 * i] = 0; match[2 * i + 1] = 0;
         if ((st & ST_CODE_MASK) != ST_OK) continue;
-        InspectResult r;
-        if (mode == INSPECT_STREAMING) {
-            uint32_t slot = conv_slot[i];
-            r = inspect_token(t, src, o + pl.tok_b, o + pl.tok_e, state[slot], (st & ST_DONE) != 0);
-            state[slot] = r.state;
-        } else {
-            r = inspect_token(t, src, o + pl.tok_b, o + pl.tok_e, 0, true);
-        }
+        const bool streaming = mode == INSPECT_STREAMING;
+        const bool eot = !streaming || (st & ST_DONE) != 0;
+        const uint32_t slot = streaming ? conv_slot[i] : 0;
+        const uint32_t state_in = streaming ? state[slot] : 0;
+        InspectResult r{0, 0, 0, 0};
+        bool done_fast = false;
+        if (fastp && !pl.tok_esc) done_fast = inspect_raw(t, cache, src, o + pl.tok_b, o + pl.tok_e, state_in, eot, r);
+        if (!done_fast) r = inspect_token(t, src, o + pl.tok_b, o + pl.tok_e, state_in, eot);
+        if (streaming) state[slot] = r.state;
         verdict[i] = r.verdict; match[2 * i] = r.begin; match[2 * i + 1] = r.end;
     }
     return 0;
@@ -120,6 +125,7 @@ extern "C" int hc_interest(const hc_delta* d, uint32_t nd, const uint8_t* in, co
     InterestDev dev{};
     dev.slots = t.slots.data(); dev.keys = t.keys.data(); dev.mask = (uint32_t)t.slots.size() - 1;
     dev.n_wild = (uint32_t)t.wild_ids.size(); dev.wild_bytes = t.wild_bytes.data();
+    dev.wild_single = t.wild_single; dev.wild_generic = t.wild_generic;
     for (size_t i = 0; i < t.wild_off.size(); i++) dev.wild_off[i] = t.wild_off[i];
     std::vector<uint32_t> nest(NEST_WORDS);
     PtrSrc src{in};
@@ -127,10 +133,14 @@ extern "C" int hc_interest(const hc_delta* d, uint32_t nd, const uint8_t* in, co
         Plan pl;
         uint32_t len = 0;
         const uint32_t o = in_off[i], L = in_off[i + 1] - in_off[i];
-        uint32_t st = plan_record(src, o, L, OP_BRIDGE, 0, pl, nest.data(), len);
+        uint32_t st = ST_OK;
+        const bool fastp = plan_record_fast(src, o, L, OP_BRIDGE, 0, pl, st, len);      // same dispatch as the kernel
+        if (!fastp) st = plan_record(src, o, L, OP_BRIDGE, 0, pl, nest.data(), len);
         hit[3 * i] = hit[3 * i + 1] = hit[3 * i + 2] = 0;
         if ((st & ST_CODE_MASK) == ST_OK) {
-            InterestHit h = interest_lookup(dev, src, o + pl.cid_b, o + pl.cid_e);
+            InterestHit h{0, 0, 0};
+            if (!(fastp && !pl.cid_esc && interest_lookup_raw(dev, src, o + pl.cid_b, o + pl.cid_e, h)))
+                h = interest_lookup(dev, src, o + pl.cid_b, o + pl.cid_e);
             hit[3 * i] = h.list_off; hit[3 * i + 1] = h.list_cnt; hit[3 * i + 2] = h.wild_mask;
             if (h.list_cnt == 0 && h.wild_mask == 0) st = ST_NO_INTEREST;
         }

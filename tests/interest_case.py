@@ -7,7 +7,7 @@ import make_golden as mg
 import nats_model
 
 
-def build(n_conv=400, seed=17):
+def build(n_conv=400, seed=17, generic_wildcard=True):
     rng = random.Random(seed)
     ids = ["conv-%d" % i for i in range(n_conv)] + ["we\"ird\\id", "d.o.t", "sp ace", "café", "", "x" * 200, "a*", ">"]
     deltas, live = [], []
@@ -20,7 +20,12 @@ def build(n_conv=400, seed=17):
             deltas.append((0, sid, subj))
             live.append((subj, sid))
             sid += 1
-    for subj in (b"chat.*.tokens", b"chat.*.control", b"chat.conv-7.>", b"other.subject", b"chat.conv-3.tokens.extra"):
+    wilds = [b"chat.*.tokens", b"chat.*.control", b"other.subject", b"chat.conv-3.tokens.extra"]
+    if generic_wildcard:                      # a wildcard with a literal in the id position forces the token-by-token matcher
+        wilds.append(b"chat.conv-7.>")
+    else:
+        wilds += [b"chat.>", b"*.*.*", b"chat.*.tokens.>"]
+    for subj in wilds:
         deltas.append((0, sid, subj))
         live.append((subj, sid))
         sid += 1

@@ -15,9 +15,10 @@ from gpu_util import normalise, slices  # noqa: E402
 pytestmark = pytest.mark.gpu
 
 
-def test_interest_lookup_and_bridge_reframe(oracle):
+@pytest.mark.parametrize("generic", [True, False])
+def test_interest_lookup_and_bridge_reframe(oracle, generic):
     pkg = load_package()
-    deltas, live, payloads, subjects = interest_case.build()
+    deltas, live, payloads, subjects = interest_case.build(generic_wildcard=generic)
     arena, off = oracle.pack(payloads)
     n = len(off) - 1
     eng = pkg.SseGpu(device=0, max_records=1 << 13, max_in_bytes=4 << 20, ring_slots=1)

@@ -17,9 +17,13 @@ def test_nats_subject_rules():
     assert not m(b"chat.*.tokens", b"chat..tokens") and not m(b"chat.*", b"chat.a.tokens")
 
 
-def test_lookup_matches_model(oracle):
+import pytest  # noqa: E402
+
+
+@pytest.mark.parametrize("generic", [True, False])
+def test_lookup_matches_model(oracle, generic):
     lib = hc.load()
-    deltas, live, payloads, subjects = interest_case.build()
+    deltas, live, payloads, subjects = interest_case.build(generic_wildcard=generic)
     arena, off = oracle.pack(payloads)
     hit, status, subs, wild_ids = hc.interest(lib, deltas, arena, off)
     assert interest_case.check(hit, status, subs, wild_ids, live, subjects) > 1000
