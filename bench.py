@@ -159,6 +159,7 @@ def run_gpu(args):
     use_dist = world > 1
     if use_dist:
         import torch.distributed as dist
+        os.environ["NCCL_DEBUG"] = "WARN"       # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = load_package()
     arena, off = make_workload(pkg, rank, world)
