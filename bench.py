@@ -72,7 +72,9 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        # under load = samples at or above half the maximum clock seen (idle samples between phases are dropped)
+        sm = [int(r[0]) for r in self.rows if r and r[0].isdigit()]
+        sm = sorted(x for x in sm if 2 * x >= max(sm)) if sm else []
         mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k].lower().startswith("active") for r in self.rows)]
@@ -184,6 +186,9 @@ def run_gpu(args):
         eng.frame_launch(d_in.data_ptr(), d_off.data_ptr(), 0, n, op, d_out.data_ptr(), cap, d_out_off.data_ptr(),
                          d_out_len.data_ptr(), 0, d_status.data_ptr(), stream.cuda_stream)
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()                         # samples through warm-up, the device-timed region and the e2e region
     for _ in range(max(args.warmup, 3)):
         launch()
     torch.cuda.synchronize()
@@ -192,9 +197,6 @@ def run_gpu(args):
     out_bytes = c0["bytes_out"]
     if use_dist:
         dist.barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     launches0 = eng.launch_count()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     torch.cuda.synchronize()
@@ -209,7 +211,6 @@ def run_gpu(args):
     torch.cuda.synchronize()
     if use_dist:
         dist.barrier()
-    clocks = sampler.stop() if rank == 0 else None
     launches = eng.launch_count() - launches0
     dev_ms = t_all0.elapsed_time(t_all1)
     kern_ms = sum(a.elapsed_time(b) for a, b in evs) / args.steps
@@ -252,6 +253,7 @@ def run_gpu(args):
         e2e_frames += e2e_step()
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
     # spot check the e2e output of the last step against the device-resident arm
     last = slots[-1]
     lo, hi = bounds[-1]

@@ -14,3 +14,4 @@ from .binding import (  # noqa: F401
 )
 from . import workload  # noqa: F401
 from . import sharding  # noqa: F401
+from . import host  # noqa: F401

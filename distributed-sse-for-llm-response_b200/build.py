@@ -41,13 +41,28 @@ def build_host(force=False):
     return LOADLIB
 
 
+HOSTLIB = os.path.join(HERE, "libssehost.so")
+HOSTSRC = os.path.join(HERE, "host", "adapter_host.cpp")
+
+
+def build_adapter_host(force=False):
+    """host-side C++ mirror of the adapter's per-connection flow; links against libssegpu.so (same directory)"""
+    deps = [HOSTSRC, os.path.join(os.path.dirname(HERE), "include", "ssegpu.h"), LIB]
+    if force or not os.path.exists(HOSTLIB) or any(os.path.getmtime(d) > os.path.getmtime(HOSTLIB) for d in deps):
+        subprocess.check_call([os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", "-fPIC", "-shared", "-o", HOSTLIB, HOSTSRC,
+                               "-L" + HERE, "-lssegpu", "-Wl,-rpath,$ORIGIN"])
+    return HOSTLIB
+
+
 def build(force=False, verbose=False):
     build_host(force)
     if not force and not needs_build():
+        build_adapter_host(force)
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     subprocess.check_call(cmd)
+    build_adapter_host(True)
     return LIB
 
 
