@@ -284,7 +284,7 @@ def run_gpu(args):
             "config": {"workload": "configs[1]: 10k conversations x 1k tokens per GPU, UUID ids, Mistral-7B-like token lengths, arrival order",
                        "records_per_step": int(frames_all), "payload_bytes_per_step": int(in_all), "frame_bytes_per_step": int(out_all),
                        "sharding": "fnv1a64(conversation_id) % n_gpus, no data-path collective",
-                       "arena_layout": "record order (look-back scan)" if args.ordered else "tile completion order (atomic cursor)",
+                       "arena_layout": "record order (count pass + tile scan + emit pass)" if args.ordered else "tile completion order (atomic cursor)",
                        "l2": "inputs (%.2f GB per GPU) larger than L2, no flush needed" % (in_bytes / 1e9),
                        "bytes_per_sec": (in_all + out_all) * args.steps / dev_s},
             "e2e": {"value": e2e_all / mx[2], "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -311,7 +311,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
-    ap.add_argument("--ordered", action="store_true", help="SSEGPU_OP_ORDERED: record-ordered arena via look-back scan")
+    ap.add_argument("--ordered", action="store_true", help="SSEGPU_OP_ORDERED: record-ordered arena (two decode passes)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -7,17 +7,16 @@
 // that has a token pending.
 //
 // Shape (sm_100a):
-//   * persistent CTAs (grid = SMs x resident CTAs), tiles of TILE records handed out in order
-//     by an atomic ticket, so the decoupled look-back below can never wait on a tile that has
-//     not started;
+//   * persistent CTAs (grid = SMs x resident CTAs), tiles of TILE records handed out by an
+//     atomic ticket;
 //   * a tile's payload bytes arrive in shared memory as ONE TMA bulk copy
 //     (cp.async.bulk ... mbarrier::complete_tx), 16-byte aligned, no register staging;
 //   * one thread per record runs sse_record.cuh (SWAR canonical check / general decoder);
-//   * frame lengths: warp-shuffle scan -> CTA scan -> single-pass decoupled look-back
-//     (64-bit {flag,prefix} words, 256 predecessors inspected per L2 round trip) for the
-//     tile's global byte offset;
+//   * frame lengths: warp-shuffle scan -> CTA scan; the tile's slice of the arena comes from an
+//     atomic cursor (arrival order, the default) or, in ordered mode, from a counting pass +
+//     one-CTA scan over the tile totals (see "ordered placement" below);
 //   * frames are assembled in a shared-memory staging tile BEFORE the tile's global offset is
-//     known (so the look-back latency hides behind the emission and the next tile's TMA load),
+//     needed (the slice comes back from the atomic cursor while the frames are being written),
 //     then leave as coalesced 16-byte vector stores, byte-shifted on the fly to the arena's
 //     alignment, plus at most 15 head and 15 tail bytes: HBM sees only full-line traffic.
 //   No tensor cores: nothing here is a contraction.
@@ -73,61 +72,37 @@ __device__ __forceinline__ void st_relaxed_u64(uint64_t* p, uint64_t v) {
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// ---------------------------------------------------------------- tile status ----
-constexpr uint64_t FLAG_AGG = 1ull << 62;      // value = this tile's own byte count
-constexpr uint64_t FLAG_PFX = 2ull << 62;      // value = inclusive prefix up to and including this tile
-constexpr uint64_t VAL_MASK = (1ull << 62) - 1;
+// ------------------------------------------------------------ ordered placement ----
+// SSEGPU_OP_ORDERED lays the frames out back to back in record order.  A tile's offset is then the sum of ALL
+// earlier tiles' byte counts, i.e. it depends on the decode of every earlier record.  A single-pass decoupled
+// look-back was tried first (round 1, 2.2-2.3 ms per 10 M records): with ~740 persistent CTAs in flight every tile
+// waits for the slowest of hundreds of predecessors, the CTAs fall into lock-step waves and the 5 CTAs per SM stop
+// hiding one another's latencies.  Ordered mode is therefore two passes over the payload with a kernel boundary
+// as the global synchronisation: pass A decodes and records each tile's byte count, a one-CTA scan turns the
+// counts into offsets, pass B decodes again and emits at the known offsets.  The default (arrival-order) mode
+// stays a single pass.
+constexpr int MODE_ARRIVAL = 0, MODE_ORDERED_COUNT = 1, MODE_ORDERED_EMIT = 2;
 
-// Single-pass decoupled look-back, run by warp 0 AFTER the tile's aggregate was published.
-// With hundreds of phase-locked persistent CTAs the nearest tile that already owns a prefix
-// is typically hundreds of tiles back, so every L2 round trip inspects LB_WIN*32 predecessors
-// (all loads in flight together) instead of 32.  Returns the exclusive prefix of `tile`.
-constexpr int LB_WIN = 8;
-__device__ __forceinline__ void publish_aggregate(uint64_t* tile_state, uint32_t tile, uint64_t total) {
-    st_relaxed_u64(&tile_state[tile], (tile == 0 ? FLAG_PFX : FLAG_AGG) | total);
-}
-__device__ __forceinline__ uint64_t lookback(uint64_t* tile_state, uint32_t tile, uint64_t total, uint32_t lane) {
-    if (tile == 0) return 0;
-    uint64_t excl = 0;
-    int64_t j = (int64_t)tile - 1;             // nearest predecessor not yet accounted for
-    for (;;) {
-        uint64_t v[LB_WIN];
+__global__ void __launch_bounds__(1024) k_scan_tile_totals(uint64_t* tile_state, uint32_t num_tiles, uint64_t* out_total, uint32_t* ticket) {
+    __shared__ uint64_t warp_sums[32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t per = (num_tiles + 1023) / 1024;
+    const uint32_t lo = min(num_tiles, tid * per), hi = min(num_tiles, lo + per);
+    uint64_t sum = 0;
+    for (uint32_t i = lo; i < hi; i++) sum += tile_state[i];
+    uint64_t incl = sum;
 #pragma unroll
-        for (int k = 0; k < LB_WIN; k++) v[k] = 0;
-        bool pending;
-        uint32_t spins = 0;
-        do {                                       // re-poll only the words that were still empty, and back off: hundreds
-            pending = false;                       // of CTAs poll the same few L2 lines
-#pragma unroll
-            for (int k = 0; k < LB_WIN; k++) {
-                if ((v[k] >> 62) == 0) {
-                    int64_t idx = j - (int64_t)(k * 32 + lane);
-                    v[k] = idx >= 0 ? ld_relaxed_u64(&tile_state[idx]) : FLAG_PFX;   // before tile 0: prefix 0
-                    pending |= (v[k] >> 62) == 0;
-                }
-            }
-            pending = __any_sync(0xFFFFFFFFu, pending);
-            if (pending && ++spins > 1) __nanosleep(spins < 8 ? 100 : 400);
-        } while (pending);
-        uint64_t part = 0;
-        bool found = false;
-#pragma unroll
-        for (int k = 0; k < LB_WIN; k++) {
-            if (!found) {
-                uint32_t pfx_mask = __ballot_sync(0xFFFFFFFFu, (v[k] >> 62) == 2);
-                uint32_t first_pfx = pfx_mask ? (uint32_t)(__ffs((int)pfx_mask) - 1) : 32u;   // nearest tile holding a prefix
-                if (lane <= first_pfx) part += v[k] & VAL_MASK;
-                found = pfx_mask != 0;
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
-        excl += part;
-        if (found) break;
-        j -= 32 * LB_WIN;
+    for (int d = 1; d < 32; d <<= 1) {
+        uint64_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += v;
     }
-    if (lane == 0) st_relaxed_u64(&tile_state[tile], FLAG_PFX | (excl + total));
-    return excl;
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    uint64_t wpre = 0, total = 0;
+    for (uint32_t w = 0; w < 32; w++) { const uint64_t v = warp_sums[w]; if (w < warp) wpre += v; total += v; }
+    uint64_t run = wpre + incl - sum;
+    for (uint32_t i = lo; i < hi; i++) { const uint64_t v = tile_state[i]; tile_state[i] = run; run += v; }
+    if (tid == 0) { *out_total = total; *ticket = 0; }         // pass B hands the tiles out again from 0
 }
 
 // ---------------------------------------------------------------------- kernel ----
@@ -234,7 +209,7 @@ __device__ __forceinline__ void copy_out(uint8_t* __restrict__ out, const uint8_
 
 // EXT is a compile-time switch so that the plain framing kernel carries none of the registers of the optional
 // stages (content inspection, interest lookup).
-template <bool EXT>
+template <bool EXT, int MODE>
 __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* s_in = smem;                                   // in_cap + 32 (word reads run up to 24 bytes past a record)
@@ -311,14 +286,15 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
                 bool valid = true;
                 if (streaming) {          // a conversation slot may be touched once per launch: stamp it with the launch epoch
                     slot = a.conv_slot[r0 + tid];
-                    valid = slot < a.conv_slots && atomicExch(&a.conv_epoch[slot], a.epoch) != a.epoch;
+                    // (the counting pass of ordered mode is a dry run: it neither stamps nor commits conversation state)
+                    valid = slot < a.conv_slots && (MODE == MODE_ORDERED_COUNT || atomicExch(&a.conv_epoch[slot], a.epoch) != a.epoch);
                     if (valid) state_in = a.conv_state[slot]; else atomicExch(a.dup_conv, 1u);
                 }
                 if (valid) {
                     bool done_fast = false;
                     if (fastp && !pl.tok_esc) { PtrSrc src{s_in}; done_fast = inspect_raw(t, dcache, src, o + pl.tok_b, o + pl.tok_e, state_in, eot, io); }
                     if (!done_fast) io = inspect_slow(a.insp, sb, o + pl.tok_b, o + pl.tok_e, state_in, eot);
-                    if (streaming) a.conv_state[slot] = io.state;
+                    if (streaming && MODE != MODE_ORDERED_COUNT) a.conv_state[slot] = io.state;
                 }
                 if (a.op & OP_INSPECT_INLINE) {                               // sse_handler.go:200-207
                     const uint32_t act = io.verdict & 0xFF;
@@ -336,7 +312,7 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
                     }
                 }
             }
-            if (active) {
+            if (active && MODE != MODE_ORDERED_COUNT) {
                 a.verdict[r0 + tid] = io.verdict;
                 a.match[2 * (size_t)(r0 + tid)] = io.begin;
                 a.match[2 * (size_t)(r0 + tid) + 1] = io.end;
@@ -352,7 +328,7 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
                 if (!done_fast) h = interest_slow(a, smem_in ? s_in : a.in + abase, o, pl.cid_b, pl.cid_e);
                 if (h.list_cnt == 0 && h.wild_mask == 0) { st = ST_NO_INTEREST; len = 0; }   // nobody subscribed: nothing to frame
             }
-            if (active) {
+            if (active && MODE != MODE_ORDERED_COUNT) {
                 const size_t k = 3 * (size_t)(r0 + tid);
                 a.hit[k] = h.list_off; a.hit[k + 1] = h.list_cnt; a.hit[k + 2] = h.wild_mask;
             }
@@ -371,17 +347,22 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
         uint32_t wpre = 0, total = 0;
 #pragma unroll
         for (int w = 0; w < TILE / 32; w++) { uint32_t v = ts->wsum[w]; if (w < (int)warp) wpre += v; total += v; }
-        const bool ordered = (a.op & OP_ORDERED) != 0;                        // launch-uniform
+        if (MODE == MODE_ORDERED_COUNT) {        // pass A of ordered mode: only the tile's byte count is wanted
+            if (tid == 0) {
+                a.tile_state[tile] = total;
+                setup_tile(a, ts, s_in, next_t, c_in);                        // every thread is past (B): the tile has been consumed
+            }
+            continue;
+        }
+        constexpr bool ordered = MODE == MODE_ORDERED_EMIT;
         const bool smem_out = total <= a.out_cap_smem();                      // tile-uniform
         // arrival-order placement: every tile owns a 16-byte aligned slice of the arena, so its staging
         // tile leaves as ONE TMA bulk store; the <=15 pad bytes after its last frame are zeroed.
         const uint32_t alloc = ordered ? total : ((total + 15u) & ~15u);
         if (tid == 0) {
             c_out += total;
-            if (ordered) publish_aggregate(a.tile_state, tile, total);
-            else {
-                ts->base = atomicAdd(a.cursor, (unsigned long long)alloc);    // nothing to wait for
-            }
+            if (ordered) ts->base = a.tile_state[tile];                       // exclusive prefix from k_scan_tile_totals
+            else ts->base = atomicAdd(a.cursor, (unsigned long long)alloc);   // nothing to wait for
         }
         const uint32_t local = wpre + incl - len;
         const uint32_t code = st & ST_CODE_MASK;
@@ -405,20 +386,9 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
                 fence_proxy_async_smem();                                     // staging writes -> visible to the TMA store
             }
             __syncthreads();                                                  // (D) s_in free, staging tile complete, base visible
-            if (warp == 0) {
-                if (lane == 0) setup_tile(a, ts, s_in, next_t, c_in);         // next tile's TMA load flies during the copy-out
-                if (ordered) {
-                    uint64_t excl = lookback(a.tile_state, tile, total, lane);
-                    if (lane == 0) ts->base = excl;
-                }
-            }
-            if (ordered) __syncthreads();                                     // (E)
+            if (tid == 0) setup_tile(a, ts, s_in, next_t, c_in);              // next tile's TMA load flies during the copy-out
         } else {
             // ---- oversize tile: emit straight into the arena ---------------------------
-            if (ordered && warp == 0) {
-                uint64_t excl = lookback(a.tile_state, tile, total, lane);
-                if (lane == 0) ts->base = excl;
-            }
             __syncthreads();                                                  // (D')
         }
         const uint64_t base = ts->base;
@@ -461,15 +431,15 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
         for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o2);
         if (lane == 0 && v) atomicAdd(&row[k], (unsigned long long)v);
     }
-    if (tid == 0) {
+    if (tid == 0 && MODE != MODE_ORDERED_COUNT) {
         if (c_in) atomicAdd(&row[6], (unsigned long long)c_in);
         if (c_out) atomicAdd(&row[7], (unsigned long long)c_out);
-        // the CTA that finishes last publishes the arena's total size as out_off[n]
-        __threadfence();
-        if (atomicAdd(a.done_ctas, 1u) == gridDim.x - 1) {
+        if (MODE == MODE_ARRIVAL) {     // the CTA that finishes last publishes the arena's total size as out_off[n]
             __threadfence();
-            a.out_off[a.n] = (a.op & OP_ORDERED) ? (ld_relaxed_u64(&a.tile_state[a.num_tiles - 1]) & VAL_MASK)
-                                                 : (uint64_t)atomicAdd(a.cursor, 0ull);
+            if (atomicAdd(a.done_ctas, 1u) == gridDim.x - 1) {
+                __threadfence();
+                a.out_off[a.n] = (uint64_t)atomicAdd(a.cursor, 0ull);
+            }
         }
     }
 }
@@ -481,20 +451,35 @@ static int g_ctas_per_sm[64][2];
 // Shared memory per CTA: a tile of TILE records is ~17 KB in / ~21 KB out at the BASELINE workload; the caps leave
 // ~15% slack.  Tiles that exceed them take the direct global-memory path inside the same kernel.  The EXT kernel
 // (inspection / interest lookup) adds the on-chip DFA cache.
+template <bool EXT, int MODE>
+static cudaError_t configure_one(int device, uint32_t sm, int* per_sm) {
+    cudaError_t e = cudaFuncSetAttribute(k_frame_tiles<EXT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    if (e != cudaSuccess) return e;
+    int per = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<EXT, MODE>, TILE, sm);
+    if (e != cudaSuccess) return e;
+    *per_sm = per < 1 ? 1 : per;
+    (void)device;
+    return cudaSuccess;
+}
+
 static cudaError_t configure_variant(int device, bool ext, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
     const uint32_t ic = 20 * 1024, oc = 24 * 1024;
     const uint32_t sm = ic + 32 + oc + 48 + (uint32_t)sizeof(TileSmem) + (ext ? DFA_CACHE_BYTES : 0u);
-    cudaError_t e = ext ? cudaFuncSetAttribute(k_frame_tiles<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)
-                        : cudaFuncSetAttribute(k_frame_tiles<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    if (e != cudaSuccess) return e;
     if (g_ctas_per_sm[device][ext] == 0) {
-        int sms = 0, per = 0;
-        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        int sms = 0, per = 0, p1 = 0, p2 = 0;
+        cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         if (e != cudaSuccess) return e;
-        e = ext ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<true>, TILE, sm)
-                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<false>, TILE, sm);
-        if (e != cudaSuccess) return e;
-        if (per < 1) per = 1;
+        if (ext) {
+            if ((e = configure_one<true, MODE_ARRIVAL>(device, sm, &per)) != cudaSuccess) return e;
+            if ((e = configure_one<true, MODE_ORDERED_COUNT>(device, sm, &p1)) != cudaSuccess) return e;
+            if ((e = configure_one<true, MODE_ORDERED_EMIT>(device, sm, &p2)) != cudaSuccess) return e;
+        } else {
+            if ((e = configure_one<false, MODE_ARRIVAL>(device, sm, &per)) != cudaSuccess) return e;
+            if ((e = configure_one<false, MODE_ORDERED_COUNT>(device, sm, &p1)) != cudaSuccess) return e;
+            if ((e = configure_one<false, MODE_ORDERED_EMIT>(device, sm, &p2)) != cudaSuccess) return e;
+        }
+        per = min(per, min(p1, p2));
         g_num_sms[device] = sms;
         g_ctas_per_sm[device][ext] = per;
     }
@@ -509,6 +494,17 @@ cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uin
     return configure_variant(device, false, in_cap, out_cap, smem_bytes, grid);
 }
 
+template <bool EXT>
+static void launch_variant(const FrameArgs& a, int grid, uint32_t smem_bytes, cudaStream_t stream) {
+    if (a.op & OP_ORDERED) {
+        k_frame_tiles<EXT, MODE_ORDERED_COUNT><<<grid, TILE, smem_bytes, stream>>>(a);
+        k_scan_tile_totals<<<1, 1024, 0, stream>>>(a.tile_state, a.num_tiles, a.out_off + a.n, a.ticket);
+        k_frame_tiles<EXT, MODE_ORDERED_EMIT><<<grid, TILE, smem_bytes, stream>>>(a);
+    } else {
+        k_frame_tiles<EXT, MODE_ARRIVAL><<<grid, TILE, smem_bytes, stream>>>(a);
+    }
+}
+
 cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     uint32_t smem_bytes;
     int grid;
@@ -516,13 +512,13 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     cudaError_t e = configure_variant(device, ext, &a.in_cap, &a.out_cap_s, &smem_bytes, &grid);
     if (e != cudaSuccess) return e;
     a.num_tiles = (a.n + TILE - 1) / TILE;
-    // scratch: ticket + overflow flag + counters + tile status words, zeroed per launch
+    // scratch: ticket + overflow flag + cursor + counters + per-tile words, zeroed per launch
     e = cudaMemsetAsync(a.scratch_base, 0, scratch_bytes(a.n), stream);
     if (e != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
     if ((int)a.num_tiles < grid) grid = (int)a.num_tiles;
-    if (ext) k_frame_tiles<true><<<grid, TILE, smem_bytes, stream>>>(a);
-    else k_frame_tiles<false><<<grid, TILE, smem_bytes, stream>>>(a);
+    if (ext) launch_variant<true>(a, grid, smem_bytes, stream);
+    else launch_variant<false>(a, grid, smem_bytes, stream);
     return cudaGetLastError();
 }
 

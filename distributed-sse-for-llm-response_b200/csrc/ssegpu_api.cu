@@ -345,7 +345,7 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     {
         std::lock_guard<std::mutex> lk(ctx->mu);
         b->state = SUBMITTED;
-        ctx->launches += n ? 1 : 0;
+        ctx->launches += n ? ((op & SSEGPU_OP_ORDERED) ? 3 : 1) : 0;   // ordered mode: count pass, scan, emit pass
     }
     return SSEGPU_OK;
 }
@@ -425,7 +425,7 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
     CU(sse::frame_launch(ctx->cfg.device, a, st));
     std::lock_guard<std::mutex> lk(ctx->mu);
-    ctx->launches += n ? 1 : 0;
+    ctx->launches += n ? ((op & SSEGPU_OP_ORDERED) ? 3 : 1) : 0;
     return SSEGPU_OK;
 }
 

@@ -6,7 +6,7 @@
 // fragment the little that is left), and latency-critical host loops that cannot afford the
 // device-wide synchronisation cudaMalloc/cudaFree imply.  Such a caller brings its own input and
 // output buffers; the only other memory the kernel needs is its per-launch scratch (tile ticket,
-// arena cursor, counter rows, one look-back word per tile), and here that scratch is a fixed
+// arena cursor, counter rows, one word per tile), and here that scratch is a fixed
 // array that is part of the library image instead of a cudaMalloc'ed block.
 //
 // The array below is a `static __device__` object: every GPU on which this library is loaded
@@ -70,7 +70,7 @@ int ssegpu_frame_launch_static(int device, const void* d_in, const uint32_t* d_i
     }
     if (n > SSEGPU_STATIC_MAX_RECORDS) {
         snprintf(g_err, sizeof g_err, "n_records = %u exceeds SSEGPU_STATIC_MAX_RECORDS = %u: the built-in scratch array holds "
-                 "one look-back word per tile for at most that many records; split the batch or use ssegpu_frame_launch",
+                 "one scratch word per tile for at most that many records; split the batch or use ssegpu_frame_launch",
                  n, (unsigned)SSEGPU_STATIC_MAX_RECORDS);
         return SSEGPU_E_TOOBIG;
     }
@@ -90,7 +90,7 @@ int ssegpu_frame_launch_static(int device, const void* d_in, const uint32_t* d_i
     a.out = static_cast<uint8_t*>(d_out); a.out_cap = out_cap; a.out_off = d_out_off; a.out_len = d_out_len;
     a.subj_len = d_subj_len; a.status = d_status;
     sse::scratch_carve(scratch, a);                  // the DEVICE address, never the symbol's name
-    // frame_launch clears scratch_bytes(n) of the array on `stream` (ticket, cursor, counters, look-back words
+    // frame_launch clears scratch_bytes(n) of the array on `stream` (ticket, cursor, counters, per-tile words
     // must start at zero; the array still holds the previous call's values) and launches the kernel.
     e = sse::frame_launch(device, a, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) { snprintf(g_err, sizeof g_err, "launch: %s", cudaGetErrorString(e)); return SSEGPU_E_CUDA; }

@@ -73,9 +73,10 @@ typedef enum {
                                     subscriber ids (ssegpu_sub_span); records nobody subscribed to are not framed
                                     (status SSEGPU_ST_NO_INTEREST) */
 #define SSEGPU_OP_ORDERED   8u   /* lay the frames out back to back in record order (the arena then equals the
-                                    sequential Go output byte for byte).  Default: each tile of 128 consecutive
-                                    records lands 16-byte aligned in completion order (<=15 zero bytes between
-                                    tiles); every frame is still out[out_off[i] .. out_off[i]+out_len[i]) */
+                                    sequential Go output byte for byte); costs a second decode pass.  Default: each
+                                    tile of 128 consecutive records lands 16-byte aligned in completion order (<=15
+                                    zero bytes between tiles); every frame is still
+                                    out[out_off[i] .. out_off[i]+out_len[i]) */
 
 typedef struct ssegpu_ctx ssegpu_ctx;
 typedef struct ssegpu_batch ssegpu_batch;
@@ -206,7 +207,7 @@ uint64_t ssegpu_launch_count(ssegpu_ctx *ctx);
  * allocate GPU memory: a service sharing its GPU with an inference server that has already reserved nearly
  * all of HBM, or a latency-critical loop that cannot take the device-wide synchronisation of cudaMalloc.
  * Same computation as ssegpu_frame_launch, but context-free: the kernel's scratch (tile ticket, arena
- * cursor, counter rows, one look-back word per tile) lives in a fixed array inside the library image
+ * cursor, counter rows, one word per tile) lives in a fixed array inside the library image
  * (SSEGPU_STATIC_SCRATCH_BYTES per GPU that loads the library, held until the process exits) and the call
  * performs no cudaMalloc / cudaFree / pinned allocation.  The caller supplies every input and output
  * buffer (same requirements as ssegpu_frame_launch).
