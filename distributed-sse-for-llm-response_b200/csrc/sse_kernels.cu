@@ -17,8 +17,9 @@
 //     one-CTA scan over the tile totals (see "ordered placement" below);
 //   * frames are assembled in a shared-memory staging tile BEFORE the tile's global offset is
 //     needed (the slice comes back from the atomic cursor while the frames are being written),
-//     then leave as coalesced 16-byte vector stores, byte-shifted on the fly to the arena's
-//     alignment, plus at most 15 head and 15 tail bytes: HBM sees only full-line traffic.
+//     then leave as ONE TMA bulk store into the tile's 16-byte aligned slice (ordered mode:
+//     coalesced 16-byte vector stores, byte-shifted on the fly to the dense arena's alignment,
+//     plus at most 15 head and 15 tail bytes): HBM sees only full-line traffic.
 //   No tensor cores: nothing here is a contraction.
 #include <cuda_runtime.h>
 #include <stdint.h>

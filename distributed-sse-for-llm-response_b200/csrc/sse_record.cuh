@@ -514,7 +514,7 @@ template <class Src> SSE_HD bool check_canon_tail_int(const Src& s, uint32_t pos
     uint32_t ws[6] = {funnel_r(x0, x1, shb), funnel_r(x1, x2, shb), funnel_r(x2, x3, shb), funnel_r(x3, x4, shb), funnel_r(x4, x5, shb), x5 >> shb};
     const uint32_t neg = ((ws[0] & 0xFF) == '-') ? 1u : 0u;
     if (neg) {                                                  // drop the sign byte (timestamps are positive in practice)
-#if defined(__CUDACC__)
+#if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
         for (int k = 0; k < 5; k++) ws[k] = funnel_r(ws[k], ws[k + 1], 8);
@@ -526,7 +526,7 @@ template <class Src> SSE_HD bool check_canon_tail_int(const Src& s, uint32_t pos
     ok = ok && !(d0 == '0' && (nd != 1 || neg));                // leading zero, "-0"
     ok = ok && !(nd == 19 && d0 == '9');                        // might overflow: exact check in the general path
     uint32_t bad = 0;
-#if defined(__CUDACC__)
+#if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
     for (int k = 0; k < 5; k++) {
