@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(1024) k_scan_tile_totals(uint64_t* tile_state,
 struct TileSmem {
     uint64_t mbar;
     uint64_t base;           // global byte offset of the tile's output
-    uint32_t tile, tb, te, pad;
+    uint32_t tile, tb, te, in_total;
     uint32_t wsum[TILE / 32];
 };
 
@@ -142,7 +142,10 @@ __device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uin
     if (t < a.num_tiles) {
         const uint32_t r0 = t * TILE;
         const uint32_t nrec = min((uint32_t)TILE, a.n - r0);
-        const uint32_t tb = a.in_off[r0], te = a.in_off[r0 + nrec];
+        // offsets come from the host: clamp them so that nothing below can leave the arena, and say so
+        const uint32_t in_total = ts->in_total;
+        uint32_t tb = a.in_off[r0], te = a.in_off[r0 + nrec];
+        if (te > in_total || tb > te) { atomicExch(a.bad_offsets, 1u); te = min(te, in_total); tb = min(tb, te); }
         ts->tb = tb; ts->te = te;
         const uint32_t abase = tb & ~15u;
         const uint32_t bytes = (te - abase + 15u) & ~15u;
@@ -235,6 +238,7 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
     }
     if (tid == 0) {
         mbar_init(&ts->mbar, 1);
+        ts->in_total = a.in_off[a.n];
         setup_tile(a, ts, s_in, atomicAdd(a.ticket, 1u), c_in);
     }
 
@@ -257,6 +261,10 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
         if (active) {
             my_b = a.in_off[r0 + tid];
             my_e = a.in_off[r0 + tid + 1];
+            if (my_b < tb || my_e > te || my_b > my_e) {                     // malformed offsets: clamp into the tile
+                atomicExch(a.bad_offsets, 1u);
+                my_e = min(max(my_e, tb), te); my_b = min(max(my_b, tb), my_e);
+            }
             if (a.start_seq) my_start = a.start_seq[r0 + tid];
         }
         if (smem_in && in_bytes != 0) { mbar_wait(&ts->mbar, parity); parity ^= 1; }

@@ -12,7 +12,7 @@ struct InterestDev;              // sse_interest.cuh
 constexpr int TILE = 128;        // records per tile == threads per CTA
 constexpr int CTR_ROWS = 64;     // counter rows (CTA i adds into row i % CTR_ROWS; the host sums rows)
 constexpr int CTR_COLS = 8;      // ok, syntax, type, filtered, done, fast, bytes_in, bytes_out
-constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32, [20] duplicate-conversation flag u32
+constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32, [20] duplicate-conversation flag u32, [24] bad-offsets flag u32
 
 struct FrameArgs {
     const uint8_t* in;           // packed payload arena, 16-byte aligned, 32 readable bytes after the last record
@@ -44,6 +44,7 @@ struct FrameArgs {
     unsigned long long* cursor;  // arrival-order placement: next free output byte
     uint32_t* done_ctas;
     uint32_t* dup_conv;
+    uint32_t* bad_offsets;       // set when in_off was not monotonic / ran past in_off[n] (records are clamped, never read out of bounds)
     unsigned long long* counters;
     uint64_t* tile_state;
     // filled by frame_launch
@@ -64,6 +65,7 @@ inline void scratch_carve(void* base, FrameArgs& a) {
     a.cursor = reinterpret_cast<unsigned long long*>(p + 8);
     a.done_ctas = reinterpret_cast<uint32_t*>(p + 16);
     a.dup_conv = reinterpret_cast<uint32_t*>(p + 20);
+    a.bad_offsets = reinterpret_cast<uint32_t*>(p + 24);
     a.counters = reinterpret_cast<unsigned long long*>(p + SCRATCH_HDR);
     a.tile_state = reinterpret_cast<uint64_t*>(p + SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8);
 }

@@ -370,7 +370,8 @@ int ssegpu_batch_wait(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t timeout_us) {
     const uint32_t overflow = reinterpret_cast<const uint32_t*>(b->h_hdr)[1];
     b->total_out = b->h_out_off[b->n];
     int rc = SSEGPU_OK;
-    if (reinterpret_cast<const uint32_t*>(b->h_hdr)[5]) rc = SSEGPU_E_DUPCONV;
+    if (reinterpret_cast<const uint32_t*>(b->h_hdr)[6]) rc = SSEGPU_E_INVAL;           // in_off was not monotonic
+    else if (reinterpret_cast<const uint32_t*>(b->h_hdr)[5]) rc = SSEGPU_E_DUPCONV;
     else if (overflow) rc = SSEGPU_E_OVERFLOW;
     else if (b->total_out > b->spec_out) {
         CU(cudaMemcpyAsync(b->h_out + b->spec_out, b->d_out + b->spec_out, b->total_out - b->spec_out, cudaMemcpyDeviceToHost, b->stream));
@@ -434,6 +435,7 @@ int ssegpu_frame_launch_result(ssegpu_ctx* ctx, ssegpu_counters* out) {
     CU(cudaSetDevice(ctx->cfg.device));
     CU(cudaMemcpy(ctx->h_launch_hdr, ctx->d_launch_scratch, sse::scratch_readback_bytes(), cudaMemcpyDeviceToHost));
     if (out) add_rows(ctx->h_launch_hdr, out, 0);
+    if (reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[6]) return SSEGPU_E_INVAL;
     if (reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[5]) return SSEGPU_E_DUPCONV;
     return reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[1] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
 }

@@ -208,3 +208,29 @@ def test_device_resident_launch_full_size_properties(pkg, oracle, op):
             sum(b"event: token\nid: \ndata: \n\n") * n + int(sum((ord(ch) for s in (np.arange(n_tok) + 1).astype(str) for ch in s))) * n_conv
     finally:
         eng.close()
+
+
+def test_malformed_offsets_are_refused_not_followed(pkg, oracle):
+    """in_off that is not monotonic or runs past in_off[n] must neither crash nor read outside the arena."""
+    arena, off = pkg.workload.generate(1, 300, 2)
+    n = len(off) - 1
+    e = pkg.SseGpu(device=0, max_records=4096, max_in_bytes=1 << 20, ring_slots=1)
+    try:
+        for mutate in (lambda o: o.__setitem__(100, o[100] + 5000000), lambda o: o.__setitem__(200, 3),
+                       lambda o: o.__setitem__(slice(50, 60), o[50:60][::-1].copy())):
+            bad = off.copy()
+            mutate(bad)
+            b = e.acquire()
+            b.fill(arena, off)
+            b.in_off[: n + 1] = bad
+            b.submit(n, 0)
+            with pytest.raises(pkg.SseGpuError) as err:
+                b.wait()
+            assert err.value.code == -1
+            b.release()
+        # and a good batch afterwards is processed normally
+        out, out_off, status, _ = run_batch(e, arena, off)
+        want_out, want_off, want_status = oracle.adapter(arena, off)
+        assert np.array_equal(out, want_out) and np.array_equal(status, want_status)
+    finally:
+        e.close()

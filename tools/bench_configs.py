@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
-"""Measurements for BASELINE.json configs 2, 3 and 4 (bench.py covers config 1, the headline).
+"""Measurements for BASELINE.json configs 0, 2, 3 and 4 (bench.py covers config 1, the headline).
 
-  python tools/bench_configs.py [--config 2|3|4|all] [--scale S]
+  python tools/bench_configs.py [--config 0|2|3|4|all] [--scale S]
 
 One JSON line per measurement.  Device-resident inputs, CUDA events on the launching stream, >= 3 warm-up launches.
 config 2  full inspection pattern set (Set A and Set A+B) on 100 000 conversations: per-token mode in one launch and
@@ -75,6 +75,34 @@ class DevBatch:
         eng.frame_launch(self.d_in.data_ptr(), self.d_off.data_ptr(), 0, self.n, op, self.d_out.data_ptr(), self.cap,
                          self.d_out_off.data_ptr(), self.d_out_len.data_ptr(), self.d_subj.data_ptr(), self.d_status.data_ptr(),
                          stream.cuda_stream)
+
+
+def config0(pkg, scale):
+    """configs[0]: the reference's own CPU-runnable case -- 1 000 conversations x 512 load-generator tokens."""
+    import oracle_lib
+    oracle = oracle_lib.load()
+    arena, off = pkg.workload.generate(0, int(1000 * scale), 512)
+    n = len(off) - 1
+    stream = torch.cuda.Stream()
+    eng = pkg.SseGpu(device=0, max_records=n, max_in_bytes=1 << 20)
+    db = DevBatch(arena, off)
+    ms = time_launches(lambda: db.launch(eng, 0, stream), stream, 10)
+    rc, c = eng.launch_result()
+    threads = os.cpu_count() or 1
+    sec, frames, out_bytes = oracle.bench_adapter(arena, off, threads, reps=3)
+    sec1, _, _ = oracle.bench_adapter(arena, off, 1, reps=2)
+    # bit-exact against the oracle on the whole config
+    want_out, want_off, want_status = oracle.adapter(arena, off)
+    from gpu_util import normalise
+    out, out_off = normalise(db.d_out.cpu().numpy(), db.d_out_off.cpu().numpy().astype(np.uint64),
+                             db.d_out_len.cpu().numpy().astype(np.uint32), False)
+    assert np.array_equal(out, want_out) and np.array_equal(db.d_status.cpu().numpy().astype(np.uint32), want_status)
+    eng.close()
+    return [{"config": 0, "records": n, "payload_bytes": db.in_bytes, "frame_bytes": int(c["bytes_out"]), "gpu_ms_per_launch": ms,
+             "gpu_frames_per_sec": n / ms * 1e3, "gpu_alg_GBps": (db.in_bytes + c["bytes_out"] + 16 * n) / ms / 1e6,
+             "cpu_oracle_frames_per_sec_all_cores": frames / sec, "cpu_cores": threads, "cpu_oracle_frames_per_sec_1_core": frames / sec1,
+             "bit_exact_vs_oracle": True,
+             "note": "CPU arm = C restatement of the Go path (no Go toolchain on the box); 66 MB of input fits in L2, so this small config is not an HBM measurement"}]
 
 
 def config2(pkg, scale):
@@ -244,7 +272,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     args = ap.parse_args()
     pkg = load_package()
-    for name, fn in (("2", config2), ("3", config3), ("4", config4)):
+    for name, fn in (("0", config0), ("2", config2), ("3", config3), ("4", config4)):
         if args.config in ("all", name):
             for line in fn(pkg, args.scale):
                 print(json.dumps(line), flush=True)
