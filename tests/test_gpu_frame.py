@@ -234,3 +234,40 @@ def test_malformed_offsets_are_refused_not_followed(pkg, oracle):
         assert np.array_equal(out, want_out) and np.array_equal(status, want_status)
     finally:
         e.close()
+
+
+def test_api_error_paths(pkg, oracle):
+    """The ABI reports misuse with error codes instead of undefined behaviour."""
+    arena, off = pkg.workload.generate(1, 50, 2)
+    n = len(off) - 1
+    e = pkg.SseGpu(device=0, max_records=64, max_in_bytes=1 << 16, ring_slots=1)
+    try:
+        b = e.acquire()
+        with pytest.raises(pkg.SseGpuError) as err:          # ring of one slot is exhausted
+            e.acquire()
+        assert err.value.code == -4
+        with pytest.raises(pkg.SseGpuError) as err:          # wait before submit
+            b.wait()
+        assert err.value.code == -7
+        b.fill(arena, off[:61].copy())
+        with pytest.raises(pkg.SseGpuError) as err:          # more records than the slot holds
+            b.submit(n, 0)
+        assert err.value.code == -5
+        with pytest.raises(pkg.SseGpuError) as err:          # inspection requested without a loaded pattern set
+            b.submit(32, pkg.OP_INSPECT)
+        assert err.value.code == -7
+        with pytest.raises(pkg.SseGpuError) as err:          # interest lookup requested without a table
+            b.submit(32, pkg.OP_MATCH)
+        assert err.value.code == -7
+        b.submit(32, 0)                                      # and the slot is still usable afterwards
+        b.wait()
+        want_out, want_off, want_status = oracle.adapter(arena, off[:33].copy())
+        assert np.array_equal(b.status, want_status) and int(b.out_off[32]) >= int(want_off[32])
+        b.release()
+        b2 = e.acquire()                                     # released slot can be acquired again
+        b2.release()
+    finally:
+        e.close()
+    with pytest.raises(pkg.SseGpuError) as err:              # no such device
+        pkg.SseGpu(device=63, max_records=16, max_in_bytes=4096)
+    assert err.value.code == -2
