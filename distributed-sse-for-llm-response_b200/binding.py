@@ -99,6 +99,10 @@ def load_library():
     lib.ssegpu_frame_launch_result.argtypes = [vp, C.POINTER(Counters)]
     lib.ssegpu_launch_count.restype = C.c_uint64
     lib.ssegpu_launch_count.argtypes = [vp]
+    lib.ssegpu_encode_launch.restype = C.c_int
+    lib.ssegpu_encode_launch.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, C.c_uint32, C.c_uint32, vp, C.c_uint64, vp, vp, vp, vp]
+    lib.ssegpu_encode_launch_result.restype = C.c_int
+    lib.ssegpu_encode_launch_result.argtypes = [vp, C.POINTER(C.c_uint64)]
     lib.ssegpu_interest_apply.restype = C.c_int
     lib.ssegpu_interest_apply.argtypes = [vp, C.POINTER(SubDelta), C.c_uint32]
     lib.ssegpu_interest_subs.restype = u32p
@@ -275,6 +279,21 @@ class SseGpu:
         if rc not in (0, E_OVERFLOW):
             self._check(rc)
         return rc, c.as_dict()
+
+    def encode_launch(self, d_cid, d_cid_off, d_tok, d_tok_off, d_seq, d_done, d_ts, n, op, d_out, out_cap, d_out_off, d_out_len,
+                      d_chan_len=0, stream=0):
+        """Producer-side batch encode (publishToken, llm-stream-proxy/main.go:230-245); raw device addresses, asynchronous."""
+        self._check(self.lib.ssegpu_encode_launch(self.ctx, d_cid or None, d_cid_off or None, d_tok or None, d_tok_off or None,
+                                                  d_seq or None, d_done or None, d_ts or None, n, op, d_out or None, out_cap, d_out_off,
+                                                  d_out_len or None, d_chan_len or None, stream or None))
+
+    def encode_result(self):
+        """-> (rc, bytes used); call after the stream has been synchronised."""
+        used = C.c_uint64(0)
+        rc = self.lib.ssegpu_encode_launch_result(self.ctx, C.byref(used))
+        if rc not in (0, E_OVERFLOW):
+            self._check(rc)
+        return rc, used.value
 
     def launch_count(self):
         return int(self.lib.ssegpu_launch_count(self.ctx))

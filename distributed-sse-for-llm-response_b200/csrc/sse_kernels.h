@@ -70,6 +70,24 @@ inline void scratch_carve(void* base, FrameArgs& a) {
     a.tile_state = reinterpret_cast<uint64_t*>(p + SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8);
 }
 
+// producer-side encoder (sse_encode.cu)
+struct EncodeArgs {
+    const uint8_t* cid; const uint32_t* cid_off;   // conversation ids, packed, n+1 offsets
+    const uint8_t* tok; const uint32_t* tok_off;   // token texts, packed, n+1 offsets
+    const int64_t* seq; const uint8_t* done; const int64_t* ts;
+    uint32_t n, op;                                // OP_BRIDGE: prepend the channel "chat.<id>.tokens"; OP_GO122
+    uint8_t* out; uint64_t out_cap; uint64_t* out_off; uint32_t* out_len; uint32_t* chan_len;
+    void* scratch_base; uint32_t* overflow; unsigned long long* cursor; uint32_t* done_ctas;
+};
+inline void encode_scratch_carve(void* base, EncodeArgs& a) {
+    uint8_t* p = static_cast<uint8_t*>(base);
+    a.scratch_base = base;
+    a.overflow = reinterpret_cast<uint32_t*>(p + 4);
+    a.cursor = reinterpret_cast<unsigned long long*>(p + 8);
+    a.done_ctas = reinterpret_cast<uint32_t*>(p + 16);
+}
+cudaError_t encode_launch(EncodeArgs a, cudaStream_t stream);
+
 cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid);
 cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream);
 

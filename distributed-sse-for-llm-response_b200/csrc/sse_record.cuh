@@ -309,6 +309,47 @@ template <class Src, class W> SSE_HD void put_json_string(const Src& s, uint32_t
     w.put('"');
 }
 
+// encode.go appendString(escapeHTML=true) over a RAW Go string (not a JSON literal): bytes that do not start a
+// valid UTF-8 sequence become the six characters \ufffd, one per byte (producer side: llm-stream-proxy/main.go:230-239).
+template <class Src, class W> SSE_HD void put_go_string(const Src& s, uint32_t b, uint32_t e, W& w, bool go122) {
+    w.put('"');
+    while (b < e) {
+        uint32_t r;
+        const uint32_t n = utf8_decode(s, b, e, r);
+        if (r == 0xFFFD && n == 1) { w.put('\\'); w.put('u'); w.put('f'); w.put('f'); w.put('f'); w.put('d'); }
+        else put_rune_json(w, r, go122);
+        b += n;
+    }
+    w.put('"');
+}
+
+// json.Marshal(TokenMessage{...}) from columnar fields; with_channel prepends the Redis channel / NATS subject
+// "chat." + id + ".tokens" built from the raw id (llm-stream-proxy/main.go:240).
+template <class Src, class W>
+SSE_HD uint32_t encode_message(const Src& cid, uint32_t cb, uint32_t ce, const Src& tok, uint32_t tb, uint32_t te, int64_t seq, bool done,
+                               int64_t ts, bool go122, bool with_channel, W& w) {
+    uint32_t chan = 0;
+    if (with_channel) {
+        SSE_PUT_LIT(w, "chat.");
+        for (uint32_t i = cb; i < ce; i++) w.put(cid.ld8(i));
+        SSE_PUT_LIT(w, ".tokens");
+        chan = 12 + (ce - cb);
+    }
+    SSE_PUT_LIT(w, "{\"conversation_id\":");
+    put_go_string(cid, cb, ce, w, go122);
+    SSE_PUT_LIT(w, ",\"token\":");
+    put_go_string(tok, tb, te, w, go122);
+    SSE_PUT_LIT(w, ",\"sequence\":");
+    put_int(w, seq);
+    SSE_PUT_LIT(w, ",\"done\":");
+    if (done) SSE_PUT_LIT(w, "true"); else SSE_PUT_LIT(w, "false");
+    SSE_PUT_LIT(w, ",\"timestamp\":");
+    put_int(w, ts);
+    w.put('}');
+    w.finish();
+    return chan;
+}
+
 // verbatim copy of n source bytes starting at byte position sp: bytes until the destination is
 // word aligned, then one aligned load + funnel shift + aligned store per word (the relative
 // alignment of source and destination is constant), then the tail bytes.  NF: the writer's

@@ -62,6 +62,7 @@ struct ssegpu_ctx {
     cudaStream_t stream = nullptr;
     void* d_launch_scratch = nullptr;     // for ssegpu_frame_launch
     uint8_t* h_launch_hdr = nullptr;
+    void* d_encode_scratch = nullptr;     // for ssegpu_encode_launch (header only)
     std::vector<ssegpu_batch*> slots;
     std::mutex mu;
     ssegpu_counters totals{};
@@ -236,6 +237,7 @@ int ssegpu_init(const ssegpu_config* cfg, ssegpu_ctx** out) {
         if (e != cudaSuccess) { rc = cuda_fail(e, "frame_configure"); break; }
         if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(e, "cudaStreamCreate"); break; }
         if ((e = cudaMalloc(&ctx->d_launch_scratch, sse::scratch_bytes(cfg->max_records))) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc scratch"); break; }
+        if ((e = cudaMalloc(&ctx->d_encode_scratch, sse::SCRATCH_HDR)) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc scratch"); break; }
         if ((e = cudaHostAlloc(&ctx->h_launch_hdr, sse::scratch_readback_bytes(), cudaHostAllocDefault)) != cudaSuccess) { rc = cuda_fail(e, "cudaHostAlloc"); break; }
         for (uint32_t i = 0; i < cfg->ring_slots; i++) {
             ssegpu_batch* b = nullptr;
@@ -255,6 +257,7 @@ void ssegpu_destroy(ssegpu_ctx* ctx) {
     cudaDeviceSynchronize();
     for (ssegpu_batch* b : ctx->slots) free_batch(b);
     cudaFree(ctx->d_launch_scratch);
+    cudaFree(ctx->d_encode_scratch);
     cudaFree(ctx->d_int_slots); cudaFree(ctx->d_int_keys); cudaFree(ctx->d_int_wild); cudaFree(ctx->d_interest);
     cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp); cudaFree(ctx->d_conv_state); cudaFree(ctx->d_conv_epoch);
     cudaFreeHost(ctx->h_launch_hdr);
@@ -438,6 +441,35 @@ int ssegpu_frame_launch_result(ssegpu_ctx* ctx, ssegpu_counters* out) {
     if (reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[6]) return SSEGPU_E_INVAL;
     if (reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[5]) return SSEGPU_E_DUPCONV;
     return reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[1] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
+}
+
+// ---- producer-side encode --------------------------------------------------------------------
+int ssegpu_encode_launch(ssegpu_ctx* ctx, const void* d_cid, const uint32_t* d_cid_off, const void* d_tok, const uint32_t* d_tok_off,
+                         const int64_t* d_seq, const uint8_t* d_done, const int64_t* d_ts, uint32_t n, uint32_t op,
+                         void* d_out, uint64_t out_cap, uint64_t* d_out_off, uint32_t* d_out_len, uint32_t* d_chan_len, void* stream) {
+    if (!ctx || !d_out_off || (op & ~(uint32_t)(SSEGPU_OP_BRIDGE | SSEGPU_OP_GO122))) return SSEGPU_E_INVAL;
+    if (n && (!d_cid || !d_cid_off || !d_tok || !d_tok_off || !d_seq || !d_done || !d_ts || !d_out || !d_out_len)) return SSEGPU_E_INVAL;
+    if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
+    CU(cudaSetDevice(ctx->cfg.device));
+    sse::EncodeArgs a{};
+    a.cid = static_cast<const uint8_t*>(d_cid); a.cid_off = d_cid_off; a.tok = static_cast<const uint8_t*>(d_tok); a.tok_off = d_tok_off;
+    a.seq = d_seq; a.done = d_done; a.ts = d_ts; a.n = n; a.op = op;
+    a.out = static_cast<uint8_t*>(d_out); a.out_cap = out_cap; a.out_off = d_out_off; a.out_len = d_out_len; a.chan_len = d_chan_len;
+    sse::encode_scratch_carve(ctx->d_encode_scratch, a);
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
+    CU(sse::encode_launch(a, st));
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->launches += n ? 1 : 0;
+    return SSEGPU_OK;
+}
+
+int ssegpu_encode_launch_result(ssegpu_ctx* ctx, uint64_t* out_bytes) {
+    if (!ctx) return SSEGPU_E_INVAL;
+    CU(cudaSetDevice(ctx->cfg.device));
+    uint32_t hdr[sse::SCRATCH_HDR / 4];
+    CU(cudaMemcpy(hdr, ctx->d_encode_scratch, sizeof hdr, cudaMemcpyDeviceToHost));
+    if (out_bytes) memcpy(out_bytes, &hdr[2], 8);
+    return hdr[1] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
 }
 
 // ---- content inspection --------------------------------------------------------------------

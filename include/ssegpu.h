@@ -199,6 +199,25 @@ int ssegpu_frame_launch(ssegpu_ctx *ctx, const void *d_in, const uint32_t *d_in_
  * returns SSEGPU_E_OVERFLOW if out_cap was too small. */
 int ssegpu_frame_launch_result(ssegpu_ctx *ctx, ssegpu_counters *out);
 
+/* ---- producer-side batch encode (row N3) ------------------------------------------------ */
+/* Replaces, for a batch of n messages, publishToken() of src/llm-stream-proxy/main.go:230-245 (and the
+ * load generator's producer, demo/load-generator/main.go:215-223): message i is
+ * json.Marshal(TokenMessage{cid_i, tok_i, seq[i], done[i] != 0, ts[i]}) -- field order, escapeHTML and the
+ * \ufffd replacement of invalid UTF-8 exactly as encoding/json -- written at d_out + d_out_off[i],
+ * d_out_len[i] bytes.  cid_i / tok_i are the RAW string bytes d_cid[d_cid_off[i] .. d_cid_off[i+1]) and likewise
+ * for tok.  With SSEGPU_OP_BRIDGE each record is preceded by its channel "chat.<cid>.tokens" (the PUBLISH
+ * channel, main.go:240) and d_chan_len[i] (may be NULL otherwise) receives the channel's length.  SSEGPU_OP_GO122
+ * selects the Go >= 1.22 spelling of \b and \f.  Records of one 128-message tile are contiguous and tiles
+ * start on 16-byte boundaries in completion order (as in the default frame launch); d_out_off[n] = bytes used.
+ * All pointers are device memory of this context's GPU.  Asynchronous on stream (NULL = the context's). */
+int ssegpu_encode_launch(ssegpu_ctx *ctx, const void *d_cid, const uint32_t *d_cid_off,
+                         const void *d_tok, const uint32_t *d_tok_off, const int64_t *d_seq,
+                         const uint8_t *d_done, const int64_t *d_ts, uint32_t n_messages,
+                         uint32_t op_flags, void *d_out, uint64_t out_cap, uint64_t *d_out_off,
+                         uint32_t *d_out_len, uint32_t *d_chan_len, void *stream);
+/* After the stream has been synchronised: bytes of d_out used; SSEGPU_E_OVERFLOW if out_cap was too small. */
+int ssegpu_encode_launch_result(ssegpu_ctx *ctx, uint64_t *out_bytes);
+
 /* Number of kernel launches this context has issued so far (bench.py "gpu_launches"). */
 uint64_t ssegpu_launch_count(ssegpu_ctx *ctx);
 

@@ -483,6 +483,35 @@ size_t sseo_marshal(const sseo_msg *m, uint8_t *d, int go122)
     return w;
 }
 
+/* Producer side: publishToken (llm-stream-proxy/main.go:230-245) and the load generator's producer
+ * (demo/load-generator/main.go:215-223) for n messages given as columns.  Record i = [channel "chat.<cid>.tokens"
+ * when with_channel (main.go:240)] + json.Marshal(TokenMessage{...}); records are packed back to back, off[i]..off[i+1]. */
+size_t sseo_encode_batch(const uint8_t *cid, const uint32_t *cid_off, const uint8_t *tok, const uint32_t *tok_off,
+                         const int64_t *seq, const uint8_t *done, const int64_t *ts, uint32_t n, int go122, int with_channel,
+                         uint8_t *out, size_t out_cap, uint64_t *off, uint32_t *chan_len)
+{
+    size_t w = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        sseo_msg m;
+        m.cid = cid + cid_off[i]; m.cid_len = cid_off[i + 1] - cid_off[i];
+        m.tok = tok + tok_off[i]; m.tok_len = tok_off[i + 1] - tok_off[i];
+        m.seq = seq[i]; m.done = done[i] != 0; m.ts = ts[i];
+        if (w + 12 + m.cid_len + sseo_marshal_bound(&m) > out_cap) return (size_t)-1;
+        off[i] = w;
+        uint32_t cl = 0;
+        if (with_channel) {
+            w += put(out + w, "chat.");
+            memcpy(out + w, m.cid, m.cid_len); w += m.cid_len;
+            w += put(out + w, ".tokens");
+            cl = 12 + m.cid_len;
+        }
+        if (chan_len) chan_len[i] = cl;
+        w += sseo_marshal(&m, out + w, go122);
+    }
+    off[n] = w;
+    return w;
+}
+
 size_t sseo_frame(const sseo_msg *m, uint8_t *d, int go122)
 {
     size_t w = 0;

@@ -57,6 +57,12 @@ int sseo_unmarshal(const uint8_t *data, size_t n, sseo_msg *m, uint8_t *scratch)
 size_t sseo_marshal(const sseo_msg *m, uint8_t *dst, int go122);
 size_t sseo_marshal_bound(const sseo_msg *m);
 
+/* Producer side (llm-stream-proxy/main.go:230-245, demo/load-generator/main.go:215-223): n messages from columns,
+ * packed back to back; returns bytes written or (size_t)-1 when out_cap is too small. */
+size_t sseo_encode_batch(const uint8_t *cid, const uint32_t *cid_off, const uint8_t *tok, const uint32_t *tok_off,
+                         const int64_t *seq, const uint8_t *done, const int64_t *ts, uint32_t n, int go122, int with_channel,
+                         uint8_t *out, size_t out_cap, uint64_t *off, uint32_t *chan_len);
+
 /* The three Fprintf calls (sse_handler.go:212-214, :428-430). Returns frame length. */
 size_t sseo_frame(const sseo_msg *m, uint8_t *dst, int go122);
 

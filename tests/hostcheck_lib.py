@@ -29,7 +29,23 @@ def load():
     lib.hc_inspect.restype = C.c_int
     lib.hc_inspect.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, u8p, u32p, C.c_uint32, u32p, C.c_uint32, u32p,
                                C.POINTER(C.c_int32), u32p, u32p]
+    lib.hc_encode.restype = C.c_int
+    lib.hc_encode.argtypes = [u8p, u32p, u8p, u32p, i64p, u8p, i64p, C.c_uint32, C.c_uint32, u8p, C.c_uint64, u64p, u32p]
     return lib
+
+
+def encode(lib, cols, op=0):
+    """cols = tests.encode_case.columns(...) -> (list of record bytes, chan_len)"""
+    cid, cid_off, tok, tok_off, seq, done, ts = cols
+    n = len(seq)
+    cap = (int(cid_off[n]) * 7 + int(tok_off[n]) * 6) + 128 * n + 64
+    out = np.zeros(cap, dtype=np.uint8)
+    out_off = np.empty(n + 1, dtype=np.uint64)
+    chan = np.empty(n, dtype=np.uint32)
+    rc = lib.hc_encode(_ptr(cid, u8p), _ptr(cid_off, u32p), _ptr(tok, u8p), _ptr(tok_off, u32p), _ptr(seq, i64p), _ptr(done, u8p),
+                       _ptr(ts, i64p), n, op, _ptr(out, u8p), cap, _ptr(out_off, u64p), _ptr(chan, u32p))
+    assert rc == 0, rc
+    return [out[int(out_off[i]):int(out_off[i + 1])].tobytes() for i in range(n)], chan
 
 
 class HcDelta(C.Structure):

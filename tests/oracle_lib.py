@@ -30,6 +30,22 @@ class Oracle:
         lib.sseo_fnv1a64.restype = C.c_uint64
         lib.sseo_fnv1a64.argtypes = [u8p, C.c_size_t]
 
+    def encode(self, cols, go122=False, with_channel=False):
+        """cols = tests.encode_case.columns(...) -> (list of record bytes, chan_len)"""
+        cid, cid_off, tok, tok_off, seq, done, ts = cols
+        n = len(seq)
+        cap = (int(cid_off[n]) * 7 + int(tok_off[n]) * 6) + 128 * n + 64
+        out = np.empty(cap, dtype=np.uint8)
+        off = np.empty(n + 1, dtype=np.uint64)
+        chan = np.empty(n, dtype=np.uint32)
+        self.lib.sseo_encode_batch.restype = C.c_size_t
+        self.lib.sseo_encode_batch.argtypes = [u8p, u32p, u8p, u32p, i64p, u8p, i64p, C.c_uint32, C.c_int, C.c_int, u8p, C.c_size_t, u64p, u32p]
+        w = self.lib.sseo_encode_batch(_ptr(cid, u8p), _ptr(cid_off, u32p), _ptr(tok, u8p), _ptr(tok_off, u32p), _ptr(seq, i64p),
+                                       _ptr(done, u8p), _ptr(ts, i64p), n, int(go122), int(with_channel), _ptr(out, u8p), cap,
+                                       _ptr(off, u64p), _ptr(chan, u32p))
+        assert w == int(off[n])
+        return [out[int(off[i]):int(off[i + 1])].tobytes() for i in range(n)], chan
+
     def inspector(self, patterns):
         """patterns: list of (kind, action, text-bytes) -> OracleInspector"""
         return OracleInspector(self.lib, patterns)

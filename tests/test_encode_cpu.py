@@ -1,0 +1,88 @@
+"""CPU tests of the producer-side encoder (row N3): oracle and the product's encode_message() (host test double) against
+the hand-written known answers and an independent Python model, and the round trip into the adapter path."""
+import numpy as np
+import pytest
+
+import encode_case as ec
+import hostcheck_lib as hc
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return hc.load()
+
+
+def test_model_against_hand_vectors():
+    for msg, want in ec.HAND:
+        assert ec.model_encode(msg) == want, msg
+    for msg, want in ec.HAND_GO122:
+        assert ec.model_encode(msg, go122=True) == want, msg
+
+
+def test_oracle_hand_vectors(oracle):
+    got, _ = oracle.encode(ec.columns([m for m, _ in ec.HAND]))
+    assert got == [w for _, w in ec.HAND]
+    got, _ = oracle.encode(ec.columns([m for m, _ in ec.HAND_GO122]), go122=True)
+    assert got == [w for _, w in ec.HAND_GO122]
+    got, chan = oracle.encode(ec.columns([m for m, _, _ in ec.HAND_CHANNEL]), with_channel=True)
+    assert got == [c + w for _, c, w in ec.HAND_CHANNEL]
+    assert list(chan) == [len(c) for _, c, _ in ec.HAND_CHANNEL]
+
+
+def test_hostcheck_hand_vectors(lib):
+    got, _ = hc.encode(lib, ec.columns([m for m, _ in ec.HAND]))
+    assert got == [w for _, w in ec.HAND]
+    got, _ = hc.encode(lib, ec.columns([m for m, _ in ec.HAND_GO122]), hc.OP_GO122)
+    assert got == [w for _, w in ec.HAND_GO122]
+    got, chan = hc.encode(lib, ec.columns([m for m, _, _ in ec.HAND_CHANNEL]), hc.OP_BRIDGE)
+    assert got == [c + w for _, c, w in ec.HAND_CHANNEL]
+    assert list(chan) == [len(c) for _, c, _ in ec.HAND_CHANNEL]
+
+
+@pytest.mark.parametrize("go122", [False, True])
+def test_random_messages_three_ways(lib, oracle, go122):
+    msgs = ec.random_messages(4000, seed=11 + go122)
+    cols = ec.columns(msgs)
+    want = [ec.model_encode(m, go122) for m in msgs]
+    got_o, _ = oracle.encode(cols, go122=go122)
+    got_h, _ = hc.encode(lib, cols, hc.OP_GO122 if go122 else 0)
+    assert got_o == want
+    assert got_h == want
+    got_o, chan_o = oracle.encode(cols, go122=go122, with_channel=True)
+    got_h, chan_h = hc.encode(lib, cols, hc.OP_BRIDGE | (hc.OP_GO122 if go122 else 0))
+    assert got_o == [ec.model_channel(m) + w for m, w in zip(msgs, want)]
+    assert got_h == got_o
+    assert (chan_o == chan_h).all() and list(chan_o) == [12 + len(m[0]) for m in msgs]
+
+
+def test_empty_batch(lib, oracle):
+    cols = ec.columns([])
+    assert oracle.encode(cols)[0] == []
+    assert hc.encode(lib, cols)[0] == []
+
+
+def test_encoded_payloads_take_the_adapter_fast_path(lib, oracle):
+    """whatever the producer emits is canonical: the adapter recognises it and frames it verbatim -- except that a
+    \\ufffd escape (an invalid byte at the producer) decodes to U+FFFD and is re-marshalled as its three UTF-8 bytes."""
+    def clean(raw):
+        return "".join(ch for ch, _ in ec.go_decode(raw)).encode("utf-8")
+
+    msgs = ec.random_messages(3000, seed=3)
+    payloads, _ = hc.encode(lib, ec.columns(msgs))
+    arena, off = oracle.pack(payloads)
+    out, out_off, _, status, nfast = hc.run(lib, arena, off, None, 0)
+    b = out.tobytes()
+    for i, m in enumerate(msgs):
+        assert int(status[i]) & 0xF == 0
+        assert bool(int(status[i]) & 0x100) == bool(m[3])
+        assert b[int(out_off[i]):int(out_off[i + 1])] == b"event: token\nid: %d\ndata: " % m[2] + ec.model_encode((clean(m[0]), clean(m[1])) + m[2:]) + b"\n\n"
+    o_out, o_off, o_status = oracle.adapter(arena, off)
+    assert o_out.tobytes() == b and (o_status == status).all()
+    # ordinary traffic (valid UTF-8, sequences of up to 8 digits) goes through the canonical fast lane, every record
+    plain = [m for m in msgs if m[0].startswith(b"conv-")]
+    payloads, _ = hc.encode(lib, ec.columns(plain))
+    arena, off = oracle.pack(payloads)
+    out, out_off, _, status, nfast = hc.run(lib, arena, off, None, 0)
+    assert nfast == len(plain) > 1000
+    assert [out.tobytes()[int(out_off[i]):int(out_off[i + 1])] for i in range(len(plain))] == \
+        [b"event: token\nid: %d\ndata: " % m[2] + p + b"\n\n" for m, p in zip(plain, payloads)]
