@@ -13,7 +13,12 @@
 
 namespace sse {
 
+constexpr uint32_t ENC_STAGE = 24 * 1024;       // staging tile: 128 records x up to 192 bytes (a config-1 record is ~133)
+
+__device__ __forceinline__ uint32_t enc_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
 __global__ void __launch_bounds__(TILE) k_encode_messages(const EncodeArgs a) {
+    __shared__ __align__(128) uint8_t s_out[ENC_STAGE + 16];
     __shared__ uint32_t wsum[TILE / 32];
     __shared__ unsigned long long s_base;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -21,18 +26,17 @@ __global__ void __launch_bounds__(TILE) k_encode_messages(const EncodeArgs a) {
     const bool active = i < a.n;
     const bool go122 = (a.op & OP_GO122) != 0, chan = (a.op & OP_BRIDGE) != 0;
     PtrSrc cid{a.cid}, tok{a.tok};
-    uint32_t cb = 0, ce = 0, tb = 0, te = 0, len = 0;
+    uint32_t cb = 0, ce = 0, tb = 0, te = 0;
     int64_t seq = 0, ts = 0;
     bool done = false;
+    EncPlan p{};
     if (active) {
         cb = a.cid_off[i]; ce = max(cb, a.cid_off[i + 1]);
         tb = a.tok_off[i]; te = max(tb, a.tok_off[i + 1]);
         seq = a.seq[i]; ts = a.ts[i]; done = a.done[i] != 0;
-        Ptr32Dst nd{nullptr};
-        Writer<Ptr32Dst, false> w(nd, 0);
-        encode_message(cid, cb, ce, tok, tb, te, seq, done, ts, go122, chan, w);
-        len = w.pos();
+        p = encode_plan(cid, cb, ce, tok, tb, te, seq, done, ts, go122, chan);
     }
+    const uint32_t len = p.len;
     uint32_t incl = len;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -45,23 +49,39 @@ __global__ void __launch_bounds__(TILE) k_encode_messages(const EncodeArgs a) {
 #pragma unroll
     for (int w = 0; w < TILE / 32; w++) { uint32_t v = wsum[w]; if (w < (int)warp) wpre += v; total += v; }
     const uint32_t alloc = (total + 15u) & ~15u;
-    if (tid == 0) s_base = atomicAdd(a.cursor, (unsigned long long)alloc);
+    if (tid == 0) s_base = atomicAdd(a.cursor, (unsigned long long)alloc);     // the answer is not needed until after the emission
+    const uint32_t local = wpre + incl - len;
+    const bool staged = alloc <= ENC_STAGE;                                      // tile-uniform
+    if (staged) {
+        if (active) {
+            Ptr32Dst d{s_out};
+            Writer<Ptr32Dst, true> w(d, local);
+            encode_emit(cid, cb, ce, tok, tb, te, seq, done, ts, go122, p, w);
+        }
+        if (tid < alloc - total) s_out[total + tid] = 0;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");             // staging writes -> visible to the bulk store
+    }
     __syncthreads();
     const uint64_t base = s_base;
     const bool fits = base + alloc <= a.out_cap;
-    const uint32_t local = wpre + incl - len;
-    if (active) {
-        uint32_t chan_len = 0;
-        if (fits) {
+    if (staged) {
+        if (tid == 0 && fits && alloc) {                                         // one TMA bulk store for the whole tile
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.out + base), "r"(enc_smem_u32(s_out)), "r"(alloc) : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+    } else if (fits) {                                                           // oversize tile: straight into the arena
+        if (active) {
             PtrDst d{a.out};
             Writer<PtrDst, true> w(d, base + local);
-            chan_len = encode_message(cid, cb, ce, tok, tb, te, seq, done, ts, go122, chan, w);
+            encode_emit(cid, cb, ce, tok, tb, te, seq, done, ts, go122, p, w);
         }
+        if (tid < alloc - total) a.out[base + total + tid] = 0;
+    }
+    if (active) {
         a.out_off[i] = base + local;
         a.out_len[i] = len;
-        if (a.chan_len) a.chan_len[i] = chan_len;
+        if (a.chan_len) a.chan_len[i] = p.chan;
     }
-    if (fits && tid < alloc - total) a.out[base + total + tid] = 0;
     if (tid == 0) {
         if (!fits) atomicExch(a.overflow, 1u);
         __threadfence();
@@ -69,6 +89,7 @@ __global__ void __launch_bounds__(TILE) k_encode_messages(const EncodeArgs a) {
             __threadfence();
             a.out_off[a.n] = (uint64_t)atomicAdd(a.cursor, 0ull);
         }
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
 }
 

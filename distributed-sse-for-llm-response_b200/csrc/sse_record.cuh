@@ -254,22 +254,37 @@ template <class W> SSE_HD void put_lit(W& w, const char* s, uint32_t n) {
 #define SSE_PUT_LIT(w, lit) put_lit(w, lit, (uint32_t)(sizeof(lit) - 1))
 #define SSE_PUT_LIT_NF(w, lit) put_lit_nf(w, lit, (uint32_t)(sizeof(lit) - 1))
 
+SSE_HD uint32_t digits_u32(uint32_t x) {               // x < 10^8
+    return 1u + (x >= 10u) + (x >= 100u) + (x >= 1000u) + (x >= 10000u) + (x >= 100000u) + (x >= 1000000u) + (x >= 10000000u);
+}
 SSE_HD uint32_t dec_digits(uint64_t u) {
-    uint32_t n = 1;
-    while (u >= 10) { u /= 10; n++; }
-    return n;
+    if (u < 100000000ull) return digits_u32((uint32_t)u);
+    if (u < 10000000000000000ull) return 8u + digits_u32((uint32_t)(u / 100000000ull));
+    return 16u + digits_u32((uint32_t)(u / 10000000000000000ull));
 }
 SSE_HD uint32_t dec_len(int64_t v) {                   // strconv.AppendInt / fmt %d length
     uint64_t u = v < 0 ? 0 - (uint64_t)v : (uint64_t)v;
     return dec_digits(u) + (v < 0 ? 1u : 0u);
 }
+SSE_HD uint32_t ascii4(uint32_t x) {                   // x < 10^4 -> its four digits, most significant in byte 0
+    const uint32_t d0 = x / 1000u, r0 = x - d0 * 1000u, d1 = r0 / 100u, r1 = r0 - d1 * 100u, d2 = r1 / 10u, d3 = r1 - d2 * 10u;
+    return 0x30303030u + (d0 | d1 << 8 | d2 << 16 | d3 << 24);
+}
+template <class W> SSE_HD void put_dec8(W& w, uint32_t c, uint32_t k) {   // the low k (1..8) decimal digits of c < 10^8
+    const uint32_t hi = c / 10000u, lo = c - hi * 10000u;
+    const uint64_t v = ((uint64_t)ascii4(hi) | (uint64_t)ascii4(lo) << 32) >> (8u * (8u - k));
+    if (k > 4) { w.put32((uint32_t)v); w.put_n((uint32_t)(v >> 32), k - 4); }
+    else w.put_n((uint32_t)v, k);
+}
 template <class W> SSE_HD void put_int(W& w, int64_t v) {
-    uint64_t u = v < 0 ? 0 - (uint64_t)v : (uint64_t)v;
+    const uint64_t u = v < 0 ? 0 - (uint64_t)v : (uint64_t)v;
     if (v < 0) w.put('-');
-    uint32_t n = dec_digits(u);
-    uint64_t p = 1;
-    for (uint32_t k = 1; k < n; k++) p *= 10;
-    for (uint32_t k = 0; k < n; k++) { uint64_t q = u / p; w.put('0' + (uint32_t)q); u -= q * p; p /= 10; }
+    if (u < 100000000ull) { put_dec8(w, (uint32_t)u, digits_u32((uint32_t)u)); return; }
+    const uint64_t a = u / 10000000000000000ull, r = u - a * 10000000000000000ull;
+    const uint32_t b = (uint32_t)(r / 100000000ull), c = (uint32_t)(r - (uint64_t)b * 100000000ull);
+    if (a) { put_dec8(w, (uint32_t)a, digits_u32((uint32_t)a)); put_dec8(w, b, 8); }
+    else put_dec8(w, b, digits_u32(b));
+    put_dec8(w, c, 8);
 }
 
 SSE_HD uint32_t hexl(uint32_t v) { return v < 10 ? '0' + v : 'a' + (v - 10); }
@@ -321,33 +336,6 @@ template <class Src, class W> SSE_HD void put_go_string(const Src& s, uint32_t b
         b += n;
     }
     w.put('"');
-}
-
-// json.Marshal(TokenMessage{...}) from columnar fields; with_channel prepends the Redis channel / NATS subject
-// "chat." + id + ".tokens" built from the raw id (llm-stream-proxy/main.go:240).
-template <class Src, class W>
-SSE_HD uint32_t encode_message(const Src& cid, uint32_t cb, uint32_t ce, const Src& tok, uint32_t tb, uint32_t te, int64_t seq, bool done,
-                               int64_t ts, bool go122, bool with_channel, W& w) {
-    uint32_t chan = 0;
-    if (with_channel) {
-        SSE_PUT_LIT(w, "chat.");
-        for (uint32_t i = cb; i < ce; i++) w.put(cid.ld8(i));
-        SSE_PUT_LIT(w, ".tokens");
-        chan = 12 + (ce - cb);
-    }
-    SSE_PUT_LIT(w, "{\"conversation_id\":");
-    put_go_string(cid, cb, ce, w, go122);
-    SSE_PUT_LIT(w, ",\"token\":");
-    put_go_string(tok, tb, te, w, go122);
-    SSE_PUT_LIT(w, ",\"sequence\":");
-    put_int(w, seq);
-    SSE_PUT_LIT(w, ",\"done\":");
-    if (done) SSE_PUT_LIT(w, "true"); else SSE_PUT_LIT(w, "false");
-    SSE_PUT_LIT(w, ",\"timestamp\":");
-    put_int(w, ts);
-    w.put('}');
-    w.finish();
-    return chan;
 }
 
 // verbatim copy of n source bytes starting at byte position sp: bytes until the destination is
@@ -900,6 +888,62 @@ SSE_HD uint32_t plan_record(const Src& s, uint32_t o, uint32_t L, uint32_t op, i
     emit_record(s, o, L, pl, op, w, nullptr);
     out_len = (uint32_t)w.pos();
     return pl.done ? (ST_OK | ST_DONE) : ST_OK;
+}
+
+// ------------------------------------------------------------ producer side ----
+// json.Marshal(TokenMessage{...}) from columnar fields (llm-stream-proxy/main.go:230-239).  A string whose bytes are
+// all "plain" (special_mask) is its own JSON spelling: it is measured by its length and copied word-wise; anything
+// else goes through the rune loop.  with_channel prepends "chat." + raw id + ".tokens" (main.go:240).
+struct EncPlan { uint32_t cid_n, tok_n, len, chan; bool cid_plain, tok_plain; };
+
+template <class Src> SSE_HD bool go_string_is_plain(const Src& s, uint32_t b, uint32_t e) {
+    uint32_t bad = 0;
+    for (uint32_t pos = b; pos < e; pos += 4) {
+        uint32_t w = ld32u(s, pos);
+        const uint32_t rem = e - pos;
+        if (rem < 4) { const uint32_t keep = 0xFFFFFFFFu >> (32 - 8 * rem); w = (w & keep) | (0x20202020u & ~keep); }
+        bad |= special_mask(w);
+    }
+    return bad == 0;
+}
+template <class Src> SSE_HD uint32_t go_string_len(const Src& s, uint32_t b, uint32_t e, bool go122) {
+    Ptr32Dst nd{nullptr};
+    Writer<Ptr32Dst, false> w(nd, 0);
+    put_go_string(s, b, e, w, go122);
+    return w.pos();
+}
+template <class Src>
+SSE_HD EncPlan encode_plan(const Src& cid, uint32_t cb, uint32_t ce, const Src& tok, uint32_t tb, uint32_t te, int64_t seq, bool done,
+                           int64_t ts, bool go122, bool with_channel) {
+    EncPlan p;
+    p.cid_plain = go_string_is_plain(cid, cb, ce);
+    p.tok_plain = go_string_is_plain(tok, tb, te);
+    p.cid_n = p.cid_plain ? ce - cb + 2 : go_string_len(cid, cb, ce, go122);
+    p.tok_n = p.tok_plain ? te - tb + 2 : go_string_len(tok, tb, te, go122);
+    p.chan = with_channel ? 12 + (ce - cb) : 0;
+    p.len = p.chan + 62u + p.cid_n + p.tok_n + dec_len(seq) + dec_len(ts) + (done ? 4u : 5u);
+    return p;
+}
+template <class Src, class W>
+SSE_HD void encode_emit(const Src& cid, uint32_t cb, uint32_t ce, const Src& tok, uint32_t tb, uint32_t te, int64_t seq, bool done,
+                        int64_t ts, bool go122, const EncPlan& p, W& w) {
+    if (p.chan) {
+        SSE_PUT_LIT(w, "chat.");
+        put_copy(cid, cb, ce - cb, w);
+        SSE_PUT_LIT(w, ".tokens");
+    }
+    SSE_PUT_LIT(w, "{\"conversation_id\":");
+    if (p.cid_plain) { w.put('"'); put_copy(cid, cb, ce - cb, w); w.put('"'); }
+    else put_go_string(cid, cb, ce, w, go122);
+    SSE_PUT_LIT(w, ",\"token\":");
+    if (p.tok_plain) { w.put('"'); put_copy(tok, tb, te - tb, w); w.put('"'); }
+    else put_go_string(tok, tb, te, w, go122);
+    SSE_PUT_LIT(w, ",\"sequence\":");
+    put_int(w, seq);
+    if (done) SSE_PUT_LIT(w, ",\"done\":true,\"timestamp\":"); else SSE_PUT_LIT(w, ",\"done\":false,\"timestamp\":");
+    put_int(w, ts);
+    w.put('}');
+    w.finish();
 }
 
 }  // namespace sse

@@ -99,8 +99,8 @@ def columns(msgs):
     if n:
         cid_off[1:] = np.cumsum([len(m[0]) for m in msgs])
         tok_off[1:] = np.cumsum([len(m[1]) for m in msgs])
-    cid = np.frombuffer(b"".join(m[0] for m in msgs) + b"\0" * 16, dtype=np.uint8).copy()
-    tok = np.frombuffer(b"".join(m[1] for m in msgs) + b"\0" * 16, dtype=np.uint8).copy()
+    cid = np.frombuffer(b"".join(m[0] for m in msgs) + b"\0" * 32, dtype=np.uint8).copy()
+    tok = np.frombuffer(b"".join(m[1] for m in msgs) + b"\0" * 32, dtype=np.uint8).copy()
     seq = np.array([m[2] for m in msgs], dtype=np.int64)
     done = np.array([1 if m[3] else 0 for m in msgs], dtype=np.uint8)
     ts = np.array([m[4] for m in msgs], dtype=np.int64)

@@ -149,26 +149,23 @@ extern "C" int hc_interest(const hc_delta* d, uint32_t nd, const uint8_t* in, co
     return 0;
 }
 
-// producer-side encoder: encode_message() of sse_record.cuh run sequentially (records packed back to back)
+// producer-side encoder: encode_plan()/encode_emit() of sse_record.cuh run sequentially (records packed back to back)
 extern "C" int hc_encode(const uint8_t* cid, const uint32_t* cid_off, const uint8_t* tok, const uint32_t* tok_off, const int64_t* seq,
                          const uint8_t* done, const int64_t* ts, uint32_t n, uint32_t op, uint8_t* out, uint64_t out_cap,
                          uint64_t* out_off, uint32_t* chan_len) {
     PtrSrc c{cid}, t{tok};
     PtrDst dst{out};
-    Ptr32Dst nd{nullptr};
+    const bool go122 = (op & OP_GO122) != 0, chan = (op & OP_BRIDGE) != 0;
     uint64_t w = 0;
     for (uint32_t i = 0; i < n; i++) {
-        Writer<Ptr32Dst, false> m(nd, 0);
-        encode_message(c, cid_off[i], cid_off[i + 1], t, tok_off[i], tok_off[i + 1], seq[i], done[i] != 0, ts[i], (op & OP_GO122) != 0,
-                       (op & OP_BRIDGE) != 0, m);
-        const uint32_t len = m.pos();
-        if (w + len + 4 > out_cap) return -1;
+        const EncPlan p = encode_plan(c, cid_off[i], cid_off[i + 1], t, tok_off[i], tok_off[i + 1], seq[i], done[i] != 0, ts[i], go122, chan);
+        if (w + p.len + 4 > out_cap) return -1;
         Writer<PtrDst, true> e(dst, w);
-        chan_len[i] = encode_message(c, cid_off[i], cid_off[i + 1], t, tok_off[i], tok_off[i + 1], seq[i], done[i] != 0, ts[i],
-                                     (op & OP_GO122) != 0, (op & OP_BRIDGE) != 0, e);
-        if (e.pos() != w + len) return -2;
+        encode_emit(c, cid_off[i], cid_off[i + 1], t, tok_off[i], tok_off[i + 1], seq[i], done[i] != 0, ts[i], go122, p, e);
+        if (e.pos() != w + p.len) return -2;
+        chan_len[i] = p.chan;
         out_off[i] = w;
-        w += len;
+        w += p.len;
     }
     out_off[n] = w;
     return 0;
