@@ -48,7 +48,7 @@ class SseGpuError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(HERE, "libssegpu.so")
+    return os.environ.get("SSEGPU_LIB") or os.path.join(HERE, "libssegpu.so")      # SSEGPU_LIB: experimental builds only
 
 
 _LIB = None

@@ -59,6 +59,10 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gsrc, ui
 __device__ __forceinline__ void tma_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
 }
+// global -> L2 prefetch of a byte range (16-byte aligned address, size a multiple of 16): no shared memory is tied up
+__device__ __forceinline__ void l2_prefetch(const void* gsrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
@@ -107,6 +111,10 @@ __global__ void __launch_bounds__(1024) k_scan_tile_totals(uint64_t* tile_state,
 }
 
 // ---------------------------------------------------------------------- kernel ----
+#ifndef SSE_PREFETCH_WAVES
+#define SSE_PREFETCH_WAVES 1
+#endif
+constexpr uint32_t PREFETCH_WAVES = SSE_PREFETCH_WAVES;
 struct TileSmem {
     uint64_t mbar;
     uint64_t base;           // global byte offset of the tile's output
@@ -214,7 +222,7 @@ __device__ __forceinline__ void copy_out(uint8_t* __restrict__ out, const uint8_
 // EXT is a compile-time switch so that the plain framing kernel carries none of the registers of the optional
 // stages (content inspection, interest lookup).
 template <bool EXT, int MODE>
-__global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
+__global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* s_in = smem;                                   // in_cap + 32 (word reads run up to 24 bytes past a record)
     uint8_t* s_out = smem + a.in_cap + 32;                  // out_cap_s + 48
@@ -255,6 +263,17 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
         const uint32_t in_bytes = (te - abase + 15u) & ~15u;
         const bool smem_in = in_bytes <= a.in_cap;
 
+        // One wave ahead: the payload bytes of tile (tile + gridDim.x) are pulled into L2 now, so that the TMA load of
+        // whichever CTA gets that tile pays an L2 hit instead of a DRAM round trip.  The bytes in flight towards DRAM are
+        // then no longer limited by the shared-memory buffers (which spend most of their cycle being parsed/copied).
+        uint32_t pf_b = 0, pf_e = 0;
+        const uint32_t pf_tile = tile + gridDim.x * PREFETCH_WAVES;
+        const bool pf = PREFETCH_WAVES != 0 && tid == TILE / 2 && pf_tile < a.num_tiles;
+        if (pf) {
+            pf_b = a.in_off[pf_tile * TILE];
+            pf_e = a.in_off[min((pf_tile + 1) * TILE, a.n)];
+        }
+
         uint32_t my_b = 0, my_e = 0;
         int64_t my_start = 0;
         const bool active = tid < nrec;
@@ -281,6 +300,13 @@ __global__ void __launch_bounds__(TILE, 5) k_frame_tiles(const FrameArgs a) {
                 st = plan_slow(smem_in ? s_in : a.in + abase, o, L, a.op, my_start, &sp, &len);
                 pl = sp;
             }
+        }
+
+        if (pf) {
+            const uint32_t in_total = ts->in_total;
+            pf_e = min(pf_e, in_total); pf_b = min(pf_b, pf_e) & ~15u;
+            const uint32_t bytes = min((pf_e - pf_b + 15u) & ~15u, 64u * 1024u);
+            if (bytes) l2_prefetch(a.in + pf_b, bytes);
         }
 
         // ---- content inspection of the decoded token text (optional) ------------------------
@@ -473,7 +499,7 @@ static cudaError_t configure_one(int device, uint32_t sm, int* per_sm) {
 }
 
 static cudaError_t configure_variant(int device, bool ext, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
-    const uint32_t ic = 20 * 1024, oc = 24 * 1024;
+    const uint32_t ic = TILE * 160, oc = TILE * 192;
     const uint32_t sm = ic + 32 + oc + 48 + (uint32_t)sizeof(TileSmem) + (ext ? DFA_CACHE_BYTES : 0u);
     if (g_ctas_per_sm[device][ext] == 0) {
         int sms = 0, per = 0, p1 = 0, p2 = 0;

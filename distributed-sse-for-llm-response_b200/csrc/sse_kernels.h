@@ -9,7 +9,10 @@ namespace sse {
 struct InspectDev;               // sse_inspect.cuh
 struct InterestDev;              // sse_interest.cuh
 
-constexpr int TILE = 128;        // records per tile == threads per CTA
+#ifndef SSE_TILE
+#define SSE_TILE 128
+#endif
+constexpr int TILE = SSE_TILE;   // records per tile == threads per CTA
 constexpr int CTR_ROWS = 64;     // counter rows (CTA i adds into row i % CTR_ROWS; the host sums rows)
 constexpr int CTR_COLS = 8;      // ok, syntax, type, filtered, done, fast, bytes_in, bytes_out
 constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32, [20] duplicate-conversation flag u32, [24] bad-offsets flag u32

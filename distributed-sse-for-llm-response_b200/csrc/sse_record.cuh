@@ -219,6 +219,18 @@ template <class Dst, bool EMIT> struct Writer {
         if (EMIT) d.st32a(wpos, v);
         wpos += 4;
     }
+    SSE_HD void store_words4(uint32_t v0, uint32_t v1, uint32_t v2, uint32_t v3) {     // same precondition
+        if (EMIT) { d.st32a(wpos, v0); d.st32a(wpos + 4, v1); d.st32a(wpos + 8, v2); d.st32a(wpos + 12, v3); }
+        wpos += 16;
+    }
+    SSE_HD void store_words_upto3(uint32_t v0, uint32_t v1, uint32_t v2, uint32_t r) {  // the first r (0..3) of them
+        if (EMIT) {
+            if (r > 0) d.st32a(wpos, v0);
+            if (r > 1) d.st32a(wpos + 4, v1);
+            if (r > 2) d.st32a(wpos + 8, v2);
+        }
+        wpos += 4 * r;
+    }
     SSE_HD void skip(uint32_t n) {                      // counting only
         uint32_t t = (sh >> 3) + n;
         wpos += t & ~3u; sh = (t & 3u) * 8;
@@ -348,19 +360,21 @@ template <bool NF, class Src, class W> SSE_HD void put_copy_t(const Src& s, uint
     if (k) { if (NF) w.put_n_nf(ld32u(s, sp), k); else w.put_n(ld32u(s, sp), k); sp += k; n -= k; }
     const uint32_t nw = n >> 2;
     if (nw) {
-        // one loop, four words per trip, the last trip predicated per word: every lane of the warp runs the
-        // same trips (no divergent remainder loop); loads past the last word stay inside the padded tile
+        // full groups of four words in a plain loop (offsets are immediates, no per-word predicates), then the 0..3
+        // remaining words as straight-line predicated code: lanes differ only in the trip count and meet again right
+        // after the loop.  Loads past the last word stay inside the padded tile.
         uint32_t a = sp & ~3u;
         const uint32_t shb = (sp & 3u) * 8;
         uint32_t lo = s.ld32a(a);
-        for (uint32_t i = 0; i < nw; i += 4) {
+        uint32_t i = 0;
+        for (; i + 4 <= nw; i += 4) {
             const uint32_t h0 = s.ld32a(a + 4), h1 = s.ld32a(a + 8), h2 = s.ld32a(a + 12), h3 = s.ld32a(a + 16);
-            w.store_word(funnel_r(lo, h0, shb));
-            if (i + 1 < nw) w.store_word(funnel_r(h0, h1, shb));
-            if (i + 2 < nw) w.store_word(funnel_r(h1, h2, shb));
-            if (i + 3 < nw) w.store_word(funnel_r(h2, h3, shb));
+            w.store_words4(funnel_r(lo, h0, shb), funnel_r(h0, h1, shb), funnel_r(h1, h2, shb), funnel_r(h2, h3, shb));
             lo = h3; a += 16;
         }
+        const uint32_t r = nw - i;
+        const uint32_t h0 = s.ld32a(a + 4), h1 = s.ld32a(a + 8), h2 = s.ld32a(a + 12);
+        w.store_words_upto3(funnel_r(lo, h0, shb), funnel_r(h0, h1, shb), funnel_r(h1, h2, shb), r);
         sp += nw * 4; n -= nw * 4;
     }
     if (n) { if (NF) w.put_n_nf(ld32u(s, sp), n); else w.put_n(ld32u(s, sp), n); }
