@@ -7,6 +7,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_ORDERED, OP_INSPECT, OP_INSPECT_INLINE, OP_MATCH = 0, 1, 2, 4, 8, 16, 32, 64
+OP_NATS_PUB, OP_RESP = 128, 256
 ST_NO_INTEREST = 5
 INSPECT_PER_TOKEN, INSPECT_STREAMING = 0, 1
 KIND_LITERAL, KIND_REGEX = 0, 1

@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(TILE) k_encode_messages(const EncodeArgs a) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t i = blockIdx.x * TILE + tid;
     const bool active = i < a.n;
-    const bool go122 = (a.op & OP_GO122) != 0, chan = (a.op & OP_BRIDGE) != 0;
+    const bool go122 = (a.op & OP_GO122) != 0;
     PtrSrc cid{a.cid}, tok{a.tok};
     uint32_t cb = 0, ce = 0, tb = 0, te = 0;
     int64_t seq = 0, ts = 0;
@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(TILE) k_encode_messages(const EncodeArgs a) {
         cb = a.cid_off[i]; ce = max(cb, a.cid_off[i + 1]);
         tb = a.tok_off[i]; te = max(tb, a.tok_off[i + 1]);
         seq = a.seq[i]; ts = a.ts[i]; done = a.done[i] != 0;
-        p = encode_plan(cid, cb, ce, tok, tb, te, seq, done, ts, go122, chan);
+        p = encode_plan(cid, cb, ce, tok, tb, te, seq, done, ts, a.op);
     }
     const uint32_t len = p.len;
     uint32_t incl = len;

@@ -41,7 +41,8 @@ enum : uint32_t {
     ST_CODE_MASK = 0xF, ST_DONE = 0x100, ST_REDACTED = 0x200,
 };
 // op flags (mirrors include/ssegpu.h)
-enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u, OP_ORDERED = 8u, OP_INSPECT = 16u, OP_INSPECT_INLINE = 32u, OP_MATCH = 64u };
+enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u, OP_ORDERED = 8u, OP_INSPECT = 16u, OP_INSPECT_INLINE = 32u, OP_MATCH = 64u,
+                  OP_NATS_PUB = 128u, OP_RESP = 256u };
 
 constexpr uint32_t MAX_NESTING = 10000;            // encoding/json scanner.go maxNestingDepth
 constexpr uint32_t NEST_WORDS = MAX_NESTING / 32 + 1;
@@ -385,37 +386,52 @@ template <class Src, class W> SSE_HD void put_copy(const Src& s, uint32_t sp, ui
 // Writes the record's output (SSE frame, or bridge subject+JSON) at w.pos.  With a counting
 // writer it measures the length.  `o` = record start inside Src.
 template <class Src, class W>
+SSE_HD void put_marshal(const Src& s, uint32_t o, const Plan& pl, bool go122, W& w) {
+    SSE_PUT_LIT(w, "{\"conversation_id\":");
+    put_json_string(s, o + pl.cid_b, o + pl.cid_e, w, go122);
+    SSE_PUT_LIT(w, ",\"token\":");
+    if (pl.tok_redacted) SSE_PUT_LIT(w, "\"[REDACTED]\"");   // RedactedContent of the Spin inspector (lib.rs:73)
+    else put_json_string(s, o + pl.tok_b, o + pl.tok_e, w, go122);
+    SSE_PUT_LIT(w, ",\"sequence\":");
+    put_int(w, pl.seq);
+    SSE_PUT_LIT(w, ",\"done\":");
+    if (pl.done) SSE_PUT_LIT(w, "true"); else SSE_PUT_LIT(w, "false");
+    SSE_PUT_LIT(w, ",\"timestamp\":");
+    put_int(w, pl.ts);
+    w.put('}');
+}
+template <class Src, class W>
 SSE_HD void emit_record(const Src& s, uint32_t o, uint32_t L, const Plan& pl, uint32_t op, W& w, uint32_t* subj_len) {
     const bool go122 = (op & OP_GO122) != 0;
+    const bool pub = (op & (OP_BRIDGE | OP_NATS_PUB)) == (OP_BRIDGE | OP_NATS_PUB);
     if (op & OP_BRIDGE) {
+        // NATS client protocol, as nats.go's publish() writes it: PUB <subject> <#bytes>\r\n<payload>\r\n
+        if (pub) SSE_PUT_LIT(w, "PUB ");
         // redis-nats-bridge/main.go:160  fmt.Sprintf("chat.%s.tokens", token.ConversationID)
         auto p0 = w.pos();
         SSE_PUT_LIT(w, "chat.");
         for (uint32_t b = o + pl.cid_b, e = o + pl.cid_e; b < e;) put_rune_raw(w, next_rune(s, b, e));
         SSE_PUT_LIT(w, ".tokens");
         if (subj_len) *subj_len = (uint32_t)(w.pos() - p0);
+        if (pub) {
+            uint32_t plen = L;
+            if (!pl.fast) {
+                Ptr32Dst nd{nullptr};
+                Writer<Ptr32Dst, false> c(nd, 0);
+                put_marshal(s, o, pl, go122, c);
+                plen = c.pos();
+            }
+            w.put(' '); put_int(w, (int64_t)plen); w.put('\r'); w.put('\n');
+        }
     } else {
         SSE_PUT_LIT(w, "event: token\nid: ");            // sse_handler.go:212-213
         put_int(w, pl.seq);
         SSE_PUT_LIT(w, "\ndata: ");                      // :214
     }
-    if (pl.fast) {
-        put_copy(s, o, L, w);                            // Marshal(Unmarshal(x)) == x for canonical x
-    } else {
-        SSE_PUT_LIT(w, "{\"conversation_id\":");
-        put_json_string(s, o + pl.cid_b, o + pl.cid_e, w, go122);
-        SSE_PUT_LIT(w, ",\"token\":");
-        if (pl.tok_redacted) SSE_PUT_LIT(w, "\"[REDACTED]\"");   // RedactedContent of the Spin inspector (lib.rs:73)
-        else put_json_string(s, o + pl.tok_b, o + pl.tok_e, w, go122);
-        SSE_PUT_LIT(w, ",\"sequence\":");
-        put_int(w, pl.seq);
-        SSE_PUT_LIT(w, ",\"done\":");
-        if (pl.done) SSE_PUT_LIT(w, "true"); else SSE_PUT_LIT(w, "false");
-        SSE_PUT_LIT(w, ",\"timestamp\":");
-        put_int(w, pl.ts);
-        w.put('}');
-    }
+    if (pl.fast) put_copy(s, o, L, w);                   // Marshal(Unmarshal(x)) == x for canonical x
+    else put_marshal(s, o, pl, go122, w);
     if (!(op & OP_BRIDGE)) { w.put('\n'); w.put('\n'); }
+    if (pub) { w.put('\r'); w.put('\n'); }
     w.finish();
 }
 
@@ -853,6 +869,7 @@ SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, 
     out_len = 0;
     if (!(op & OP_BRIDGE) && start_seq > 0 && pl.seq <= start_seq) { st = ST_FILTERED; return true; }   // sse_handler.go:143
     out_len = (op & OP_BRIDGE) ? 12 + (pl.cid_e - pl.cid_b) + L : 26 + pl.seq_n + L;
+    if ((op & (OP_BRIDGE | OP_NATS_PUB)) == (OP_BRIDGE | OP_NATS_PUB)) out_len += 9 + dec_digits(L);   // "PUB " + " " + digits + CRLF, CRLF
     st = pl.done ? (ST_OK | ST_DONE) : ST_OK;
     return true;
 }
@@ -861,12 +878,15 @@ SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, 
 template <class Src, class W>
 SSE_HD void emit_record_fast(const Src& s, uint32_t o, uint32_t L, const Plan& pl, uint32_t op, W& w, uint32_t* subj_len) {
     if (op & OP_BRIDGE) {
-        w.put32(w4("chat"));                              // redis-nats-bridge/main.go:160 (first word: bytewise if shared)
-        w.put_n_nf('.', 1);
+        const bool pub = (op & OP_NATS_PUB) != 0;
+        if (pub) { w.put32(w4("PUB ")); SSE_PUT_LIT_NF(w, "chat."); }   // nats.go publish(): PUB <subject> <#bytes>CRLF<payload>CRLF
+        else { w.put32(w4("chat")); w.put_n_nf('.', 1); }  // redis-nats-bridge/main.go:160 (first word: bytewise if shared)
         put_copy_t<true>(s, o + pl.cid_b, pl.cid_e - pl.cid_b, w);
         SSE_PUT_LIT_NF(w, ".tokens");
         if (subj_len) *subj_len = 12 + (pl.cid_e - pl.cid_b);
+        if (pub) { w.put_n_nf(' ', 1); put_int(w, (int64_t)L); w.put_n_nf(w4("\r\n\0\0"), 2); }
         put_copy_t<true>(s, o, L, w);                     // main.go:161
+        if (pub) w.put_n_nf(w4("\r\n\0\0"), 2);
     } else {
         w.put32(w4("even"));                              // sse_handler.go:212-213
         SSE_PUT_LIT_NF(w, "t: token\nid: ");
@@ -907,8 +927,9 @@ SSE_HD uint32_t plan_record(const Src& s, uint32_t o, uint32_t L, uint32_t op, i
 // ------------------------------------------------------------ producer side ----
 // json.Marshal(TokenMessage{...}) from columnar fields (llm-stream-proxy/main.go:230-239).  A string whose bytes are
 // all "plain" (special_mask) is its own JSON spelling: it is measured by its length and copied word-wise; anything
-// else goes through the rune loop.  with_channel prepends "chat." + raw id + ".tokens" (main.go:240).
-struct EncPlan { uint32_t cid_n, tok_n, len, chan; bool cid_plain, tok_plain; };
+// else goes through the rune loop.  OP_BRIDGE prepends "chat." + raw id + ".tokens" (main.go:240); OP_RESP wraps channel and
+// payload in the RESP2 command go-redis writes for rdb.Publish (main.go:244): *3 $7 publish $<n> <channel> $<m> <payload>.
+struct EncPlan { uint32_t cid_n, tok_n, len, chan, json; bool cid_plain, tok_plain, resp; };
 
 template <class Src> SSE_HD bool go_string_is_plain(const Src& s, uint32_t b, uint32_t e) {
     uint32_t bad = 0;
@@ -928,24 +949,29 @@ template <class Src> SSE_HD uint32_t go_string_len(const Src& s, uint32_t b, uin
 }
 template <class Src>
 SSE_HD EncPlan encode_plan(const Src& cid, uint32_t cb, uint32_t ce, const Src& tok, uint32_t tb, uint32_t te, int64_t seq, bool done,
-                           int64_t ts, bool go122, bool with_channel) {
+                           int64_t ts, uint32_t op) {
+    const bool go122 = (op & OP_GO122) != 0;
     EncPlan p;
     p.cid_plain = go_string_is_plain(cid, cb, ce);
     p.tok_plain = go_string_is_plain(tok, tb, te);
     p.cid_n = p.cid_plain ? ce - cb + 2 : go_string_len(cid, cb, ce, go122);
     p.tok_n = p.tok_plain ? te - tb + 2 : go_string_len(tok, tb, te, go122);
-    p.chan = with_channel ? 12 + (ce - cb) : 0;
-    p.len = p.chan + 62u + p.cid_n + p.tok_n + dec_len(seq) + dec_len(ts) + (done ? 4u : 5u);
+    p.resp = (op & OP_RESP) != 0;
+    p.chan = (op & (OP_BRIDGE | OP_RESP)) ? 12 + (ce - cb) : 0;
+    p.json = 62u + p.cid_n + p.tok_n + dec_len(seq) + dec_len(ts) + (done ? 4u : 5u);
+    p.len = p.chan + p.json + (p.resp ? 27u + dec_digits(p.chan) + dec_digits(p.json) : 0u);
     return p;
 }
 template <class Src, class W>
 SSE_HD void encode_emit(const Src& cid, uint32_t cb, uint32_t ce, const Src& tok, uint32_t tb, uint32_t te, int64_t seq, bool done,
                         int64_t ts, bool go122, const EncPlan& p, W& w) {
+    if (p.resp) { SSE_PUT_LIT(w, "*3\r\n$7\r\npublish\r\n$"); put_int(w, (int64_t)p.chan); SSE_PUT_LIT(w, "\r\n"); }
     if (p.chan) {
         SSE_PUT_LIT(w, "chat.");
         put_copy(cid, cb, ce - cb, w);
         SSE_PUT_LIT(w, ".tokens");
     }
+    if (p.resp) { SSE_PUT_LIT(w, "\r\n$"); put_int(w, (int64_t)p.json); SSE_PUT_LIT(w, "\r\n"); }
     SSE_PUT_LIT(w, "{\"conversation_id\":");
     if (p.cid_plain) { w.put('"'); put_copy(cid, cb, ce - cb, w); w.put('"'); }
     else put_go_string(cid, cb, ce, w, go122);
@@ -957,6 +983,7 @@ SSE_HD void encode_emit(const Src& cid, uint32_t cb, uint32_t ce, const Src& tok
     if (done) SSE_PUT_LIT(w, ",\"done\":true,\"timestamp\":"); else SSE_PUT_LIT(w, ",\"done\":false,\"timestamp\":");
     put_int(w, ts);
     w.put('}');
+    if (p.resp) SSE_PUT_LIT(w, "\r\n");
     w.finish();
 }
 

@@ -82,6 +82,9 @@ struct ssegpu_ctx {
 
 namespace {
 
+// SSEGPU_OP_NATS_PUB is a bridge-mode framing; SSEGPU_OP_RESP belongs to the encoder
+bool bad_frame_op(uint32_t op) { return (op & SSEGPU_OP_RESP) || ((op & SSEGPU_OP_NATS_PUB) && !(op & SSEGPU_OP_BRIDGE)); }
+
 void add_rows(const uint8_t* hdr, ssegpu_counters* c, uint32_t n_records) {
     const unsigned long long* rows = reinterpret_cast<const unsigned long long*>(hdr + sse::SCRATCH_HDR);
     unsigned long long s[sse::CTR_COLS] = {0};
@@ -290,6 +293,7 @@ const uint32_t* ssegpu_sub_span(const ssegpu_batch* b) { return b ? b->h_hit : n
 int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t op, int use_filter) {
     if (!ctx || !b || b->ctx != ctx) return SSEGPU_E_INVAL;
     if (b->state != ACQUIRED && b->state != DONE) return SSEGPU_E_STATE;   // DONE: the owner re-submits the slot
+    if (bad_frame_op(op)) return SSEGPU_E_INVAL;
     if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
     const uint64_t in_total = n ? b->h_in_off[n] : 0;
     if (in_total > ctx->cfg.max_in_bytes) return SSEGPU_E_TOOBIG;
@@ -340,7 +344,7 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     CU(cudaMemcpyAsync(b->h_hdr, b->d_scratch, sse::scratch_readback_bytes(), cudaMemcpyDeviceToHost, st));
     // Speculative copy of the frames: a canonical record grows by 26 + digits(seq) bytes
     // (28 + len("chat..tokens")=40ish in bridge mode); anything beyond is fetched in wait().
-    uint64_t spec = in_total + (uint64_t)n * ((op & SSEGPU_OP_BRIDGE) ? 80 : 32) + 16ull * ((n + sse::TILE - 1) / sse::TILE);
+    uint64_t spec = in_total + (uint64_t)n * ((op & SSEGPU_OP_BRIDGE) ? ((op & SSEGPU_OP_NATS_PUB) ? 96 : 80) : 32) + 16ull * ((n + sse::TILE - 1) / sse::TILE);
     if (spec > ctx->out_cap) spec = ctx->out_cap;
     b->spec_out = spec;
     if (spec) CU(cudaMemcpyAsync(b->h_out, b->d_out, spec, cudaMemcpyDeviceToHost, st));
@@ -405,6 +409,7 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
                         uint32_t n, uint32_t op, void* d_out, uint64_t out_cap, uint64_t* d_out_off,
                         uint32_t* d_out_len, uint32_t* d_subj_len, uint32_t* d_status, void* stream) {
     if (!ctx || !d_in_off || !d_out_off || (n && (!d_in || !d_out || !d_status || !d_out_len))) return SSEGPU_E_INVAL;
+    if (bad_frame_op(op)) return SSEGPU_E_INVAL;
     if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
     if (reinterpret_cast<uintptr_t>(d_in) & 15) return SSEGPU_E_INVAL;
     CU(cudaSetDevice(ctx->cfg.device));
@@ -447,7 +452,7 @@ int ssegpu_frame_launch_result(ssegpu_ctx* ctx, ssegpu_counters* out) {
 int ssegpu_encode_launch(ssegpu_ctx* ctx, const void* d_cid, const uint32_t* d_cid_off, const void* d_tok, const uint32_t* d_tok_off,
                          const int64_t* d_seq, const uint8_t* d_done, const int64_t* d_ts, uint32_t n, uint32_t op,
                          void* d_out, uint64_t out_cap, uint64_t* d_out_off, uint32_t* d_out_len, uint32_t* d_chan_len, void* stream) {
-    if (!ctx || !d_out_off || (op & ~(uint32_t)(SSEGPU_OP_BRIDGE | SSEGPU_OP_GO122))) return SSEGPU_E_INVAL;
+    if (!ctx || !d_out_off || (op & ~(uint32_t)(SSEGPU_OP_BRIDGE | SSEGPU_OP_GO122 | SSEGPU_OP_RESP))) return SSEGPU_E_INVAL;
     if (n && (!d_cid || !d_cid_off || !d_tok || !d_tok_off || !d_seq || !d_done || !d_ts || !d_out || !d_out_len)) return SSEGPU_E_INVAL;
     if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
     if ((reinterpret_cast<uintptr_t>(d_cid) | reinterpret_cast<uintptr_t>(d_tok)) & 3) return SSEGPU_E_INVAL;

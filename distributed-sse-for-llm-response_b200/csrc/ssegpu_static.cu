@@ -68,6 +68,10 @@ int ssegpu_frame_launch_static(int device, const void* d_in, const uint32_t* d_i
         snprintf(g_err, sizeof g_err, "invalid argument");
         return SSEGPU_E_INVAL;
     }
+    if ((op & SSEGPU_OP_RESP) || ((op & SSEGPU_OP_NATS_PUB) && !(op & SSEGPU_OP_BRIDGE))) {
+        snprintf(g_err, sizeof g_err, "SSEGPU_OP_NATS_PUB needs SSEGPU_OP_BRIDGE; SSEGPU_OP_RESP belongs to ssegpu_encode_launch");
+        return SSEGPU_E_INVAL;
+    }
     if (n > SSEGPU_STATIC_MAX_RECORDS) {
         snprintf(g_err, sizeof g_err, "n_records = %u exceeds SSEGPU_STATIC_MAX_RECORDS = %u: the built-in scratch array holds "
                  "one scratch word per tile for at most that many records; split the batch or use ssegpu_frame_launch",

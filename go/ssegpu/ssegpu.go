@@ -26,6 +26,9 @@ const (
 	OpBridge  = 1
 	OpGo122   = 2
 	OpOrdered = 8
+	OpInspect, OpInspectInline, OpMatch = 16, 32, 64
+	OpNatsPub = 128 // with OpBridge: records are complete "PUB <subject> <#bytes>\r\n<payload>\r\n" messages
+	OpResp    = 256 // EncodeLaunch only: records are RESP2 PUBLISH commands
 )
 
 // Status codes (low 4 bits of the status word) and flags.

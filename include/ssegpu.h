@@ -72,6 +72,14 @@ typedef enum {
 #define SSEGPU_OP_MATCH     64u  /* look the record's subject chat.<cid>.tokens up in the interest table: per record a span of
                                     subscriber ids (ssegpu_sub_span); records nobody subscribed to are not framed
                                     (status SSEGPU_ST_NO_INTEREST) */
+#define SSEGPU_OP_NATS_PUB  128u /* with SSEGPU_OP_BRIDGE: each record is a complete NATS client-protocol message as nats.go's
+                                  * publish() writes it, "PUB <subject> <#bytes>\r\n<payload>\r\n" (what nc.Publish puts on the
+                                  * wire for main.go:164); with SSEGPU_OP_ORDERED the whole arena is one write() to the NATS
+                                  * connection.  subj_len[i] is still the subject's length (it starts 4 bytes into the record).
+                                  * The host keeps nats.go's checks that concern the connection (MaxPayload, closed/draining). */
+#define SSEGPU_OP_RESP      256u /* ssegpu_encode_launch only: each record is the RESP2 command go-redis writes for
+                                  * rdb.Publish(ctx, channel, payload) (llm-stream-proxy/main.go:244):
+                                  * "*3\r\n$7\r\npublish\r\n$<n>\r\n<channel>\r\n$<m>\r\n<payload>\r\n"; implies the channel. */
 #define SSEGPU_OP_ORDERED   8u   /* lay the frames out back to back in record order (the arena then equals the
                                     sequential Go output byte for byte); costs a second decode pass.  Default: each
                                     tile of 128 consecutive records lands 16-byte aligned in completion order (<=15

@@ -612,6 +612,86 @@ int sseo_bridge_batch(const uint8_t *in, const uint32_t *in_off, uint32_t n, int
     return 0;
 }
 
+/* Bridge records as complete NATS client-protocol messages: what nc.Publish(subject, data) (redis-nats-bridge/main.go:164)
+ * puts on the wire.  The reference delegates this to github.com/nats-io/nats.go v1.31.0 (src/redis-nats-bridge/go.mod),
+ * which is not vendored; its publish() writes "PUB " subject " " decimal(len(data)) "\r\n" data "\r\n" (the NATS client
+ * protocol's PUB <subject> [reply-to] <#bytes>; no reply subject, no headers on this path). */
+int sseo_bridge_pub_batch(const uint8_t *in, const uint32_t *in_off, uint32_t n, int go122,
+                          uint8_t *out, uint64_t out_cap, uint64_t *out_off,
+                          uint32_t *subj_len, uint32_t *status)
+{
+    uint64_t w = 0;
+    size_t scap = 0;
+    uint8_t *scratch = NULL, *tmp = NULL;
+    for (uint32_t i = 0; i < n; i++) {
+        const uint8_t *p = in + in_off[i];
+        size_t len = in_off[i + 1] - in_off[i];
+        if (6 * len + 16 > scap) {
+            scap = 2 * (6 * len + 16);
+            free(scratch); free(tmp);
+            scratch = (uint8_t *)malloc(scap); tmp = (uint8_t *)malloc(scap + 128);
+        }
+        sseo_msg m;
+        out_off[i] = w;
+        subj_len[i] = 0;
+        uint32_t st = (uint32_t)sseo_unmarshal(p, len, &m, scratch);
+        if (st == SSEO_OK) {
+            if (w + sseo_marshal_bound(&m) + m.cid_len + 48 > out_cap) { free(scratch); free(tmp); return -1; }
+            size_t plen = sseo_marshal(&m, tmp, go122);
+            w += put(out + w, "PUB ");
+            uint64_t w0 = w;
+            w += put(out + w, "chat.");
+            memcpy(out + w, m.cid, m.cid_len); w += m.cid_len;
+            w += put(out + w, ".tokens");
+            subj_len[i] = (uint32_t)(w - w0);
+            out[w++] = ' ';
+            w += append_int(out + w, (int64_t)plen);
+            out[w++] = '\r'; out[w++] = '\n';
+            memcpy(out + w, tmp, plen); w += plen;
+            out[w++] = '\r'; out[w++] = '\n';
+            if (m.done) st |= SSEO_DONE;
+        }
+        status[i] = st;
+    }
+    out_off[n] = w;
+    free(scratch); free(tmp);
+    return 0;
+}
+
+/* Producer records as the RESP2 command go-redis writes for rdb.Publish(ctx, channel, data) (llm-stream-proxy/main.go:244).
+ * github.com/redis/go-redis/v9 v9.3.0 (not vendored): Publish builds NewIntCmd(ctx, "publish", channel, message) and the
+ * protocol writer emits an array of bulk strings: *3 CRLF $7 CRLF publish CRLF $<n> CRLF channel CRLF $<m> CRLF data CRLF. */
+size_t sseo_encode_resp_batch(const uint8_t *cid, const uint32_t *cid_off, const uint8_t *tok, const uint32_t *tok_off,
+                              const int64_t *seq, const uint8_t *done, const int64_t *ts, uint32_t n, int go122,
+                              uint8_t *out, size_t out_cap, uint64_t *off, uint32_t *chan_len)
+{
+    size_t w = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        sseo_msg m;
+        m.cid = cid + cid_off[i]; m.cid_len = cid_off[i + 1] - cid_off[i];
+        m.tok = tok + tok_off[i]; m.tok_len = tok_off[i + 1] - tok_off[i];
+        m.seq = seq[i]; m.done = done[i] != 0; m.ts = ts[i];
+        size_t bound = sseo_marshal_bound(&m);
+        if (w + 96 + m.cid_len + bound > out_cap) return (size_t)-1;
+        uint8_t *tmp = (uint8_t *)malloc(bound);
+        size_t plen = sseo_marshal(&m, tmp, go122);
+        off[i] = w;
+        w += put(out + w, "*3\r\n$7\r\npublish\r\n$");
+        w += append_int(out + w, (int64_t)(12 + m.cid_len));
+        w += put(out + w, "\r\nchat.");
+        memcpy(out + w, m.cid, m.cid_len); w += m.cid_len;
+        w += put(out + w, ".tokens\r\n$");
+        w += append_int(out + w, (int64_t)plen);
+        w += put(out + w, "\r\n");
+        memcpy(out + w, tmp, plen); w += plen;
+        w += put(out + w, "\r\n");
+        free(tmp);
+        if (chan_len) chan_len[i] = 12 + m.cid_len;
+    }
+    off[n] = w;
+    return w;
+}
+
 /* ------------------------------------------------------------- baseline ---- */
 typedef struct {
     const uint8_t *in; const uint32_t *in_off; uint32_t lo, hi;

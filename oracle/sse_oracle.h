@@ -63,6 +63,15 @@ size_t sseo_encode_batch(const uint8_t *cid, const uint32_t *cid_off, const uint
                          const int64_t *seq, const uint8_t *done, const int64_t *ts, uint32_t n, int go122, int with_channel,
                          uint8_t *out, size_t out_cap, uint64_t *off, uint32_t *chan_len);
 
+/* Bridge records as NATS client-protocol messages "PUB <subject> <#bytes>\r\n<payload>\r\n" (what nc.Publish writes
+ * for redis-nats-bridge/main.go:164; nats.go v1.31.0, not vendored -- stated from the NATS protocol). */
+int sseo_bridge_pub_batch(const uint8_t *in, const uint32_t *in_off, uint32_t n, int go122,
+                          uint8_t *out, uint64_t out_cap, uint64_t *out_off, uint32_t *subj_len, uint32_t *status);
+/* Producer records as the RESP2 PUBLISH command go-redis v9.3.0 writes (llm-stream-proxy/main.go:244; not vendored). */
+size_t sseo_encode_resp_batch(const uint8_t *cid, const uint32_t *cid_off, const uint8_t *tok, const uint32_t *tok_off,
+                              const int64_t *seq, const uint8_t *done, const int64_t *ts, uint32_t n, int go122,
+                              uint8_t *out, size_t out_cap, uint64_t *off, uint32_t *chan_len);
+
 /* The three Fprintf calls (sse_handler.go:212-214, :428-430). Returns frame length. */
 size_t sseo_frame(const sseo_msg *m, uint8_t *dst, int go122);
 

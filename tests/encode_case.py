@@ -105,3 +105,18 @@ def columns(msgs):
     done = np.array([1 if m[3] else 0 for m in msgs], dtype=np.uint8)
     ts = np.array([m[4] for m in msgs], dtype=np.int64)
     return cid, cid_off, tok, tok_off, seq, done, ts
+
+
+# SSEGPU_OP_RESP: the RESP2 command go-redis writes for rdb.Publish(ctx, "chat.<id>.tokens", payload), typed out by hand
+HAND_RESP = [
+    ((b"abc", b"t", 1, False, 2),
+     b'*3\r\n$7\r\npublish\r\n$15\r\nchat.abc.tokens\r\n$77\r\n{"conversation_id":"abc","token":"t","sequence":1,"done":false,"timestamp":2}\r\n'),
+    ((b"", b"", 0, True, 0), b'*3\r\n$7\r\npublish\r\n$12\r\nchat..tokens\r\n$72\r\n{"conversation_id":"","token":"","sequence":0,"done":true,"timestamp":0}\r\n'),
+    ((b"a\r\nb", b"<", 10, False, 5),
+     b'*3\r\n$7\r\npublish\r\n$16\r\nchat.a\r\nb.tokens\r\n$86\r\n{"conversation_id":"a\\r\\nb","token":"\\u003c","sequence":10,"done":false,"timestamp":5}\r\n'),
+]
+
+
+def model_resp(msg, go122=False):
+    chan, payload = model_channel(msg), model_encode(msg, go122)
+    return b"*3\r\n$7\r\npublish\r\n$%d\r\n%s\r\n$%d\r\n%s\r\n" % (len(chan), chan, len(payload), payload)

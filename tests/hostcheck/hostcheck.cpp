@@ -155,10 +155,10 @@ extern "C" int hc_encode(const uint8_t* cid, const uint32_t* cid_off, const uint
                          uint64_t* out_off, uint32_t* chan_len) {
     PtrSrc c{cid}, t{tok};
     PtrDst dst{out};
-    const bool go122 = (op & OP_GO122) != 0, chan = (op & OP_BRIDGE) != 0;
+    const bool go122 = (op & OP_GO122) != 0;
     uint64_t w = 0;
     for (uint32_t i = 0; i < n; i++) {
-        const EncPlan p = encode_plan(c, cid_off[i], cid_off[i + 1], t, tok_off[i], tok_off[i + 1], seq[i], done[i] != 0, ts[i], go122, chan);
+        const EncPlan p = encode_plan(c, cid_off[i], cid_off[i + 1], t, tok_off[i], tok_off[i + 1], seq[i], done[i] != 0, ts[i], op);
         if (w + p.len + 4 > out_cap) return -1;
         Writer<PtrDst, true> e(dst, w);
         encode_emit(c, cid_off[i], cid_off[i + 1], t, tok_off[i], tok_off[i + 1], seq[i], done[i] != 0, ts[i], go122, p, e);

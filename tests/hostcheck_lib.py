@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HC_DIR = os.path.join(ROOT, "tests", "hostcheck")
 CSRC = os.path.join(ROOT, "distributed-sse-for-llm-response_b200", "csrc")
 u8p, u32p, u64p, i64p = (C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_int64))
-OP_BRIDGE, OP_GO122, OP_NO_FAST = 1, 2, 4
+OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_NATS_PUB, OP_RESP = 1, 2, 4, 128, 256
 
 
 def _ptr(a, t):
@@ -38,7 +38,7 @@ def encode(lib, cols, op=0):
     """cols = tests.encode_case.columns(...) -> (list of record bytes, chan_len)"""
     cid, cid_off, tok, tok_off, seq, done, ts = cols
     n = len(seq)
-    cap = (int(cid_off[n]) * 7 + int(tok_off[n]) * 6) + 128 * n + 64
+    cap = (int(cid_off[n]) * 8 + int(tok_off[n]) * 6) + 256 * n + 64
     out = np.zeros(cap, dtype=np.uint8)
     out_off = np.empty(n + 1, dtype=np.uint64)
     chan = np.empty(n, dtype=np.uint32)
@@ -90,7 +90,7 @@ def inspect(lib, patterns, mode, arena, off, conv_slot=None, conv_slots=0):
 
 def run(lib, arena, off, start_seq=None, op=0):
     n = len(off) - 1
-    cap = int(off[n]) * 9 + 200 * n + 64
+    cap = int(off[n]) * 9 + 260 * n + 64
     out = np.zeros(cap, dtype=np.uint8)
     out_off = np.empty(n + 1, dtype=np.uint64)
     subj = np.empty(n, dtype=np.uint32)

@@ -83,6 +83,34 @@ class Oracle:
         assert rc == 0
         return out[: int(out_off[n])], out_off, subj_len, status
 
+    def bridge_pub(self, arena, off, go122=False):
+        n = len(off) - 1
+        cap = int(off[n]) * 9 + 260 * n + 64
+        out = np.empty(cap, dtype=np.uint8)
+        out_off = np.empty(n + 1, dtype=np.uint64)
+        subj_len = np.empty(n, dtype=np.uint32)
+        status = np.empty(n, dtype=np.uint32)
+        self.lib.sseo_bridge_pub_batch.restype = C.c_int
+        self.lib.sseo_bridge_pub_batch.argtypes = [u8p, u32p, C.c_uint32, C.c_int, u8p, C.c_uint64, u64p, u32p, u32p]
+        rc = self.lib.sseo_bridge_pub_batch(_ptr(arena, u8p), _ptr(off, u32p), n, int(go122), _ptr(out, u8p), cap,
+                                            _ptr(out_off, u64p), _ptr(subj_len, u32p), _ptr(status, u32p))
+        assert rc == 0
+        return out[: int(out_off[n])], out_off, subj_len, status
+
+    def encode_resp(self, cols, go122=False):
+        cid, cid_off, tok, tok_off, seq, done, ts = cols
+        n = len(seq)
+        cap = (int(cid_off[n]) * 8 + int(tok_off[n]) * 6) + 256 * n + 64
+        out = np.empty(cap, dtype=np.uint8)
+        off = np.empty(n + 1, dtype=np.uint64)
+        chan = np.empty(n, dtype=np.uint32)
+        self.lib.sseo_encode_resp_batch.restype = C.c_size_t
+        self.lib.sseo_encode_resp_batch.argtypes = [u8p, u32p, u8p, u32p, i64p, u8p, i64p, C.c_uint32, C.c_int, u8p, C.c_size_t, u64p, u32p]
+        w = self.lib.sseo_encode_resp_batch(_ptr(cid, u8p), _ptr(cid_off, u32p), _ptr(tok, u8p), _ptr(tok_off, u32p), _ptr(seq, i64p),
+                                            _ptr(done, u8p), _ptr(ts, i64p), n, int(go122), _ptr(out, u8p), cap, _ptr(off, u64p), _ptr(chan, u32p))
+        assert w == int(off[n])
+        return [out[int(off[i]):int(off[i + 1])].tobytes() for i in range(n)], chan
+
     def bench_adapter(self, arena, off, threads, reps=1):
         n = len(off) - 1
         frames, nbytes = C.c_uint64(0), C.c_uint64(0)

@@ -86,3 +86,20 @@ def test_encoded_payloads_take_the_adapter_fast_path(lib, oracle):
     assert nfast == len(plain) > 1000
     assert [out.tobytes()[int(out_off[i]):int(out_off[i + 1])] for i in range(len(plain))] == \
         [b"event: token\nid: %d\ndata: " % m[2] + p + b"\n\n" for m, p in zip(plain, payloads)]
+
+
+def test_resp_publish_framing(lib, oracle):
+    """SSEGPU_OP_RESP: the command go-redis writes for rdb.Publish (llm-stream-proxy/main.go:244)."""
+    for m, want in ec.HAND_RESP:
+        assert ec.model_resp(m) == want, m
+    cols = ec.columns([m for m, _ in ec.HAND_RESP])
+    assert oracle.encode_resp(cols)[0] == [w for _, w in ec.HAND_RESP]
+    assert hc.encode(lib, cols, hc.OP_RESP)[0] == [w for _, w in ec.HAND_RESP]
+    msgs = ec.random_messages(3000, seed=21)
+    cols = ec.columns(msgs)
+    for go122 in (False, True):
+        want = [ec.model_resp(m, go122) for m in msgs]
+        got_o, chan_o = oracle.encode_resp(cols, go122=go122)
+        got_h, chan_h = hc.encode(lib, cols, hc.OP_RESP | (hc.OP_GO122 if go122 else 0))
+        assert got_o == want and got_h == want
+        assert list(chan_o) == list(chan_h) == [12 + len(m[0]) for m in msgs]

@@ -8,7 +8,7 @@ from __graft_entry__ import load_package
 from gpu_util import normalise
 
 pytestmark = pytest.mark.gpu
-OP_BRIDGE, OP_GO122 = 1, 2
+OP_BRIDGE, OP_GO122, OP_RESP = 1, 2, 256
 
 
 @pytest.fixture(scope="module")
@@ -29,7 +29,7 @@ def gpu_encode(eng, cols, op=0, cap=None, keep=False):
     cid, cid_off, tok, tok_off, seq, done, ts = cols
     n = len(seq)
     if cap is None:
-        cap = (int(cid_off[n]) * 7 + int(tok_off[n]) * 6) + 128 * n + 64
+        cap = (int(cid_off[n]) * 8 + int(tok_off[n]) * 6) + 256 * n + 64
     dev = lambda a, t: torch.from_numpy(a.view(t)).cuda()  # noqa: E731
     d = dict(cid=dev(cid, np.uint8), cid_off=dev(cid_off, np.int32), tok=dev(tok, np.uint8), tok_off=dev(tok_off, np.int32),
              seq=dev(seq, np.int64), done=dev(done, np.uint8), ts=dev(ts, np.int64),
@@ -79,6 +79,19 @@ def test_random_messages_vs_oracle_and_model(eng, oracle, n, op):
     assert got == model
 
 
+@pytest.mark.parametrize("op", [OP_RESP, OP_RESP | OP_GO122, OP_RESP | OP_BRIDGE])
+def test_resp_publish_framing(eng, oracle, op):
+    """SSEGPU_OP_RESP: records are the RESP2 PUBLISH commands go-redis writes (llm-stream-proxy/main.go:244)."""
+    got, chan, rc = gpu_encode(eng, ec.columns([m for m, _ in ec.HAND_RESP]), OP_RESP)
+    assert rc == 0 and got == [w for _, w in ec.HAND_RESP]
+    msgs = ec.random_messages(5000, seed=31 + op)
+    cols = ec.columns(msgs)
+    got, chan, rc = gpu_encode(eng, cols, op)
+    want, want_chan = oracle.encode_resp(cols, go122=bool(op & OP_GO122))
+    assert rc == 0 and got == want and np.array_equal(chan, want_chan)
+    assert got == [ec.model_resp(m, bool(op & OP_GO122)) for m in msgs]
+
+
 def test_overflow_is_reported_and_nothing_is_written_past_the_cap(eng):
     msgs = ec.random_messages(3000, seed=9)
     cols = ec.columns(msgs)
@@ -94,10 +107,10 @@ def test_argument_checks(eng, pkg):
         eng.encode_launch(0, 0, 0, 0, 0, 0, 0, 5, 0, 0, 0, 0, 0)
     assert err.value.code == -1
     with pytest.raises(pkg.SseGpuError) as err:       # only BRIDGE and GO122 mean anything here
-        eng.encode_launch(1, 1, 1, 1, 1, 1, 1, 5, 8, 1, 100, 1, 1)
+        eng.encode_launch(4, 4, 4, 4, 4, 4, 4, 5, 8, 16, 100, 4, 4)
     assert err.value.code == -1
     with pytest.raises(pkg.SseGpuError) as err:
-        eng.encode_launch(1, 1, 1, 1, 1, 1, 1, (1 << 20) + 1, 0, 1, 100, 1, 1)
+        eng.encode_launch(4, 4, 4, 4, 4, 4, 4, (1 << 20) + 1, 0, 16, 100, 4, 4)
     assert err.value.code == -5
 
 

@@ -89,6 +89,42 @@ def test_differential_fuzz_vs_oracle(pkg, eng, oracle):
     assert np.array_equal(subj, want_subj) and np.array_equal(out, want_out)
 
 
+@pytest.mark.parametrize("op", [1 | 128, 1 | 128 | 4, 1 | 128 | 2, 1 | 128 | 8])
+def test_nats_pub_framing(pkg, eng, oracle, golden, op):
+    """SSEGPU_OP_NATS_PUB: bridge records as complete NATS PUB messages; in ordered mode the arena IS the byte stream
+    nats.go would have written for the same sequence of nc.Publish calls (redis-nats-bridge/main.go:164)."""
+    arena, off = oracle.pack([v[0] for v in hv.BRIDGE_PUB])
+    out, out_off, status, subj = run_batch(eng, arena, off, None, op)
+    assert slices(out, out_off) == [v[2] for v in hv.BRIDGE_PUB]
+    assert [int(x) for x in status] == [v[1] for v in hv.BRIDGE_PUB]
+    rng = random.Random(5)
+    payloads = [bytes.fromhex(c["in"]) for c in golden]
+    base = mg.canon("7f3c2b1a-1111-4222-8333-944455556666", " hello", 42, False, 1700000000000000000)
+    for k in range(8000):
+        r = rng.random()
+        payloads.append(mg.canon(mg.rand_text(rng, rng.randrange(0, 40), 0.15), mg.rand_text(rng, rng.randrange(0, 200), 0.3),
+                                 rng.randrange(-5, 5000), rng.random() < 0.05, rng.randrange(-(1 << 63), 1 << 63)) if r < 0.6
+                        else mg.mutate(rng, rng.choice([base, payloads[-1]])))
+    arena, off = oracle.pack(payloads)
+    want_out, want_off, want_subj, want_status = oracle.bridge_pub(arena, off, go122=bool(op & 2))
+    out, out_off, status, subj = run_batch(eng, arena, off, None, op)
+    assert np.array_equal(status, want_status) and np.array_equal(subj, want_subj)
+    assert np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
+
+
+def test_nats_pub_needs_bridge_mode(pkg, eng, oracle):
+    arena, off = oracle.pack([b"{}"])
+    b = eng.acquire()
+    try:
+        b.fill(arena, off, None)
+        for op in (128, 256, 1 | 256):
+            with pytest.raises(pkg.SseGpuError) as err:
+                b.submit(1, op, use_filter=False)
+            assert err.value.code == -1
+    finally:
+        b.release()
+
+
 @pytest.mark.parametrize("op", [0, 8])
 @pytest.mark.parametrize("n", [0, 1, 2, 127, 128, 129, 255, 256, 257, 1000])
 def test_tile_boundaries(pkg, eng, oracle, n, op):

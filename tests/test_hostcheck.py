@@ -76,3 +76,35 @@ def test_differential_fuzz_vs_oracle(lib, oracle):
     out, out_off, subj, status, _ = hc.run(lib, arena, off, None, hc.OP_BRIDGE)
     assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off)
     assert np.array_equal(subj, want_subj) and np.array_equal(out, want_out)
+
+
+def test_nats_pub_framing(lib, oracle, golden):
+    """SSEGPU_OP_NATS_PUB: bridge records as complete "PUB <subject> <#bytes>\\r\\n<payload>\\r\\n" messages
+    (what nc.Publish writes for redis-nats-bridge/main.go:164)."""
+    arena, off = oracle.pack([v[0] for v in hv.BRIDGE_PUB])
+    for op in (hc.OP_BRIDGE | hc.OP_NATS_PUB, hc.OP_BRIDGE | hc.OP_NATS_PUB | hc.OP_NO_FAST):
+        out, out_off, subj, status, _ = hc.run(lib, arena, off, None, op)
+        assert _slices(out, out_off) == [v[2] for v in hv.BRIDGE_PUB]
+        assert [int(s) for s in status] == [v[1] for v in hv.BRIDGE_PUB]
+    o_out, o_off, o_subj, o_status = oracle.bridge_pub(arena, off)
+    assert _slices(o_out, o_off) == [v[2] for v in hv.BRIDGE_PUB]
+    # the committed fixtures: PUB framing == "PUB " + subject + " " + len + CRLF + json + CRLF of the plain bridge output
+    arena, off = oracle.pack([bytes.fromhex(c["in"]) for c in golden])
+    p_out, p_off, p_subj, p_status = oracle.bridge(arena, off)
+    want = []
+    for rec, sl, st in zip(_slices(p_out, p_off), p_subj, p_status):
+        sl = int(sl)
+        want.append(b"PUB " + rec[:sl] + b" %d\r\n" % (len(rec) - sl) + rec[sl:] + b"\r\n" if int(st) & 0xF == 0 else b"")
+    for op in (hc.OP_BRIDGE | hc.OP_NATS_PUB, hc.OP_BRIDGE | hc.OP_NATS_PUB | hc.OP_NO_FAST, hc.OP_BRIDGE | hc.OP_NATS_PUB | hc.OP_GO122):
+        go122 = bool(op & hc.OP_GO122)
+        if go122:
+            p_out, p_off, p_subj, p_status = oracle.bridge(arena, off, go122=True)
+            want = []
+            for rec, sl, st in zip(_slices(p_out, p_off), p_subj, p_status):
+                sl = int(sl)
+                want.append(b"PUB " + rec[:sl] + b" %d\r\n" % (len(rec) - sl) + rec[sl:] + b"\r\n" if int(st) & 0xF == 0 else b"")
+        out, out_off, subj, status, _ = hc.run(lib, arena, off, None, op)
+        assert _slices(out, out_off) == want
+        assert (subj == p_subj).all() and (status == p_status).all()
+        o_out, o_off, o_subj, o_status = oracle.bridge_pub(arena, off, go122=go122)
+        assert _slices(o_out, o_off) == want and (o_subj == p_subj).all()
