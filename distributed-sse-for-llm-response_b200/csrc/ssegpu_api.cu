@@ -224,7 +224,7 @@ int ssegpu_init(const ssegpu_config* cfg, ssegpu_ctx** out) {
     CU(cudaSetDevice(cfg->device));
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, cfg->device));
-    if (prop.major < 10) {
+    if (prop.major != 10 || prop.minor != 0) {           // sm_100a code is not forward compatible (it does not load on sm_103 / sm_120)
         snprintf(g_cuda_err, sizeof g_cuda_err, "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device,
                  prop.major, prop.minor);
         return SSEGPU_E_CUDA;
@@ -257,7 +257,8 @@ int ssegpu_init(const ssegpu_config* cfg, ssegpu_ctx** out) {
 void ssegpu_destroy(ssegpu_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
-    cudaDeviceSynchronize();
+    for (ssegpu_batch* b : ctx->slots) if (b->stream) cudaStreamSynchronize(b->stream);   // own streams only: the GPU may be shared
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     for (ssegpu_batch* b : ctx->slots) free_batch(b);
     cudaFree(ctx->d_launch_scratch);
     cudaFree(ctx->d_encode_scratch);
@@ -392,7 +393,7 @@ int ssegpu_batch_wait(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t timeout_us) {
 
 int ssegpu_batch_release(ssegpu_ctx* ctx, ssegpu_batch* b) {
     if (!ctx || !b || b->ctx != ctx) return SSEGPU_E_INVAL;
-    if (b->state == SUBMITTED) { int rc = ssegpu_batch_wait(ctx, b, 0); if (rc != SSEGPU_OK && rc != SSEGPU_E_OVERFLOW) return rc; }
+    if (b->state == SUBMITTED) { int rc = ssegpu_batch_wait(ctx, b, 0); if (b->state == SUBMITTED) return rc; }   // still in flight: a CUDA error; data-level errors free the slot
     std::lock_guard<std::mutex> lk(ctx->mu);
     b->state = FREE;
     return SSEGPU_OK;
@@ -501,8 +502,11 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
                         put(d->acc_del.data(), d->acc_del.size() * 4), put(d->acc_eot.data(), d->acc_eot.size() * 4)});
     void* d_blob = nullptr;
     sse::InspectDev* d_desc = nullptr;
-    CU(cudaMalloc(&d_blob, blob.size()));
-    CU(cudaMemcpy(d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+    // new tables are built beside the live ones; on any failure they are freed and the old set stays in force
+    auto fail = [&](cudaError_t e, const char* what) { cudaFree(d_blob); cudaFree(d_desc); return cuda_fail(e, what); };
+    cudaError_t ce;
+    if ((ce = cudaMalloc(&d_blob, blob.size())) != cudaSuccess) return fail(ce, "cudaMalloc tables");
+    if ((ce = cudaMemcpy(d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy tables");
     sse::InspectDev h{};
     auto fill = [&](sse::DfaDev& dd, const sse_inspect::Dfa& d, const Off& o) {
         const uint8_t* base = static_cast<const uint8_t*>(d_blob);
@@ -520,9 +524,9 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
         h.fixed_len[i] = c.patterns[i].min_len == c.patterns[i].max_len ? c.patterns[i].min_len : 0;
         h.anchored_of[i] = c.anchored_of[i];
     }
-    CU(cudaMalloc(&d_desc, sizeof h));
-    CU(cudaMemcpy(d_desc, &h, sizeof h, cudaMemcpyHostToDevice));
-    CU(cudaDeviceSynchronize());                                    // no batch may still be using the old tables
+    if ((ce = cudaMalloc(&d_desc, sizeof h)) != cudaSuccess) return fail(ce, "cudaMalloc descriptor");
+    if ((ce = cudaMemcpy(d_desc, &h, sizeof h, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy descriptor");
+    if ((ce = cudaDeviceSynchronize()) != cudaSuccess) return fail(ce, "cudaDeviceSynchronize");   // no batch may still be using the old tables
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp);
     ctx->d_insp_blob = d_blob; ctx->d_insp = d_desc; ctx->insp_mode = mode; ctx->insp_start_state = c.forward.start[0];
@@ -572,21 +576,25 @@ int ssegpu_interest_apply(ssegpu_ctx* ctx, const ssegpu_sub_delta* d, uint32_t n
     t.flatten();
     void *ds = nullptr, *dk = nullptr, *dw = nullptr;
     sse::InterestDev* dd = nullptr;
-    CU(cudaMalloc(&ds, t.slots.size() * sizeof(sse::InterestSlot)));
-    CU(cudaMalloc(&dk, t.keys.size() * 4));
-    CU(cudaMalloc(&dw, t.wild_bytes.size()));
-    CU(cudaMalloc(&dd, sizeof(sse::InterestDev)));
-    CU(cudaMemcpy(ds, t.slots.data(), t.slots.size() * sizeof(sse::InterestSlot), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dk, t.keys.data(), t.keys.size() * 4, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dw, t.wild_bytes.data(), t.wild_bytes.size(), cudaMemcpyHostToDevice));
+    // the new table is built beside the live one; on a CUDA failure it is freed and the device keeps the old version
+    // (the host-side table already holds the deltas: the next successful apply uploads them)
+    auto fail = [&](cudaError_t e, const char* what) { cudaFree(ds); cudaFree(dk); cudaFree(dw); cudaFree(dd); return cuda_fail(e, what); };
+    cudaError_t ce;
+    if ((ce = cudaMalloc(&ds, t.slots.size() * sizeof(sse::InterestSlot))) != cudaSuccess) return fail(ce, "cudaMalloc interest slots");
+    if ((ce = cudaMalloc(&dk, t.keys.size() * 4)) != cudaSuccess) return fail(ce, "cudaMalloc interest keys");
+    if ((ce = cudaMalloc(&dw, t.wild_bytes.size())) != cudaSuccess) return fail(ce, "cudaMalloc wildcards");
+    if ((ce = cudaMalloc(&dd, sizeof(sse::InterestDev))) != cudaSuccess) return fail(ce, "cudaMalloc descriptor");
+    if ((ce = cudaMemcpy(ds, t.slots.data(), t.slots.size() * sizeof(sse::InterestSlot), cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy interest slots");
+    if ((ce = cudaMemcpy(dk, t.keys.data(), t.keys.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy interest keys");
+    if ((ce = cudaMemcpy(dw, t.wild_bytes.data(), t.wild_bytes.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy wildcards");
     sse::InterestDev h{};
     h.slots = static_cast<const sse::InterestSlot*>(ds); h.keys = static_cast<const uint32_t*>(dk);
     h.wild_single = t.wild_single; h.wild_generic = t.wild_generic;
     h.mask = (uint32_t)t.slots.size() - 1; h.n_wild = (uint32_t)t.wild_ids.size();
     h.wild_bytes = static_cast<const uint8_t*>(dw);
     for (size_t i = 0; i < t.wild_off.size(); i++) h.wild_off[i] = t.wild_off[i];
-    CU(cudaMemcpy(dd, &h, sizeof h, cudaMemcpyHostToDevice));
-    CU(cudaDeviceSynchronize());                                   // versioned swap: no batch may still read the old table
+    if ((ce = cudaMemcpy(dd, &h, sizeof h, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy descriptor");
+    if ((ce = cudaDeviceSynchronize()) != cudaSuccess) return fail(ce, "cudaDeviceSynchronize");   // versioned swap: no batch may still read the old table
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaFree(ctx->d_int_slots); cudaFree(ctx->d_int_keys); cudaFree(ctx->d_int_wild); cudaFree(ctx->d_interest);
     ctx->d_int_slots = ds; ctx->d_int_keys = dk; ctx->d_int_wild = dw; ctx->d_interest = dd;
