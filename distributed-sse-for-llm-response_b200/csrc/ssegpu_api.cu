@@ -456,8 +456,7 @@ int ssegpu_encode_launch(ssegpu_ctx* ctx, const void* d_cid, const uint32_t* d_c
     if (!ctx || !d_out_off || (op & ~(uint32_t)(SSEGPU_OP_BRIDGE | SSEGPU_OP_GO122 | SSEGPU_OP_RESP))) return SSEGPU_E_INVAL;
     if (n && (!d_cid || !d_cid_off || !d_tok || !d_tok_off || !d_seq || !d_done || !d_ts || !d_out || !d_out_len)) return SSEGPU_E_INVAL;
     if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
-    if ((reinterpret_cast<uintptr_t>(d_cid) | reinterpret_cast<uintptr_t>(d_tok)) & 3) return SSEGPU_E_INVAL;
-    if (reinterpret_cast<uintptr_t>(d_out) & 15) return SSEGPU_E_INVAL;
+    if ((reinterpret_cast<uintptr_t>(d_cid) | reinterpret_cast<uintptr_t>(d_tok) | reinterpret_cast<uintptr_t>(d_out)) & 15) return SSEGPU_E_INVAL;
     CU(cudaSetDevice(ctx->cfg.device));
     sse::EncodeArgs a{};
     a.cid = static_cast<const uint8_t*>(d_cid); a.cid_off = d_cid_off; a.tok = static_cast<const uint8_t*>(d_tok); a.tok_off = d_tok_off;

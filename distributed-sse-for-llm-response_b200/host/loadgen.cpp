@@ -240,6 +240,47 @@ uint64_t sseload_generate(int config, uint32_t n_conv, uint32_t n_tok, uint32_t 
     return total;
 }
 
+// The same messages as sseload_generate, as the producer sees them BEFORE marshalling (llm-stream-proxy/main.go:230-237):
+// raw conversation ids and token texts packed back to back with offsets, plus sequence / done / timestamp columns.
+// cid / tok may be nullptr to learn the byte totals (returned through *cid_total / *tok_total).  Single pass per column,
+// serial prefix: this is bench / test input preparation, not a measured path.
+int sseload_generate_columns(int config, uint32_t n_conv, uint32_t n_tok, uint32_t conv_first, const uint32_t* conv_map,
+                             uint64_t seed_id, uint64_t seed_tok, uint8_t* cid, uint64_t cid_cap, uint32_t* cid_off,
+                             uint8_t* tok, uint64_t tok_cap, uint32_t* tok_off, int64_t* seq, uint8_t* done, int64_t* ts,
+                             uint64_t* cid_total, uint64_t* tok_total) {
+    const uint64_t n = (uint64_t)n_conv * n_tok;
+    uint64_t cw = 0, tw = 0;
+    for (uint64_t r = 0; r < n; r++) {
+        const uint32_t i_local = (uint32_t)(r % n_conv), j = (uint32_t)(r / n_conv);
+        const uint32_t i = conv_map ? conv_map[i_local] : conv_first + i_local;
+        uint8_t cb[64], tb[64];
+        size_t cl, tl;
+        const uint8_t* tp = tb;
+        if (config == 0) {
+            cl = loadtest_id(cb, i);
+            tp = reinterpret_cast<const uint8_t*>(kWords[j % 56]);
+            tl = strlen(kWords[j % 56]);
+        } else {
+            cl = uuid_id(cb, seed_id, i);
+            tl = llm_token(tb, seed_tok, i, j);
+        }
+        if (cw + cl > 0xFFFFFFF0ull || tw + tl > 0xFFFFFFF0ull) return -1;
+        if (cid) { if (cw + cl > cid_cap) return -2; memcpy(cid + cw, cb, cl); }
+        if (tok) { if (tw + tl > tok_cap) return -2; memcpy(tok + tw, tp, tl); }
+        if (cid_off) cid_off[r] = (uint32_t)cw;
+        if (tok_off) tok_off[r] = (uint32_t)tw;
+        if (seq) seq[r] = (int64_t)j + 1;
+        if (done) done[r] = j == n_tok - 1;
+        if (ts) ts[r] = kClock + (int64_t)j * 50000000ll + i;
+        cw += cl; tw += tl;
+    }
+    if (cid_off) cid_off[n] = (uint32_t)cw;
+    if (tok_off) tok_off[n] = (uint32_t)tw;
+    if (cid_total) *cid_total = cw;
+    if (tok_total) *tok_total = tw;
+    return 0;
+}
+
 // Conversation id of conversation i under a config (for sharding / interest tables). Returns length.
 uint32_t sseload_conversation_id(int config, uint64_t seed_id, uint32_t i, uint8_t* dst) {
     return (uint32_t)(config == 0 ? loadtest_id(dst, i) : uuid_id(dst, seed_id, i));

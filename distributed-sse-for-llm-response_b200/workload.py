@@ -64,6 +64,33 @@ def generate(config, n_conv, n_tok, conv_first=0, seed_ids=SEED_IDS, seed_tok=SE
     return arena, off
 
 
+def generate_columns(config, n_conv, n_tok, conv_first=0, seed_ids=SEED_IDS, seed_tok=SEED_TOK, conv_map=None):
+    """The messages of generate() before marshalling, as the producer-side encoder takes them:
+    -> (cid uint8[], cid_off uint32[n+1], tok uint8[], tok_off uint32[n+1], seq int64[n], done uint8[n], ts int64[n]);
+    both byte arenas carry 32 bytes of padding."""
+    lib = _lib()
+    cm = None
+    if conv_map is not None:
+        conv_map = np.ascontiguousarray(conv_map, dtype=np.uint32)
+        n_conv = len(conv_map)
+        cm = conv_map.ctypes.data
+    n = n_conv * n_tok
+    ct, tt = C.c_uint64(0), C.c_uint64(0)
+    f = lib.sseload_generate_columns
+    f.restype = C.c_int
+    f.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p,
+                  C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    if f(config, n_conv, n_tok, conv_first, cm, seed_ids, seed_tok, None, 0, None, None, 0, None, None, None, None, C.byref(ct), C.byref(tt)) != 0:
+        raise ValueError("workload exceeds the 4 GiB arena limit")
+    cid, tok = np.zeros(ct.value + 32, dtype=np.uint8), np.zeros(tt.value + 32, dtype=np.uint8)
+    cid_off, tok_off = np.empty(n + 1, dtype=np.uint32), np.empty(n + 1, dtype=np.uint32)
+    seq, ts, done = np.empty(n, dtype=np.int64), np.empty(n, dtype=np.int64), np.empty(n, dtype=np.uint8)
+    rc = f(config, n_conv, n_tok, conv_first, cm, seed_ids, seed_tok, cid.ctypes.data, ct.value, cid_off.ctypes.data, tok.ctypes.data, tt.value,
+           tok_off.ctypes.data, seq.ctypes.data, done.ctypes.data, ts.ctypes.data, None, None)
+    assert rc == 0, rc
+    return cid, cid_off, tok, tok_off, seq, done, ts
+
+
 def conversation_id(config, i, seed_ids=SEED_IDS):
     buf = C.create_string_buffer(64)
     n = _lib().sseload_conversation_id(config, seed_ids, i, buf)

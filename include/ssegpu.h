@@ -213,7 +213,7 @@ int ssegpu_frame_launch_result(ssegpu_ctx *ctx, ssegpu_counters *out);
  * json.Marshal(TokenMessage{cid_i, tok_i, seq[i], done[i] != 0, ts[i]}) -- field order, escapeHTML and the
  * \ufffd replacement of invalid UTF-8 exactly as encoding/json -- written at d_out + d_out_off[i],
  * d_out_len[i] bytes.  cid_i / tok_i are the RAW string bytes d_cid[d_cid_off[i] .. d_cid_off[i+1]) and likewise
- * for tok; both arenas must be 4-byte aligned with 32 readable bytes after their last byte, d_out 16-byte aligned.
+ * for tok; both arenas and d_out must be 16-byte aligned, the arenas with 32 readable bytes after their last byte.
  * With SSEGPU_OP_BRIDGE each record is preceded by its channel "chat.<cid>.tokens" (the PUBLISH
  * channel, main.go:240) and d_chan_len[i] (may be NULL otherwise) receives the channel's length.  SSEGPU_OP_GO122
  * selects the Go >= 1.22 spelling of \b and \f.  Records of one 128-message tile are contiguous and tiles

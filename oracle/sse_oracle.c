@@ -612,6 +612,31 @@ int sseo_bridge_batch(const uint8_t *in, const uint32_t *in_off, uint32_t n, int
     return 0;
 }
 
+/* Inverse view for tests and the encoder bench: json.Unmarshal every payload (all must decode) into the columns the
+ * producer-side encoder takes.  cid / tok receive the decoded strings back to back; returns 0, or -1 - i for the first
+ * payload i that does not decode, or -(n+2) when a capacity is too small. */
+int64_t sseo_decode_columns(const uint8_t *in, const uint32_t *in_off, uint32_t n,
+                            uint8_t *cid, size_t cid_cap, uint32_t *cid_off, uint8_t *tok, size_t tok_cap, uint32_t *tok_off,
+                            int64_t *seq, uint8_t *done, int64_t *ts)
+{
+    size_t scap = 0, cw = 0, tw = 0;
+    uint8_t *scratch = NULL;
+    for (uint32_t i = 0; i < n; i++) {
+        const uint8_t *p = in + in_off[i];
+        size_t len = in_off[i + 1] - in_off[i];
+        if (6 * len + 16 > scap) { scap = 2 * (6 * len + 16); free(scratch); scratch = (uint8_t *)malloc(scap); }
+        sseo_msg m;
+        if (sseo_unmarshal(p, len, &m, scratch) != SSEO_OK) { free(scratch); return -1 - (int64_t)i; }
+        if (cw + m.cid_len > cid_cap || tw + m.tok_len > tok_cap) { free(scratch); return -((int64_t)n + 2); }
+        cid_off[i] = (uint32_t)cw; memcpy(cid + cw, m.cid, m.cid_len); cw += m.cid_len;
+        tok_off[i] = (uint32_t)tw; memcpy(tok + tw, m.tok, m.tok_len); tw += m.tok_len;
+        seq[i] = m.seq; done[i] = m.done ? 1 : 0; ts[i] = m.ts;
+    }
+    cid_off[n] = (uint32_t)cw; tok_off[n] = (uint32_t)tw;
+    free(scratch);
+    return 0;
+}
+
 /* Bridge records as complete NATS client-protocol messages: what nc.Publish(subject, data) (redis-nats-bridge/main.go:164)
  * puts on the wire.  The reference delegates this to github.com/nats-io/nats.go v1.31.0 (src/redis-nats-bridge/go.mod),
  * which is not vendored; its publish() writes "PUB " subject " " decimal(len(data)) "\r\n" data "\r\n" (the NATS client

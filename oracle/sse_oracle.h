@@ -63,6 +63,11 @@ size_t sseo_encode_batch(const uint8_t *cid, const uint32_t *cid_off, const uint
                          const int64_t *seq, const uint8_t *done, const int64_t *ts, uint32_t n, int go122, int with_channel,
                          uint8_t *out, size_t out_cap, uint64_t *off, uint32_t *chan_len);
 
+/* json.Unmarshal every payload into the encoder's columns (tests, encoder bench). 0 = ok. */
+int64_t sseo_decode_columns(const uint8_t *in, const uint32_t *in_off, uint32_t n,
+                            uint8_t *cid, size_t cid_cap, uint32_t *cid_off, uint8_t *tok, size_t tok_cap, uint32_t *tok_off,
+                            int64_t *seq, uint8_t *done, int64_t *ts);
+
 /* Bridge records as NATS client-protocol messages "PUB <subject> <#bytes>\r\n<payload>\r\n" (what nc.Publish writes
  * for redis-nats-bridge/main.go:164; nats.go v1.31.0, not vendored -- stated from the NATS protocol). */
 int sseo_bridge_pub_batch(const uint8_t *in, const uint32_t *in_off, uint32_t n, int go122,

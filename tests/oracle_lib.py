@@ -83,6 +83,20 @@ class Oracle:
         assert rc == 0
         return out[: int(out_off[n])], out_off, subj_len, status
 
+    def decode_columns(self, arena, off):
+        """payload arena -> the encoder's columns (cid, cid_off, tok, tok_off, seq, done, ts); every payload must decode."""
+        n = len(off) - 1
+        cap = int(off[n]) + 64
+        cid, tok = np.zeros(cap, dtype=np.uint8), np.zeros(cap, dtype=np.uint8)
+        cid_off, tok_off = np.empty(n + 1, dtype=np.uint32), np.empty(n + 1, dtype=np.uint32)
+        seq, ts, done = np.empty(n, dtype=np.int64), np.empty(n, dtype=np.int64), np.empty(n, dtype=np.uint8)
+        self.lib.sseo_decode_columns.restype = C.c_int64
+        self.lib.sseo_decode_columns.argtypes = [u8p, u32p, C.c_uint32, u8p, C.c_size_t, u32p, u8p, C.c_size_t, u32p, i64p, u8p, i64p]
+        rc = self.lib.sseo_decode_columns(_ptr(arena, u8p), _ptr(off, u32p), n, _ptr(cid, u8p), cap - 32, _ptr(cid_off, u32p), _ptr(tok, u8p), cap - 32,
+                                          _ptr(tok_off, u32p), _ptr(seq, i64p), _ptr(done, u8p), _ptr(ts, i64p))
+        assert rc == 0, rc
+        return cid[: int(cid_off[n]) + 32].copy(), cid_off, tok[: int(tok_off[n]) + 32].copy(), tok_off, seq, done, ts
+
     def bridge_pub(self, arena, off, go122=False):
         n = len(off) - 1
         cap = int(off[n]) * 9 + 260 * n + 64

@@ -103,3 +103,20 @@ def test_resp_publish_framing(lib, oracle):
         got_h, chan_h = hc.encode(lib, cols, hc.OP_RESP | (hc.OP_GO122 if go122 else 0))
         assert got_o == want and got_h == want
         assert list(chan_o) == list(chan_h) == [12 + len(m[0]) for m in msgs]
+
+
+def test_workload_columns_are_the_workload_before_marshalling(oracle):
+    """workload.generate_columns() vs the oracle's decode of workload.generate(), configs 0 and 1; and marshalling the
+    columns gives the payload arena back (this is what the encoder bench and the full-shape GPU test rely on)."""
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    for config in (0, 1):
+        n_conv, n_tok = 250, 40
+        n = n_conv * n_tok
+        arena, off = pkg.workload.generate(config, n_conv, n_tok)
+        cols = pkg.workload.generate_columns(config, n_conv, n_tok)
+        for got, want in zip(cols, oracle.decode_columns(arena, off)):
+            k = len(want) if want.dtype != np.uint8 or len(want) == n else len(want) - 32
+            assert np.array_equal(got[:k], want[:k])
+        recs, _ = oracle.encode(cols)
+        assert b"".join(recs) == arena[: int(off[n])].tobytes()

@@ -154,3 +154,47 @@ def test_encode_then_adapter_on_the_device(pkg, oracle):
             assert out[int(oo[i]):int(oo[i + 1])] == b"event: token\nid: %d\ndata: " % msgs[i][2] + recs[i] + b"\n\n"
     finally:
         eng.close()
+
+
+def test_encode_reproduces_the_baseline_workload_byte_for_byte(pkg, oracle):
+    """Full-shape property: the config-1 workload (10 000 conversations x 200 tokens, UUID ids, 1.5 % escapes, 1 % multi-byte
+    UTF-8) as columns -> GPU encoder -> must be the workload's payload arena itself; the columns are also what the oracle
+    decodes from that arena."""
+    n_conv, n_tok = 10000, 200
+    arena, off = pkg.workload.generate(1, n_conv, n_tok)
+    n = n_conv * n_tok
+    cols = pkg.workload.generate_columns(1, n_conv, n_tok)
+    for got, want in zip(cols, oracle.decode_columns(arena, off)):
+        k = len(want) if want.dtype != np.uint8 or len(want) == n else len(want) - 32          # byte arenas: ignore the padding
+        assert np.array_equal(got[:k], want[:k])
+    eng = pkg.SseGpu(device=0, max_records=n, max_in_bytes=64 << 20, ring_slots=1)
+    try:
+        recs, _, rc, d = gpu_encode(eng, cols, 0, keep=True)
+        assert rc == 0
+        assert b"".join(recs) == arena[: int(off[n])].tobytes()
+        assert [len(r) for r in recs[:1000]] == list(np.diff(off[:1001].astype(np.int64)))
+    finally:
+        eng.close()
+
+
+def test_long_and_hostile_strings_take_every_path(eng, oracle):
+    """ids and tokens longer than one warp trip (32 positions), multi-byte sequences across the trip boundary, tiles that
+    overflow the staging tile (emitted serially into the arena) and tiles whose strings overflow the input buffers."""
+    import random
+    rng = random.Random(77)
+    pieces = [b"a", b"\n", b"\"", "é".encode(), "世".encode(), "\U0001f600".encode(), b"\xff", b"\xe4\xb8", b"<", " ".encode()]
+    msgs = []
+    for i in range(1500):
+        k = rng.choice([0, 1, 5, 30, 31, 32, 33, 34, 63, 64, 65, 200, 700])
+        tok = b"".join(rng.choice(pieces) for _ in range(k))
+        cid = b"".join(rng.choice(pieces) for _ in range(rng.choice([0, 3, 36, 40, 100])))
+        msgs.append((cid, tok, i, i % 7 == 0, 1700000000000000000 + i))
+    cols = ec.columns(msgs)
+    for op in (0, OP_GO122, OP_BRIDGE, OP_RESP):
+        got, chan, rc = gpu_encode(eng, cols, op)
+        assert rc == 0
+        if op & OP_RESP:
+            want = [ec.model_resp(m) for m in msgs]
+        else:
+            want = [(ec.model_channel(m) if op & OP_BRIDGE else b"") + ec.model_encode(m, bool(op & OP_GO122)) for m in msgs]
+        assert got == want

@@ -17,25 +17,20 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--conversations", type=int, default=10000)
     ap.add_argument("--tokens", type=int, default=1000)
+    ap.add_argument("--plain", action="store_true", help="experiment: replace every token byte that needs escaping or is not ASCII by 'x'")
     a = ap.parse_args()
     import torch
     pkg = load_package()
     n_conv, n_tok = a.conversations, a.tokens
     n = n_conv * n_tok
-    rng = np.random.default_rng(1)
-    vocab = [b" the", b" of", b" and", b"Hello", b",", b" world", b".", b"\n", b" caf\xc3\xa9", b" token", b" stream", b" a", b" is", b" response"]
-    ids = np.array([b"%08x-%04x-4%03x-a%03x-%012x" % (i, i & 0xFFFF, i & 0xFFF, i & 0xFFF, i * 2654435761 & 0xFFFFFFFFFFFF) for i in range(n_conv)])
-    conv = np.tile(np.arange(n_conv), n_tok)                       # message i belongs to conversation i % n_conv (interleaved arrival)
-    cid = np.frombuffer(b"".join(ids[conv].tolist()) + b"\0" * 16, dtype=np.uint8)
-    cid_off = (np.arange(n + 1, dtype=np.uint64) * 36).astype(np.uint32)
-    pick = rng.integers(0, len(vocab), n)
-    lens = np.array([len(v) for v in vocab])[pick]
-    tok_off = np.zeros(n + 1, dtype=np.uint32)
-    tok_off[1:] = np.cumsum(lens)
-    tok = np.frombuffer(b"".join(vocab[k] for k in pick) + b"\0" * 16, dtype=np.uint8)
-    seq = (np.arange(n) // n_conv + 1).astype(np.int64)
-    done = (seq == n_tok).astype(np.uint8)
-    ts = 1700000000000000000 + np.arange(n, dtype=np.int64) * 1000
+    # columns = the BASELINE config-1 workload before marshalling (UUID ids, Mistral-7B-like token lengths, 1.5 % tokens with an
+    # escape, 1 % with multi-byte UTF-8); the encoder must reproduce the workload's payloads, checked below
+    arena, off = pkg.workload.generate(1, n_conv, n_tok)
+    cid, cid_off, tok, tok_off, seq, done, ts = pkg.workload.generate_columns(1, n_conv, n_tok)
+    if a.plain:
+        bad = (tok < 0x20) | (tok >= 0x80) | np.isin(tok, np.frombuffer(b'"\\<>&', dtype=np.uint8))
+        tok = np.where(bad, np.uint8(ord("x")), tok)
+        tok[int(tok_off[n]):] = 0
     eng = pkg.SseGpu(device=0, max_records=n, max_in_bytes=64 << 20, ring_slots=1)
     dev = lambda x, t: torch.from_numpy(np.ascontiguousarray(x).view(t)).cuda()  # noqa: E731
     d = [dev(cid, np.uint8), dev(cid_off, np.int32), dev(tok, np.uint8), dev(tok_off, np.int32), dev(seq, np.int64), dev(done, np.uint8), dev(ts, np.int64)]
@@ -57,6 +52,10 @@ def main():
     torch.cuda.synchronize()
     rc, used = eng.encode_result()
     assert rc == 0
+    got_len = out_len.cpu().numpy().astype(np.int64)
+    assert os.environ.get("SSEGPU_LIB") or a.plain or np.array_equal(got_len, np.diff(off.astype(np.int64))), "encoded lengths differ from the workload's payloads"
+    k0 = int(out_off[12345].item())
+    assert os.environ.get("SSEGPU_LIB") or a.plain or out[k0:k0 + int(got_len[12345])].cpu().numpy().tobytes() == arena[int(off[12345]):int(off[12346])].tobytes()
     ms = float(np.mean([e0.elapsed_time(e1) for e0, e1 in evs[a.warmup:]]))
     in_bytes = int(cid_off[n]) + int(tok_off[n]) + n * (4 + 4 + 8 + 1 + 8)
     out_bytes = int(out_len.sum().item()) + n * (8 + 4)

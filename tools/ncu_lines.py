@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Per-source-line instruction and stall-sample totals for the frame kernel.
 
-usage: tools/ncu_lines.py <report.ncu-rep> [libssegpu.so] [--top N] [--func regex]
+usage: tools/ncu_lines.py <report.ncu-rep> [libssegpu.so] [--top N] [--func regex] [--unit sse_encode --kernel k_encode_messages]
 Joins `ncu --page source --csv` (SASS rows, in order) with `nvdisasm -g` line info of the kernel cubin
 extracted from the library that was profiled (must be the same build)."""
 import csv
@@ -18,7 +18,9 @@ top = int(sys.argv[sys.argv.index("--top") + 1]) if "--top" in sys.argv else 45
 
 tmp = tempfile.mkdtemp()
 subprocess.check_call(["cuobjdump", "-xelf", "all", lib], cwd=tmp, stdout=subprocess.DEVNULL)
-cubin = [f for f in os.listdir(tmp) if f.startswith("sse_kernels.")][0]
+unit = sys.argv[sys.argv.index("--unit") + 1] if "--unit" in sys.argv else "sse_kernels"
+kern = sys.argv[sys.argv.index("--kernel") + 1] if "--kernel" in sys.argv else "k_frame_tiles"
+cubin = [f for f in os.listdir(tmp) if f.startswith(unit + ".")][0]
 dis = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
 
 # instruction order -> (innermost file:line, chain of frames innermost..outermost)
@@ -29,7 +31,7 @@ pending = []
 in_kernel = False
 for ln in dis.splitlines():
     if ln.startswith(".text."):
-        in_kernel = "k_frame_tiles" in ln and ("Lb0" in ln or "ILb0" in ln)
+        in_kernel = kern in ln and (kern != "k_frame_tiles" or "Lb0" in ln or "ILb0" in ln)
     m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
     if m:
         pending.append((os.path.basename(m.group(1)), int(m.group(2))))
