@@ -11,7 +11,9 @@
 // memory as two TMA bulk copies, issued one tile AHEAD into the other half of a double buffer; the per-message scalars
 // of the next tile are loaded into registers while the current tile is encoded.  One thread per message: measure,
 // CTA scan, one atomic for the tile's 16-byte aligned slice of the arena (tiles land in completion order, like
-// k_frame_tiles), records assembled in a staging tile, one TMA bulk store per tile.
+// k_frame_tiles), records assembled in a staging tile, one TMA bulk store per tile.  (A warp-cooperative, one-byte-per-lane
+// escaper for the non-plain strings was built and measured: 1.40 ms against 1.18 ms for the in-lane walk on the BASELINE
+// workload, where 2.5 % of the tokens need it -- see profiles/r01_encode_notes.md.)
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "sse_kernels.h"
@@ -58,37 +60,7 @@ __device__ __noinline__ void encode_emit_global(uint32_t op, const uint8_t* cbas
     PtrSrc cid{cbase}, tok{tbase};
     PtrDst d{dst};
     Writer<PtrDst, true> w(d, pos);
-    encode_emit<false>(cid, cb, ce, tok, tb, te, seq, done, ts, (op & OP_GO122) != 0, *p, w, nullptr);
-}
-
-// Warp-cooperative appendString for ONE string [b, e): every lane takes one byte position per trip of 32, computes what
-// that position contributes (escape_unit), a warp scan places the contributions, the bytes go out with byte stores.
-// dst == nullptr: count only.  Returns the quoted length.  Must be called by the whole (converged) warp.
-__device__ __forceinline__ uint32_t warp_escape_string(const uint8_t* base, uint32_t b, uint32_t e, bool go122, uint8_t* dst, uint32_t lane) {
-    PtrSrc s{base};
-    uint32_t off = 1;                                                     // after the opening quote
-    for (uint32_t p0 = b; p0 < e; p0 += 32) {
-        const uint32_t pos = p0 + lane;
-        EscUnit u{0, 0};
-        const uint32_t c = pos < e ? s.ld8(pos) : 0u;
-        // a trip whose 32 bytes (and the three before it, which could start a sequence reaching into it) are all ASCII needs no decoding
-        const uint32_t prev_hi = (lane < 3 && p0 + lane >= b + 3) ? s.ld8(p0 - 3 + lane) : 0u;
-        const bool ascii = !__any_sync(0xFFFFFFFFu, ((c | prev_hi) & 0x80u) != 0);
-        if (pos < e) u = ascii ? escape_unit_ascii(c, go122) : escape_unit(s, b, e, pos, go122);
-        uint32_t incl = u.n;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-            if (lane >= (uint32_t)d) incl += v;
-        }
-        if (dst) {
-            uint8_t* q = dst + off + incl - u.n;
-            for (uint32_t k = 0; k < u.n; k++) q[k] = (uint8_t)(u.bytes >> (8 * k));
-        }
-        off += __shfl_sync(0xFFFFFFFFu, incl, 31);
-    }
-    if (dst && lane == 0) { dst[0] = '"'; dst[off] = '"'; }
-    return off + 1;
+    encode_emit(cid, cb, ce, tok, tb, te, seq, done, ts, (op & OP_GO122) != 0, *p, w);
 }
 
 // byte ranges of a tile's ids and tokens, clamped into the arenas (offsets are caller data)
@@ -179,20 +151,12 @@ __global__ void __launch_bounds__(ENC_TILE) k_encode_messages(const EncodeArgs a
             cb = min(max(cb, clo), chi); ce = min(max(ce, cb), chi);
             tb = min(max(tb, tlo), thi); te = min(max(te, tb), thi);
         }
-        // plan: plain strings are their own spelling; the others are measured by the whole warp, one string at a time
+        // plan: plain strings are their own spelling; the others are measured by their lane
         bool cplain = true, tplain = true;
         if (active) { cplain = go_string_is_plain(cid, cb, ce); tplain = go_string_is_plain(tok, tb, te); }
         uint32_t cid_n = ce - cb + 2, tok_n = te - tb + 2;
-        for (uint32_t m = __ballot_sync(0xFFFFFFFFu, !cplain); m; m &= m - 1) {
-            const int owner = __ffs((int)m) - 1;
-            const uint32_t n = warp_escape_string(cbase, __shfl_sync(0xFFFFFFFFu, cb, owner), __shfl_sync(0xFFFFFFFFu, ce, owner), go122, nullptr, lane);
-            if ((int)lane == owner) cid_n = n;
-        }
-        for (uint32_t m = __ballot_sync(0xFFFFFFFFu, !tplain); m; m &= m - 1) {
-            const int owner = __ffs((int)m) - 1;
-            const uint32_t n = warp_escape_string(tbase, __shfl_sync(0xFFFFFFFFu, tb, owner), __shfl_sync(0xFFFFFFFFu, te, owner), go122, nullptr, lane);
-            if ((int)lane == owner) tok_n = n;
-        }
+        if (!cplain) cid_n = go_string_len(cid, cb, ce, go122);
+        if (!tplain) tok_n = go_string_len(tok, tb, te, go122);
         if (active) p = encode_plan_from(ce - cb, cid_n, cplain, tok_n, tplain, seq, done != 0, ts, a.op);
         const uint32_t len = p.len;
         uint32_t incl = len;
@@ -211,23 +175,11 @@ __global__ void __launch_bounds__(ENC_TILE) k_encode_messages(const EncodeArgs a
         if (tid == 0) es->base = atomicAdd(a.cursor, (unsigned long long)alloc);        // the answer is not needed until after the emission
         const uint32_t local = wpre + incl - len;
         const bool staged = alloc <= stage_bytes;                                     // tile-uniform
-        uint32_t gap[2] = {0, 0};
         if (staged) {
             if (active) {
                 Ptr32Dst d{s_out};
                 Writer<Ptr32Dst, true> w(d, local);
-                encode_emit<true>(cid, cb, ce, tok, tb, te, seq, done != 0, ts, go122, p, w, gap);
-            }
-            // the strings that were jumped over: whole warp, one string at a time, one byte position per lane
-            for (uint32_t m = __ballot_sync(0xFFFFFFFFu, !cplain); m; m &= m - 1) {
-                const int owner = __ffs((int)m) - 1;
-                warp_escape_string(cbase, __shfl_sync(0xFFFFFFFFu, cb, owner), __shfl_sync(0xFFFFFFFFu, ce, owner), go122,
-                                   s_out + __shfl_sync(0xFFFFFFFFu, gap[0], owner), lane);
-            }
-            for (uint32_t m = __ballot_sync(0xFFFFFFFFu, !tplain); m; m &= m - 1) {
-                const int owner = __ffs((int)m) - 1;
-                warp_escape_string(tbase, __shfl_sync(0xFFFFFFFFu, tb, owner), __shfl_sync(0xFFFFFFFFu, te, owner), go122,
-                                   s_out + __shfl_sync(0xFFFFFFFFu, gap[1], owner), lane);
+                encode_emit(cid, cb, ce, tok, tb, te, seq, done != 0, ts, go122, p, w);
             }
             if (tid < alloc - total) s_out[total + tid] = 0;
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");              // staging writes -> visible to the bulk store

@@ -236,10 +236,6 @@ template <class Dst, bool EMIT> struct Writer {
         uint32_t t = (sh >> 3) + n;
         wpos += t & ~3u; sh = (t & 3u) * 8;
     }
-    SSE_HD void jump(pos_t to) {                        // close the stream here, reopen it at `to` (somebody else fills the gap)
-        finish();
-        wpos = to & ~(pos_t)3; acc = 0; sh = ((uint32_t)to & 3u) * 8; first = (uint32_t)to & 3u;
-    }
     SSE_HD void finish() {                              // trailing partial word: bytes [first, sh/8)
         if (EMIT) {
             const uint32_t k1 = sh >> 3, v = (uint32_t)acc;
@@ -943,62 +939,33 @@ template <class Src> SSE_HD bool go_string_is_plain(const Src& s, uint32_t b, ui
 // encode.go appendString(escapeHTML=true) over a RAW Go string (not a JSON literal; producer side,
 // llm-stream-proxy/main.go:230-239): bytes that do not start a valid UTF-8 sequence become the six characters \\ufffd, one per byte.
 
-// ---- one byte position of a raw Go string -> its share of the JSON spelling -------------------------------------------
-// Lane-parallel form of appendString (escapeHTML on): position `pos` of the string [b, e) contributes 0..6 output bytes,
-// independently of every other position.  A byte inside a valid multi-byte sequence that starts up to three positions
-// earlier contributes nothing (the sequence's first byte emits all of it); lead bytes are >= 0xC2 and continuation bytes
-// are 0x80..0xBF, so a byte that starts a valid sequence is never itself covered, and walking the positions
-// independently is the same as utf8.DecodeRune's sequential walk.  The warp-cooperative encoder gives one position to
-// each lane; the host test double walks the positions in a loop.
-struct EscUnit { uint32_t n; uint64_t bytes; };          // bytes: little endian, n of them
-struct RegOut {                                          // the smallest possible writer: up to 8 bytes in a register pair
-    uint64_t v; uint32_t n;
-    SSE_HD void put(uint32_t b) { v |= (uint64_t)(b & 0xFFu) << (8 * n); n++; }
-};
-template <class Src> SSE_HD EscUnit escape_unit(const Src& s, uint32_t b, uint32_t e, uint32_t pos, bool go122) {
-    EscUnit u{0, 0};
-    uint32_t r;
-    bool covered = false;
-    for (uint32_t d = 1; d <= 3; d++)
-        if (pos >= b + d && utf8_decode(s, pos - d, e, r) > d) covered = true;
-    if (covered) return u;
-    const uint32_t n = utf8_decode(s, pos, e, r);
-    RegOut o{0, 0};
-    if (r == 0xFFFD && n == 1) { o.put('\\'); o.put('u'); o.put('f'); o.put('f'); o.put('f'); o.put('d'); }
-    else put_rune_json(o, r, go122);
-    u.n = o.n; u.bytes = o.v;
-    return u;
-}
-// The same for a position known to hold an ASCII byte with only ASCII around it (no sequence can cover it): no decoding.
-SSE_HD EscUnit escape_unit_ascii(uint32_t c, bool go122) {
-    EscUnit u;
-    if (c >= 0x20 && c != '"' && c != '\\' && c != '<' && c != '>' && c != '&') { u.n = 1; u.bytes = c; return u; }
-    uint32_t e = 0;                                                        // second byte of a two-byte escape
-    if (c == '"' || c == '\\') e = c;
-    else if (c == '\n') e = 'n';
-    else if (c == '\r') e = 'r';
-    else if (c == '\t') e = 't';
-    else if (go122 && c == 8) e = 'b';
-    else if (go122 && c == 12) e = 'f';
-    if (e) { u.n = 2; u.bytes = '\\' | (e << 8); return u; }
-    u.n = 6;                                                               // \u00XX, lower-case hex
-    u.bytes = (uint64_t)('\\' | ('u' << 8) | ('0' << 16) | ('0' << 24)) | (uint64_t)(hexl(c >> 4) | (hexl(c & 0xF) << 8)) << 32;
-    return u;
-}
-// serial walk over the units (host test double; device code outside a converged warp)
+// One thread walks the string: runs of plain bytes go out up to four at a time, every other byte takes
+// the rune path for that one rune.
 template <class Src, class W> SSE_HD void put_go_string_units(const Src& s, uint32_t b, uint32_t e, W& w, bool go122) {
     w.put('"');
-    for (uint32_t pos = b; pos < e; pos++) {
-        const EscUnit u = escape_unit(s, b, e, pos, go122);
-        for (uint32_t k = 0; k < u.n; k++) w.put((uint32_t)(u.bytes >> (8 * k)) & 0xFFu);
+    uint32_t pos = b;
+    while (pos < e) {
+        uint32_t wd = ld32u(s, pos);
+        const uint32_t rem = e - pos;
+        if (rem < 4) { const uint32_t keep = 0xFFFFFFFFu >> (32 - 8 * rem); wd = (wd & keep) | (0x01010101u & ~keep); }   // bytes past the end stop the run
+        const uint32_t m = special_mask(wd);
+        const uint32_t np = m ? first_byte_idx(m) : 4u;
+        if (np) { w.put_n(wd, np); pos += np; }
+        if (m && pos < e) {
+            uint32_t r;
+            const uint32_t n = utf8_decode(s, pos, e, r);
+            if (r == 0xFFFD && n == 1) { w.put('\\'); w.put('u'); w.put('f'); w.put('f'); w.put('f'); w.put('d'); }
+            else put_rune_json(w, r, go122);
+            pos += n;
+        }
     }
     w.put('"');
 }
-
 template <class Src> SSE_HD uint32_t go_string_len(const Src& s, uint32_t b, uint32_t e, bool go122) {
-    uint32_t n = 2;
-    for (uint32_t pos = b; pos < e; pos++) n += escape_unit(s, b, e, pos, go122).n;
-    return n;
+    Ptr32Dst nd{nullptr};
+    Writer<Ptr32Dst, false> w(nd, 0);
+    put_go_string_units(s, b, e, w, go122);
+    return w.pos();
 }
 
 // ---- whole message -----------------------------------------------------------------------------------------------------
@@ -1028,14 +995,11 @@ template <class W> struct NfView {
     SSE_HD void put_n(uint32_t v, uint32_t n) { w.put_n_nf(v, n); }
     SSE_HD void put32(uint32_t v) { w.put32_nf(v); }
 };
-// SKIP: a string that is not plain is NOT written; the writer jumps over its p.cid_n / p.tok_n bytes and reports where it
-// starts (gap[0] = id, gap[1] = token; position of the opening quote) -- the warp fills it afterwards, one position per
-// lane.  !SKIP: such strings are written here, serially.
-template <bool SKIP, class Src, class W>
+template <class Src, class W>
 SSE_HD void encode_emit(const Src& cid, uint32_t cb, uint32_t ce, const Src& tok, uint32_t tb, uint32_t te, int64_t seq, bool done,
-                        int64_t ts, bool go122, const EncPlan& p, W& w, typename W::pos_t* gap) {
-    // a record's first word (and the first word after a jump) may share its 32-bit word with foreign bytes: general put;
-    // everything else goes through the no-first-word forms
+                        int64_t ts, bool go122, const EncPlan& p, W& w) {
+    // a record's first word may share its 32-bit word with the previous record: general put; everything after it goes
+    // through the no-first-word forms
     NfView<W> v{w};
     if (p.resp) {
         w.put32(w4("*3\r\n"));
@@ -1062,11 +1026,8 @@ SSE_HD void encode_emit(const Src& cid, uint32_t cb, uint32_t ce, const Src& tok
         const Src src = k ? tok : cid;
         const uint32_t sb = k ? tb : cb, se = k ? te : ce;
         if (k ? p.tok_plain : p.cid_plain) { w.put_n_nf('"', 1); put_copy_t<true>(src, sb, se - sb, w); w.put_n_nf('"', 1); }
-        else if (SKIP) { gap[k] = w.pos(); w.jump(w.pos() + (k ? p.tok_n : p.cid_n)); }
         else put_go_string_units(src, sb, se, v, go122);
-        // the literal after a string starts with a general put: the string may have been jumped over
-        if (k == 0) { w.put32(w4(",\"to")); SSE_PUT_LIT_NF(w, "ken\":"); }
-        else { w.put32(w4(",\"se")); SSE_PUT_LIT_NF(w, "quence\":"); }
+        if (k == 0) SSE_PUT_LIT_NF(w, ",\"token\":"); else SSE_PUT_LIT_NF(w, ",\"sequence\":");
     }
     put_int(v, seq);
     if (done) SSE_PUT_LIT_NF(w, ",\"done\":true,\"timestamp\":"); else SSE_PUT_LIT_NF(w, ",\"done\":false,\"timestamp\":");

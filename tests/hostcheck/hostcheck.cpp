@@ -149,24 +149,8 @@ extern "C" int hc_interest(const hc_delta* d, uint32_t nd, const uint8_t* in, co
     return 0;
 }
 
-// producer-side encoder, with the kernel's dispatch: plain strings are copied by the record's own writer, every other
-// string is jumped over (encode_emit<true>) and filled in afterwards position by position (escape_unit) -- the serial
-// image of the warp-cooperative routine in sse_encode.cu.  Records are packed back to back.
-static uint32_t fill_gap(const uint8_t* base, uint32_t b, uint32_t e, bool go122, uint8_t* dst) {
-    PtrSrc s{base};
-    uint32_t off = 1;
-    for (uint32_t p0 = b; p0 < e; p0 += 32) {                  // one warp trip
-        bool ascii = true;                                     // the trip's bytes and the three before it
-        for (uint32_t q = (p0 >= b + 3 ? p0 - 3 : b); q < p0 + 32 && q < e; q++) ascii = ascii && base[q] < 0x80;
-        for (uint32_t pos = p0; pos < p0 + 32 && pos < e; pos++) {
-            const EscUnit u = ascii ? escape_unit_ascii(base[pos], go122) : escape_unit(s, b, e, pos, go122);
-            for (uint32_t k = 0; k < u.n; k++) dst[off + k] = (uint8_t)(u.bytes >> (8 * k));
-            off += u.n;
-        }
-    }
-    dst[0] = '"'; dst[off] = '"';
-    return off + 1;
-}
+// producer-side encoder: the kernel's per-message steps (plain test, lengths, emission) run sequentially; records are
+// packed back to back.
 extern "C" int hc_encode(const uint8_t* cid, const uint32_t* cid_off, const uint8_t* tok, const uint32_t* tok_off, const int64_t* seq,
                          const uint8_t* done, const int64_t* ts, uint32_t n, uint32_t op, uint8_t* out, uint64_t out_cap,
                          uint64_t* out_off, uint32_t* chan_len) {
@@ -180,18 +164,9 @@ extern "C" int hc_encode(const uint8_t* cid, const uint32_t* cid_off, const uint
         const EncPlan p = encode_plan_from(ce - cb, cp ? ce - cb + 2 : go_string_len(c, cb, ce, go122), cp,
                                            tp ? te - tb + 2 : go_string_len(t, tb, te, go122), tp, seq[i], done[i] != 0, ts[i], op);
         if (w + p.len + 4 > out_cap) return -1;
-        uint64_t gap[2] = {0, 0};
         Writer<PtrDst, true> e(dst, w);
-        encode_emit<true>(c, cb, ce, t, tb, te, seq[i], done[i] != 0, ts[i], go122, p, e, gap);
+        encode_emit(c, cb, ce, t, tb, te, seq[i], done[i] != 0, ts[i], go122, p, e);
         if (e.pos() != w + p.len) return -2;
-        if (!cp && fill_gap(cid, cb, ce, go122, out + gap[0]) != p.cid_n) return -3;
-        if (!tp && fill_gap(tok, tb, te, go122, out + gap[1]) != p.tok_n) return -3;
-        // the serial emitter (oversize tiles in the kernel) must give the same bytes
-        std::vector<uint8_t> chk(p.len + 8);
-        PtrDst cd{chk.data()};
-        Writer<PtrDst, true> e2(cd, 0);
-        encode_emit<false>(c, cb, ce, t, tb, te, seq[i], done[i] != 0, ts[i], go122, p, e2, nullptr);
-        if (e2.pos() != p.len || memcmp(chk.data(), out + w, p.len) != 0) return -4;
         chan_len[i] = p.chan;
         out_off[i] = w;
         w += p.len;
