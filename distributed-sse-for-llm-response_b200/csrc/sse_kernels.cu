@@ -481,14 +481,20 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
 
 // ---------------------------------------------------------------------- launch ----
 static int g_num_sms[64];
-static int g_ctas_per_sm[64][2];
+static int g_ctas_per_sm[64][2][2];    // [device][ext][wide]
 
 // Shared memory per CTA: a tile of TILE records is ~17 KB in / ~21 KB out at the BASELINE workload; the caps leave
 // ~15% slack.  Tiles that exceed them take the direct global-memory path inside the same kernel.  The EXT kernel
-// (inspection / interest lookup) adds the on-chip DFA cache.
+// (inspection / interest lookup) adds the on-chip DFA cache.  "wide": NATS PUB framing adds ~60 bytes per record to
+// the bridge output (subject + protocol line), which would push every tile past the 192-byte-per-record staging cap.
+static uint32_t variant_smem(bool ext, bool wide, uint32_t* ic, uint32_t* oc) {
+    *ic = TILE * 160; *oc = TILE * (wide ? 224 : 192);
+    return *ic + 32 + *oc + 48 + (uint32_t)sizeof(TileSmem) + (ext ? DFA_CACHE_BYTES : 0u);
+}
 template <bool EXT, int MODE>
 static cudaError_t configure_one(int device, uint32_t sm, int* per_sm) {
-    cudaError_t e = cudaFuncSetAttribute(k_frame_tiles<EXT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    uint32_t ic, oc;
+    cudaError_t e = cudaFuncSetAttribute(k_frame_tiles<EXT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)variant_smem(EXT, true, &ic, &oc));
     if (e != cudaSuccess) return e;
     int per = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<EXT, MODE>, TILE, sm);
@@ -498,10 +504,10 @@ static cudaError_t configure_one(int device, uint32_t sm, int* per_sm) {
     return cudaSuccess;
 }
 
-static cudaError_t configure_variant(int device, bool ext, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
-    const uint32_t ic = TILE * 160, oc = TILE * 192;
-    const uint32_t sm = ic + 32 + oc + 48 + (uint32_t)sizeof(TileSmem) + (ext ? DFA_CACHE_BYTES : 0u);
-    if (g_ctas_per_sm[device][ext] == 0) {
+static cudaError_t configure_variant(int device, bool ext, bool wide, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
+    uint32_t ic, oc;
+    const uint32_t sm = variant_smem(ext, wide, &ic, &oc);
+    if (g_ctas_per_sm[device][ext][wide] == 0) {
         int sms = 0, per = 0, p1 = 0, p2 = 0;
         cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         if (e != cudaSuccess) return e;
@@ -516,17 +522,19 @@ static cudaError_t configure_variant(int device, bool ext, uint32_t* in_cap, uin
         }
         per = min(per, min(p1, p2));
         g_num_sms[device] = sms;
-        g_ctas_per_sm[device][ext] = per;
+        g_ctas_per_sm[device][ext][wide] = per;
     }
     *in_cap = ic; *out_cap = oc; *smem_bytes = sm;
-    *grid = g_num_sms[device] * g_ctas_per_sm[device][ext];
+    *grid = g_num_sms[device] * g_ctas_per_sm[device][ext][wide];
     return cudaSuccess;
 }
 
 cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
-    cudaError_t e = configure_variant(device, true, in_cap, out_cap, smem_bytes, grid);
+    cudaError_t e = configure_variant(device, true, true, in_cap, out_cap, smem_bytes, grid);
+    if (e == cudaSuccess) e = configure_variant(device, false, true, in_cap, out_cap, smem_bytes, grid);
+    if (e == cudaSuccess) e = configure_variant(device, true, false, in_cap, out_cap, smem_bytes, grid);
     if (e != cudaSuccess) return e;
-    return configure_variant(device, false, in_cap, out_cap, smem_bytes, grid);
+    return configure_variant(device, false, false, in_cap, out_cap, smem_bytes, grid);
 }
 
 template <bool EXT>
@@ -544,7 +552,8 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     uint32_t smem_bytes;
     int grid;
     const bool ext = a.insp != nullptr || a.interest != nullptr;
-    cudaError_t e = configure_variant(device, ext, &a.in_cap, &a.out_cap_s, &smem_bytes, &grid);
+    const bool wide = (a.op & OP_NATS_PUB) != 0;
+    cudaError_t e = configure_variant(device, ext, wide, &a.in_cap, &a.out_cap_s, &smem_bytes, &grid);
     if (e != cudaSuccess) return e;
     a.num_tiles = (a.n + TILE - 1) / TILE;
     // scratch: ticket + overflow flag + cursor + counters + per-tile words, zeroed per launch
