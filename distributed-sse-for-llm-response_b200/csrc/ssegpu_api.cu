@@ -82,6 +82,12 @@ struct ssegpu_ctx {
 
 namespace {
 
+// kernels per frame launch: ordered = count pass, tile scan, emit pass; arrival = tile kernel (+ k_frame_pending behind the plain kernel)
+uint32_t launches_of(uint32_t op) {
+    if (op & SSEGPU_OP_ORDERED) return 3;
+    return (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE | SSEGPU_OP_MATCH)) ? 1 : 2;
+}
+
 // SSEGPU_OP_NATS_PUB is a bridge-mode framing; SSEGPU_OP_RESP belongs to the encoder
 bool bad_frame_op(uint32_t op) { return (op & SSEGPU_OP_RESP) || ((op & SSEGPU_OP_NATS_PUB) && !(op & SSEGPU_OP_BRIDGE)); }
 
@@ -353,7 +359,7 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     {
         std::lock_guard<std::mutex> lk(ctx->mu);
         b->state = SUBMITTED;
-        ctx->launches += n ? ((op & SSEGPU_OP_ORDERED) ? 3 : 1) : 0;   // ordered mode: count pass, scan, emit pass
+        ctx->launches += n ? launches_of(op) : 0;
     }
     return SSEGPU_OK;
 }
@@ -435,7 +441,7 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
     CU(sse::frame_launch(ctx->cfg.device, a, st));
     std::lock_guard<std::mutex> lk(ctx->mu);
-    ctx->launches += n ? ((op & SSEGPU_OP_ORDERED) ? 3 : 1) : 0;
+    ctx->launches += n ? launches_of(op) : 0;
     return SSEGPU_OK;
 }
 

@@ -81,9 +81,10 @@ typedef enum {
                                   * rdb.Publish(ctx, channel, payload) (llm-stream-proxy/main.go:244):
                                   * "*3\r\n$7\r\npublish\r\n$<n>\r\n<channel>\r\n$<m>\r\n<payload>\r\n"; implies the channel. */
 #define SSEGPU_OP_ORDERED   8u   /* lay the frames out back to back in record order (the arena then equals the
-                                    sequential Go output byte for byte); costs a second decode pass.  Default: each
-                                    tile of 128 consecutive records lands 16-byte aligned in completion order (<=15
-                                    zero bytes between tiles); every frame is still
+                                    sequential Go output byte for byte); costs a second decode pass.  Default: frames
+                                    land in completion order -- the Go-marshalled records of a tile of 128 consecutive
+                                    records as one 16-byte aligned slice, records that needed the general decoder
+                                    possibly elsewhere (<=15 zero bytes between slices); every frame is still
                                     out[out_off[i] .. out_off[i]+out_len[i]) */
 
 typedef struct ssegpu_ctx ssegpu_ctx;

@@ -1,9 +1,10 @@
 """Helpers for the GPU parity tests: run a batch through the C ABI and normalise the result.
 
-By default the library places tiles (128 consecutive records) in the arena in completion order, each tile 16-byte
-aligned with at most 15 zero bytes after its last frame; every frame is out[out_off[i] : out_off[i]+out_len[i]].
-normalise() checks exactly that (alignment, no overlap, no gap beyond the pad, zeroed pads, record order inside a tile)
-and rebuilds the record-ordered arena, which must then equal the oracle's byte for byte.
+By default the library places frames in the arena in completion order: the canonical records of a tile (128 consecutive
+records) leave as one 16-byte aligned slice, records that needed the general decoder are framed afterwards, a warp's
+worth per 16-byte aligned slice.  Every frame is out[out_off[i] : out_off[i]+out_len[i]].  normalise() checks exactly
+that -- the frames are disjoint, they tile the arena from 0 to out_off[n] with gaps of at most 15 bytes, every gap byte
+is zero -- and rebuilds the record-ordered arena, which must then equal the oracle's byte for byte.
 With OP_ORDERED the arena must equal the oracle's without any normalisation."""
 import numpy as np
 
@@ -13,38 +14,35 @@ OP_ORDERED = 8
 
 def normalise(out, out_off, out_len, ordered):
     n = len(out_len)
-    lens = out_len.astype(np.uint64)
+    lens = out_len.astype(np.int64)
     total = int(lens.sum())
     arena_bytes = int(out_off[n])
     want_off = np.zeros(n + 1, dtype=np.uint64)
-    np.cumsum(lens, out=want_off[1:])
+    np.cumsum(lens, out=want_off[1:].view(np.int64))
     if ordered:
         assert arena_bytes == total, "ordered mode: out_off[n] is not the sum of the record lengths"
         assert np.array_equal(out_off[: n + 1], want_off), "ordered mode: offsets are not the prefix sum of the lengths"
         return out[:total], want_off
-    off = out_off[:n].astype(np.uint64)
-    arena = np.empty(total, dtype=np.uint8)
-    starts, sizes = [], []
-    for t0 in range(0, n, TILE):
-        t1 = min(n, t0 + TILE)
-        # record order and contiguity inside the tile
-        assert np.array_equal(off[t0 + 1:t1], off[t0:t1 - 1] + lens[t0:t1 - 1]), "records of a tile are not contiguous"
-        size = int(want_off[t1] - want_off[t0])
-        starts.append(int(off[t0]))
-        sizes.append(size)
-        arena[int(want_off[t0]):int(want_off[t1])] = out[int(off[t0]):int(off[t0]) + size]
-    # the tiles partition the arena: 16-byte aligned, no overlap, only zero pad bytes in between
-    order = np.argsort(np.array(starts, dtype=np.int64), kind="stable")
-    pos = 0
-    for k in order:
-        if sizes[k] == 0:
-            continue
-        assert starts[k] % 16 == 0 and starts[k] == pos, "tiles overlap, are misaligned or leave a gap in the arena"
-        end = starts[k] + sizes[k]
-        pos = (end + 15) & ~15
-        assert not out[end:pos].any(), "pad bytes after a tile are not zero"
-    assert pos == arena_bytes, "out_off[n] is not the arena size"
-    return arena, want_off
+    off = out_off[:n].astype(np.int64)
+    nz = np.nonzero(lens)[0]
+    if len(nz) == 0:
+        assert arena_bytes == 0
+        return out[:0], want_off
+    order = nz[np.argsort(off[nz], kind="stable")]
+    starts, ends = off[order], off[order] + lens[order]
+    gaps = starts[1:] - ends[:-1]
+    assert starts[0] == 0, "the arena does not start with a frame"
+    assert (gaps >= 0).all(), "frames overlap"
+    assert (gaps < 16).all(), "a gap between frames is longer than an alignment pad"
+    assert arena_bytes % 16 == 0 and 0 <= arena_bytes - ends[-1] < 16, "out_off[n] is not the arena size"
+    cover = np.zeros(arena_bytes + 1, dtype=np.int32)
+    cover[starts] += 1
+    cover[ends] -= 1
+    inside = np.cumsum(cover[:arena_bytes]) > 0
+    assert not out[:arena_bytes][~inside].any(), "pad bytes between frames are not zero"
+    # record-ordered arena: byte k of record i comes from out[off[i] + k]
+    src = np.repeat(off - want_off[:n].astype(np.int64), lens) + np.arange(total, dtype=np.int64)
+    return out[src], want_off
 
 
 def run_batch(eng, arena, off, start=None, op=0):

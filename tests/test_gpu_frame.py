@@ -125,6 +125,50 @@ def test_nats_pub_needs_bridge_mode(pkg, eng, oracle):
         b.release()
 
 
+@pytest.mark.parametrize("pct", [0.05, 1.0, 20.0])
+@pytest.mark.parametrize("op", [0, 1, 1 | 128, 8])
+def test_sparse_non_canonical_records_in_canonical_traffic(pkg, eng, oracle, pct, op):
+    """Mostly Go-marshalled traffic with a few records that need the general decoder (a "Token" key, a payload with a
+    space after the brace, a syntax error, a type error): in arrival mode the tile kernel leaves them to k_frame_pending
+    when they are few in their warp -- statuses, frames, counters and the arena invariants must not notice."""
+    n_conv, n_tok = 2000, 30
+    arena, off = pkg.workload.generate(1, n_conv, n_tok)
+    n = n_conv * n_tok
+    payloads = [arena[int(off[i]):int(off[i + 1])].tobytes() for i in range(n)]
+    rng = random.Random(int(pct * 100) + op)
+    odd = 0
+    for i in range(n):
+        if rng.random() < pct / 100.0:
+            p, k = payloads[i], rng.randrange(4)
+            payloads[i] = (p.replace(b'"token"', b'"Token"') if k == 0 else b"{ " + p[1:] if k == 1 else p[:-1] if k == 2
+                           else p.replace(b'"sequence":', b'"sequence":"x",'  b'"q":'))
+            odd += 1
+    arena, off = oracle.pack(payloads)
+    start = None if op & 1 else np.array([rng.choice([0, 0, 0, 7]) for _ in range(n)], dtype=np.int64)
+    if op & 128:
+        want_out, want_off, want_subj, want_status = oracle.bridge_pub(arena, off)
+    elif op & 1:
+        want_out, want_off, want_subj, want_status = oracle.bridge(arena, off)
+    else:
+        want_out, want_off, want_status = oracle.adapter(arena, off, start)
+        want_subj = None
+    before = eng.counters()
+    out, out_off, status, subj = run_batch(eng, arena, off, start, op)
+    after = eng.counters()
+    assert np.array_equal(status, want_status)
+    assert np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
+    if want_subj is not None:
+        assert np.array_equal(subj, want_subj)
+    code = want_status & 0xF
+    assert after["frames"] - before["frames"] == int((code == 0).sum())
+    assert after["err_syntax"] - before["err_syntax"] == int((code == 1).sum())
+    assert after["err_type"] - before["err_type"] == int((code == 2).sum())
+    assert after["filtered"] - before["filtered"] == int((code == 3).sum())
+    assert after["done"] - before["done"] == int(((want_status & 0x100) != 0).sum())
+    assert after["bytes_out"] - before["bytes_out"] == int(want_off[n])
+    assert after["fast_path"] - before["fast_path"] <= n - odd + int((code == 3).sum())
+
+
 @pytest.mark.parametrize("op", [0, 8])
 @pytest.mark.parametrize("n", [0, 1, 2, 127, 128, 129, 255, 256, 257, 1000])
 def test_tile_boundaries(pkg, eng, oracle, n, op):
