@@ -119,7 +119,7 @@ struct TileSmem {
     uint64_t mbar;
     uint64_t base;           // global byte offset of the tile's output
     uint32_t tile, tb, te, in_total;
-    uint32_t npend;          // records of this tile left to k_frame_pending
+    uint32_t npend;          // records of this tile left to the tail phase (later: fill of the tail's list)
     uint32_t wsum[TILE / 32];
 };
 
@@ -234,6 +234,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
     uint32_t c_ok = 0, c_syn = 0, c_typ = 0, c_fil = 0, c_done = 0, c_fast = 0;
     uint64_t c_in = 0, c_out = 0;
     uint32_t parity = 0;
+    uint32_t my_chain = 0;                                  // tid 0: last tile (+1) of this CTA that left records to the tail phase
 
     // EXT: on-chip copy of the inspection DFA's byte-class map and hottest transition rows
     DfaCache dcache{nullptr, nullptr, 0};
@@ -291,8 +292,8 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
         if (smem_in && in_bytes != 0) { mbar_wait(&ts->mbar, parity); parity ^= 1; }
 
         // ---- pass 1: decode + filter, output length --------------------------------
-        // Arrival mode of the plain kernel: a record that is not canonical is left to k_frame_pending, which runs the general
-        // decoder over all such records densely (one per lane).  Inline, ONE such record makes its whole warp -- and at
+        // Arrival mode of the plain kernel: a record that is not canonical is left to the tail phase of this CTA, which runs
+        // the general decoder over all such records densely (one per lane).  Inline, ONE such record makes its whole warp -- and at
         // the next barrier its CTA -- wait ten times as long as a canonical tile takes (measured: 1 % of them cost 7x).
         constexpr bool DEFER = MODE == MODE_ARRIVAL && !EXT;
         constexpr uint32_t DEFER_MAX_PER_WARP = 9;
@@ -301,7 +302,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
         const uint32_t o = my_b - abase, L = my_e - my_b;
         bool fastp = false;
         if (active && smem_in) { PtrSrc src{s_in}; fastp = plan_record_fast(src, o, L, a.op, my_start, pl, st, len); }
-        // A few such records in a warp: deferred (the kernel behind this one runs them densely at 2.5 ns each).  Many of
+        // A few such records in a warp: deferred (the tail phase runs them densely).  Many of
         // them: decoded here, where the tile is in shared memory (22 ns per warp however many of its lanes take part).
         const bool slow = active && !fastp;
         const uint32_t nslow = __popc(__ballot_sync(0xFFFFFFFFu, slow));
@@ -408,7 +409,10 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
         // arrival-order placement: every tile owns a 16-byte aligned slice of the arena, so its staging
         // tile leaves as ONE TMA bulk store; the <=15 pad bytes after its last frame are zeroed.
         const uint32_t alloc = ordered ? total : ((total + 15u) & ~15u);
-        if (DEFER && tid == 0 && ts->npend) { a.tile_state[tile] = ts->npend; atomicAdd(a.pending_total, ts->npend); }
+        if (DEFER && tid == 0 && ts->npend) {          // chain this tile to the CTA's list of tiles with records left over
+            a.tile_state[tile] = (uint64_t)ts->npend | ((uint64_t)my_chain << 32);
+            my_chain = tile + 1;
+        }
         if (tid == 0) {
             c_out += total;
             if (ordered) ts->base = a.tile_state[tile];                       // exclusive prefix from k_scan_tile_totals
@@ -470,9 +474,73 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
     }
 
     if (tid == 0) bulk_wait0();
+    unsigned long long* row = a.counters + (size_t)(blockIdx.x % CTR_ROWS) * CTR_COLS;
+
+    // ---- tail: the records this CTA left over --------------------------------------------------
+    // Arrival mode of the plain kernel.  The tiles that left records behind are chained through tile_state; their record
+    // numbers are gathered in the (now idle) staging tile and the general decoder runs over them one record per lane,
+    // 128 at a time, straight from and to global memory.  Each warp takes a 16-byte aligned slice of the arena from the
+    // same cursor, so such a frame simply lives somewhere else in the arena (out_off/out_len address it like any other).
+    if (MODE == MODE_ARRIVAL && !EXT) {
+        uint32_t* s_list = reinterpret_cast<uint32_t*>(s_out);
+        __syncthreads();                                                      // every thread has read the loop's last ts->tile
+        if (tid == 0) { ts->tile = my_chain; ts->npend = 0; }
+        __syncthreads();
+        uint32_t t1 = ts->tile;                                               // CTA-uniform
+        const uint32_t in_total = ts->in_total;
+        while (t1 != 0) {
+            uint32_t cnt = 0;
+            while (t1 != 0 && cnt < (uint32_t)TILE) {                         // gather until there is a full group
+                const uint32_t t = t1 - 1, i = t * TILE + tid;
+                if (i < a.n && (a.status[i] & ST_CODE_MASK) == ST_PENDING) s_list[atomicAdd(&ts->npend, 1u)] = i;
+                t1 = (uint32_t)(a.tile_state[t] >> 32);
+                __syncthreads();
+                cnt = ts->npend;
+            }
+            for (uint32_t g = 0; g < cnt; g += TILE) {
+                const bool act = g + tid < cnt;
+                uint32_t i = 0, b = 0, e = 0, st = ST_OK, len = 0;
+                Plan pl;
+                if (act) {
+                    i = s_list[g + tid];
+                    b = min(a.in_off[i], in_total); e = min(max(a.in_off[i + 1], b), in_total);
+                    st = plan_slow(a.in, b, e - b, a.op, a.start_seq ? a.start_seq[i] : 0, &pl, &len);
+                }
+                uint32_t incl = len;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                    if (lane >= (uint32_t)d) incl += v;
+                }
+                const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31), alloc = (total + 15u) & ~15u;
+                unsigned long long base = 0;
+                if (lane == 0 && alloc) base = atomicAdd(a.cursor, (unsigned long long)alloc);
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                const bool fits = base + alloc <= a.out_cap;
+                const uint32_t code = st & ST_CODE_MASK;
+                if (act) {
+                    uint32_t subj = 0;
+                    if (code == ST_OK && fits) subj = emit_slow(a.in, b, e - b, &pl, a.op, a.out, base + incl - len);
+                    a.out_off[i] = base + incl - len;
+                    a.out_len[i] = len;
+                    a.status[i] = st;
+                    if (a.subj_len) a.subj_len[i] = subj;
+                    if (code == ST_OK) { c_ok++; if (st & ST_DONE) c_done++; }
+                    else if (code == ST_ERR_SYNTAX) c_syn++;
+                    else if (code == ST_ERR_TYPE) c_typ++;
+                    else if (code == ST_FILTERED) c_fil++;
+                }
+                if (fits && lane < alloc - total) a.out[base + total + lane] = 0;
+                if (lane == 0 && total) atomicAdd(&row[7], (unsigned long long)total);
+                if (lane == 0 && !fits) atomicExch(a.overflow, 1u);
+            }
+            __syncthreads();
+            if (tid == 0) ts->npend = 0;
+            __syncthreads();
+        }
+    }
 
     // ---- counters: one row per CTA slot, summed by the host --------------------------
-    unsigned long long* row = a.counters + (size_t)(blockIdx.x % CTR_ROWS) * CTR_COLS;
     uint32_t vals[6] = {c_ok, c_syn, c_typ, c_fil, c_done, c_fast};
 #pragma unroll
     for (int k = 0; k < 6; k++) {
@@ -494,98 +562,8 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
     }
 }
 
-// ------------------------------------------------------- the records left over ----
-// Arrival mode of the plain kernel leaves every record that is not canonical Go output (status ST_PENDING, per-tile
-// counts in tile_state) to this kernel: CTAs walk groups of 64 tiles, gather the pending record numbers of the group in
-// shared memory and run the general decoder over them 128 at a time, one record per lane, straight from and to global
-// memory.  Each warp takes a 16-byte aligned slice of the arena from the same cursor the tile kernel used, so a
-// frame of such a record simply lives somewhere else in the arena (out_off/out_len address it like any other).
-constexpr uint32_t PEND_TILES = 64;                     // tiles per group
-__global__ void __launch_bounds__(128) k_frame_pending(const FrameArgs a) {
-    __shared__ uint32_t s_list[PEND_TILES * TILE];
-    __shared__ uint32_t s_cnt;
-    const uint32_t tid = threadIdx.x, lane = tid & 31;
-    uint32_t c_ok = 0, c_syn = 0, c_typ = 0, c_fil = 0, c_done = 0;
-    uint64_t c_out = 0;
-    asm volatile("griddepcontrol.wait;" ::: "memory");          // everything the tile kernel wrote is visible from here on
-    const uint32_t in_total = a.in_off[a.n];
-    if (*a.pending_total != 0) {
-        for (uint32_t g0 = blockIdx.x * PEND_TILES; g0 < a.num_tiles; g0 += gridDim.x * PEND_TILES) {
-            if (tid == 0) s_cnt = 0;
-            __syncthreads();
-            for (uint32_t t = g0 + (tid >> 5); t < min(g0 + PEND_TILES, a.num_tiles); t += 128 / 32) {      // a warp per tile
-                if (a.tile_state[t] == 0) continue;                                                          // warp-uniform
-                for (uint32_t k = lane; k < (uint32_t)TILE; k += 32) {
-                    const uint32_t i = t * TILE + k;
-                    if (i < a.n && (a.status[i] & ST_CODE_MASK) == ST_PENDING) s_list[atomicAdd(&s_cnt, 1u)] = i;
-                }
-            }
-            __syncthreads();
-            const uint32_t cnt = s_cnt;
-            for (uint32_t g = 0; g < cnt; g += 128) {
-                const bool active = g + tid < cnt;
-                uint32_t i = 0, b = 0, e = 0, st = ST_OK, len = 0;
-                Plan pl;
-                if (active) {
-                    i = s_list[g + tid];
-                    b = min(a.in_off[i], in_total); e = min(max(a.in_off[i + 1], b), in_total);
-                    st = plan_slow(a.in, b, e - b, a.op, a.start_seq ? a.start_seq[i] : 0, &pl, &len);
-                }
-                // a 16-byte aligned slice of the arena per warp
-                uint32_t incl = len;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-                    if (lane >= (uint32_t)d) incl += v;
-                }
-                const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31), alloc = (total + 15u) & ~15u;
-                unsigned long long base = 0;
-                if (lane == 0 && alloc) base = atomicAdd(a.cursor, (unsigned long long)alloc);
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                const bool fits = base + alloc <= a.out_cap;
-                const uint32_t code = st & ST_CODE_MASK;
-                uint32_t subj = 0;
-                if (active) {
-                    if (code == ST_OK && fits) subj = emit_slow(a.in, b, e - b, &pl, a.op, a.out, base + incl - len);
-                    a.out_off[i] = base + incl - len;
-                    a.out_len[i] = len;
-                    a.status[i] = st;
-                    if (a.subj_len) a.subj_len[i] = subj;
-                    if (code == ST_OK) { c_ok++; if (st & ST_DONE) c_done++; }
-                    else if (code == ST_ERR_SYNTAX) c_syn++;
-                    else if (code == ST_ERR_TYPE) c_typ++;
-                    else if (code == ST_FILTERED) c_fil++;
-                }
-                if (fits && lane < alloc - total) a.out[base + total + lane] = 0;
-                if (lane == 0) { c_out += total; if (!fits) atomicExch(a.overflow, 1u); }
-            }
-            __syncthreads();
-        }
-        unsigned long long* row = a.counters + (size_t)(blockIdx.x % CTR_ROWS) * CTR_COLS;
-        uint32_t vals[5] = {c_ok, c_syn, c_typ, c_fil, c_done};
-#pragma unroll
-        for (int k = 0; k < 5; k++) {
-            uint32_t v = vals[k];
-#pragma unroll
-            for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o2);
-            if (lane == 0 && v) atomicAdd(&row[k], (unsigned long long)v);
-        }
-        if (lane == 0 && c_out) atomicAdd(&row[7], (unsigned long long)c_out);
-    }
-    // the CTA that finishes last publishes the arena's total size (the tile kernel published its own share already)
-    __syncthreads();
-    if (tid == 0) {
-        __threadfence();
-        if (atomicAdd(a.pend_done, 1u) == gridDim.x - 1) {
-            __threadfence();
-            a.out_off[a.n] = (uint64_t)atomicAdd(a.cursor, 0ull);
-        }
-    }
-}
-
 // ---------------------------------------------------------------------- launch ----
 static int g_num_sms[64];
-static int g_pend_per_sm[64];
 static int g_ctas_per_sm[64][2][2];    // [device][ext][wide]
 
 // Shared memory per CTA: a tile of TILE records is ~17 KB in / ~21 KB out at the BASELINE workload; the caps leave
@@ -643,26 +621,13 @@ cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uin
 }
 
 template <bool EXT>
-static void launch_variant(const FrameArgs& a, int grid, uint32_t smem_bytes, cudaStream_t stream, int pend_grid) {
+static void launch_variant(const FrameArgs& a, int grid, uint32_t smem_bytes, cudaStream_t stream) {
     if (a.op & OP_ORDERED) {
         k_frame_tiles<EXT, MODE_ORDERED_COUNT><<<grid, TILE, smem_bytes, stream>>>(a);
         k_scan_tile_totals<<<1, 1024, 0, stream>>>(a.tile_state, a.num_tiles, a.out_off + a.n, a.ticket);
         k_frame_tiles<EXT, MODE_ORDERED_EMIT><<<grid, TILE, smem_bytes, stream>>>(a);
     } else {
         k_frame_tiles<EXT, MODE_ARRIVAL><<<grid, TILE, smem_bytes, stream>>>(a);
-        if (!EXT) {
-            // programmatic dependent launch: the launch latency of this (usually idle) kernel overlaps the tile kernel's tail;
-            // it waits for the tile kernel's memory with griddepcontrol.wait before it reads anything
-            cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = dim3((unsigned)min(pend_grid, (int)((a.num_tiles + PEND_TILES - 1) / PEND_TILES)));
-            cfg.blockDim = dim3(128);
-            cfg.stream = stream;
-            cudaLaunchAttribute at[1];
-            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-            at[0].val.programmaticStreamSerializationAllowed = 1;
-            cfg.attrs = at; cfg.numAttrs = 1;
-            cudaLaunchKernelEx(&cfg, k_frame_pending, a);
-        }
     }
 }
 
@@ -679,14 +644,8 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
     if ((int)a.num_tiles < grid) grid = (int)a.num_tiles;
-    if (g_pend_per_sm[device] == 0) {
-        int per = 0;
-        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_pending, 128, 0)) != cudaSuccess) return e;
-        g_pend_per_sm[device] = per < 1 ? 1 : per;
-    }
-    const int pend_grid = g_num_sms[device] * g_pend_per_sm[device];
-    if (ext) launch_variant<true>(a, grid, smem_bytes, stream, pend_grid);
-    else launch_variant<false>(a, grid, smem_bytes, stream, pend_grid);
+    if (ext) launch_variant<true>(a, grid, smem_bytes, stream);
+    else launch_variant<false>(a, grid, smem_bytes, stream);
     return cudaGetLastError();
 }
 

@@ -15,7 +15,7 @@ struct InterestDev;              // sse_interest.cuh
 constexpr int TILE = SSE_TILE;   // records per tile == threads per CTA
 constexpr int CTR_ROWS = 64;     // counter rows (CTA i adds into row i % CTR_ROWS; the host sums rows)
 constexpr int CTR_COLS = 8;      // ok, syntax, type, filtered, done, fast, bytes_in, bytes_out
-constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32, [20] duplicate-conversation flag u32, [24] bad-offsets flag u32, [28] records left to k_frame_pending u32, [32] its finished CTAs u32
+constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32, [20] duplicate-conversation flag u32, [24] bad-offsets flag u32
 
 struct FrameArgs {
     const uint8_t* in;           // packed payload arena, 16-byte aligned, 32 readable bytes after the last record
@@ -48,10 +48,8 @@ struct FrameArgs {
     uint32_t* done_ctas;
     uint32_t* dup_conv;
     uint32_t* bad_offsets;       // set when in_off was not monotonic / ran past in_off[n] (records are clamped, never read out of bounds)
-    uint32_t* pending_total;     // records the tile kernel left to k_frame_pending (arrival mode, plain kernel)
-    uint32_t* pend_done;
     unsigned long long* counters;
-    uint64_t* tile_state;         // ordered mode: per-tile byte totals / prefix; arrival mode: per-tile count of pending records
+    uint64_t* tile_state;         // ordered mode: per-tile byte totals / prefix; arrival mode: count of records left to the tail phase | previous such tile of the CTA << 32
     // filled by frame_launch
     uint32_t num_tiles, in_cap, out_cap_s;
     __host__ __device__ uint32_t out_cap_smem() const { return out_cap_s; }
@@ -71,8 +69,6 @@ inline void scratch_carve(void* base, FrameArgs& a) {
     a.done_ctas = reinterpret_cast<uint32_t*>(p + 16);
     a.dup_conv = reinterpret_cast<uint32_t*>(p + 20);
     a.bad_offsets = reinterpret_cast<uint32_t*>(p + 24);
-    a.pending_total = reinterpret_cast<uint32_t*>(p + 28);
-    a.pend_done = reinterpret_cast<uint32_t*>(p + 32);
     a.counters = reinterpret_cast<unsigned long long*>(p + SCRATCH_HDR);
     a.tile_state = reinterpret_cast<uint64_t*>(p + SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8);
 }

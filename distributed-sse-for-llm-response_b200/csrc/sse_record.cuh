@@ -38,7 +38,7 @@ namespace sse {
 // status word (mirrors include/ssegpu.h)
 enum : uint32_t {
     ST_OK = 0, ST_ERR_SYNTAX = 1, ST_ERR_TYPE = 2, ST_FILTERED = 3, ST_INSPECT_DROP = 4, ST_NO_INTEREST = 5,
-    ST_PENDING = 0xE,            // internal: left for k_frame_pending by the tile kernel, never visible to the caller
+    ST_PENDING = 0xE,            // internal: left to the tail phase of the tile kernel, never visible to the caller
     ST_CODE_MASK = 0xF, ST_DONE = 0x100, ST_REDACTED = 0x200,
 };
 // op flags (mirrors include/ssegpu.h)

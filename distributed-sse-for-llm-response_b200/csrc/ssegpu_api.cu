@@ -82,11 +82,8 @@ struct ssegpu_ctx {
 
 namespace {
 
-// kernels per frame launch: ordered = count pass, tile scan, emit pass; arrival = tile kernel (+ k_frame_pending behind the plain kernel)
-uint32_t launches_of(uint32_t op) {
-    if (op & SSEGPU_OP_ORDERED) return 3;
-    return (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE | SSEGPU_OP_MATCH)) ? 1 : 2;
-}
+// kernels per frame launch: ordered = count pass, tile scan, emit pass; arrival = the tile kernel
+uint32_t launches_of(uint32_t op) { return (op & SSEGPU_OP_ORDERED) ? 3 : 1; }
 
 // SSEGPU_OP_NATS_PUB is a bridge-mode framing; SSEGPU_OP_RESP belongs to the encoder
 bool bad_frame_op(uint32_t op) { return (op & SSEGPU_OP_RESP) || ((op & SSEGPU_OP_NATS_PUB) && !(op & SSEGPU_OP_BRIDGE)); }

@@ -129,7 +129,7 @@ def test_nats_pub_needs_bridge_mode(pkg, eng, oracle):
 @pytest.mark.parametrize("op", [0, 1, 1 | 128, 8])
 def test_sparse_non_canonical_records_in_canonical_traffic(pkg, eng, oracle, pct, op):
     """Mostly Go-marshalled traffic with a few records that need the general decoder (a "Token" key, a payload with a
-    space after the brace, a syntax error, a type error): in arrival mode the tile kernel leaves them to k_frame_pending
+    space after the brace, a syntax error, a type error): in arrival mode the tile kernel leaves them to its tail phase
     when they are few in their warp -- statuses, frames, counters and the arena invariants must not notice."""
     n_conv, n_tok = 2000, 30
     arena, off = pkg.workload.generate(1, n_conv, n_tok)
