@@ -161,7 +161,6 @@ def run_gpu(args):
     use_dist = world > 1
     if use_dist:
         import torch.distributed as dist
-        os.environ["NCCL_DEBUG"] = "WARN"       # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = load_package()
     arena, off = make_workload(pkg, rank, world)
@@ -313,10 +312,18 @@ def main():
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
     ap.add_argument("--ordered", action="store_true", help="SSEGPU_OP_ORDERED: record-ordered arena (two decode passes)")
     args = ap.parse_args()
+    # Exactly one JSON line may reach stdout.  Libraries write there behind Python's back (NCCL prints its version banner
+    # from C when the first communicator is created, whatever NCCL_DEBUG says short of NONE), so the process's fd 1 is
+    # pointed at stderr for the whole run and the result line goes to the saved descriptor.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     if args.impl == "reference":
         run_reference(args)
     else:
         run_gpu(args)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":
