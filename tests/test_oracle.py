@@ -89,3 +89,99 @@ def test_fnv1a64(oracle):
     assert oracle.fnv1a64(b"") == 0xCBF29CE484222325
     assert oracle.fnv1a64(b"a") == 0xAF63DC4C8601EC8C
     assert oracle.fnv1a64(b"foobar") == 0x85944171F73967E8
+
+
+def _cpython_view(payload):
+    """What CPython's json module (an implementation nobody on this project wrote) says about a payload, translated to the Go
+    rules where the two languages differ only in typing: -> None when the comparison does not apply, "syntax" when it is not
+    JSON, else (status, fields) with status 0 / 2 and the five decoded fields."""
+    import json
+    try:
+        text = payload.decode("utf-8")          # Go replaces invalid UTF-8 inside strings, Python cannot read it at all
+    except UnicodeDecodeError:
+        return None
+    if "NaN" in text or "Infinity" in text:     # CPython extension
+        return None
+    depth = run = 0
+    for ch in text:
+        run += ch in "[{"
+        run -= ch in "]}"
+        depth = max(depth, run)
+    if depth > 200:
+        return None
+    try:
+        doc = json.loads(text, parse_float=lambda s: ("float", s), parse_int=lambda s: ("int", s),
+                         object_pairs_hook=lambda pairs: ("object", pairs))
+    except (ValueError, RecursionError):
+        return "syntax"
+    msg = {"cid": "", "tok": "", "seq": 0, "done": False, "ts": 0}
+    if doc is None:
+        return 0, msg
+    if not (isinstance(doc, tuple) and doc[0] == "object"):
+        return 2, None
+    names = {"conversation_id": "cid", "token": "tok", "sequence": "seq", "done": "done", "timestamp": "ts"}
+    bad = False
+    for key, val in doc[1]:
+        field = names.get(key)
+        if field is None:                        # encoding/json folds case (and two non-ASCII look-alikes) when no exact match exists
+            folded = key.replace("ſ", "s").replace("K", "k").lower()
+            field = names.get(folded)
+        if field is None or val is None:
+            continue
+        want_str, want_bool = field in ("cid", "tok"), field == "done"
+        if want_str:
+            if isinstance(val, str):
+                msg[field] = val
+            else:
+                bad = True
+        elif want_bool:
+            if isinstance(val, bool):
+                msg[field] = val
+            else:
+                bad = True
+        else:
+            if isinstance(val, tuple) and val[0] == "int" and -(1 << 63) <= int(val[1]) < (1 << 63):
+                msg[field] = int(val[1])
+            else:
+                bad = True
+    return (2 if bad else 0), msg
+
+
+def test_oracle_against_cpython_json(oracle, golden):
+    """Third witness for the decoder: CPython's json parser decides what is JSON and what the values are, a thin layer maps its
+    result onto TokenMessage with Go's typing rules; syntax verdicts must agree on every comparable payload, status and frame
+    on every payload whose strings carry no lone surrogates (Go replaces those, Python keeps them)."""
+    import random
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import make_golden as mg
+    rng = random.Random(2024)
+    payloads = [bytes.fromhex(c["in"]) for c in golden]
+    base = mg.canon("7f3c2b1a-1111-4222-8333-944455556666", " hello", 42, False, 1700000000000000000)
+    for _ in range(20000):
+        r = rng.random()
+        payloads.append(mg.structured(rng) if r < 0.5 else mg.mutate(rng, rng.choice([base, payloads[-1]])))
+    arena, off = oracle.pack(payloads)
+    out, out_off, status = oracle.adapter(arena, off)
+    raw = out.tobytes()
+    compared = syntax_errors = framed = 0
+    for i, p in enumerate(payloads):
+        view = _cpython_view(p)
+        if view is None:
+            continue
+        compared += 1
+        code = int(status[i]) & 0xF
+        if view == "syntax":
+            assert code == 1, (p, code)
+            syntax_errors += 1
+            continue
+        assert code != 1, (p, "oracle says syntax error, CPython parses it")
+        want_code, msg = view
+        assert code == want_code, (p, code, want_code)
+        if code == 0:
+            try:
+                (msg["cid"] + msg["tok"]).encode("utf-8")
+            except UnicodeEncodeError:
+                continue                          # lone surrogate from a \\ud800 escape: Go -> U+FFFD, Python keeps it
+            assert raw[int(out_off[i]):int(out_off[i + 1])] == pymodel.frame(msg), p
+            framed += 1
+    assert compared > 10000 and syntax_errors > 1000 and framed > 2000, (compared, syntax_errors, framed)
