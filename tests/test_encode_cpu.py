@@ -120,3 +120,24 @@ def test_workload_columns_are_the_workload_before_marshalling(oracle):
             assert np.array_equal(got[:k], want[:k])
         recs, _ = oracle.encode(cols)
         assert b"".join(recs) == arena[: int(off[n])].tobytes()
+
+
+def test_marshal_against_cpython_json(lib, oracle):
+    """Independent witness for the encoder half: for valid UTF-8 strings without < > & U+2028 U+2029 (which only Go escapes),
+    CPython's json.dumps(ensure_ascii=False, separators=(",", ":")) spells a message exactly as Go >= 1.22 does (Go 1.21 differs
+    in \\b and \\f only, covered by the hand vectors)."""
+    import json
+    import random
+    rng = random.Random(8)
+    alphabet = ["a", "Z", " ", "the", " quick", '"', "\\", "\n", "\t", "\r", "\x00", "\x08", "\x0c", "\x1f", "\x7f", "é", "世", "\U0001f600", "�", "/"]
+    msgs, want = [], []
+    for i in range(3000):
+        cid = "".join(rng.choice(alphabet) for _ in range(rng.randrange(0, 8)))
+        tok = "".join(rng.choice(alphabet) for _ in range(rng.randrange(0, 40)))
+        seq, done, ts = rng.choice(ec._INTS), rng.random() < 0.5, rng.choice(ec._INTS)
+        msgs.append((cid.encode(), tok.encode(), seq, done, ts))
+        want.append(json.dumps({"conversation_id": cid, "token": tok, "sequence": seq, "done": done, "timestamp": ts},
+                               ensure_ascii=False, separators=(",", ":")).encode())
+    cols = ec.columns(msgs)
+    assert oracle.encode(cols, go122=True)[0] == want
+    assert hc.encode(lib, cols, hc.OP_GO122)[0] == want
