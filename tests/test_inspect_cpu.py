@@ -110,3 +110,26 @@ def test_dfa_matches_oracle_streaming(lib, oracle, pats):
         assert (int(verdict[i]), int(match[i, 0]), int(match[i, 1])) == (v, b, e), (i, c, hist[c], tok, done)
         if done:
             hist[c] = b""
+
+
+@pytest.mark.parametrize("pats", [SET_A, SET_B, SET_A + SET_B])
+def test_oracle_verdicts_against_python_re(oracle, pats):
+    """Witness nobody here wrote: which pattern fires (all the reference's is_match-style snippets use) must be what Python's
+    `re` says on the same bytes -- bytes patterns give ASCII \\d \\w \\b, the declared semantics.  (Match offsets are this
+    project's own definition -- earliest end, leftmost start -- and have no counterpart in `re`'s leftmost-greedy search.)"""
+    import re
+    rxs = [re.compile(p) if kind == 1 else re.compile(re.escape(p), re.IGNORECASE) for kind, _, p in pats]
+    rng = random.Random(11)
+    insp = oracle.inspector(pats)
+    fired = 0
+    for _ in range(20000):
+        text = b"".join(rng.choice(FRAGMENTS) for _ in range(rng.randrange(0, 5)))
+        want = 0
+        for pid, rx in enumerate(rxs):
+            if rx.search(text):
+                want = pats[pid][1] | pid << 8
+                break
+        v, _, _ = insp.token(text)
+        assert v & 0xFFFF == want, text
+        fired += want != 0
+    assert fired > 3000
