@@ -157,3 +157,24 @@ func (b *Batch) Wait() (*Result, error) {
 
 // Release returns the slot to the ring; every slice obtained from it becomes invalid.
 func (b *Batch) Release() error { return errOf(C.ssegpu_batch_release(b.ctx.c, b.b)) }
+
+// EncodeLaunch is the producer side (publishToken, src/llm-stream-proxy/main.go:230-245) for a batch of messages whose
+// columns already sit in this GPU's memory (device pointers as uintptr: the proxy owns their allocation and the pinned
+// staging buffers it fills them through).  With OpBridge every record is preceded by its channel name, with OpResp it is
+// the complete RESP2 PUBLISH command.  Asynchronous on `stream` (0 = the context's stream); EncodeResult after the
+// stream has been synchronised.
+func (x *Context) EncodeLaunch(dCid, dCidOff, dTok, dTokOff, dSeq, dDone, dTs uintptr, n uint32, op uint32,
+	dOut uintptr, outCap uint64, dOutOff, dOutLen, dChanLen uintptr, stream unsafe.Pointer) error {
+	return errOf(C.ssegpu_encode_launch(x.c, unsafe.Pointer(dCid), (*C.uint32_t)(unsafe.Pointer(dCidOff)),
+		unsafe.Pointer(dTok), (*C.uint32_t)(unsafe.Pointer(dTokOff)), (*C.int64_t)(unsafe.Pointer(dSeq)),
+		(*C.uint8_t)(unsafe.Pointer(dDone)), (*C.int64_t)(unsafe.Pointer(dTs)), C.uint32_t(n), C.uint32_t(op),
+		unsafe.Pointer(dOut), C.uint64_t(outCap), (*C.uint64_t)(unsafe.Pointer(dOutOff)),
+		(*C.uint32_t)(unsafe.Pointer(dOutLen)), (*C.uint32_t)(unsafe.Pointer(dChanLen)), stream))
+}
+
+// EncodeResult returns the bytes of the output arena the last EncodeLaunch used (error "output arena too small" on overflow).
+func (x *Context) EncodeResult() (uint64, error) {
+	var used C.uint64_t
+	rc := C.ssegpu_encode_launch_result(x.c, &used)
+	return uint64(used), errOf(rc)
+}
