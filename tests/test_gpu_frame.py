@@ -290,6 +290,40 @@ def test_device_resident_launch_full_size_properties(pkg, oracle, op):
         eng.close()
 
 
+@pytest.mark.parametrize("op", [0, 8])
+def test_baseline_config1_full_size_bit_exact(pkg, oracle, op):
+    """The BASELINE workload at its full size -- 10 000 conversations x 1 000 tokens = 10 M records in one launch -- against the
+    oracle over EVERY record: statuses, lengths and all 1.6 GB of frames (arrival mode after the placement check, ordered mode
+    as the arena lies)."""
+    import torch
+    n_conv, n_tok = 10000, 1000
+    arena, off = pkg.workload.generate(1, n_conv, n_tok)
+    n = n_conv * n_tok
+    want_out, want_off, want_status = oracle.adapter(arena, off)
+    eng = pkg.SseGpu(device=0, max_records=n, max_in_bytes=int(off[n]) + 64, ring_slots=1)
+    try:
+        d_in = torch.from_numpy(arena).cuda()
+        d_off = torch.from_numpy(off.view(np.int32)).cuda()
+        cap = int(off[n]) + 48 * n
+        d_out = torch.zeros(cap, dtype=torch.uint8, device="cuda")
+        d_out_off = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
+        d_out_len = torch.zeros(n, dtype=torch.int32, device="cuda")
+        d_status = torch.zeros(n, dtype=torch.int32, device="cuda")
+        stream = torch.cuda.Stream()
+        torch.cuda.synchronize()
+        eng.frame_launch(d_in.data_ptr(), d_off.data_ptr(), 0, n, op, d_out.data_ptr(), cap, d_out_off.data_ptr(), d_out_len.data_ptr(), 0,
+                         d_status.data_ptr(), stream.cuda_stream)
+        torch.cuda.synchronize()
+        rc, c = eng.launch_result()
+        assert rc == 0 and c["frames"] == n and c["fast_path"] == n and c["bytes_out"] == int(want_off[n])
+        assert np.array_equal(d_status.cpu().numpy().astype(np.uint32), want_status)
+        out, out_off = normalise(d_out.cpu().numpy(), d_out_off.cpu().numpy().astype(np.uint64), d_out_len.cpu().numpy().astype(np.uint32), bool(op & 8))
+        assert np.array_equal(out_off, want_off)
+        assert np.array_equal(out[: int(want_off[n])], want_out)
+    finally:
+        eng.close()
+
+
 def test_malformed_offsets_are_refused_not_followed(pkg, oracle):
     """in_off that is not monotonic or runs past in_off[n] must neither crash nor read outside the arena."""
     arena, off = pkg.workload.generate(1, 300, 2)
