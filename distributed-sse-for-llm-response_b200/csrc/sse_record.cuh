@@ -332,9 +332,15 @@ template <class W> SSE_HD void put_rune_raw(W& w, uint32_t r) {   // utf8.Encode
     w.put(0xF0 | (r >> 18)); w.put(0x80 | ((r >> 12) & 0x3F)); w.put(0x80 | ((r >> 6) & 0x3F)); w.put(0x80 | (r & 0x3F));
 }
 
+template <class Src> SSE_HD bool go_string_is_plain(const Src& s, uint32_t b, uint32_t e);
+template <class Src, class W> SSE_HD void put_copy(const Src& s, uint32_t sp, uint32_t n, W& w);
+
+// Re-encode the interior [b, e) of a JSON string literal.  A literal made of plain bytes only (no escape, nothing
+// appendString would escape, no byte >= 0x80) decodes to itself and encodes to itself: word-wise test, word-wise copy.
 template <class Src, class W> SSE_HD void put_json_string(const Src& s, uint32_t b, uint32_t e, W& w, bool go122) {
     w.put('"');
-    while (b < e) put_rune_json(w, next_rune(s, b, e), go122);
+    if (go_string_is_plain(s, b, e)) put_copy(s, b, e - b, w);
+    else while (b < e) put_rune_json(w, next_rune(s, b, e), go122);
     w.put('"');
 }
 
