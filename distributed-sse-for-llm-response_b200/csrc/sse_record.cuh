@@ -661,6 +661,14 @@ SSE_HD bool is_digit(uint32_t c) { return c - '0' <= 9u; }
 // quote or 0 on error.
 template <class Src> SSE_HD uint32_t scan_string(const Src& s, uint32_t pos, uint32_t end) {
     for (pos++; pos < end; pos++) {
+        // runs of plain bytes four at a time (special_mask also stops at < > & and bytes >= 0x80, which the byte step
+        // below lets through)
+        while (pos + 4 <= end) {
+            const uint32_t m = special_mask(ld32u(s, pos));
+            if (m) { pos += first_byte_idx(m); break; }
+            pos += 4;
+        }
+        if (pos >= end) break;
         uint32_t c = s.ld8(pos);
         if (c == '"') return pos + 1;
         if (c < 0x20) return 0;
