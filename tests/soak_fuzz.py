@@ -1,6 +1,6 @@
 """One-off differential soak on a GPU box: many seeds of the test suite's payload fuzzers (canonical, structured,
 mutated), every op mode, GPU (through the batch API) against the C oracle, bit-exact.  Test infrastructure, like tests/.
-python tools/soak_fuzz.py [--seeds 10] [--records 200000]"""
+python tests/soak_fuzz.py [--seeds 10] [--records 200000]"""
 import argparse
 import os
 import random
@@ -11,7 +11,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))   # this file lives there: it uses the oracle, which only tests may
 sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 import make_golden as mg  # noqa: E402
 import oracle_lib  # noqa: E402
