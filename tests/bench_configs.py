@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Measurements for BASELINE.json configs 0, 2, 3 and 4 (bench.py covers config 1, the headline).
 
-  python tools/bench_configs.py [--config 0|2|3|4|all] [--scale S]
+  python tests/bench_configs.py [--config 0|2|3|4|all] [--scale S]
 
 One JSON line per measurement.  Device-resident inputs, CUDA events on the launching stream, >= 3 warm-up launches.
 config 2  full inspection pattern set (Set A and Set A+B) on 100 000 conversations: per-token mode in one launch and

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Small all-modes run for compute-sanitizer (memcheck / racecheck): golden fixtures (adversarial JSON, oversize tiles),
 a canonical workload, bridge, ordered, inspection (per-token + streaming + inline) and the interest table.
-  compute-sanitizer --tool memcheck python tools/sanitize_smoke.py"""
+  compute-sanitizer --tool memcheck python tests/sanitize_smoke.py"""
 import os
 import sys
 
