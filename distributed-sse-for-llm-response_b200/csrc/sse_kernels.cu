@@ -640,7 +640,7 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     a.num_tiles = (a.n + TILE - 1) / TILE;
     // scratch: ticket + overflow flag + cursor + counters + per-tile words, zeroed per launch
-    e = cudaMemsetAsync(a.scratch_base, 0, scratch_bytes(a.n), stream);
+    e = a.zero_base ? cudaMemsetAsync(a.zero_base, 0, a.zero_bytes, stream) : cudaMemsetAsync(a.scratch_base, 0, scratch_bytes(a.n), stream);
     if (e != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
     if ((int)a.num_tiles < grid) grid = (int)a.num_tiles;

@@ -50,6 +50,8 @@ struct FrameArgs {
     uint32_t* bad_offsets;       // set when in_off was not monotonic / ran past in_off[n] (records are clamped, never read out of bounds)
     unsigned long long* counters;
     uint64_t* tile_state;         // ordered mode: per-tile byte totals / prefix; arrival mode: count of records left to the tail phase | previous such tile of the CTA << 32
+    void* zero_base = nullptr;   // what frame_launch clears before the launch (default: scratch_base, scratch_bytes(n))
+    size_t zero_bytes = 0;
     // filled by frame_launch
     uint32_t num_tiles, in_cap, out_cap_s;
     __host__ __device__ uint32_t out_cap_smem() const { return out_cap_s; }
@@ -90,6 +92,16 @@ inline void encode_scratch_carve(void* base, EncodeArgs& a) {
     a.done_ctas = reinterpret_cast<uint32_t*>(p + 16);
 }
 cudaError_t encode_launch(EncodeArgs a, cudaStream_t stream);
+
+// Batch slots keep header + counters directly in front of the per-record result arrays (one D2H copy for all of
+// them) and the per-tile words directly in front of the header (one clear for both).
+inline void scratch_carve_split(void* hdr_base, uint32_t n, FrameArgs& a) {
+    scratch_carve(hdr_base, a);
+    const size_t tiles = ((size_t)n + TILE - 1) / TILE;
+    a.tile_state = reinterpret_cast<uint64_t*>(static_cast<uint8_t*>(hdr_base) - tiles * 8);
+    a.zero_base = a.tile_state;
+    a.zero_bytes = tiles * 8 + scratch_readback_bytes();
+}
 
 cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid);
 cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream);

@@ -47,11 +47,16 @@ struct ssegpu_batch {
     uint8_t* h_out = nullptr; uint64_t* h_out_off = nullptr; uint32_t* h_out_len = nullptr; uint32_t* h_status = nullptr; uint32_t* h_subj = nullptr;
     uint32_t* h_verdict = nullptr; int32_t* h_match = nullptr; uint32_t* h_hit = nullptr; uint32_t* d_hit = nullptr;
     uint8_t* h_hdr = nullptr;    // scratch header + counter rows read back
+    // Everything the kernel reports per batch lives in ONE device block and ONE pinned block of the same layout,
+    // [per-tile words | header + counters | out_off | out_len | status | subj_len | verdict | match | sub_span], laid out per
+    // submit for that batch's record count: one clear, one D2H copy.  The h_*/d_* result pointers above point into them.
+    uint8_t* d_block = nullptr; uint8_t* h_block = nullptr;
+    size_t ts_cap = 0;           // bytes reserved for the per-tile words in front of the header
+    size_t meta_bytes = 0;       // header .. end of the last array of the current layout
     // device
     uint8_t* d_in = nullptr; uint32_t* d_in_off = nullptr; int64_t* d_start = nullptr;
     uint8_t* d_out = nullptr; uint64_t* d_out_off = nullptr; uint32_t* d_out_len = nullptr; uint32_t* d_status = nullptr; uint32_t* d_subj = nullptr;
     uint32_t* d_conv = nullptr; uint32_t* d_verdict = nullptr; int32_t* d_match = nullptr;
-    void* d_scratch = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_done = nullptr;
 };
@@ -102,15 +107,37 @@ void add_rows(const uint8_t* hdr, ssegpu_counters* c, uint32_t n_records) {
 void free_batch(ssegpu_batch* b) {
     if (!b) return;
     cudaFreeHost(b->h_in); cudaFreeHost(b->h_in_off); cudaFreeHost(b->h_start); cudaFreeHost(b->h_conv);
-    cudaFreeHost(b->h_out); cudaFreeHost(b->h_out_off); cudaFreeHost(b->h_out_len); cudaFreeHost(b->h_status); cudaFreeHost(b->h_subj);
-    cudaFreeHost(b->h_hdr); cudaFreeHost(b->h_verdict); cudaFreeHost(b->h_match); cudaFreeHost(b->h_hit); cudaFree(b->d_hit);
-    cudaFree(b->d_conv); cudaFree(b->d_verdict); cudaFree(b->d_match);
+    cudaFreeHost(b->h_out); cudaFreeHost(b->h_block);
+    cudaFree(b->d_conv);
     cudaFree(b->d_in); cudaFree(b->d_in_off); cudaFree(b->d_start);
-    cudaFree(b->d_out); cudaFree(b->d_out_off); cudaFree(b->d_out_len); cudaFree(b->d_status); cudaFree(b->d_subj);
-    cudaFree(b->d_scratch);
+    cudaFree(b->d_out); cudaFree(b->d_block);
     if (b->ev_done) cudaEventDestroy(b->ev_done);
     if (b->stream) cudaStreamDestroy(b->stream);
     delete b;
+}
+
+constexpr uint32_t kPackInputsMax = 16384;      // batches up to this many records send their inputs in one H2D copy
+
+// Result arrays of a batch of n records inside the slot's blocks (16-byte aligned pieces; arrays an op does not produce take no room)
+void layout_results(ssegpu_batch* b, uint32_t n, uint32_t op) {
+    uint8_t* dh = b->d_block + b->ts_cap;        // device: header + counters sit right behind the per-tile words
+    uint8_t* hh = b->h_block;
+    size_t off = sse::scratch_readback_bytes();
+    auto take = [&](size_t bytes) { const size_t o = off; off = (off + bytes + 15) & ~(size_t)15; return o; };
+    const size_t o_off = take(((size_t)n + 1) * 8), o_len = take((size_t)n * 4 + 4), o_st = take((size_t)n * 4 + 4);
+    const size_t o_subj = (op & SSEGPU_OP_BRIDGE) ? take((size_t)n * 4 + 4) : o_st;
+    const bool insp = (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) != 0;
+    const size_t o_ver = insp ? take((size_t)n * 4 + 4) : o_st, o_mat = insp ? take((size_t)n * 8 + 8) : o_st;
+    const size_t o_hit = (op & SSEGPU_OP_MATCH) ? take((size_t)n * 12 + 12) : o_st;
+    b->meta_bytes = off;
+    b->h_hdr = hh;
+    b->d_out_off = reinterpret_cast<uint64_t*>(dh + o_off); b->h_out_off = reinterpret_cast<uint64_t*>(hh + o_off);
+    b->d_out_len = reinterpret_cast<uint32_t*>(dh + o_len); b->h_out_len = reinterpret_cast<uint32_t*>(hh + o_len);
+    b->d_status = reinterpret_cast<uint32_t*>(dh + o_st); b->h_status = reinterpret_cast<uint32_t*>(hh + o_st);
+    b->d_subj = reinterpret_cast<uint32_t*>(dh + o_subj); b->h_subj = reinterpret_cast<uint32_t*>(hh + o_subj);
+    b->d_verdict = reinterpret_cast<uint32_t*>(dh + o_ver); b->h_verdict = reinterpret_cast<uint32_t*>(hh + o_ver);
+    b->d_match = reinterpret_cast<int32_t*>(dh + o_mat); b->h_match = reinterpret_cast<int32_t*>(hh + o_mat);
+    b->d_hit = reinterpret_cast<uint32_t*>(dh + o_hit); b->h_hit = reinterpret_cast<uint32_t*>(hh + o_hit);
 }
 
 int alloc_batch(ssegpu_ctx* ctx, ssegpu_batch** out) {
@@ -119,24 +146,19 @@ int alloc_batch(ssegpu_ctx* ctx, ssegpu_batch** out) {
     *out = b;
     b->ctx = ctx;
     const size_t n = ctx->cfg.max_records;
-    const size_t in_bytes = ctx->cfg.max_in_bytes + 64;
+    const size_t in_bytes = ctx->cfg.max_in_bytes + 64 + kPackInputsMax * 12 + 128;   // room for offsets + start sequences of a small batch
     CU(cudaHostAlloc(&b->h_in, in_bytes, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_in_off, (n + 1) * 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_start, n * 8 + 8, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_conv, n * 4 + 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&b->h_out, ctx->out_cap + 64, cudaHostAllocDefault));
-    CU(cudaHostAlloc(&b->h_out_off, (n + 1) * 8, cudaHostAllocDefault));
-    CU(cudaHostAlloc(&b->h_out_len, n * 4 + 4, cudaHostAllocDefault));
-    CU(cudaHostAlloc(&b->h_status, n * 4 + 4, cudaHostAllocDefault));
-    CU(cudaHostAlloc(&b->h_subj, n * 4 + 4, cudaHostAllocDefault));
-    CU(cudaHostAlloc(&b->h_hdr, sse::scratch_readback_bytes(), cudaHostAllocDefault));
-    CU(cudaHostAlloc(&b->h_verdict, n * 4 + 4, cudaHostAllocDefault));
-    CU(cudaHostAlloc(&b->h_match, n * 8 + 8, cudaHostAllocDefault));
     CU(cudaMalloc(&b->d_conv, n * 4 + 4));
-    CU(cudaMalloc(&b->d_verdict, n * 4 + 4));
-    CU(cudaMalloc(&b->d_match, n * 8 + 8));
-    CU(cudaHostAlloc(&b->h_hit, n * 12 + 12, cudaHostAllocDefault));
-    CU(cudaMalloc(&b->d_hit, n * 12 + 12));
+    b->ts_cap = (((n + sse::TILE - 1) / sse::TILE) * 8 + 15) & ~(size_t)15;
+    const size_t meta_cap = sse::scratch_readback_bytes() + (n + 1) * 8 + n * (4 + 4 + 4 + 4 + 8 + 12) + 8 * 16;
+    CU(cudaMalloc(&b->d_block, b->ts_cap + meta_cap));
+    CU(cudaHostAlloc(&b->h_block, meta_cap, cudaHostAllocDefault));
+    memset(b->h_block, 0, meta_cap);
+    layout_results(b, (uint32_t)n, ~0u);
     memset(b->h_in, 0, in_bytes);
     memset(b->h_start, 0, n * 8 + 8);
     memset(b->h_conv, 0, n * 4 + 4);
@@ -145,11 +167,6 @@ int alloc_batch(ssegpu_ctx* ctx, ssegpu_batch** out) {
     CU(cudaMalloc(&b->d_in_off, (n + 1) * 4));
     CU(cudaMalloc(&b->d_start, n * 8 + 8));
     CU(cudaMalloc(&b->d_out, ctx->out_cap + 64));
-    CU(cudaMalloc(&b->d_out_off, (n + 1) * 8));
-    CU(cudaMalloc(&b->d_out_len, n * 4 + 4));
-    CU(cudaMalloc(&b->d_status, n * 4 + 4));
-    CU(cudaMalloc(&b->d_subj, n * 4 + 4));
-    CU(cudaMalloc(&b->d_scratch, sse::scratch_bytes((uint32_t)n)));
     CU(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&b->ev_done, cudaEventDisableTiming));
     return SSEGPU_OK;
@@ -304,19 +321,33 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     CU(cudaSetDevice(ctx->cfg.device));
     cudaStream_t st = b->stream;
     b->n = n; b->op = op;
+    layout_results(b, n, op);
     // 32 readable bytes after the last payload byte (TMA tiles are 16-byte granular, word reads overrun a little)
     memset(b->h_in + in_total, 0, 48);
-    CU(cudaMemcpyAsync(b->d_in, b->h_in, ((in_total + 15) & ~15ull) + 32, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(b->d_in_off, b->h_in_off, ((size_t)n + 1) * 4, cudaMemcpyHostToDevice, st));
-    if (use_filter && n) CU(cudaMemcpyAsync(b->d_start, b->h_start, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    const size_t pay = ((in_total + 15) & ~15ull) + 32;
+    const uint32_t* d_in_off = b->d_in_off;
+    const int64_t* d_start = b->d_start;
+    if (n <= kPackInputsMax) {
+        // small batch (the latency case): offsets and start sequences ride behind the payload, one H2D copy instead of three
+        const size_t o_io = (pay + 15) & ~(size_t)15, o_ss = o_io + ((((size_t)n + 1) * 4 + 15) & ~(size_t)15);
+        memcpy(b->h_in + o_io, b->h_in_off, ((size_t)n + 1) * 4);
+        if (use_filter && n) memcpy(b->h_in + o_ss, b->h_start, (size_t)n * 8);
+        CU(cudaMemcpyAsync(b->d_in, b->h_in, o_ss + (use_filter ? (size_t)n * 8 : 0), cudaMemcpyHostToDevice, st));
+        d_in_off = reinterpret_cast<const uint32_t*>(b->d_in + o_io);
+        d_start = reinterpret_cast<const int64_t*>(b->d_in + o_ss);
+    } else {
+        CU(cudaMemcpyAsync(b->d_in, b->h_in, pay, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(b->d_in_off, b->h_in_off, ((size_t)n + 1) * 4, cudaMemcpyHostToDevice, st));
+        if (use_filter && n) CU(cudaMemcpyAsync(b->d_start, b->h_start, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    }
 
     sse::FrameArgs a{};
-    a.in = b->d_in; a.in_off = b->d_in_off; a.start_seq = use_filter ? b->d_start : nullptr;
+    a.in = b->d_in; a.in_off = d_in_off; a.start_seq = use_filter ? d_start : nullptr;
     a.n = n; a.op = op;
     a.out = b->d_out; a.out_cap = ctx->out_cap; a.out_off = b->d_out_off; a.out_len = b->d_out_len;
     a.subj_len = (op & SSEGPU_OP_BRIDGE) ? b->d_subj : nullptr;
     a.status = b->d_status;
-    sse::scratch_carve(b->d_scratch, a);
+    sse::scratch_carve_split(b->d_block + b->ts_cap, n, a);
     const bool inspect = (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) != 0;
     if (inspect) {
         if (!ctx->d_insp) return SSEGPU_E_STATE;                  // ssegpu_patterns_load first
@@ -335,17 +366,8 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
         a.interest = ctx->d_interest; a.hit = b->d_hit;
     }
     CU(sse::frame_launch(ctx->cfg.device, a, st));
-    if (match && n) CU(cudaMemcpyAsync(b->h_hit, b->d_hit, (size_t)n * 12, cudaMemcpyDeviceToHost, st));
-    if (inspect && n) {
-        CU(cudaMemcpyAsync(b->h_verdict, b->d_verdict, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
-        CU(cudaMemcpyAsync(b->h_match, b->d_match, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
-    }
-
-    CU(cudaMemcpyAsync(b->h_out_off, b->d_out_off, ((size_t)n + 1) * 8, cudaMemcpyDeviceToHost, st));
-    if (n) CU(cudaMemcpyAsync(b->h_out_len, b->d_out_len, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
-    if (n) CU(cudaMemcpyAsync(b->h_status, b->d_status, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
-    if ((op & SSEGPU_OP_BRIDGE) && n) CU(cudaMemcpyAsync(b->h_subj, b->d_subj, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(b->h_hdr, b->d_scratch, sse::scratch_readback_bytes(), cudaMemcpyDeviceToHost, st));
+    // header, counters and every per-record result array of this batch: one copy
+    CU(cudaMemcpyAsync(b->h_block, b->d_block + b->ts_cap, b->meta_bytes, cudaMemcpyDeviceToHost, st));
     // Speculative copy of the frames: a canonical record grows by 26 + digits(seq) bytes
     // (28 + len("chat..tokens")=40ish in bridge mode); anything beyond is fetched in wait().
     uint64_t spec = in_total + (uint64_t)n * ((op & SSEGPU_OP_BRIDGE) ? ((op & SSEGPU_OP_NATS_PUB) ? 96 : 80) : 32) + 16ull * ((n + sse::TILE - 1) / sse::TILE);
