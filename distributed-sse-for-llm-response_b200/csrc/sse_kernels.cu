@@ -115,6 +115,7 @@ __global__ void __launch_bounds__(1024) k_scan_tile_totals(uint64_t* tile_state,
 #define SSE_PREFETCH_WAVES 1
 #endif
 constexpr uint32_t PREFETCH_WAVES = SSE_PREFETCH_WAVES;
+constexpr uint32_t PLAN_REDO = 0xFFFFFFFFu;             // FrameArgs::plan: decode this record again in the emit pass
 struct TileSmem {
     uint64_t mbar;
     uint64_t base;           // global byte offset of the tile's output
@@ -301,7 +302,17 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
         uint32_t st = ST_OK, len = 0;
         const uint32_t o = my_b - abase, L = my_e - my_b;
         bool fastp = false;
-        if (active && smem_in) { PtrSrc src{s_in}; fastp = plan_record_fast(src, o, L, a.op, my_start, pl, st, len); }
+        bool planned = false;
+        if (MODE == MODE_ORDERED_EMIT && !EXT && a.plan && active && smem_in) {
+            const uint32_t pw = a.plan[r0 + tid];                             // left by the count pass
+            if (pw != PLAN_REDO) {
+                st = a.status[r0 + tid]; len = a.out_len[r0 + tid];
+                pl.fast = 1; pl.cid_b = 20; pl.seq_b = pw & 0x3FFFu; pl.cid_e = (pw >> 14) & 0x3FFFu; pl.seq_n = pw >> 28;
+                pl.done = (st & ST_DONE) ? 1u : 0u; pl.cid_esc = 0; pl.tok_esc = 0; pl.tok_redacted = 0;
+                fastp = true; planned = true;
+            }
+        }
+        if (active && smem_in && !planned) { PtrSrc src{s_in}; fastp = plan_record_fast(src, o, L, a.op, my_start, pl, st, len); }
         // A few such records in a warp: deferred (the tail phase runs them densely).  Many of
         // them: decoded here, where the tile is in shared memory (22 ns per warp however many of its lanes take part).
         const bool slow = active && !fastp;
@@ -398,6 +409,13 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
 #pragma unroll
         for (int w = 0; w < TILE / 32; w++) { uint32_t v = ts->wsum[w]; if (w < (int)warp) wpre += v; total += v; }
         if (MODE == MODE_ORDERED_COUNT) {        // pass A of ordered mode: only the tile's byte count is wanted
+            if (!EXT && a.plan && active) {      // what the emit pass needs of a canonical record, so that it does not decode it again
+                uint32_t pw = PLAN_REDO;
+                if (fastp && pl.seq_b < (1u << 14) && pl.cid_e < (1u << 14)) pw = pl.seq_b | (pl.cid_e << 14) | (pl.seq_n << 28);
+                a.plan[r0 + tid] = pw;
+                a.status[r0 + tid] = st;
+                a.out_len[r0 + tid] = len;
+            }
             if (tid == 0) {
                 a.tile_state[tile] = total;
                 setup_tile(a, ts, s_in, next_t, c_in);                        // every thread is past (B): the tile has been consumed

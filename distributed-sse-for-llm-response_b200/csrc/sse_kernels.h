@@ -50,6 +50,7 @@ struct FrameArgs {
     uint32_t* bad_offsets;       // set when in_off was not monotonic / ran past in_off[n] (records are clamped, never read out of bounds)
     unsigned long long* counters;
     uint64_t* tile_state;         // ordered mode: per-tile byte totals / prefix; arrival mode: count of records left to the tail phase | previous such tile of the CTA << 32
+    uint32_t* plan = nullptr;    // n words or nullptr: ordered mode's count pass leaves each canonical record's plan here for the emit pass
     void* zero_base = nullptr;   // what frame_launch clears before the launch (default: scratch_base, scratch_bytes(n))
     size_t zero_bytes = 0;
     // filled by frame_launch
@@ -61,6 +62,7 @@ inline size_t scratch_bytes(uint32_t n) {
     size_t tiles = ((size_t)n + TILE - 1) / TILE;
     return SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8 + tiles * 8;
 }
+inline size_t scratch_bytes_with_plan(uint32_t n) { return ((scratch_bytes(n) + 15) & ~(size_t)15) + (size_t)n * 4; }   // + FrameArgs::plan (never cleared)
 inline size_t scratch_readback_bytes() { return SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8; }
 inline void scratch_carve(void* base, FrameArgs& a) {
     uint8_t* p = static_cast<uint8_t*>(base);

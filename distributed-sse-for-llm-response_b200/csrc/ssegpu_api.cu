@@ -53,6 +53,7 @@ struct ssegpu_batch {
     uint8_t* d_block = nullptr; uint8_t* h_block = nullptr;
     size_t ts_cap = 0;           // bytes reserved for the per-tile words in front of the header
     size_t meta_bytes = 0;       // header .. end of the last array of the current layout
+    size_t plan_off = 0;         // ordered mode's plan words inside d_block
     // device
     uint8_t* d_in = nullptr; uint32_t* d_in_off = nullptr; int64_t* d_start = nullptr;
     uint8_t* d_out = nullptr; uint64_t* d_out_off = nullptr; uint32_t* d_out_len = nullptr; uint32_t* d_status = nullptr; uint32_t* d_subj = nullptr;
@@ -155,7 +156,8 @@ int alloc_batch(ssegpu_ctx* ctx, ssegpu_batch** out) {
     CU(cudaMalloc(&b->d_conv, n * 4 + 4));
     b->ts_cap = (((n + sse::TILE - 1) / sse::TILE) * 8 + 15) & ~(size_t)15;
     const size_t meta_cap = sse::scratch_readback_bytes() + (n + 1) * 8 + n * (4 + 4 + 4 + 4 + 8 + 12) + 8 * 16;
-    CU(cudaMalloc(&b->d_block, b->ts_cap + meta_cap));
+    CU(cudaMalloc(&b->d_block, b->ts_cap + meta_cap + n * 4 + 16));      // + the ordered-mode plan words (device only)
+    b->plan_off = b->ts_cap + meta_cap;
     CU(cudaHostAlloc(&b->h_block, meta_cap, cudaHostAllocDefault));
     memset(b->h_block, 0, meta_cap);
     layout_results(b, (uint32_t)n, ~0u);
@@ -259,7 +261,7 @@ int ssegpu_init(const ssegpu_config* cfg, ssegpu_ctx** out) {
         cudaError_t e = sse::frame_configure(cfg->device, &ic, &oc, &sm, &grid);
         if (e != cudaSuccess) { rc = cuda_fail(e, "frame_configure"); break; }
         if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(e, "cudaStreamCreate"); break; }
-        if ((e = cudaMalloc(&ctx->d_launch_scratch, sse::scratch_bytes(cfg->max_records))) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc scratch"); break; }
+        if ((e = cudaMalloc(&ctx->d_launch_scratch, sse::scratch_bytes_with_plan(cfg->max_records))) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc scratch"); break; }
         if ((e = cudaMalloc(&ctx->d_encode_scratch, sse::SCRATCH_HDR)) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc scratch"); break; }
         if ((e = cudaHostAlloc(&ctx->h_launch_hdr, sse::scratch_readback_bytes(), cudaHostAllocDefault)) != cudaSuccess) { rc = cuda_fail(e, "cudaHostAlloc"); break; }
         for (uint32_t i = 0; i < cfg->ring_slots; i++) {
@@ -348,6 +350,7 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     a.subj_len = (op & SSEGPU_OP_BRIDGE) ? b->d_subj : nullptr;
     a.status = b->d_status;
     sse::scratch_carve_split(b->d_block + b->ts_cap, n, a);
+    a.plan = reinterpret_cast<uint32_t*>(b->d_block + b->plan_off);
     const bool inspect = (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) != 0;
     if (inspect) {
         if (!ctx->d_insp) return SSEGPU_E_STATE;                  // ssegpu_patterns_load first
@@ -445,6 +448,7 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
     a.out = static_cast<uint8_t*>(d_out); a.out_cap = out_cap; a.out_off = d_out_off; a.out_len = d_out_len;
     a.subj_len = d_subj_len; a.status = d_status;
     sse::scratch_carve(ctx->d_launch_scratch, a);
+    a.plan = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(ctx->d_launch_scratch) + ((sse::scratch_bytes(ctx->cfg.max_records) + 15) & ~(size_t)15));
     if (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) {
         if (!ctx->d_insp || !ctx->bound_verdict || !ctx->bound_match) return SSEGPU_E_STATE;
         if (ctx->insp_mode == sse::INSPECT_STREAMING && (!ctx->bound_conv || !ctx->d_conv_state)) return SSEGPU_E_STATE;
