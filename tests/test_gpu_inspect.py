@@ -35,6 +35,12 @@ def run(eng, arena, off, op, conv=None):
     return res
 
 
+def odd_payload(rng, cid, tok, seq, done, ts):
+    """the same message, not as json.Marshal would write it (key order, a space, maybe other escapes in the token)"""
+    return (b'{ "done":' + (b"true" if done else b"false") + b',"token":' + mg.json_str_variants(rng, tok) + b',"timestamp":%d' % ts
+            + b',"sequence":%d,"conversation_id":' % seq + mg.json_str_variants(rng, cid) + b'}')
+
+
 def test_reference_known_answers_set_b(pkg, oracle):
     eng = pkg.SseGpu(device=0, max_records=4096, max_in_bytes=1 << 20, ring_slots=1)
     try:
@@ -84,7 +90,9 @@ def test_streaming_matches_oracle_and_carries_state_across_batches(pkg, oracle):
             convs = [c for c in range(n_conv) if rng.random() < 0.9]
             toks = [rand_token(rng) for _ in convs]
             dones = [j == n_tok - 1 or rng.random() < 0.03 for _ in convs]
-            payloads = [mg.canon("conv-%d" % c, t.decode("utf-8", "replace"), j + 1, d, 9) for c, t, d in zip(convs, toks, dones)]
+            # a few records per warp are not Go-marshalled: they take the general decoder in the kernel's tail phase
+            payloads = [mg.canon("conv-%d" % c, t.decode("utf-8", "replace"), j + 1, d, 9) if rng.random() < 0.9 else
+                        odd_payload(rng, "conv-%d" % c, t.decode("utf-8", "replace"), j + 1, d, 9) for c, t, d in zip(convs, toks, dones)]
             arena, off = oracle.pack(payloads)
             r = run(eng, arena, off, pkg.OP_INSPECT, np.array(convs, dtype=np.uint32))
             for i, (c, t, d) in enumerate(zip(convs, toks, dones)):
@@ -115,7 +123,8 @@ def test_inline_drop_and_redact(pkg, oracle):
     rng = random.Random(5)
     insp = oracle.inspector(SET_B)
     toks = [rand_token(rng) for _ in range(5000)]
-    payloads = [mg.canon("c%d" % i, t.decode("utf-8", "replace"), i, i % 50 == 0, 5) for i, t in enumerate(toks)]
+    payloads = [mg.canon("c%d" % i, t.decode("utf-8", "replace"), i, i % 50 == 0, 5) if i % 17 else
+                odd_payload(rng, "c%d" % i, t.decode("utf-8", "replace"), i, i % 50 == 0, 5) for i, t in enumerate(toks)]
     arena, off = oracle.pack(payloads)
     eng = pkg.SseGpu(device=0, max_records=1 << 16, max_in_bytes=4 << 20, ring_slots=1)
     try:
