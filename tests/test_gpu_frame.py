@@ -324,6 +324,53 @@ def test_baseline_config1_full_size_bit_exact(pkg, oracle, op):
         eng.close()
 
 
+def test_concurrent_submitters_on_one_context(pkg, oracle):
+    """The ABI's thread model: every entry point may be called from any OS thread, a batch belongs to one thread between
+    acquire and release.  Four threads hammer one context (ctypes drops the GIL inside the calls), each on its own slots,
+    mixing modes; every result must be the oracle's and the context totals must add up."""
+    import threading
+    n_conv, n_tok = 400, 8
+    arena, off = pkg.workload.generate(1, n_conv, n_tok)
+    n = n_conv * n_tok
+    want = {0: oracle.adapter(arena, off), 8: oracle.adapter(arena, off), 1: oracle.bridge(arena, off)}
+    eng = pkg.SseGpu(device=0, max_records=n, max_in_bytes=int(off[n]) + 64, ring_slots=4)
+    errors = []
+
+    def worker(k):
+        try:
+            for it in range(40):
+                op = (0, 8, 1)[(k + it) % 3]
+                while True:
+                    try:
+                        b = eng.acquire()
+                        break
+                    except pkg.SseGpuError as e:          # ring momentarily empty
+                        assert e.code == -4
+                b.fill(arena, off, None)
+                b.submit(n, op)
+                b.wait()
+                out, out_off = normalise(b.out.copy(), b.out_off.copy(), b.out_len.copy(), bool(op & 8))
+                assert np.array_equal(b.status, want[op][-1])
+                assert np.array_equal(out_off, want[op][1]) and np.array_equal(out, want[op][0])
+                b.release()
+        except BaseException as e:                        # noqa: BLE001 -- reported by the main thread
+            errors.append((k, repr(e)))
+
+    try:
+        before = eng.counters()
+        threads = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        assert not errors, errors
+        after = eng.counters()
+        assert after["records"] - before["records"] == 4 * 40 * n and after["frames"] - before["frames"] == 4 * 40 * n
+        assert after["batches"] - before["batches"] == 160
+    finally:
+        eng.close()
+
+
 def test_malformed_offsets_are_refused_not_followed(pkg, oracle):
     """in_off that is not monotonic or runs past in_off[n] must neither crash nor read outside the arena."""
     arena, off = pkg.workload.generate(1, 300, 2)
