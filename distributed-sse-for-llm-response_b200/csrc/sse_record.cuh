@@ -714,12 +714,11 @@ template <class Src> SSE_HD uint32_t scan_number(const Src& s, uint32_t pos, uin
 template <class Src> SSE_HD bool parse_int64(const Src& s, uint32_t b, uint32_t e, int64_t& out) {
     bool neg = false;
     if (s.ld8(b) == '-') { neg = true; b++; }
+    // a JSON integer literal has no leading zeros, so 20 digits or more are out of range whatever they are, and up to
+    // 19 digits (< 10^19 < 2^64) accumulate without overflow: no per-digit range test
+    if (e - b > 19) return false;
     uint64_t v = 0;
-    for (; b < e; b++) {
-        uint64_t d = s.ld8(b) - '0';
-        if (v > (0xFFFFFFFFFFFFFFFFull - d) / 10) return false;
-        v = v * 10 + d;
-    }
+    for (; b < e; b++) v = v * 10 + (uint64_t)(s.ld8(b) - '0');
     if (neg) { if (v > (1ull << 63)) return false; out = (int64_t)(0 - v); }
     else     { if (v > 0x7FFFFFFFFFFFFFFFull) return false; out = (int64_t)v; }
     return true;
