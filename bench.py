@@ -229,8 +229,12 @@ def run_gpu(args):
         b.in_off[: m + 1] = off[lo:hi + 1] - off[lo]
         b.n = m
         slots.append(b)
-        h2d += ((int(off[hi]) - int(off[lo]) + 15) & ~15) + 16 + 4 * (m + 1)
-        d2h += int(off[hi]) - int(off[lo]) + 32 * m + 8 * (m + 1) + 4 * m + 4 * m + 4160
+        nbytes = int(off[hi]) - int(off[lo])
+        a16 = lambda x: (x + 15) & ~15                                                      # noqa: E731
+        # exactly what ssegpu_batch_submit copies: payload (+32 pad) and offsets in; the packed result block (header + counters,
+        # out_off, out_len, status) and the speculative frame copy out
+        h2d += a16(nbytes) + 32 + 4 * (m + 1)
+        d2h += 4160 + a16(8 * (m + 1)) + 2 * a16(4 * m + 4) + nbytes + 32 * m + 16 * ((m + 127) // 128)
 
     def e2e_step():
         for b in slots:
