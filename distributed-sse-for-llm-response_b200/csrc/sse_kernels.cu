@@ -23,6 +23,7 @@
 //   No tensor cores: nothing here is a contraction.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <mutex>
 #include "sse_kernels.h"
 #include "sse_record.cuh"
 #include "sse_inspect.cuh"
@@ -581,6 +582,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
 }
 
 // ---------------------------------------------------------------------- launch ----
+static std::mutex g_cfg_mu;             // the cache below is filled once per device, from whichever thread launches first
 static int g_num_sms[64];
 static int g_ctas_per_sm[64][2][2];    // [device][ext][wide]
 
@@ -608,6 +610,7 @@ static cudaError_t configure_one(int device, uint32_t sm, int* per_sm) {
 static cudaError_t configure_variant(int device, bool ext, bool wide, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
     uint32_t ic, oc;
     const uint32_t sm = variant_smem(ext, wide, &ic, &oc);
+    std::lock_guard<std::mutex> lk(g_cfg_mu);
     if (g_ctas_per_sm[device][ext][wide] == 0) {
         int sms = 0, per = 0, p1 = 0, p2 = 0;
         cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);

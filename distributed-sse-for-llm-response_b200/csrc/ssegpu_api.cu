@@ -440,7 +440,7 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
     if (!ctx || !d_in_off || !d_out_off || (n && (!d_in || !d_out || !d_status || !d_out_len))) return SSEGPU_E_INVAL;
     if (bad_frame_op(op)) return SSEGPU_E_INVAL;
     if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
-    if (reinterpret_cast<uintptr_t>(d_in) & 15) return SSEGPU_E_INVAL;
+    if ((reinterpret_cast<uintptr_t>(d_in) | reinterpret_cast<uintptr_t>(d_out)) & 15) return SSEGPU_E_INVAL;   // bulk copies are 16-byte granular
     CU(cudaSetDevice(ctx->cfg.device));
     sse::FrameArgs a{};
     a.in = static_cast<const uint8_t*>(d_in); a.in_off = d_in_off; a.start_seq = d_start_seq;

@@ -33,6 +33,10 @@ static_assert(kStaticBytes <= SSEGPU_STATIC_SCRATCH_BYTES, "static scratch array
 // The scratch itself.  One copy per GPU that loads the library, kept until exit.
 static __device__ __align__(256) unsigned char g_static_scratch[SSEGPU_STATIC_SCRATCH_BYTES];
 
+__global__ void k_publish_bad_offsets(const uint32_t* bad_offsets, uint64_t* out_total) {
+    if (*bad_offsets) *out_total |= SSEGPU_STATIC_BAD_OFFSETS;
+}
+
 constexpr int kMaxDevices = 64;
 std::mutex g_mu;
 void* g_scratch_addr[kMaxDevices];      // device address of g_static_scratch on device d (nullptr = not set up yet)
@@ -72,14 +76,21 @@ int ssegpu_frame_launch_static(int device, const void* d_in, const uint32_t* d_i
         snprintf(g_err, sizeof g_err, "SSEGPU_OP_NATS_PUB needs SSEGPU_OP_BRIDGE; SSEGPU_OP_RESP belongs to ssegpu_encode_launch");
         return SSEGPU_E_INVAL;
     }
+    if (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE | SSEGPU_OP_MATCH)) {
+        // pattern tables and the interest table belong to a context; this entry has none, and running the plain kernel
+        // instead would hand back unredacted, undropped frames with status OK
+        snprintf(g_err, sizeof g_err, "SSEGPU_OP_INSPECT / SSEGPU_OP_INSPECT_INLINE / SSEGPU_OP_MATCH need a context's tables: "
+                 "use ssegpu_frame_launch or the batch ring");
+        return SSEGPU_E_INVAL;
+    }
     if (n > SSEGPU_STATIC_MAX_RECORDS) {
         snprintf(g_err, sizeof g_err, "n_records = %u exceeds SSEGPU_STATIC_MAX_RECORDS = %u: the built-in scratch array holds "
                  "one scratch word per tile for at most that many records; split the batch or use ssegpu_frame_launch",
                  n, (unsigned)SSEGPU_STATIC_MAX_RECORDS);
         return SSEGPU_E_TOOBIG;
     }
-    if (reinterpret_cast<uintptr_t>(d_in) & 15) {
-        snprintf(g_err, sizeof g_err, "d_in must be 16-byte aligned");
+    if ((reinterpret_cast<uintptr_t>(d_in) | reinterpret_cast<uintptr_t>(d_out)) & 15) {
+        snprintf(g_err, sizeof g_err, "d_in and d_out must be 16-byte aligned (tiles move as 16-byte granular bulk copies)");
         return SSEGPU_E_INVAL;
     }
     cudaError_t e = cudaSetDevice(device);
@@ -97,6 +108,12 @@ int ssegpu_frame_launch_static(int device, const void* d_in, const uint32_t* d_i
     // frame_launch clears scratch_bytes(n) of the array on `stream` (ticket, cursor, counters, per-tile words
     // must start at zero; the array still holds the previous call's values) and launches the kernel.
     e = sse::frame_launch(device, a, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) { snprintf(g_err, sizeof g_err, "launch: %s", cudaGetErrorString(e)); return SSEGPU_E_CUDA; }
+    // There is no result call on this entry, so the one data-level error the kernel can find -- offsets in in_off that
+    // are not monotonic or run past in_off[n]; such records are clamped, never read out of bounds -- travels in bit 63
+    // of out_off[n].
+    k_publish_bad_offsets<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(a.bad_offsets, d_out_off + n);
+    e = cudaGetLastError();
     if (e != cudaSuccess) { snprintf(g_err, sizeof g_err, "launch: %s", cudaGetErrorString(e)); return SSEGPU_E_CUDA; }
     return SSEGPU_OK;
 }

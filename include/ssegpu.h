@@ -196,7 +196,7 @@ int ssegpu_interest_bind(ssegpu_ctx *ctx, uint32_t *d_sub_span);             /* 
 
 /* ---- device-resident launch (kernel-level path, used by the bench and the parity tests) -- */
 /* Same computation as submit, on buffers that already live in this context's GPU memory.
- * d_in must be 16-byte aligned with 32 readable bytes after the last payload byte.
+ * d_in and d_out must be 16-byte aligned, d_in with 32 readable bytes after the last payload byte.
  * d_subj_len may be NULL in adapter mode, d_start_seq NULL switches the filter off.
  * stream is a cudaStream_t (NULL = the context's stream).  Asynchronous. Not re-entrant per
  * context (the launch scratch is per context). */
@@ -246,8 +246,15 @@ uint64_t ssegpu_launch_count(ssegpu_ctx *ctx);
  *   - all calls on one device share the one array: it is cleared on `stream` at the start of every call, and
  *     two calls whose GPU work overlaps (different streams, or different threads) race on it -- serialise them;
  *   - there is no result call: out_off[n_records] holds the arena bytes needed, so the batch overflowed the
- *     output arena exactly when out_off[n_records] > out_cap after the stream has been synchronised.
- * stream is a cudaStream_t (NULL = the legacy default stream).  Asynchronous. */
+ *     output arena exactly when out_off[n_records] > out_cap after the stream has been synchronised; bit 63 of
+ *     that word (SSEGPU_STATIC_BAD_OFFSETS) is set when d_in_off was not monotonic or ran past d_in_off[n_records]
+ *     (such records are clamped into the arena, the context entries report the same as SSEGPU_E_INVAL);
+ *   - SSEGPU_OP_INSPECT, SSEGPU_OP_INSPECT_INLINE and SSEGPU_OP_MATCH are refused with SSEGPU_E_INVAL: their tables
+ *     belong to a context and this entry has none;
+ *   - the text behind ssegpu_static_last_error (and ssegpu_last_cuda_error) is kept per OS thread: fetch it on the
+ *     thread that made the failing call (cgo: runtime.LockOSThread around the pair).
+ * d_in and d_out must be 16-byte aligned.  stream is a cudaStream_t (NULL = the legacy default stream).  Asynchronous. */
+#define SSEGPU_STATIC_BAD_OFFSETS   (1ull << 63)
 #define SSEGPU_STATIC_MAX_RECORDS   (1u << 20)
 #define SSEGPU_STATIC_SCRATCH_BYTES (72u * 1024u)
 int ssegpu_frame_launch_static(int device, const void *d_in, const uint32_t *d_in_off,

@@ -185,3 +185,18 @@ def test_oracle_against_cpython_json(oracle, golden):
             assert raw[int(out_off[i]):int(out_off[i + 1])] == pymodel.frame(msg), p
             framed += 1
     assert compared > 10000 and syntax_errors > 1000 and framed > 2000, (compared, syntax_errors, framed)
+
+
+def test_go_crosscheck_inputs_are_in_sync():
+    """oracle/go_crosscheck/main.go replays tests/golden/hand_vectors.json; it must say what hand_vectors.py says."""
+    import json
+    import hand_vectors as hv
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "hand_vectors.json")) as f:
+        recs = {r["name"]: r for r in json.load(f)}
+    for name, payload, start, status, frame in hv.ADAPTER:
+        r = recs["hand_" + name]
+        assert (bytes.fromhex(r["in"]), r["start"], r["status"], bytes.fromhex(r["frame"])) == (payload, start, status, frame)
+    for k, (payload, status, subject, js) in enumerate(hv.BRIDGE):
+        r = recs["hand_bridge_%d" % k]
+        assert (bytes.fromhex(r["in"]), r["bstatus"], bytes.fromhex(r["subject"]), bytes.fromhex(r["json"])) == (payload, status, subject, js)
+    assert len(recs) == len(hv.ADAPTER) + len(hv.BRIDGE)

@@ -57,18 +57,22 @@ def test_static_entry_matches_regular_entry_twice_in_a_row(oracle):
     torch.cuda.synchronize()
     eng = pkg.SseGpu(device=0, max_records=1 << 16, max_in_bytes=8 << 20)     # regular entry point: scratch from ssegpu_init
     try:
-        for call, ((arena, off), op) in enumerate(zip(_workloads(pkg, oracle), (pkg.OP_ADAPTER, pkg.OP_ADAPTER | pkg.OP_ORDERED))):
+        work = _workloads(pkg, oracle)
+        calls = list(zip(work, (pkg.OP_ADAPTER, pkg.OP_ADAPTER | pkg.OP_ORDERED))) + [(work[0], pkg.OP_BRIDGE), (work[1], pkg.OP_BRIDGE | pkg.OP_NATS_PUB)]
+        for call, ((arena, off), op) in enumerate(calls):
             n = len(off) - 1
-            cap = int(off[n]) * 7 + 64 * n + 4096
+            cap = int(off[n]) * 7 + 128 * n + 4096
             ref = _device_buffers(torch, arena, off, cap)
             got = _device_buffers(torch, arena, off, cap)
+            ref["d_subj"] = torch.zeros(n, dtype=torch.int32, device="cuda")
+            got["d_subj"] = torch.zeros(n, dtype=torch.int32, device="cuda")
             eng.frame_launch(ref["d_in"].data_ptr(), ref["d_off"].data_ptr(), 0, n, op, ref["d_out"].data_ptr(), cap,
-                             ref["d_out_off"].data_ptr(), ref["d_out_len"].data_ptr(), 0, ref["d_status"].data_ptr(),
+                             ref["d_out_off"].data_ptr(), ref["d_out_len"].data_ptr(), ref["d_subj"].data_ptr(), ref["d_status"].data_ptr(),
                              stream.cuda_stream)
             stream.synchronize()
             # the entry point under test: no context, no allocation
             pkg.frame_launch_static(0, got["d_in"].data_ptr(), got["d_off"].data_ptr(), 0, n, op, got["d_out"].data_ptr(), cap,
-                                    got["d_out_off"].data_ptr(), got["d_out_len"].data_ptr(), 0, got["d_status"].data_ptr(),
+                                    got["d_out_off"].data_ptr(), got["d_out_len"].data_ptr(), got["d_subj"].data_ptr(), got["d_status"].data_ptr(),
                                     stream.cuda_stream)
             stream.synchronize()
             ordered = bool(op & pkg.OP_ORDERED)
@@ -77,8 +81,14 @@ def test_static_entry_matches_regular_entry_twice_in_a_row(oracle):
             assert np.array_equal(g_status, r_status), "call %d: status words differ" % call
             assert np.array_equal(g_len, r_len), "call %d: frame lengths differ" % call
             assert np.array_equal(g_off, r_off) and np.array_equal(g_out, r_out), "call %d: frame bytes differ" % call
+            assert np.array_equal(got["d_subj"].cpu().numpy(), ref["d_subj"].cpu().numpy()), "call %d: subject lengths differ" % call
             # and both agree with the CPU oracle
-            want_out, want_off, want_status = oracle.adapter(arena, off)
+            if op & pkg.OP_NATS_PUB:
+                want_out, want_off, want_subj, want_status = oracle.bridge_pub(arena, off)
+            elif op & pkg.OP_BRIDGE:
+                want_out, want_off, want_subj, want_status = oracle.bridge(arena, off)
+            else:
+                want_out, want_off, want_status = oracle.adapter(arena, off)
             assert np.array_equal(g_status, want_status) and np.array_equal(g_out, want_out) and np.array_equal(g_off, want_off)
             assert int(got["d_out_off"][n].item()) <= cap
     finally:
@@ -91,6 +101,14 @@ def test_static_entry_rejects_oversize_and_reports_overflow(oracle):
     with pytest.raises(pkg.SseGpuError) as e:
         pkg.frame_launch_static(0, 256, 256, 0, pkg.STATIC_MAX_RECORDS + 1, 0, 256, 1 << 20, 256, 256, 0, 256, 0)
     assert e.value.code == -5 and "SSEGPU_STATIC_MAX_RECORDS" in str(e.value)
+    # inspection and the interest table live in a context: this context-free entry must refuse them, not ignore them
+    for op in (pkg.OP_INSPECT, pkg.OP_INSPECT_INLINE, pkg.OP_BRIDGE | pkg.OP_MATCH):
+        with pytest.raises(pkg.SseGpuError) as e:
+            pkg.frame_launch_static(0, 256, 256, 0, 16, op, 256, 1 << 20, 256, 256, 0, 256, 0)
+        assert e.value.code == -1
+    with pytest.raises(pkg.SseGpuError) as e:           # d_out off the 16-byte grid
+        pkg.frame_launch_static(0, 256, 256, 0, 16, 0, 264, 1 << 20, 256, 256, 0, 256, 0)
+    assert e.value.code == -1
     # an output arena that is too small is visible as out_off[n] > out_cap, nothing is written past out_cap
     arena, off = pkg.workload.generate(1, 500, 4)
     n = len(off) - 1
@@ -105,3 +123,17 @@ def test_static_entry_rejects_oversize_and_reports_overflow(oracle):
     stream.synchronize()
     assert int(buf["d_out_off"][n].item()) > cap
     assert bool((buf["d_out"][cap:] == 0xAB).all())
+    # offsets that are not monotonic: records are clamped into the arena and bit 63 of out_off[n] says so
+    bad = off.copy()
+    bad[7] = bad[9] + 5
+    buf = _device_buffers(torch, arena, bad, 1 << 20)
+    pkg.frame_launch_static(0, buf["d_in"].data_ptr(), buf["d_off"].data_ptr(), 0, n, 0, buf["d_out"].data_ptr(), 1 << 20,
+                            buf["d_out_off"].data_ptr(), buf["d_out_len"].data_ptr(), 0, buf["d_status"].data_ptr(), stream.cuda_stream)
+    stream.synchronize()
+    # (torch reads the word as int64: the flag is the sign bit)
+    assert int(buf["d_out_off"][n].item()) < 0
+    buf = _device_buffers(torch, arena, off, 1 << 20)
+    pkg.frame_launch_static(0, buf["d_in"].data_ptr(), buf["d_off"].data_ptr(), 0, n, 0, buf["d_out"].data_ptr(), 1 << 20,
+                            buf["d_out_off"].data_ptr(), buf["d_out_len"].data_ptr(), 0, buf["d_status"].data_ptr(), stream.cuda_stream)
+    stream.synchronize()
+    assert int(buf["d_out_off"][n].item()) >= 0

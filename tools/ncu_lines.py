@@ -20,6 +20,7 @@ tmp = tempfile.mkdtemp()
 subprocess.check_call(["cuobjdump", "-xelf", "all", lib], cwd=tmp, stdout=subprocess.DEVNULL)
 unit = sys.argv[sys.argv.index("--unit") + 1] if "--unit" in sys.argv else "sse_kernels"
 kern = sys.argv[sys.argv.index("--kernel") + 1] if "--kernel" in sys.argv else "k_frame_tiles"
+MANGLED = sys.argv[sys.argv.index("--mangled") + 1] if "--mangled" in sys.argv else ""      # e.g. Lb1ELi0 = k_frame_tiles<true, 0>
 cubin = [f for f in os.listdir(tmp) if f.startswith(unit + ".")][0]
 dis = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
 
@@ -31,7 +32,7 @@ pending = []
 in_kernel = False
 for ln in dis.splitlines():
     if ln.startswith(".text."):
-        in_kernel = kern in ln and (kern != "k_frame_tiles" or "Lb0" in ln or "ILb0" in ln)
+        in_kernel = kern in ln and (MANGLED in ln if MANGLED else (kern != "k_frame_tiles" or "Lb0" in ln or "ILb0" in ln))
     m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
     if m:
         pending.append((os.path.basename(m.group(1)), int(m.group(2))))
