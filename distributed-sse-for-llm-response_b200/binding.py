@@ -15,7 +15,7 @@ ACT_ALLOW, ACT_REDACT, ACT_DROP, ACT_ALERT = 0, 1, 2, 3
 VERDICT_BEGIN_UNKNOWN = 0x10000
 ST_OK, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_INSPECT_DROP = 0, 1, 2, 3, 4
 ST_CODE_MASK, ST_DONE, ST_REDACTED = 0xF, 0x100, 0x200
-E_OVERFLOW, E_AGAIN, E_DUPCONV, E_PATTERN = -6, -4, -9, -10
+E_OVERFLOW, E_AGAIN, E_CONVSLOT, E_PATTERN = -6, -4, -9, -10
 
 u8p, u32p, u64p, i64p = (C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_int64))
 

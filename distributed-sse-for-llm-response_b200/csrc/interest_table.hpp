@@ -91,7 +91,7 @@ struct HostTable {
         for (auto& kv : literal) if (id_of(kv.first, id)) n_keys++;
         size_t cap = 16;
         while (cap < 2 * n_keys + 2) cap <<= 1;
-        slots.assign(cap, sse::InterestSlot{0, 0, 0, 0, 0, {0, 0, 0}});
+        slots.assign(cap, sse::InterestSlot{});
         for (auto& kv : literal) {
             if (!id_of(kv.first, id)) continue;                       // cannot match this path's subjects
             const uint32_t len = (uint32_t)id.size(), nw = (len + 3) / 4;
@@ -100,8 +100,10 @@ struct HostTable {
             uint32_t h = sse::key_hash_init(len);
             for (uint32_t w : words) h = sse::key_hash_step(h, w);
             h = sse::key_hash_fin(h);
-            sse::InterestSlot e{h, (uint32_t)keys.size(), len, (uint32_t)subs.size(), (uint32_t)kv.second.size(), {0, 0, 0}};
-            keys.insert(keys.end(), words.begin(), words.end());
+            sse::InterestSlot e{};
+            e.hash = h; e.key_len = len; e.list_off = (uint32_t)subs.size(); e.list_cnt = (uint32_t)kv.second.size();
+            if (len <= sse::INTEREST_INLINE_KEY) memcpy(e.key, words.data(), nw * 4);
+            else { e.key[0] = (uint32_t)keys.size(); keys.insert(keys.end(), words.begin(), words.end()); }
             subs.insert(subs.end(), kv.second.begin(), kv.second.end());
             size_t p = (size_t)(h & (uint32_t)(cap - 1));
             while (slots[p].hash != 0) p = (p + 1) & (cap - 1);

@@ -10,24 +10,26 @@
 // (docs/security-inspection-patterns.md:110,268; kubernetes/base/nats-core/core-cluster.yaml:234,248).
 //
 // Layout: literal subscriptions of the form chat.<id>.tokens live in an open-addressing hash table keyed
-// by the DECODED id bytes (the bridge builds the subject from the decoded id, main.go:160): 32-byte slots
-// (one L2 sector each), linear probing, <= 50% load, a word-wise multiplicative hash, keys stored as
-// zero-padded 32-bit words so that the compare is word-wise too; values are CSR spans of subscriber ids.
-// The few wildcard subscriptions are a side list; the common shapes are pre-classified by the host so that
-// an id without dots never needs the token-by-token matcher.  At 100 k subjects the table is ~8 MB: far beyond
-// one SM's shared memory, so it is read through L2 (126 MB holds it entirely).
+// by the DECODED id bytes (the bridge builds the subject from the decoded id, main.go:160): 64-byte slots
+// that carry tag, value and the key itself (ids of up to 48 bytes; a UUID is 36), so that a lookup is ONE
+// 64-byte access and one L2 round trip instead of slot -> key arena -> compare; linear probing, <= 50 % load,
+// a word-wise multiplicative hash, keys as zero-padded 32-bit words so that hash and compare are word-wise;
+// values are spans of subscriber ids in an append-only arena.  The few wildcard subscriptions are a side
+// list; the common shapes are pre-classified by the host so that an id without dots never needs the
+// token-by-token matcher.  At 100 k subjects the table is 17 MB: far beyond one SM's shared memory (SURVEY.md
+// H3), so it is read through L2 (126 MB holds it entirely).
 #pragma once
 #include <stdint.h>
 #include "sse_inspect.cuh"
 
 namespace sse {
 
-struct InterestSlot {
-    uint32_t hash;               // 0 = empty
-    uint32_t key_off;            // first word of the key in keys[]
-    uint32_t key_len;            // bytes
-    uint32_t list_off, list_cnt; // span in the CSR subscriber array
-    uint32_t pad[3];
+constexpr uint32_t INTEREST_INLINE_KEY = 48;   // bytes of id a slot holds itself
+struct alignas(64) InterestSlot {
+    uint32_t hash;               // 0 = empty (never a valid hash)
+    uint32_t key_len;            // bytes; > INTEREST_INLINE_KEY: key[0] is the first word of the key in keys[]
+    uint32_t list_off, list_cnt; // span in the subscriber arena; count 0 = every subscriber has left (slot kept until the next rebuild)
+    uint32_t key[INTEREST_INLINE_KEY / 4];   // the id, zero-padded little-endian words
 };
 
 constexpr uint32_t INTEREST_MAX_WILD = 32;
@@ -63,7 +65,7 @@ SSE_HD void lookup_literal(const InterestDev& t, WordFn&& word, uint32_t len, In
         const uint32_t eh = e.hash;
         if (eh == 0) return;
         if (eh == hash && e.key_len == len) {
-            const uint32_t* key = t.keys + e.key_off;
+            const uint32_t* key = len <= INTEREST_INLINE_KEY ? e.key : t.keys + e.key[0];
             bool same = true;
             for (uint32_t k = 0; k < nw; k++) same = same && key[k] == word(k);
             if (same) { h.list_off = e.list_off; h.list_cnt = e.list_cnt; return; }
@@ -132,27 +134,58 @@ SSE_HD_NOINLINE InterestHit interest_lookup(const InterestDev& t, const Src& s, 
     return h;
 }
 
-// Fast lane: the id's decoded text IS its raw bytes (canonical record, no backslash escape in the id) and it has
-// no dot (one NATS token) and no wildcard needs the general matcher.  Word loads from the tile.  Returns false
-// when the general routine must take over.
+// Fast lane: the id's decoded text IS its raw bytes (canonical record, no backslash escape in the id), it fits a
+// slot, it has no dot (one NATS token) and no wildcard needs the general matcher.  One pass over the id's words
+// (aligned loads from the tile + a funnel shift each) yields the dot test, the hash and the words kept in registers
+// for the compare; a probe is one 64-byte slot.  Returns false when the general routine must take over.
 template <class Src>
 SSE_HD bool interest_lookup_raw(const InterestDev& t, const Src& s, uint32_t cid_b, uint32_t cid_e, InterestHit& h) {
     const uint32_t len = cid_e - cid_b;
-    if (len == 0 || len > 64 || t.wild_generic) return false;
-    uint32_t dots = 0;
-    for (uint32_t i = 0; i < len; i += 4) {
-        const uint32_t w = ld32u(s, cid_b + i);
-        const uint32_t keep = len - i >= 4 ? 0xFFFFFFFFu : (0xFFFFFFFFu >> (8 * (4 - (len - i))));
-        const uint32_t x = (w ^ 0x2E2E2E2Eu) | ~keep;                // bytes past the id can never look like '.'
-        dots |= (x - 0x01010101u) & ~x & 0x80808080u;
+    if (len == 0 || len > INTEREST_INLINE_KEY || t.wild_generic) return false;
+    constexpr uint32_t NW = INTEREST_INLINE_KEY / 4;
+    uint32_t kw[NW];
+    const uint32_t a = cid_b & ~3u, shb = (cid_b & 3u) * 8, nw = (len + 3) >> 2;
+    uint32_t lo = s.ld32a(a), dots = 0, hash = key_hash_init(len);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (uint32_t k = 0; k < NW; k++) {
+        uint32_t w = 0;
+        if (k < nw) {
+            const uint32_t hi = s.ld32a(a + 4 * k + 4);
+            w = funnel_r(lo, hi, shb);
+            lo = hi;
+            const uint32_t rem = len - 4 * k;
+            if (rem < 4) w &= 0xFFFFFFFFu >> (8 * (4 - rem));
+            const uint32_t x = w ^ 0x2E2E2E2Eu;                      // a '.' byte becomes zero (the zero padding does not)
+            dots |= (x - 0x01010101u) & ~x & 0x80808080u;
+            hash = key_hash_step(hash, w);
+        }
+        kw[k] = w;
     }
     if (dots) return false;
+    hash = key_hash_fin(hash);
     h.list_off = 0; h.list_cnt = 0; h.wild_mask = t.wild_single;
-    lookup_literal(t, [&](uint32_t k) {
-        const uint32_t w = ld32u(s, cid_b + 4 * k), rem = len - 4 * k;
-        return rem >= 4 ? w : (w & (0xFFFFFFFFu >> (8 * (4 - rem))));
-    }, len, h);
-    return true;
+    if (!t.slots) return true;
+    for (uint32_t p = hash & t.mask;; p = (p + 1) & t.mask) {
+        const uint32_t* e = reinterpret_cast<const uint32_t*>(t.slots + p);
+#if defined(__CUDA_ARCH__)
+        const uint4 q0 = *reinterpret_cast<const uint4*>(e), q1 = *reinterpret_cast<const uint4*>(e + 4),
+                    q2 = *reinterpret_cast<const uint4*>(e + 8), q3 = *reinterpret_cast<const uint4*>(e + 12);
+        const uint32_t sw[16] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, q3.x, q3.y, q3.z, q3.w};
+#else
+        const uint32_t* sw = e;
+#endif
+        if (sw[0] == 0) return true;                                 // empty slot: nobody subscribed to this id
+        if (sw[0] == hash && sw[1] == len) {
+            uint32_t diff = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (uint32_t k = 0; k < NW; k++) diff |= sw[4 + k] ^ kw[k];
+            if (diff == 0) { h.list_off = sw[2]; h.list_cnt = sw[3]; return true; }
+        }
+    }
 }
 
 }  // namespace sse

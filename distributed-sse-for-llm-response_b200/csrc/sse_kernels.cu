@@ -169,12 +169,12 @@ __device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uin
     }
 }
 
-// Inspection of one record's token text, general case (out of line, generic pointers): escapes in the token,
-// non-canonical records, or the leftmost-start search of a variable-length match.
-__device__ __noinline__ InspectResult inspect_slow(const InspectDev* t, const uint8_t* src_base, uint32_t tok_b, uint32_t tok_e,
-                                                   uint32_t state_in, bool eot) {
+// Inspection of one record's token text, general case (out of line, generic pointers): records that are not
+// canonical, or the leftmost-start search of a variable-length match.  per_token mode only: streaming mode is a
+// per-conversation walk in sse_stream.cu.
+__device__ __noinline__ InspectResult inspect_slow(const InspectDev* t, const uint8_t* src_base, uint32_t tok_b, uint32_t tok_e) {
     PtrSrc src{src_base};
-    return inspect_token(*t, src, tok_b, tok_e, state_in, eot);
+    return inspect_token(*t, src, tok_b, tok_e, 0, true);
 }
 __device__ __noinline__ InterestHit interest_slow(const FrameArgs& a, const uint8_t* src_base, uint32_t o, uint32_t cid_b, uint32_t cid_e) {
     PtrSrc src{src_base};
@@ -183,6 +183,50 @@ __device__ __noinline__ InterestHit interest_slow(const FrameArgs& a, const uint
 __device__ __noinline__ uint32_t measure_slow(const uint8_t* src_base, uint32_t o, uint32_t L, const Plan* pl, uint32_t op) {
     PtrSrc src{src_base};
     return measure_record(src, o, L, *pl, op);
+}
+// Token entry of record i for the streaming walk (sb + o = the record's first byte, abs_b its offset in the arena)
+__device__ __forceinline__ void store_token_entry(const FrameArgs& a, uint32_t i, const uint8_t* sb, uint32_t o, uint32_t abs_b, const Plan& pl,
+                                                  uint32_t st, bool raw_text) {
+    PtrSrc src{sb};
+    const uint32_t flags = ((st & ST_CODE_MASK) == ST_OK ? ENTRY_OK : 0u) | (raw_text ? 0u : ENTRY_DECODE) | ((st & ST_DONE) ? ENTRY_DONE : 0u);
+    uint32_t e[4];
+    make_token_entry(src, o + pl.tok_b, pl.tok_e - pl.tok_b, abs_b + pl.tok_b, flags, e);
+    a.tok_entry[i] = make_uint4(e[0], e[1], e[2], e[3]);
+}
+// The optional stages for one record that went through the GENERAL decoder (out of line: inline in a few places,
+// densely in the tail phase).  In: the record's plan, status and length.  Out: verdict/match/hit/entry stored, status
+// and length updated (inline drop / redact, nobody interested).
+__device__ __noinline__ void ext_stage_slow(const FrameArgs& a, uint32_t i, const uint8_t* sb, uint32_t o, uint32_t L, uint32_t abs_b, Plan* plp,
+                                            uint32_t* stp, uint32_t* lenp, bool write_results, bool write_entry) {
+    Plan pl = *plp;
+    uint32_t st = *stp, len = *lenp;
+    const bool ok = (st & ST_CODE_MASK) == ST_OK;
+    if (a.insp != nullptr || (a.xflags & XF_PRE_VERDICT)) {
+        InspectResult io{0, 0, 0, 0};
+        if (ok) {
+            if (a.xflags & XF_PRE_VERDICT) io.verdict = a.verdict[i];
+            else io = inspect_slow(a.insp, sb, o + pl.tok_b, o + pl.tok_e);
+            if (a.op & OP_INSPECT_INLINE) {                                   // sse_handler.go:200-207
+                const uint32_t act = io.verdict & 0xFF;
+                if (act == ACT_DROP) { st = ST_INSPECT_DROP; len = 0; }
+                else if (act == ACT_REDACT) { pl.tok_redacted = 1; pl.fast = 0; len = measure_slow(sb, o, L, &pl, a.op); st |= ST_REDACTED; }
+            }
+        }
+        if (write_results && !(a.xflags & XF_PRE_VERDICT)) {
+            a.verdict[i] = io.verdict;
+            reinterpret_cast<int2*>(a.match)[i] = make_int2(io.begin, io.end);
+        }
+    }
+    if (a.tok_entry != nullptr && write_entry) store_token_entry(a, i, sb, o, abs_b, *plp, *stp, false);
+    if (a.interest != nullptr) {
+        InterestHit h{0, 0, 0};
+        if ((st & ST_CODE_MASK) == ST_OK) {
+            h = interest_slow(a, sb, o, pl.cid_b, pl.cid_e);
+            if (h.list_cnt == 0 && h.wild_mask == 0) { st = ST_NO_INTEREST; len = 0; }
+        }
+        if (write_results) { const size_t k = 3 * (size_t)i; a.hit[k] = h.list_off; a.hit[k + 1] = h.list_cnt; a.hit[k + 2] = h.wild_mask; }
+    }
+    *plp = pl; *stp = st; *lenp = len;
 }
 
 __device__ __forceinline__ uint4 lds128(const uint8_t* p) { return *reinterpret_cast<const uint4*>(p); }
@@ -224,9 +268,9 @@ __device__ __forceinline__ void copy_out(uint8_t* __restrict__ out, const uint8_
 }
 
 // EXT is a compile-time switch so that the plain framing kernel carries none of the registers of the optional
-// stages (content inspection, interest lookup).
+// stages (per-token content inspection, interest lookup, token entries for the streaming walk).
 template <bool EXT, int MODE>
-__global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArgs a) {
+__global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_constant__ FrameArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* s_in = smem;                                   // in_cap + 32 (word reads run up to 24 bytes past a record)
     uint8_t* s_out = smem + a.in_cap + 32;                  // out_cap_s + 48
@@ -238,16 +282,25 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
     uint32_t parity = 0;
     uint32_t my_chain = 0;                                  // tid 0: last tile (+1) of this CTA that left records to the tail phase
 
-    // EXT: on-chip copy of the inspection DFA's byte-class map and hottest transition rows
-    DfaCache dcache{nullptr, nullptr, 0};
-    if (EXT && a.insp != nullptr) {
+    // EXT, fused per-token inspection: on-chip copy of the forward DFA's byte-class map, end-of-text bitmap and hottest rows
+    const bool pre_verdict = EXT && (a.xflags & XF_PRE_VERDICT) != 0;          // launch-uniform
+    const bool inspect_fused = EXT && a.insp != nullptr && !pre_verdict;
+    DfaCache dcache{nullptr, nullptr, 0, nullptr};
+    if (inspect_fused) {
         uint8_t* s_cls = reinterpret_cast<uint8_t*>(ts + 1);
-        uint16_t* s_rows = reinterpret_cast<uint16_t*>(s_cls + 256);
+        uint32_t* s_eot = reinterpret_cast<uint32_t*>(s_cls + 256);
+        uint16_t* s_rows = reinterpret_cast<uint16_t*>(s_eot + DFA_EOT_WORDS);
         const DfaDev& d = a.insp->fwd;
         const uint32_t nc = min(d.n_states, DFA_CACHE_ENTRIES / d.n_classes);
         for (uint32_t i = tid; i < 256; i += TILE) s_cls[i] = d.cls[i];
         for (uint32_t i = tid; i < nc * d.n_classes; i += TILE) s_rows[i] = d.next[i];
-        dcache.cls = s_cls; dcache.rows = s_rows; dcache.n_cached = nc;
+        if (d.n_states <= 32 * DFA_EOT_WORDS)
+            for (uint32_t w = tid; w < DFA_EOT_WORDS; w += TILE) {
+                uint32_t bits = 0;
+                for (uint32_t k = 0; k < 32 && 32 * w + k < d.n_states; k++) bits |= (d.acc_eot[32 * w + k] != 0 ? 1u : 0u) << k;
+                s_eot[w] = bits;
+            }
+        dcache.cls = s_cls; dcache.rows = s_rows; dcache.n_cached = nc; dcache.eot_bits = s_eot;
     }
     if (tid == 0) {
         mbar_init(&ts->mbar, 1);
@@ -294,14 +347,16 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
         if (smem_in && in_bytes != 0) { mbar_wait(&ts->mbar, parity); parity ^= 1; }
 
         // ---- pass 1: decode + filter, output length --------------------------------
-        // Arrival mode of the plain kernel: a record that is not canonical is left to the tail phase of this CTA, which runs
-        // the general decoder over all such records densely (one per lane).  Inline, ONE such record makes its whole warp -- and at
-        // the next barrier its CTA -- wait ten times as long as a canonical tile takes (measured: 1 % of them cost 7x).
-        constexpr bool DEFER = MODE == MODE_ARRIVAL && !EXT;
+        // Arrival mode: a record that is not canonical is left to the tail phase of this CTA, which runs the general
+        // decoder (and the general forms of the optional stages) over all such records densely, one per lane.  Inline,
+        // ONE such record makes its whole warp -- and at the next barrier its CTA -- wait ten times as long as a
+        // canonical tile takes (measured: 1 % of them cost 7x).
+        constexpr bool DEFER = MODE == MODE_ARRIVAL;
         constexpr uint32_t DEFER_MAX_PER_WARP = 9;
         Plan pl;
         uint32_t st = ST_OK, len = 0;
         const uint32_t o = my_b - abase, L = my_e - my_b;
+        const uint8_t* sb = smem_in ? s_in : a.in + abase;                    // where this tile's bytes are read from
         bool fastp = false;
         bool planned = false;
         if (MODE == MODE_ORDERED_EMIT && !EXT && a.plan && active && smem_in) {
@@ -323,7 +378,9 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
             if (defer) { st = ST_PENDING; len = 0; }
             else {                   // separate Plan object: taking pl's address would push the hot path's plan into local memory
                 Plan sp;
-                st = plan_slow(smem_in ? s_in : a.in + abase, o, L, a.op, my_start, &sp, &len);
+                st = plan_slow(sb, o, L, a.op, my_start, &sp, &len);
+                if (EXT) ext_stage_slow(a, r0 + tid, sb, o, L, my_b, &sp, &st, &len, MODE != MODE_ORDERED_COUNT,
+                                        MODE != MODE_ORDERED_COUNT || (a.xflags & XF_ENTRY_IN_COUNT));
                 pl = sp;
             }
         }
@@ -336,63 +393,55 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
             if (bytes) l2_prefetch(a.in + pf_b, bytes);
         }
 
-        // ---- content inspection of the decoded token text (optional) ------------------------
-        if (EXT && a.insp != nullptr) {                                       // launch-uniform
-            InspectResult io{0, 0, 0, 0};
-            if (active && (st & ST_CODE_MASK) == ST_OK) {
-                const InspectDev& t = *a.insp;
-                const uint8_t* sb = smem_in ? s_in : a.in + abase;
-                const bool streaming = t.mode == INSPECT_STREAMING;
-                const bool eot = !streaming || (st & ST_DONE) != 0;
-                uint32_t slot = 0, state_in = 0;
-                bool valid = true;
-                if (streaming) {          // a conversation slot may be touched once per launch: stamp it with the launch epoch
-                    slot = a.conv_slot[r0 + tid];
-                    // (the counting pass of ordered mode is a dry run: it neither stamps nor commits conversation state)
-                    valid = slot < a.conv_slots && (MODE == MODE_ORDERED_COUNT || atomicExch(&a.conv_epoch[slot], a.epoch) != a.epoch);
-                    if (valid) state_in = a.conv_state[slot]; else atomicExch(a.dup_conv, 1u);
-                }
-                if (valid) {
-                    bool done_fast = false;
-                    if (fastp && !pl.tok_esc) { PtrSrc src{s_in}; done_fast = inspect_raw(t, dcache, src, o + pl.tok_b, o + pl.tok_e, state_in, eot, io); }
-                    if (!done_fast) io = inspect_slow(a.insp, sb, o + pl.tok_b, o + pl.tok_e, state_in, eot);
-                    if (streaming && MODE != MODE_ORDERED_COUNT) a.conv_state[slot] = io.state;
-                }
-                if (a.op & OP_INSPECT_INLINE) {                               // sse_handler.go:200-207
-                    const uint32_t act = io.verdict & 0xFF;
-                    if (act == ACT_DROP) { st = ST_INSPECT_DROP; len = 0; }
-                    else if (act == ACT_REDACT) {
-                        Plan sp = pl;
-                        if (fastp) {                                          // the canonical path skipped values the encoder now needs
+        // ---- optional stages, canonical records (the others went through ext_stage_slow or wait for the tail) ----
+        if (EXT) {
+            const bool canon = active && fastp;
+            // content inspection of the decoded token text, per_token mode (sse_handler.go:193-208)
+            if (a.insp != nullptr || pre_verdict) {                           // launch-uniform
+                InspectResult io{0, 0, 0, 0};
+                if (canon && (st & ST_CODE_MASK) == ST_OK) {
+                    if (pre_verdict) io.verdict = a.verdict[r0 + tid];
+                    else {
+                        PtrSrc src{s_in};
+                        if (!inspect_canon_token(*a.insp, dcache, src, o + pl.tok_b, o + pl.tok_e, pl.tok_esc != 0, io))
+                            io = inspect_slow(a.insp, s_in, o + pl.tok_b, o + pl.tok_e);
+                    }
+                    if (a.op & OP_INSPECT_INLINE) {                           // sse_handler.go:200-207
+                        const uint32_t act = io.verdict & 0xFF;
+                        if (act == ACT_DROP) { st = ST_INSPECT_DROP; len = 0; }
+                        else if (act == ACT_REDACT) {                         // the canonical path skipped values the encoder now needs
+                            Plan sp;
                             uint32_t unused;
-                            plan_slow(sb, o, L, a.op | OP_NO_FAST, my_start, &sp, &unused);
+                            plan_slow(s_in, o, L, a.op | OP_NO_FAST, my_start, &sp, &unused);
+                            sp.tok_redacted = 1; sp.fast = 0; fastp = false;
+                            sp.cid_esc = pl.cid_esc; sp.tok_esc = pl.tok_esc;  // the general decoder does not note escapes; same literal ranges
+                            len = measure_slow(s_in, o, L, &sp, a.op);
+                            pl = sp;
+                            st |= ST_REDACTED;
                         }
-                        sp.tok_redacted = 1; sp.fast = 0; fastp = false;
-                        pl = sp;
-                        len = measure_slow(sb, o, L, &sp, a.op);
-                        st |= ST_REDACTED;
                     }
                 }
+                if (!pre_verdict && active && !slow && MODE != MODE_ORDERED_COUNT) {
+                    a.verdict[r0 + tid] = io.verdict;
+                    reinterpret_cast<int2*>(a.match)[r0 + tid] = make_int2(io.begin, io.end);
+                }
             }
-            if (active && MODE != MODE_ORDERED_COUNT) {
-                a.verdict[r0 + tid] = io.verdict;
-                a.match[2 * (size_t)(r0 + tid)] = io.begin;
-                a.match[2 * (size_t)(r0 + tid) + 1] = io.end;
-            }
-        }
-
-        // ---- subject -> subscriber/interest table (optional) ---------------------------------
-        if (EXT && a.interest != nullptr) {                                   // launch-uniform
-            InterestHit h{0, 0, 0};
-            if (active && (st & ST_CODE_MASK) == ST_OK) {
-                bool done_fast = false;
-                if (fastp && !pl.cid_esc) { PtrSrc src{s_in}; done_fast = interest_lookup_raw(*a.interest, src, o + pl.cid_b, o + pl.cid_e, h); }
-                if (!done_fast) h = interest_slow(a, smem_in ? s_in : a.in + abase, o, pl.cid_b, pl.cid_e);
-                if (h.list_cnt == 0 && h.wild_mask == 0) { st = ST_NO_INTEREST; len = 0; }   // nobody subscribed: nothing to frame
-            }
-            if (active && MODE != MODE_ORDERED_COUNT) {
-                const size_t k = 3 * (size_t)(r0 + tid);
-                a.hit[k] = h.list_off; a.hit[k + 1] = h.list_cnt; a.hit[k + 2] = h.wild_mask;
+            // token entry for the streaming walk
+            if (a.tok_entry != nullptr && canon && (MODE != MODE_ORDERED_COUNT || (a.xflags & XF_ENTRY_IN_COUNT)))
+                store_token_entry(a, r0 + tid, s_in, o, my_b, pl, st, !pl.tok_esc);
+            // subject -> subscriber/interest table
+            if (a.interest != nullptr) {                                      // launch-uniform
+                InterestHit h{0, 0, 0};
+                if (canon && (st & ST_CODE_MASK) == ST_OK) {
+                    bool done_fast = false;
+                    if (!pl.cid_esc) { PtrSrc src{s_in}; done_fast = interest_lookup_raw(*a.interest, src, o + pl.cid_b, o + pl.cid_e, h); }
+                    if (!done_fast) h = interest_slow(a, s_in, o, pl.cid_b, pl.cid_e);
+                    if (h.list_cnt == 0 && h.wild_mask == 0) { st = ST_NO_INTEREST; len = 0; }   // nobody subscribed: nothing to frame
+                }
+                if (active && !slow && MODE != MODE_ORDERED_COUNT) {
+                    const size_t k = 3 * (size_t)(r0 + tid);
+                    a.hit[k] = h.list_off; a.hit[k + 1] = h.list_cnt; a.hit[k + 2] = h.wild_mask;
+                }
             }
         }
 
@@ -451,7 +500,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
                     emit_record_fast(src, o, L, pl, a.op, w, &subj);
                 } else {
                     Plan sp = pl;
-                    subj = emit_slow(smem_in ? s_in : a.in + abase, o, L, &sp, a.op, s_out, (uint64_t)local);
+                    subj = emit_slow(sb, o, L, &sp, a.op, s_out, (uint64_t)local);
                 }
             }
             if (!ordered) {
@@ -469,7 +518,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
         if (!smem_out) {
             if (active && code == ST_OK && fits) {
                 Plan sp = pl;
-                subj = emit_slow(smem_in ? s_in : a.in + abase, o, L, &sp, a.op, a.out, base + local);
+                subj = emit_slow(sb, o, L, &sp, a.op, a.out, base + local);
             }
             if (fits && tid < alloc - total) a.out[base + total + tid] = 0;       // pad of an aligned tile
             __syncthreads();                                                  // (E') s_in free
@@ -496,11 +545,12 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
     unsigned long long* row = a.counters + (size_t)(blockIdx.x % CTR_ROWS) * CTR_COLS;
 
     // ---- tail: the records this CTA left over --------------------------------------------------
-    // Arrival mode of the plain kernel.  The tiles that left records behind are chained through tile_state; their record
-    // numbers are gathered in the (now idle) staging tile and the general decoder runs over them one record per lane,
-    // 128 at a time, straight from and to global memory.  Each warp takes a 16-byte aligned slice of the arena from the
-    // same cursor, so such a frame simply lives somewhere else in the arena (out_off/out_len address it like any other).
-    if (MODE == MODE_ARRIVAL && !EXT) {
+    // Arrival mode.  The tiles that left records behind are chained through tile_state; their record numbers are
+    // gathered in the (now idle) staging tile and the general decoder -- with the general forms of the optional
+    // stages -- runs over them one record per lane, 128 at a time, straight from and to global memory.  Each warp
+    // takes a 16-byte aligned slice of the arena from the same cursor, so such a frame simply lives somewhere else in
+    // the arena (out_off/out_len address it like any other).
+    if (MODE == MODE_ARRIVAL) {
         uint32_t* s_list = reinterpret_cast<uint32_t*>(s_out);
         __syncthreads();                                                      // every thread has read the loop's last ts->tile
         if (tid == 0) { ts->tile = my_chain; ts->npend = 0; }
@@ -524,6 +574,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
                     i = s_list[g + tid];
                     b = min(a.in_off[i], in_total); e = min(max(a.in_off[i + 1], b), in_total);
                     st = plan_slow(a.in, b, e - b, a.op, a.start_seq ? a.start_seq[i] : 0, &pl, &len);
+                    if (EXT) ext_stage_slow(a, i, a.in, b, e - b, b, &pl, &st, &len, true, true);
                 }
                 uint32_t incl = len;
 #pragma unroll
@@ -582,63 +633,73 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const FrameArg
 }
 
 // ---------------------------------------------------------------------- launch ----
+// Shared memory per CTA: a tile of TILE records is ~17 KB in / ~21 KB out at the BASELINE workload; the caps leave
+// ~15% slack.  Tiles that exceed them take the direct global-memory path inside the same kernel.
+//   cfg 0  160 B in / 192 B out per record                      5 CTAs per SM (the SM's shared memory is then full)
+//   cfg 1  "wide": NATS PUB framing adds ~60 bytes per record (subject + protocol line): 224 B out
+//   cfg 2  fused per-token inspection of adapter frames: the on-chip DFA part (2.4 KB) has to fit beside five tiles
+//          per SM, so the caps shrink to 152 B in / 184 B out per record (~10 % slack at the BASELINE shape)
+//   cfg 3  fused inspection of bridge records (subject + payload ~182 B: the narrow cap would overflow): full caps, 4 CTAs per SM
+//   cfg 4  fused inspection + NATS PUB framing
+constexpr int N_CFG = 5;
+static void cfg_caps(int cfg, uint32_t* ic, uint32_t* oc, uint32_t* smem) {
+    const bool cache = cfg >= 2;
+    *ic = TILE * (cfg == 2 ? 152 : 160);
+    *oc = TILE * (cfg == 2 ? 184 : ((cfg == 1 || cfg == 4) ? 224 : 192));
+    *smem = *ic + 32 + *oc + 48 + (uint32_t)sizeof(TileSmem) + (cache ? DFA_CACHE_BYTES : 0u);
+}
+
 static std::mutex g_cfg_mu;             // the cache below is filled once per device, from whichever thread launches first
 static int g_num_sms[64];
-static int g_ctas_per_sm[64][2][2];    // [device][ext][wide]
+static int g_ctas_per_sm[64][2][N_CFG]; // [device][ext][cfg]; 0 = device not configured yet
 
-// Shared memory per CTA: a tile of TILE records is ~17 KB in / ~21 KB out at the BASELINE workload; the caps leave
-// ~15% slack.  Tiles that exceed them take the direct global-memory path inside the same kernel.  The EXT kernel
-// (inspection / interest lookup) adds the on-chip DFA cache.  "wide": NATS PUB framing adds ~60 bytes per record to
-// the bridge output (subject + protocol line), which would push every tile past the 192-byte-per-record staging cap.
-static uint32_t variant_smem(bool ext, bool wide, uint32_t* ic, uint32_t* oc) {
-    *ic = TILE * 160; *oc = TILE * (wide ? 224 : 192);
-    return *ic + 32 + *oc + 48 + (uint32_t)sizeof(TileSmem) + (ext ? DFA_CACHE_BYTES : 0u);
-}
 template <bool EXT, int MODE>
-static cudaError_t configure_one(int device, uint32_t sm, int* per_sm) {
-    uint32_t ic, oc;
-    cudaError_t e = cudaFuncSetAttribute(k_frame_tiles<EXT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)variant_smem(EXT, true, &ic, &oc));
+static cudaError_t configure_one(int* per_sm /* [N_CFG] */) {
+    uint32_t ic, oc, sm, sm_max = 0;
+    for (int c = 0; c < N_CFG; c++) { cfg_caps(c, &ic, &oc, &sm); sm_max = sm > sm_max ? sm : sm_max; }
+    cudaError_t e = cudaFuncSetAttribute(k_frame_tiles<EXT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_max);
     if (e != cudaSuccess) return e;
-    int per = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<EXT, MODE>, TILE, sm);
-    if (e != cudaSuccess) return e;
-    *per_sm = per < 1 ? 1 : per;
-    (void)device;
-    return cudaSuccess;
-}
-
-static cudaError_t configure_variant(int device, bool ext, bool wide, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
-    uint32_t ic, oc;
-    const uint32_t sm = variant_smem(ext, wide, &ic, &oc);
-    std::lock_guard<std::mutex> lk(g_cfg_mu);
-    if (g_ctas_per_sm[device][ext][wide] == 0) {
-        int sms = 0, per = 0, p1 = 0, p2 = 0;
-        cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    for (int c = 0; c < N_CFG; c++) {
+        cfg_caps(c, &ic, &oc, &sm);
+        int per = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<EXT, MODE>, TILE, sm);
         if (e != cudaSuccess) return e;
-        if (ext) {
-            if ((e = configure_one<true, MODE_ARRIVAL>(device, sm, &per)) != cudaSuccess) return e;
-            if ((e = configure_one<true, MODE_ORDERED_COUNT>(device, sm, &p1)) != cudaSuccess) return e;
-            if ((e = configure_one<true, MODE_ORDERED_EMIT>(device, sm, &p2)) != cudaSuccess) return e;
-        } else {
-            if ((e = configure_one<false, MODE_ARRIVAL>(device, sm, &per)) != cudaSuccess) return e;
-            if ((e = configure_one<false, MODE_ORDERED_COUNT>(device, sm, &p1)) != cudaSuccess) return e;
-            if ((e = configure_one<false, MODE_ORDERED_EMIT>(device, sm, &p2)) != cudaSuccess) return e;
-        }
-        per = min(per, min(p1, p2));
-        g_num_sms[device] = sms;
-        g_ctas_per_sm[device][ext][wide] = per;
+        per = per < 1 ? 1 : per;
+        per_sm[c] = per_sm[c] == 0 ? per : min(per_sm[c], per);      // the three modes of one launch share a grid
     }
-    *in_cap = ic; *out_cap = oc; *smem_bytes = sm;
-    *grid = g_num_sms[device] * g_ctas_per_sm[device][ext][wide];
     return cudaSuccess;
 }
 
-cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid) {
-    cudaError_t e = configure_variant(device, true, true, in_cap, out_cap, smem_bytes, grid);
-    if (e == cudaSuccess) e = configure_variant(device, false, true, in_cap, out_cap, smem_bytes, grid);
-    if (e == cudaSuccess) e = configure_variant(device, true, false, in_cap, out_cap, smem_bytes, grid);
+cudaError_t frame_configure(int device) {
+    std::lock_guard<std::mutex> lk(g_cfg_mu);
+    if (g_ctas_per_sm[device][0][0] != 0) return cudaSuccess;
+    int sms = 0;
+    cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     if (e != cudaSuccess) return e;
-    return configure_variant(device, false, false, in_cap, out_cap, smem_bytes, grid);
+    int plain[N_CFG] = {0}, ext[N_CFG] = {0};
+    if ((e = configure_one<false, MODE_ARRIVAL>(plain)) != cudaSuccess) return e;
+    if ((e = configure_one<false, MODE_ORDERED_COUNT>(plain)) != cudaSuccess) return e;
+    if ((e = configure_one<false, MODE_ORDERED_EMIT>(plain)) != cudaSuccess) return e;
+    if ((e = configure_one<true, MODE_ARRIVAL>(ext)) != cudaSuccess) return e;
+    if ((e = configure_one<true, MODE_ORDERED_COUNT>(ext)) != cudaSuccess) return e;
+    if ((e = configure_one<true, MODE_ORDERED_EMIT>(ext)) != cudaSuccess) return e;
+    g_num_sms[device] = sms;
+    for (int c = N_CFG - 1; c >= 0; c--) { g_ctas_per_sm[device][1][c] = ext[c]; g_ctas_per_sm[device][0][c] = plain[c]; }
+    return cudaSuccess;
+}
+
+static cudaError_t choose_variant(int device, FrameArgs& a, bool* ext, uint32_t* smem_bytes, int* grid) {
+    cudaError_t e = frame_configure(device);
+    if (e != cudaSuccess) return e;
+    *ext = a.insp != nullptr || a.interest != nullptr || a.tok_entry != nullptr || (a.xflags & XF_PRE_VERDICT);
+    const bool cache = a.insp != nullptr && !(a.xflags & XF_PRE_VERDICT);
+    const bool wide = (a.op & OP_NATS_PUB) != 0, bridge = (a.op & OP_BRIDGE) != 0;
+    const int cfg = cache ? (wide ? 4 : (bridge ? 3 : 2)) : (wide ? 1 : 0);
+    cfg_caps(cfg, &a.in_cap, &a.out_cap_s, smem_bytes);
+    *grid = g_num_sms[device] * g_ctas_per_sm[device][*ext ? 1 : 0][cfg];
+    a.num_tiles = (a.n + TILE - 1) / TILE;
+    if ((int)a.num_tiles < *grid) *grid = (int)a.num_tiles;
+    return cudaSuccess;
 }
 
 template <bool EXT>
@@ -652,21 +713,39 @@ static void launch_variant(const FrameArgs& a, int grid, uint32_t smem_bytes, cu
     }
 }
 
+static cudaError_t clear_scratch(const FrameArgs& a, cudaStream_t stream) {
+    // ticket + overflow flag + cursor + counters + per-tile words, zeroed per launch
+    uint8_t* lo = static_cast<uint8_t*>(a.zero_base ? a.zero_base : a.scratch_base);
+    uint8_t* hi = lo + (a.zero_base ? a.zero_bytes : scratch_bytes(a.n));
+    if (!a.keep_bad_conv) return cudaMemsetAsync(lo, 0, (size_t)(hi - lo), stream);
+    uint8_t* flag = reinterpret_cast<uint8_t*>(a.bad_conv);
+    cudaError_t e = cudaMemsetAsync(lo, 0, (size_t)(flag - lo), stream);
+    return e != cudaSuccess ? e : cudaMemsetAsync(flag + 4, 0, (size_t)(hi - flag - 4), stream);
+}
+
 cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     uint32_t smem_bytes;
     int grid;
-    const bool ext = a.insp != nullptr || a.interest != nullptr;
-    const bool wide = (a.op & OP_NATS_PUB) != 0;
-    cudaError_t e = configure_variant(device, ext, wide, &a.in_cap, &a.out_cap_s, &smem_bytes, &grid);
+    bool ext;
+    cudaError_t e = choose_variant(device, a, &ext, &smem_bytes, &grid);
     if (e != cudaSuccess) return e;
-    a.num_tiles = (a.n + TILE - 1) / TILE;
-    // scratch: ticket + overflow flag + cursor + counters + per-tile words, zeroed per launch
-    e = a.zero_base ? cudaMemsetAsync(a.zero_base, 0, a.zero_bytes, stream) : cudaMemsetAsync(a.scratch_base, 0, scratch_bytes(a.n), stream);
-    if (e != cudaSuccess) return e;
+    if ((e = clear_scratch(a, stream)) != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
-    if ((int)a.num_tiles < grid) grid = (int)a.num_tiles;
     if (ext) launch_variant<true>(a, grid, smem_bytes, stream);
     else launch_variant<false>(a, grid, smem_bytes, stream);
+    return cudaGetLastError();
+}
+
+cudaError_t frame_plan_launch(int device, FrameArgs a, cudaStream_t stream) {
+    uint32_t smem_bytes;
+    int grid;
+    bool ext;
+    a.xflags |= XF_ENTRY_IN_COUNT;
+    cudaError_t e = choose_variant(device, a, &ext, &smem_bytes, &grid);
+    if (e != cudaSuccess) return e;
+    if ((e = clear_scratch(a, stream)) != cudaSuccess) return e;
+    if (a.n == 0) return cudaSuccess;
+    k_frame_tiles<true, MODE_ORDERED_COUNT><<<grid, TILE, smem_bytes, stream>>>(a);
     return cudaGetLastError();
 }
 

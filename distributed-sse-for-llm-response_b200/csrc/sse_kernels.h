@@ -15,7 +15,10 @@ struct InterestDev;              // sse_interest.cuh
 constexpr int TILE = SSE_TILE;   // records per tile == threads per CTA
 constexpr int CTR_ROWS = 64;     // counter rows (CTA i adds into row i % CTR_ROWS; the host sums rows)
 constexpr int CTR_COLS = 8;      // ok, syntax, type, filtered, done, fast, bytes_in, bytes_out
-constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32, [20] duplicate-conversation flag u32, [24] bad-offsets flag u32
+constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cursor u64, [16] finished CTAs u32, [20] conversation-slot-out-of-range flag u32, [24] bad-offsets flag u32
+
+enum : uint32_t { XF_PRE_VERDICT = 1u,       // verdict[] already holds this batch's verdicts: apply them (inline mode), do not inspect
+                  XF_ENTRY_IN_COUNT = 2u };  // write tok_entry in ordered mode's counting pass too (it runs alone, as a planning pass)
 
 struct FrameArgs {
     const uint8_t* in;           // packed payload arena, 16-byte aligned, 32 readable bytes after the last record
@@ -28,13 +31,13 @@ struct FrameArgs {
     uint32_t* out_len;           // n
     uint32_t* subj_len;          // n or nullptr
     uint32_t* status;            // n
-    // content inspection (nullptr insp = off): tables, per-record conversation slot, carried DFA state per slot,
-    // per-slot launch stamp (a conversation may appear once per streaming batch), outputs
+    // content inspection.  per_token mode is fused into the frame kernel (insp != nullptr).  streaming mode is a
+    // per-conversation walk in its own kernels (sse_stream.cu): the frame kernel then only leaves a 16-byte token
+    // entry per record (tok_entry != nullptr) and, for inline verdicts, a second frame pass reads the walk's
+    // verdicts back (XF_PRE_VERDICT) instead of inspecting.
     const InspectDev* insp;
-    const uint32_t* conv_slot;   // n (streaming mode)
-    uint32_t* conv_state;        // [conv_slots]
-    uint32_t* conv_epoch;        // [conv_slots]
-    uint32_t conv_slots, epoch;
+    uint4* tok_entry;            // n or nullptr
+    uint32_t xflags;
     uint32_t* verdict;           // n
     int32_t* match;              // 2n: begin, end (byte offsets into the decoded token text)
     // subscriber/interest table (nullptr = off): per record (CSR offset, count, wildcard mask)
@@ -46,13 +49,14 @@ struct FrameArgs {
     uint32_t* overflow;
     unsigned long long* cursor;  // arrival-order placement: next free output byte
     uint32_t* done_ctas;
-    uint32_t* dup_conv;
+    uint32_t* bad_conv;          // streaming inspection: a record's conversation slot is >= conv_slots (set by sse_stream.cu)
     uint32_t* bad_offsets;       // set when in_off was not monotonic / ran past in_off[n] (records are clamped, never read out of bounds)
     unsigned long long* counters;
     uint64_t* tile_state;         // ordered mode: per-tile byte totals / prefix; arrival mode: count of records left to the tail phase | previous such tile of the CTA << 32
     uint32_t* plan = nullptr;    // n words or nullptr: ordered mode's count pass leaves each canonical record's plan here for the emit pass
     void* zero_base = nullptr;   // what frame_launch clears before the launch (default: scratch_base, scratch_bytes(n))
     size_t zero_bytes = 0;
+    uint32_t keep_bad_conv = 0;  // the clear leaves the bad_conv word alone (set by the streaming walk in front of this frame pass)
     // filled by frame_launch
     uint32_t num_tiles, in_cap, out_cap_s;
     __host__ __device__ uint32_t out_cap_smem() const { return out_cap_s; }
@@ -71,7 +75,7 @@ inline void scratch_carve(void* base, FrameArgs& a) {
     a.overflow = reinterpret_cast<uint32_t*>(p + 4);
     a.cursor = reinterpret_cast<unsigned long long*>(p + 8);
     a.done_ctas = reinterpret_cast<uint32_t*>(p + 16);
-    a.dup_conv = reinterpret_cast<uint32_t*>(p + 20);
+    a.bad_conv = reinterpret_cast<uint32_t*>(p + 20);
     a.bad_offsets = reinterpret_cast<uint32_t*>(p + 24);
     a.counters = reinterpret_cast<unsigned long long*>(p + SCRATCH_HDR);
     a.tile_state = reinterpret_cast<uint64_t*>(p + SCRATCH_HDR + (size_t)CTR_ROWS * CTR_COLS * 8);
@@ -105,7 +109,28 @@ inline void scratch_carve_split(void* hdr_base, uint32_t n, FrameArgs& a) {
     a.zero_bytes = tiles * 8 + scratch_readback_bytes();
 }
 
-cudaError_t frame_configure(int device, uint32_t* in_cap, uint32_t* out_cap, uint32_t* smem_bytes, int* grid);
+cudaError_t frame_configure(int device);
 cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream);
+// the counting pass of ordered mode on its own: decodes, leaves token entries (XF_ENTRY_IN_COUNT) and emits nothing --
+// the planning pass in front of the streaming walk when its verdicts must be applied inline
+cudaError_t frame_plan_launch(int device, FrameArgs a, cudaStream_t stream);
+
+// ---- streaming inspection: per-conversation walk over the token entries (sse_stream.cu) ----
+struct StreamArgs {
+    const InspectDev* insp;      // device descriptor
+    const uint8_t* in;           // payload arena (tokens longer than 8 bytes or with escapes are read from it)
+    const uint4* tok_entry;      // n, written by the frame kernel
+    const uint32_t* conv_slot;   // n
+    uint32_t n, conv_slots;
+    uint32_t* conv_state;        // [conv_slots] carried DFA state
+    uint32_t* verdict;           // n   (cleared here; only hits are written)
+    int32_t* match;              // 2n
+    uint32_t* bad_conv;          // flag word
+    void* scratch;               // stream_scratch_bytes(n) bytes
+    uint32_t dfa_states, dfa_classes;   // of the forward DFA (sizes the on-chip table)
+};
+size_t stream_scratch_bytes(uint32_t n);
+cudaError_t stream_configure(int device);
+cudaError_t stream_inspect_launch(int device, const StreamArgs& a, cudaStream_t stream);
 
 }  // namespace sse

@@ -76,9 +76,12 @@ struct ssegpu_ctx {
     // content inspection
     void* d_insp_blob = nullptr;          // DFA tables
     sse::InspectDev* d_insp = nullptr;    // descriptor with device pointers into the blob
-    uint32_t insp_mode = 0, insp_start_state = 0;
-    uint32_t* d_conv_state = nullptr; uint32_t* d_conv_epoch = nullptr;
-    uint32_t epoch = 0;
+    uint32_t insp_mode = 0, insp_start_state = 0, insp_states = 0, insp_classes = 0;
+    uint32_t* d_conv_state = nullptr;
+    // streaming mode: token entries + sort scratch of the per-conversation walk, shared by every batch of the context
+    // (streaming batches run one after the other on the GPU: ev_stream orders them in submit order)
+    uint4* d_tok_entry = nullptr; void* d_stream_scratch = nullptr;
+    cudaEvent_t ev_stream = nullptr;
     // interest table
     sse_interest::HostTable interest;
     void* d_int_slots = nullptr; void* d_int_keys = nullptr; void* d_int_wild = nullptr; sse::InterestDev* d_interest = nullptr;
@@ -90,6 +93,49 @@ namespace {
 
 // kernels per frame launch: ordered = count pass, tile scan, emit pass; arrival = the tile kernel
 uint32_t launches_of(uint32_t op) { return (op & SSEGPU_OP_ORDERED) ? 3 : 1; }
+
+// Frame kernels plus, in streaming inspection mode, the per-conversation walk.  Streaming batches of one context run in
+// submit order (each waits for the previous one's walk): the carried DFA state of a conversation that has tokens in
+// two consecutive batches must be committed by the first before the second reads it.
+int launch_path(ssegpu_ctx* ctx, sse::FrameArgs a, const uint32_t* d_conv, cudaStream_t st, uint32_t* n_launches) {
+    const bool inspect = (a.op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) != 0;
+    *n_launches = a.n ? launches_of(a.op) : 0;
+    if (!inspect || ctx->insp_mode != sse::INSPECT_STREAMING) {
+        CU(sse::frame_launch(ctx->cfg.device, a, st));
+        return SSEGPU_OK;
+    }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    CU(cudaStreamWaitEvent(st, ctx->ev_stream, 0));
+    sse::StreamArgs w{};
+    w.insp = a.insp; w.in = a.in; w.tok_entry = ctx->d_tok_entry; w.conv_slot = d_conv; w.n = a.n; w.conv_slots = ctx->cfg.conv_slots;
+    w.conv_state = ctx->d_conv_state; w.verdict = a.verdict; w.match = a.match; w.scratch = ctx->d_stream_scratch;
+    w.dfa_states = ctx->insp_states; w.dfa_classes = ctx->insp_classes;
+    sse::FrameArgs f = a;
+    f.insp = nullptr; f.tok_entry = ctx->d_tok_entry;
+    uint32_t bits = 1;
+    while (bits < 32 && (1ull << bits) < ctx->cfg.conv_slots) bits++;
+    const uint32_t walk_launches = a.n ? 5 * ((bits + 10) / 11) + 2 : 0;
+    if (a.op & SSEGPU_OP_INSPECT_INLINE) {
+        // verdicts change the frames: planning pass (token entries only), walk, then the frame pass applies the verdicts
+        sse::FrameArgs plan = f;
+        plan.interest = nullptr;
+        CU(sse::frame_plan_launch(ctx->cfg.device, plan, st));
+        w.bad_conv = plan.bad_conv;
+        // (the frame pass below clears its scratch but leaves that flag word alone: keep_bad_conv)
+        CU(sse::stream_inspect_launch(ctx->cfg.device, w, st));
+        f.tok_entry = nullptr; f.xflags = sse::XF_PRE_VERDICT;
+        f.keep_bad_conv = 1;
+        CU(sse::frame_launch(ctx->cfg.device, f, st));
+        *n_launches += (a.n ? 1 : 0) + walk_launches;
+    } else {
+        CU(sse::frame_launch(ctx->cfg.device, f, st));
+        w.bad_conv = f.bad_conv;
+        CU(sse::stream_inspect_launch(ctx->cfg.device, w, st));
+        *n_launches += walk_launches;
+    }
+    CU(cudaEventRecord(ctx->ev_stream, st));
+    return SSEGPU_OK;
+}
 
 // SSEGPU_OP_NATS_PUB is a bridge-mode framing; SSEGPU_OP_RESP belongs to the encoder
 bool bad_frame_op(uint32_t op) { return (op & SSEGPU_OP_RESP) || ((op & SSEGPU_OP_NATS_PUB) && !(op & SSEGPU_OP_BRIDGE)); }
@@ -193,7 +239,7 @@ const char* ssegpu_strerror(int err) {
     case SSEGPU_E_OVERFLOW: return "output arena too small for this batch";
     case SSEGPU_E_STATE: return "batch used out of order";
     case SSEGPU_E_TIMEOUT: return "timed out";
-    case SSEGPU_E_DUPCONV: return "a conversation slot appears twice in one streaming-inspection batch (or is out of range)";
+    case SSEGPU_E_CONVSLOT: return "streaming inspection: a record's conversation slot is not below conv_slots";
     case SSEGPU_E_PATTERN: return "unsupported or malformed inspection pattern (see ssegpu_last_cuda_error for the reason)";
     default: return "unknown error";
     }
@@ -257,9 +303,10 @@ int ssegpu_init(const ssegpu_config* cfg, ssegpu_ctx** out) {
     ctx->out_cap = cfg->max_out_bytes ? cfg->max_out_bytes : 2 * cfg->max_in_bytes + 64ull * cfg->max_records;
     int rc = SSEGPU_OK;
     do {
-        uint32_t ic, oc, sm; int grid;
-        cudaError_t e = sse::frame_configure(cfg->device, &ic, &oc, &sm, &grid);
+        cudaError_t e = sse::frame_configure(cfg->device);
         if (e != cudaSuccess) { rc = cuda_fail(e, "frame_configure"); break; }
+        if ((e = sse::stream_configure(cfg->device)) != cudaSuccess) { rc = cuda_fail(e, "stream_configure"); break; }
+        if ((e = cudaEventCreateWithFlags(&ctx->ev_stream, cudaEventDisableTiming)) != cudaSuccess) { rc = cuda_fail(e, "cudaEventCreate"); break; }
         if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(e, "cudaStreamCreate"); break; }
         if ((e = cudaMalloc(&ctx->d_launch_scratch, sse::scratch_bytes_with_plan(cfg->max_records))) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc scratch"); break; }
         if ((e = cudaMalloc(&ctx->d_encode_scratch, sse::SCRATCH_HDR)) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc scratch"); break; }
@@ -285,7 +332,8 @@ void ssegpu_destroy(ssegpu_ctx* ctx) {
     cudaFree(ctx->d_launch_scratch);
     cudaFree(ctx->d_encode_scratch);
     cudaFree(ctx->d_int_slots); cudaFree(ctx->d_int_keys); cudaFree(ctx->d_int_wild); cudaFree(ctx->d_interest);
-    cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp); cudaFree(ctx->d_conv_state); cudaFree(ctx->d_conv_epoch);
+    cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp); cudaFree(ctx->d_conv_state); cudaFree(ctx->d_tok_entry); cudaFree(ctx->d_stream_scratch);
+    if (ctx->ev_stream) cudaEventDestroy(ctx->ev_stream);
     cudaFreeHost(ctx->h_launch_hdr);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -355,12 +403,10 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     if (inspect) {
         if (!ctx->d_insp) return SSEGPU_E_STATE;                  // ssegpu_patterns_load first
         if (ctx->insp_mode == sse::INSPECT_STREAMING) {
-            if (!ctx->d_conv_state) return SSEGPU_E_STATE;        // conv_slots was 0 at init
+            if (!ctx->d_conv_state || !ctx->d_tok_entry) return SSEGPU_E_STATE;   // conv_slots was 0 at init
             if (n) CU(cudaMemcpyAsync(b->d_conv, b->h_conv, (size_t)n * 4, cudaMemcpyHostToDevice, st));
         }
-        std::lock_guard<std::mutex> lk(ctx->mu);
-        a.insp = ctx->d_insp; a.conv_slot = b->d_conv; a.conv_state = ctx->d_conv_state; a.conv_epoch = ctx->d_conv_epoch;
-        a.conv_slots = ctx->cfg.conv_slots; a.epoch = ++ctx->epoch;
+        a.insp = ctx->d_insp;
         a.verdict = b->d_verdict; a.match = b->d_match;
     }
     const bool match = (op & SSEGPU_OP_MATCH) != 0;
@@ -368,7 +414,8 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
         if (!ctx->d_interest) return SSEGPU_E_STATE;                  // ssegpu_interest_apply first
         a.interest = ctx->d_interest; a.hit = b->d_hit;
     }
-    CU(sse::frame_launch(ctx->cfg.device, a, st));
+    uint32_t n_launches = 0;
+    { const int rc = launch_path(ctx, a, b->d_conv, st, &n_launches); if (rc != SSEGPU_OK) return rc; }
     // header, counters and every per-record result array of this batch: one copy
     CU(cudaMemcpyAsync(b->h_block, b->d_block + b->ts_cap, b->meta_bytes, cudaMemcpyDeviceToHost, st));
     // Speculative copy of the frames: a canonical record grows by 26 + digits(seq) bytes
@@ -381,7 +428,7 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     {
         std::lock_guard<std::mutex> lk(ctx->mu);
         b->state = SUBMITTED;
-        ctx->launches += n ? launches_of(op) : 0;
+        ctx->launches += n_launches;
     }
     return SSEGPU_OK;
 }
@@ -407,7 +454,7 @@ int ssegpu_batch_wait(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t timeout_us) {
     b->total_out = b->h_out_off[b->n];
     int rc = SSEGPU_OK;
     if (reinterpret_cast<const uint32_t*>(b->h_hdr)[6]) rc = SSEGPU_E_INVAL;           // in_off was not monotonic
-    else if (reinterpret_cast<const uint32_t*>(b->h_hdr)[5]) rc = SSEGPU_E_DUPCONV;
+    else if (reinterpret_cast<const uint32_t*>(b->h_hdr)[5]) rc = SSEGPU_E_CONVSLOT;
     else if (overflow) rc = SSEGPU_E_OVERFLOW;
     else if (b->total_out > b->spec_out) {
         CU(cudaMemcpyAsync(b->h_out + b->spec_out, b->d_out + b->spec_out, b->total_out - b->spec_out, cudaMemcpyDeviceToHost, b->stream));
@@ -451,10 +498,8 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
     a.plan = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(ctx->d_launch_scratch) + ((sse::scratch_bytes(ctx->cfg.max_records) + 15) & ~(size_t)15));
     if (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) {
         if (!ctx->d_insp || !ctx->bound_verdict || !ctx->bound_match) return SSEGPU_E_STATE;
-        if (ctx->insp_mode == sse::INSPECT_STREAMING && (!ctx->bound_conv || !ctx->d_conv_state)) return SSEGPU_E_STATE;
-        std::lock_guard<std::mutex> lk(ctx->mu);
-        a.insp = ctx->d_insp; a.conv_slot = ctx->bound_conv; a.conv_state = ctx->d_conv_state; a.conv_epoch = ctx->d_conv_epoch;
-        a.conv_slots = ctx->cfg.conv_slots; a.epoch = ++ctx->epoch;
+        if (ctx->insp_mode == sse::INSPECT_STREAMING && (!ctx->bound_conv || !ctx->d_conv_state || !ctx->d_tok_entry)) return SSEGPU_E_STATE;
+        a.insp = ctx->d_insp;
         a.verdict = ctx->bound_verdict; a.match = ctx->bound_match;
     }
     if (op & SSEGPU_OP_MATCH) {
@@ -462,9 +507,10 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
         a.interest = ctx->d_interest; a.hit = ctx->bound_hit;
     }
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
-    CU(sse::frame_launch(ctx->cfg.device, a, st));
+    uint32_t n_launches = 0;
+    { const int rc = launch_path(ctx, a, ctx->bound_conv, st, &n_launches); if (rc != SSEGPU_OK) return rc; }
     std::lock_guard<std::mutex> lk(ctx->mu);
-    ctx->launches += n ? launches_of(op) : 0;
+    ctx->launches += n_launches;
     return SSEGPU_OK;
 }
 
@@ -474,7 +520,7 @@ int ssegpu_frame_launch_result(ssegpu_ctx* ctx, ssegpu_counters* out) {
     CU(cudaMemcpy(ctx->h_launch_hdr, ctx->d_launch_scratch, sse::scratch_readback_bytes(), cudaMemcpyDeviceToHost));
     if (out) add_rows(ctx->h_launch_hdr, out, 0);
     if (reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[6]) return SSEGPU_E_INVAL;
-    if (reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[5]) return SSEGPU_E_DUPCONV;
+    if (reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[5]) return SSEGPU_E_CONVSLOT;
     return reinterpret_cast<const uint32_t*>(ctx->h_launch_hdr)[1] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
 }
 
@@ -545,7 +591,8 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
     };
     fill(h.fwd, c.forward, offs[0]);
     for (size_t k = 0; k < c.anchored.size(); k++) fill(h.anchored[k], c.anchored[k], offs[k + 1]);
-    h.n_patterns = n; h.mode = mode;
+    h.n_patterns = n; h.mode = mode; h.min_len = 0xFFFFFFFFu;
+    for (uint32_t i = 0; i < n; i++) h.min_len = c.patterns[i].min_len < h.min_len ? c.patterns[i].min_len : h.min_len;
     for (uint32_t i = 0; i < 32; i++) { h.action[i] = 0; h.fixed_len[i] = 0; h.anchored_of[i] = -1; }
     for (uint32_t i = 0; i < n; i++) {
         h.action[i] = c.patterns[i].action;
@@ -558,15 +605,15 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp);
     ctx->d_insp_blob = d_blob; ctx->d_insp = d_desc; ctx->insp_mode = mode; ctx->insp_start_state = c.forward.start[0];
+    ctx->insp_states = c.forward.n_states; ctx->insp_classes = c.forward.n_classes;
     if (ctx->cfg.conv_slots) {
-        if (!ctx->d_conv_state) {
-            CU(cudaMalloc(&ctx->d_conv_state, (size_t)ctx->cfg.conv_slots * 4));
-            CU(cudaMalloc(&ctx->d_conv_epoch, (size_t)ctx->cfg.conv_slots * 4));
-        }
+        if (!ctx->d_conv_state) CU(cudaMalloc(&ctx->d_conv_state, (size_t)ctx->cfg.conv_slots * 4));
         std::vector<uint32_t> init(ctx->cfg.conv_slots, ctx->insp_start_state);
         CU(cudaMemcpy(ctx->d_conv_state, init.data(), init.size() * 4, cudaMemcpyHostToDevice));
-        CU(cudaMemset(ctx->d_conv_epoch, 0, (size_t)ctx->cfg.conv_slots * 4));
-        ctx->epoch = 0;
+        if (mode == sse::INSPECT_STREAMING && !ctx->d_tok_entry) {     // token entries + sort scratch of the per-conversation walk
+            CU(cudaMalloc(&ctx->d_tok_entry, (size_t)ctx->cfg.max_records * 16 + 16));
+            CU(cudaMalloc(&ctx->d_stream_scratch, sse::stream_scratch_bytes(ctx->cfg.max_records)));
+        }
     }
     return SSEGPU_OK;
 }

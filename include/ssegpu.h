@@ -44,7 +44,7 @@ typedef enum {
     SSEGPU_E_OVERFLOW = -6,   /* output arena too small for this batch (nothing truncated silently) */
     SSEGPU_E_STATE = -7,      /* batch used out of order (submit before acquire, ...) */
     SSEGPU_E_TIMEOUT = -8,    /* ssegpu_batch_wait timed out */
-    SSEGPU_E_DUPCONV = -9,    /* streaming inspection: a conversation slot occurs twice in one batch / out of range */
+    SSEGPU_E_CONVSLOT = -9,   /* streaming inspection: a record's conversation slot is not below conv_slots */
     SSEGPU_E_PATTERN = -10    /* unsupported or malformed inspection pattern */
 } ssegpu_err;
 
@@ -164,9 +164,10 @@ int ssegpu_counters_get(ssegpu_ctx *ctx, ssegpu_counters *out);
  * token text is scanned bytewise; \d [0-9], \w [0-9A-Za-z_], \b on ASCII word bytes; literals fold ASCII case.
  * kind 0 = literal, 1 = regex subset (atoms, classes, + * ? {n,m}, \b; no groups/alternation).  Up to 32 patterns.
  * mode 0 = per_token: every token is scanned on its own; the lowest-numbered matching pattern wins.
- * mode 1 = streaming: the DFA state is carried per conversation slot (ssegpu_conv_slot) across tokens, so patterns
- *          split over token boundaries are found; the first match to become decidable wins; a conversation may
- *          occur at most once per batch (SSEGPU_E_DUPCONV otherwise); the done token resets the slot.
+ * mode 1 = streaming: the DFA state is carried per conversation slot (ssegpu_conv_slot) across tokens and across
+ *          batches, so patterns split over token boundaries are found; the first match to become decidable wins;
+ *          a conversation may occur any number of times in a batch (its records are walked in arrival order);
+ *          the done token resets the slot.  Streaming batches of one context execute in submit order.
  * verdict word: action (0 allow, 1 redact, 2 drop, 3 alert) | pattern index << 8 | SSEGPU_VERDICT_BEGIN_UNKNOWN.
  * match[2i], match[2i+1]: begin / end byte offsets into the decoded token text (begin may be negative in streaming
  * mode; INT32_MIN with SSEGPU_VERDICT_BEGIN_UNKNOWN for variable-length patterns whose start is not recoverable). */

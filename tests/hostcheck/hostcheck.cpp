@@ -73,13 +73,19 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
         t.fixed_len[i] = c.patterns[i].min_len == c.patterns[i].max_len ? c.patterns[i].min_len : 0;
         t.anchored_of[i] = c.anchored_of[i];
     }
+    t.min_len = 0xFFFFFFFFu;
+    for (uint32_t i = 0; i < n_pats; i++) t.min_len = c.patterns[i].min_len < t.min_len ? c.patterns[i].min_len : t.min_len;
     if (n_states) *n_states = c.forward.n_states;
     std::vector<uint32_t> state(conv_slots ? conv_slots : 1, c.forward.start[0]);
     std::vector<uint32_t> nest(NEST_WORDS);
     PtrSrc src{in};
     // the kernel keeps the first few states' rows on chip; here the "cache" aliases the full table but is
-    // deliberately small so that both the cached and the uncached branch of dfa_step run
-    DfaCache cache{c.forward.cls, c.forward.next.data(), c.forward.n_states < 20 ? c.forward.n_states : 20};
+    // deliberately small so that both the cached and the uncached branch of the walk run
+    std::vector<uint32_t> eot_bits(DFA_EOT_WORDS, 0);
+    if (c.forward.n_states <= 32 * DFA_EOT_WORDS)
+        for (uint32_t st = 0; st < c.forward.n_states; st++) if (c.forward.acc_eot[st]) eot_bits[st >> 5] |= 1u << (st & 31);
+    DfaCache cache{c.forward.cls, c.forward.next.data(), c.forward.n_states < 20 ? c.forward.n_states : 20, eot_bits.data()};
+    const bool streaming = mode == INSPECT_STREAMING;
     for (uint32_t i = 0; i < n; i++) {
         Plan pl;
         uint32_t len = 0, st = ST_OK;
@@ -88,16 +94,24 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
         if (!fastp) st = plan_record(src, o, L, 0, 0, pl, nest.data(), len);
         status[i] = st;
         verdict[i] = 0; match[2 * i] = 0; match[2 * i + 1] = 0;
-        if ((st & ST_CODE_MASK) != ST_OK) continue;
-        const bool streaming = mode == INSPECT_STREAMING;
-        const bool eot = !streaming || (st & ST_DONE) != 0;
-        const uint32_t slot = streaming ? conv_slot[i] : 0;
-        const uint32_t state_in = streaming ? state[slot] : 0;
         InspectResult r{0, 0, 0, 0};
-        bool done_fast = false;
-        if (fastp && !pl.tok_esc) done_fast = inspect_raw(t, cache, src, o + pl.tok_b, o + pl.tok_e, state_in, eot, r);
-        if (!done_fast) r = inspect_token(t, src, o + pl.tok_b, o + pl.tok_e, state_in, eot);
-        if (streaming) state[slot] = r.state;
+        if (streaming) {
+            // as on the GPU: the frame pass leaves a token entry, the per-conversation walk consumes the entries in
+            // arrival order (which is record order here)
+            const uint32_t flags = ((st & ST_CODE_MASK) == ST_OK ? ENTRY_OK : 0u) | ((fastp && !pl.tok_esc) ? 0u : ENTRY_DECODE) |
+                                   ((st & ST_DONE) ? ENTRY_DONE : 0u);
+            uint32_t e[4];
+            make_token_entry(src, o + pl.tok_b, pl.tok_e - pl.tok_b, o + pl.tok_b, flags, e);
+            if (!(flags & ENTRY_OK)) continue;
+            const uint32_t slot = conv_slot[i];
+            r = stream_walk(t, cache, src, e[0], e[1], e[2], e[3], state[slot]);
+            state[slot] = r.state;
+        } else {
+            if ((st & ST_CODE_MASK) != ST_OK) continue;
+            bool done_fast = false;
+            if (fastp) done_fast = inspect_canon_token(t, cache, src, o + pl.tok_b, o + pl.tok_e, pl.tok_esc != 0, r);
+            if (!done_fast) r = inspect_token(t, src, o + pl.tok_b, o + pl.tok_e, 0, true);
+        }
         verdict[i] = r.verdict; match[2 * i] = r.begin; match[2 * i + 1] = r.end;
     }
     return 0;

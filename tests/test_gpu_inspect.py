@@ -105,10 +105,13 @@ def test_streaming_matches_oracle_and_carries_state_across_batches(pkg, oracle):
                 if d:
                     hist[c] = b""
         assert hits > 200
-        # a conversation twice in one batch is refused, not silently raced
-        arena, off = oracle.pack([mg.canon("c", "a", 1, False, 2)] * 2)
+        # a conversation twice in one batch: its tokens are walked in arrival order ("pass" + "word" = password)
+        arena, off = oracle.pack([mg.canon("c", "my pass", 1, False, 2), mg.canon("c", "word is", 2, True, 2)])
+        r = run(eng, arena, off, pkg.OP_INSPECT, np.array([7, 7], dtype=np.uint32))
+        assert int(r["verdict"][0]) == 0 and int(r["verdict"][1]) == insp.stream(b"my password is", 7, 14, True)[0] != 0
+        # a conversation slot the context does not have is an error, not a wild write
         b = eng.acquire()
-        b.fill(arena, off, None, np.array([7, 7], dtype=np.uint32))
+        b.fill(arena, off, None, np.array([7, n_conv], dtype=np.uint32))
         b.submit(2, pkg.OP_INSPECT)
         with pytest.raises(pkg.SseGpuError) as e:
             b.wait()
