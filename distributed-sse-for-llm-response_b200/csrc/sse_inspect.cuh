@@ -26,15 +26,18 @@ enum : uint32_t { ACT_ALLOW = 0, ACT_REDACT = 1, ACT_DROP = 2, ACT_ALERT = 3 };
 // lowest-numbered states.  Subset construction numbers states breadth-first from the start state, so ordinary text
 // lives in the first few dozen (measured on the BASELINE token stream: 99.7 % of all steps in states < 32, 99.99 % in
 // states < 48); the other rows are read through L1/L2.
-constexpr uint32_t DFA_CACHE_ENTRIES = 1024;          // u16 transitions kept on chip
+constexpr uint32_t DFA_CACHE_ENTRIES = 1008;          // u16 transitions kept on chip (with five tiles per SM the shared memory is full to within 24 bytes)
 constexpr uint32_t DFA_EOT_WORDS = 32;
 constexpr uint32_t DFA_CACHE_BYTES = 256 + 4 * DFA_EOT_WORDS + 2 * DFA_CACHE_ENTRIES;
 
-// Streaming mode: the frame kernel leaves one 16-byte token entry per record for the per-conversation walk
-// (sse_stream.cu): x = offset of the token literal's content in the payload arena, y = its raw length (24 bits,
-// saturating) | flags << 24, z/w = the first 8 raw bytes of the token.
+// Streaming mode: the frame kernel leaves one 32-byte token entry (one DRAM sector) per record for the per-conversation
+// walk (sse_stream.cu): word 0 = offset of the token literal's content in the payload arena, word 1 = its raw length
+// (24 bits, saturating) | flags << 24, words 2..7 = the first 24 raw bytes of the literal -- every BASELINE token, so the
+// walk needs the arena only for longer ones.
 enum : uint32_t { ENTRY_OK = 1u, ENTRY_DECODE = 2u, ENTRY_DONE = 4u, ENTRY_HUGE = 8u };
 constexpr uint32_t ENTRY_LEN_MASK = 0xFFFFFFu;
+constexpr uint32_t ENTRY_WORDS = 8, ENTRY_INLINE = 24;
+constexpr uint32_t STREAM_BUF_WORDS = 16;            // the walk fetches tokens of up to 56 raw bytes from the arena in one round of word loads
 
 struct DfaDev {
     const uint8_t* cls;        // [256]
@@ -81,7 +84,14 @@ struct InspectResult { uint32_t verdict; int32_t begin, end; uint32_t state; };
 // On-chip copy of the byte-class map and of the transition rows of the first `n_cached` states of the forward
 // DFA (subset construction numbers states breadth-first from the start state, so these are the states ordinary
 // text lives in).  On the host it simply points at the full tables.
-struct DfaCache { const uint8_t* cls; const uint16_t* rows; uint32_t n_cached; const uint32_t* eot_bits; };
+// next/n_classes/n_states/min_len repeat fields of the (global-memory) descriptor so that the walk finds them in registers.
+struct DfaCache {
+    const uint8_t* cls; const uint16_t* rows; uint32_t n_cached; const uint32_t* eot_bits;
+    const uint16_t* next; uint32_t n_classes, n_states, start0, min_len;
+};
+SSE_HD DfaCache make_dfa_cache(const InspectDev& t, const uint8_t* cls, const uint16_t* rows, uint32_t n_cached, const uint32_t* eot_bits) {
+    return DfaCache{cls, rows, n_cached, eot_bits, t.fwd.next, t.fwd.n_classes, t.fwd.n_states, t.fwd.start0, t.min_len};
+}
 
 // State of one walk.  per_token: the lowest-numbered pattern wins, with its first (= smallest) end; streaming: the
 // first match to become decidable wins, ties to the lowest id.
@@ -97,9 +107,9 @@ template <bool STREAMING> SSE_HD void walk_event(Walk& w, uint32_t mask, uint32_
     }
 }
 template <bool STREAMING> SSE_HD void walk_byte(const DfaDev& d, const DfaCache& c, Walk& w, uint32_t byte) {
-    const uint32_t k = w.st * d.n_classes + c.cls[byte];
+    const uint32_t k = w.st * c.n_classes + c.cls[byte];
     uint32_t nx;
-    if (w.st < c.n_cached) nx = c.rows[k]; else nx = d.next[k];     // the unanchored forward DFA has no dead state
+    if (w.st < c.n_cached) nx = c.rows[k]; else nx = c.next[k];     // the unanchored forward DFA has no dead state
     w.st = nx & 0x7FFF;
     if (nx & 0x8000) {                                             // the target state reports a match: rare
         walk_event<STREAMING>(w, d.acc_del[w.st], w.idx);
@@ -108,7 +118,7 @@ template <bool STREAMING> SSE_HD void walk_byte(const DfaDev& d, const DfaCache&
     w.idx++;
 }
 template <bool STREAMING> SSE_HD void walk_eot(const DfaDev& d, const DfaCache& c, Walk& w) {
-    if (c.eot_bits && d.n_states <= 32 * DFA_EOT_WORDS && !((c.eot_bits[w.st >> 5] >> (w.st & 31)) & 1u)) return;
+    if (c.eot_bits && c.n_states <= 32 * DFA_EOT_WORDS && !((c.eot_bits[w.st >> 5] >> (w.st & 31)) & 1u)) return;
     walk_event<STREAMING>(w, d.acc_eot[w.st], w.idx);
 }
 
@@ -188,8 +198,8 @@ SSE_HD bool inspect_canon_token(const InspectDev& t, const DfaCache& c, const Sr
     const DfaDev& d = t.fwd;
     r.verdict = 0; r.begin = 0; r.end = 0; r.state = 0;
     const uint32_t n = tok_e - tok_b;
-    if (n < t.min_len) return true;                    // decoded text is never longer than its literal: nothing fits
-    Walk w{d.start0, 0, 0, 32, 0};
+    if (n < c.min_len) return true;                    // decoded text is never longer than its literal: nothing fits
+    Walk w{c.start0, 0, 0, 32, 0};
     if (!has_esc) {
         const uint32_t a = tok_b & ~3u, shb = (tok_b & 3u) * 8;
         uint32_t lo = s.ld32a(a);
@@ -201,7 +211,20 @@ SSE_HD bool inspect_canon_token(const InspectDev& t, const DfaCache& c, const Sr
             for (uint32_t k = 0; k < m; k++, word >>= 8) walk_byte<false>(d, c, w, word & 0xFF);
         }
     } else {
-        for_each_decoded_byte(s, tok_b, tok_e, [&](uint32_t b) { walk_byte<false>(d, c, w, b); });
+        // the escapes json.Marshal itself writes: two-character forms and u00XX (one byte each), u2028 / u2029 (three bytes)
+        for (uint32_t pos = tok_b; pos < tok_e;) {
+            uint32_t ch = s.ld8(pos++);
+            if (ch == '\\') {
+                const uint32_t e = s.ld8(pos++);
+                if (e == 'u') {
+                    const uint32_t r = (uint32_t)hex4(s, pos);
+                    pos += 4;
+                    if (r < 0x80) ch = r;
+                    else { walk_byte<false>(d, c, w, 0xE0 | (r >> 12)); walk_byte<false>(d, c, w, 0x80 | ((r >> 6) & 0x3F)); ch = 0x80 | (r & 0x3F); }
+                } else ch = e == 'n' ? 10u : e == 'r' ? 13u : e == 't' ? 9u : e == 'b' ? 8u : e == 'f' ? 12u : e;
+            }
+            walk_byte<false>(d, c, w, ch);
+        }
     }
     walk_eot<false>(d, c, w);
     if (w.win < 32) {
@@ -215,38 +238,72 @@ SSE_HD bool inspect_canon_token(const InspectDev& t, const DfaCache& c, const Sr
 
 // Token entry left by the frame kernel for the streaming walk (layout: ENTRY_* above).
 template <class Src>
-SSE_HD void make_token_entry(const Src& s, uint32_t tok_b, uint32_t raw_len, uint32_t abs_tok_b, uint32_t flags, uint32_t out[4]) {
+SSE_HD void make_token_entry(const Src& s, uint32_t tok_b, uint32_t raw_len, uint32_t abs_tok_b, uint32_t flags, uint32_t out[ENTRY_WORDS]) {
     out[0] = abs_tok_b;
     out[1] = (raw_len < ENTRY_LEN_MASK ? raw_len : ENTRY_LEN_MASK) | ((flags | (raw_len >= ENTRY_LEN_MASK ? ENTRY_HUGE : 0u)) << 24);
-    uint32_t w0 = 0, w1 = 0;
-    if ((flags & ENTRY_OK) && !(flags & ENTRY_DECODE) && raw_len != 0 && raw_len <= 8) {
-        const uint32_t a = tok_b & ~3u, shb = (tok_b & 3u) * 8;
-        const uint32_t x0 = s.ld32a(a), x1 = s.ld32a(a + 4), x2 = s.ld32a(a + 8);
-        w0 = funnel_r(x0, x1, shb); w1 = funnel_r(x1, x2, shb);
+    // the literal's first 24 bytes (whatever follows a shorter token rides along: the walk stops at raw_len)
+    const uint32_t a = tok_b & ~3u, shb = (tok_b & 3u) * 8;
+    uint32_t lo = s.ld32a(a);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (uint32_t k = 0; k < ENTRY_INLINE / 4; k++) {
+        uint32_t w = 0;
+        if ((flags & ENTRY_OK) && 4 * k < raw_len) { const uint32_t hi = s.ld32a(a + 4 * k + 4); w = funnel_r(lo, hi, shb); lo = hi; }
+        out[2 + k] = w;
     }
-    out[2] = w0; out[3] = w1;
 }
 
-// streaming mode: one token of a conversation, given by its entry; `arena` reads the payload arena at absolute
-// offsets.  state_in is the conversation's carried state; the returned state is what the next token starts from.
+// streaming mode: one token of a conversation, given by its entry e[0..7]; `arena` reads the payload arena at
+// absolute offsets.  state_in is the conversation's carried state; the returned state is what the next token starts from.
 template <class Src>
-SSE_HD InspectResult stream_walk(const InspectDev& t, const DfaCache& c, const Src& arena, uint32_t e0, uint32_t e1, uint32_t e2, uint32_t e3,
-                                 uint32_t state_in) {
+SSE_HD InspectResult stream_walk(const InspectDev& t, const DfaCache& c, const Src& arena, const uint32_t e[ENTRY_WORDS], uint32_t state_in) {
     const DfaDev& d = t.fwd;
-    const uint32_t flags = e1 >> 24;
-    uint32_t n = e1 & ENTRY_LEN_MASK;
+    const uint32_t flags = e[1] >> 24;
+    const uint32_t n = e[1] & ENTRY_LEN_MASK;
     const bool eot = (flags & ENTRY_DONE) != 0;
     Walk w{state_in, 0, 0, 32, 0};
-    if (!(flags & ENTRY_DECODE) && n <= 8) {
-        for (uint32_t k = 0; k < n; k++) walk_byte<true>(d, c, w, ((k < 4 ? e2 : e3) >> (8 * (k & 3))) & 0xFF);
+    if (!(flags & ENTRY_DECODE) && n <= ENTRY_INLINE) {
+        // the common case: the decoded text is the raw bytes and they are all in the entry (registers)
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (uint32_t k = 0; k < ENTRY_INLINE / 4; k++) {
+            if (4 * k < n) {
+                uint32_t word = e[2 + k];
+                const uint32_t m = n - 4 * k < 4 ? n - 4 * k : 4;
+                for (uint32_t b = 0; b < m; b++, word >>= 8) walk_byte<true>(d, c, w, word & 0xFF);
+            }
+        }
+    } else if (!(flags & ENTRY_HUGE) && n <= 4 * STREAM_BUF_WORDS - 8) {
+        // escapes to resolve, or a longer token: raw bytes into a small local buffer (from the entry, or from the arena as
+        // independent word loads: one memory round trip instead of one per byte), the general decoder walks that
+        uint32_t buf[STREAM_BUF_WORDS];
+        uint32_t sh = 0;
+        if (n <= ENTRY_INLINE) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (uint32_t k = 0; k < STREAM_BUF_WORDS; k++) buf[k] = k < ENTRY_INLINE / 4 ? e[2 + k] : 0u;
+        } else {
+            const uint32_t a = e[0] & ~3u, nwords = ((e[0] & 3u) + n + 3) >> 2;
+            sh = e[0] & 3u;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (uint32_t k = 0; k < STREAM_BUF_WORDS; k++) buf[k] = k < nwords ? arena.ld32a(a + 4 * k) : 0u;
+        }
+        const PtrSrc local{reinterpret_cast<const uint8_t*>(buf)};
+        if (!(flags & ENTRY_DECODE)) for (uint32_t k = 0; k < n; k++) walk_byte<true>(d, c, w, local.ld8(sh + k));
+        else for_each_decoded_byte(local, sh, sh + n, [&](uint32_t b) { walk_byte<true>(d, c, w, b); });
     } else {
-        uint32_t end = e0 + n;
-        if (flags & ENTRY_HUGE) end = scan_string(arena, e0 - 1, 0xFFFFFFFFu) - 1;     // valid literal: the closing quote exists
-        for_each_decoded_byte(arena, e0, end, [&](uint32_t b) { walk_byte<true>(d, c, w, b); });
+        uint32_t end = e[0] + n;
+        if (flags & ENTRY_HUGE) end = scan_string(arena, e[0] - 1, 0xFFFFFFFFu) - 1;     // valid literal: the closing quote exists
+        for_each_decoded_byte(arena, e[0], end, [&](uint32_t b) { walk_byte<true>(d, c, w, b); });
     }
     if (eot) walk_eot<true>(d, c, w);
     InspectResult r;
-    r.state = eot ? d.start0 : w.st;                   // a finished conversation frees its slot in the start state
+    r.state = eot ? c.start0 : w.st;                   // a finished conversation frees its slot in the start state
     r.verdict = 0; r.begin = 0; r.end = 0;
     if (w.win < 32) {
         r.verdict = t.action[w.win] | (w.win << 8);

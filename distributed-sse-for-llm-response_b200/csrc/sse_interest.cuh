@@ -135,56 +135,75 @@ SSE_HD_NOINLINE InterestHit interest_lookup(const InterestDev& t, const Src& s, 
 }
 
 // Fast lane: the id's decoded text IS its raw bytes (canonical record, no backslash escape in the id), it fits a
-// slot, it has no dot (one NATS token) and no wildcard needs the general matcher.  One pass over the id's words
-// (aligned loads from the tile + a funnel shift each) yields the dot test, the hash and the words kept in registers
-// for the compare; a probe is one 64-byte slot.  Returns false when the general routine must take over.
+// slot, it has no dot (one NATS token) and no wildcard needs the general matcher.  Two steps so that the table's
+// latency hides behind the rest of the parse:
+//   interest_prepare  (called from parse_fast's hook as soon as the id has been scanned) one pass over the id's
+//                     words -- aligned loads from the tile + a funnel shift each -- yields the dot test and the hash,
+//                     and the first 16 bytes (tag, length, value) of the first probed slot are requested;
+//   interest_finish   (after the parse) tag and length decide; on a match the slot's key words (same 64-byte slot)
+//                     are compared with the id's words, read again from the tile.
+// The descriptor fields the fast lane needs are held in registers (InterestFast), not re-read from the descriptor.
+struct InterestFast { const InterestSlot* slots; uint32_t mask, wild_single, wild_generic; };
+SSE_HD InterestFast make_interest_fast(const InterestDev& t) { return InterestFast{t.slots, t.mask, t.wild_single, t.wild_generic}; }
+struct InterestPre { uint32_t ready, hash, q0, q1, q2, q3; };     // ready 0: the general routine must take over
+
+SSE_HD void slot_head(const InterestSlot* e, uint32_t& q0, uint32_t& q1, uint32_t& q2, uint32_t& q3) {
+#if defined(__CUDA_ARCH__)
+    const uint4 q = *reinterpret_cast<const uint4*>(e);
+    q0 = q.x; q1 = q.y; q2 = q.z; q3 = q.w;
+    // the slot's second 32-byte sector (key words 4..11) is pulled next to the SM now: the compare then hits L1
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const uint8_t*>(e) + 32));
+#else
+    q0 = e->hash; q1 = e->key_len; q2 = e->list_off; q3 = e->list_cnt;
+#endif
+}
+
 template <class Src>
-SSE_HD bool interest_lookup_raw(const InterestDev& t, const Src& s, uint32_t cid_b, uint32_t cid_e, InterestHit& h) {
+SSE_HD void interest_prepare(const InterestFast& t, const Src& s, uint32_t cid_b, uint32_t cid_e, bool plain, InterestPre& pre) {
     const uint32_t len = cid_e - cid_b;
-    if (len == 0 || len > INTEREST_INLINE_KEY || t.wild_generic) return false;
-    constexpr uint32_t NW = INTEREST_INLINE_KEY / 4;
-    uint32_t kw[NW];
+    pre.ready = 0; pre.hash = 0; pre.q0 = pre.q1 = pre.q2 = pre.q3 = 0;
+    if (!plain || len == 0 || len > INTEREST_INLINE_KEY || t.wild_generic) return;
     const uint32_t a = cid_b & ~3u, shb = (cid_b & 3u) * 8, nw = (len + 3) >> 2;
     uint32_t lo = s.ld32a(a), dots = 0, hash = key_hash_init(len);
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-    for (uint32_t k = 0; k < NW; k++) {
-        uint32_t w = 0;
-        if (k < nw) {
-            const uint32_t hi = s.ld32a(a + 4 * k + 4);
-            w = funnel_r(lo, hi, shb);
-            lo = hi;
-            const uint32_t rem = len - 4 * k;
-            if (rem < 4) w &= 0xFFFFFFFFu >> (8 * (4 - rem));
-            const uint32_t x = w ^ 0x2E2E2E2Eu;                      // a '.' byte becomes zero (the zero padding does not)
-            dots |= (x - 0x01010101u) & ~x & 0x80808080u;
-            hash = key_hash_step(hash, w);
-        }
-        kw[k] = w;
+    for (uint32_t k = 0; k < nw; k++) {
+        const uint32_t hi = s.ld32a(a + 4 * k + 4);
+        uint32_t w = funnel_r(lo, hi, shb);
+        lo = hi;
+        if (k + 1 == nw) w &= 0xFFFFFFFFu >> (8 * (4 * nw - len));   // zero padding of the last word
+        const uint32_t x = w ^ 0x2E2E2E2Eu;                          // a '.' byte becomes zero (the zero padding does not)
+        dots |= (x - 0x01010101u) & ~x & 0x80808080u;
+        hash = key_hash_step(hash, w);
     }
-    if (dots) return false;
-    hash = key_hash_fin(hash);
+    if (dots) return;
+    pre.ready = 1;
+    pre.hash = key_hash_fin(hash);
+    if (t.slots) slot_head(t.slots + (pre.hash & t.mask), pre.q0, pre.q1, pre.q2, pre.q3);
+}
+
+template <class Src>
+SSE_HD void interest_finish(const InterestFast& t, const Src& s, uint32_t cid_b, uint32_t cid_e, const InterestPre& pre, InterestHit& h) {
+    const uint32_t len = cid_e - cid_b, nw = (len + 3) >> 2;
     h.list_off = 0; h.list_cnt = 0; h.wild_mask = t.wild_single;
-    if (!t.slots) return true;
-    for (uint32_t p = hash & t.mask;; p = (p + 1) & t.mask) {
-        const uint32_t* e = reinterpret_cast<const uint32_t*>(t.slots + p);
-#if defined(__CUDA_ARCH__)
-        const uint4 q0 = *reinterpret_cast<const uint4*>(e), q1 = *reinterpret_cast<const uint4*>(e + 4),
-                    q2 = *reinterpret_cast<const uint4*>(e + 8), q3 = *reinterpret_cast<const uint4*>(e + 12);
-        const uint32_t sw[16] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, q3.x, q3.y, q3.z, q3.w};
-#else
-        const uint32_t* sw = e;
-#endif
-        if (sw[0] == 0) return true;                                 // empty slot: nobody subscribed to this id
-        if (sw[0] == hash && sw[1] == len) {
-            uint32_t diff = 0;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-            for (uint32_t k = 0; k < NW; k++) diff |= sw[4 + k] ^ kw[k];
-            if (diff == 0) { h.list_off = sw[2]; h.list_cnt = sw[3]; return true; }
+    if (!t.slots) return;
+    uint32_t q0 = pre.q0, q1 = pre.q1, q2 = pre.q2, q3 = pre.q3;
+    for (uint32_t p = pre.hash & t.mask;;) {
+        if (q0 == 0) return;                                         // empty slot: nobody subscribed to this id
+        if (q0 == pre.hash && q1 == len) {
+            // the key words sit in the slot itself (second sector prefetched by slot_head): word-wise against the id in the tile
+            const uint32_t* key = t.slots[p].key;
+            const uint32_t a = cid_b & ~3u, shb = (cid_b & 3u) * 8;
+            uint32_t lo = s.ld32a(a), diff = 0, k = 0;
+            for (; k + 1 < nw; k++) {
+                const uint32_t hi = s.ld32a(a + 4 * k + 4);
+                diff |= funnel_r(lo, hi, shb) ^ key[k];
+                lo = hi;
+            }
+            const uint32_t rem = len - 4 * k;                        // 1..4 bytes in the last word
+            diff |= (funnel_r(lo, s.ld32a(a + 4 * k + 4), shb) & (0xFFFFFFFFu >> (8 * (4 - rem)))) ^ key[k];
+            if (diff == 0) { h.list_off = q2; h.list_cnt = q3; return; }
         }
+        p = (p + 1) & t.mask;
+        slot_head(t.slots + p, q0, q1, q2, q3);
     }
 }
 

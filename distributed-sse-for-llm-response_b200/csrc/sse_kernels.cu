@@ -189,9 +189,10 @@ __device__ __forceinline__ void store_token_entry(const FrameArgs& a, uint32_t i
                                                   uint32_t st, bool raw_text) {
     PtrSrc src{sb};
     const uint32_t flags = ((st & ST_CODE_MASK) == ST_OK ? ENTRY_OK : 0u) | (raw_text ? 0u : ENTRY_DECODE) | ((st & ST_DONE) ? ENTRY_DONE : 0u);
-    uint32_t e[4];
+    uint32_t e[ENTRY_WORDS];
     make_token_entry(src, o + pl.tok_b, pl.tok_e - pl.tok_b, abs_b + pl.tok_b, flags, e);
-    a.tok_entry[i] = make_uint4(e[0], e[1], e[2], e[3]);
+    a.tok_entry[2 * (size_t)i] = make_uint4(e[0], e[1], e[2], e[3]);
+    a.tok_entry[2 * (size_t)i + 1] = make_uint4(e[4], e[5], e[6], e[7]);
 }
 // The optional stages for one record that went through the GENERAL decoder (out of line: inline in a few places,
 // densely in the tail phase).  In: the record's plan, status and length.  Out: verdict/match/hit/entry stored, status
@@ -269,7 +270,8 @@ __device__ __forceinline__ void copy_out(uint8_t* __restrict__ out, const uint8_
 
 // EXT is a compile-time switch so that the plain framing kernel carries none of the registers of the optional
 // stages (per-token content inspection, interest lookup, token entries for the streaming walk).
-template <bool EXT, int MODE>
+constexpr int X_INSPECT = 1, X_INTEREST = 2;    // compile-time set of optional stages (each variant pays only for its own registers)
+template <int EXT, int MODE>
 __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_constant__ FrameArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* s_in = smem;                                   // in_cap + 32 (word reads run up to 24 bytes past a record)
@@ -283,9 +285,9 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
     uint32_t my_chain = 0;                                  // tid 0: last tile (+1) of this CTA that left records to the tail phase
 
     // EXT, fused per-token inspection: on-chip copy of the forward DFA's byte-class map, end-of-text bitmap and hottest rows
-    const bool pre_verdict = EXT && (a.xflags & XF_PRE_VERDICT) != 0;          // launch-uniform
-    const bool inspect_fused = EXT && a.insp != nullptr && !pre_verdict;
-    DfaCache dcache{nullptr, nullptr, 0, nullptr};
+    const bool pre_verdict = (EXT & X_INSPECT) && (a.xflags & XF_PRE_VERDICT) != 0;          // launch-uniform
+    const bool inspect_fused = (EXT & X_INSPECT) && a.insp != nullptr && !pre_verdict;
+    DfaCache dcache{nullptr, nullptr, 0, nullptr, nullptr, 0, 0, 0, 0};
     if (inspect_fused) {
         uint8_t* s_cls = reinterpret_cast<uint8_t*>(ts + 1);
         uint32_t* s_eot = reinterpret_cast<uint32_t*>(s_cls + 256);
@@ -300,8 +302,10 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
                 for (uint32_t k = 0; k < 32 && 32 * w + k < d.n_states; k++) bits |= (d.acc_eot[32 * w + k] != 0 ? 1u : 0u) << k;
                 s_eot[w] = bits;
             }
-        dcache.cls = s_cls; dcache.rows = s_rows; dcache.n_cached = nc; dcache.eot_bits = s_eot;
+        dcache = make_dfa_cache(*a.insp, s_cls, s_rows, nc, s_eot);
     }
+    InterestFast ifast{nullptr, 0, 0, 0};
+    if (EXT & X_INTEREST) ifast = make_interest_fast(*a.interest);
     if (tid == 0) {
         mbar_init(&ts->mbar, 1);
         ts->in_total = a.in_off[a.n];
@@ -368,7 +372,14 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
                 fastp = true; planned = true;
             }
         }
-        if (active && smem_in && !planned) { PtrSrc src{s_in}; fastp = plan_record_fast(src, o, L, a.op, my_start, pl, st, len); }
+        InterestPre ipre{0, 0, 0, 0, 0, 0};
+        if (active && smem_in && !planned) {
+            PtrSrc src{s_in};
+            if (EXT & X_INTEREST)                  // the id is hashed and its first table probe requested inside the parse
+                fastp = plan_record_fast(src, o, L, a.op, my_start, pl, st, len,
+                                         [&](const PtrSrc& ss, uint32_t b, uint32_t e, bool plain) { interest_prepare(ifast, ss, b, e, plain, ipre); });
+            else fastp = plan_record_fast(src, o, L, a.op, my_start, pl, st, len);
+        }
         // A few such records in a warp: deferred (the tail phase runs them densely).  Many of
         // them: decoded here, where the tile is in shared memory (22 ns per warp however many of its lanes take part).
         const bool slow = active && !fastp;
@@ -397,7 +408,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
         if (EXT) {
             const bool canon = active && fastp;
             // content inspection of the decoded token text, per_token mode (sse_handler.go:193-208)
-            if (a.insp != nullptr || pre_verdict) {                           // launch-uniform
+            if ((EXT & X_INSPECT) && (a.insp != nullptr || pre_verdict)) {    // launch-uniform
                 InspectResult io{0, 0, 0, 0};
                 if (canon && (st & ST_CODE_MASK) == ST_OK) {
                     if (pre_verdict) io.verdict = a.verdict[r0 + tid];
@@ -427,15 +438,14 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
                 }
             }
             // token entry for the streaming walk
-            if (a.tok_entry != nullptr && canon && (MODE != MODE_ORDERED_COUNT || (a.xflags & XF_ENTRY_IN_COUNT)))
+            if ((EXT & X_INSPECT) && a.tok_entry != nullptr && canon && (MODE != MODE_ORDERED_COUNT || (a.xflags & XF_ENTRY_IN_COUNT)))
                 store_token_entry(a, r0 + tid, s_in, o, my_b, pl, st, !pl.tok_esc);
             // subject -> subscriber/interest table
-            if (a.interest != nullptr) {                                      // launch-uniform
+            if (EXT & X_INTEREST) {
                 InterestHit h{0, 0, 0};
                 if (canon && (st & ST_CODE_MASK) == ST_OK) {
-                    bool done_fast = false;
-                    if (!pl.cid_esc) { PtrSrc src{s_in}; done_fast = interest_lookup_raw(*a.interest, src, o + pl.cid_b, o + pl.cid_e, h); }
-                    if (!done_fast) h = interest_slow(a, s_in, o, pl.cid_b, pl.cid_e);
+                    if (ipre.ready) { PtrSrc src{s_in}; interest_finish(ifast, src, o + pl.cid_b, o + pl.cid_e, ipre, h); }
+                    else h = interest_slow(a, s_in, o, pl.cid_b, pl.cid_e);
                     if (h.list_cnt == 0 && h.wild_mask == 0) { st = ST_NO_INTEREST; len = 0; }   // nobody subscribed: nothing to frame
                 }
                 if (active && !slow && MODE != MODE_ORDERED_COUNT) {
@@ -651,9 +661,9 @@ static void cfg_caps(int cfg, uint32_t* ic, uint32_t* oc, uint32_t* smem) {
 
 static std::mutex g_cfg_mu;             // the cache below is filled once per device, from whichever thread launches first
 static int g_num_sms[64];
-static int g_ctas_per_sm[64][2][N_CFG]; // [device][ext][cfg]; 0 = device not configured yet
+static int g_ctas_per_sm[64][4][N_CFG]; // [device][ext][cfg]; 0 = device not configured yet
 
-template <bool EXT, int MODE>
+template <int EXT, int MODE>
 static cudaError_t configure_one(int* per_sm /* [N_CFG] */) {
     uint32_t ic, oc, sm, sm_max = 0;
     for (int c = 0; c < N_CFG; c++) { cfg_caps(c, &ic, &oc, &sm); sm_max = sm > sm_max ? sm : sm_max; }
@@ -676,33 +686,39 @@ cudaError_t frame_configure(int device) {
     int sms = 0;
     cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     if (e != cudaSuccess) return e;
-    int plain[N_CFG] = {0}, ext[N_CFG] = {0};
-    if ((e = configure_one<false, MODE_ARRIVAL>(plain)) != cudaSuccess) return e;
-    if ((e = configure_one<false, MODE_ORDERED_COUNT>(plain)) != cudaSuccess) return e;
-    if ((e = configure_one<false, MODE_ORDERED_EMIT>(plain)) != cudaSuccess) return e;
-    if ((e = configure_one<true, MODE_ARRIVAL>(ext)) != cudaSuccess) return e;
-    if ((e = configure_one<true, MODE_ORDERED_COUNT>(ext)) != cudaSuccess) return e;
-    if ((e = configure_one<true, MODE_ORDERED_EMIT>(ext)) != cudaSuccess) return e;
+    int per[4][N_CFG] = {};
+    if ((e = configure_one<0, MODE_ARRIVAL>(per[0])) != cudaSuccess) return e;
+    if ((e = configure_one<0, MODE_ORDERED_COUNT>(per[0])) != cudaSuccess) return e;
+    if ((e = configure_one<0, MODE_ORDERED_EMIT>(per[0])) != cudaSuccess) return e;
+    if ((e = configure_one<1, MODE_ARRIVAL>(per[1])) != cudaSuccess) return e;
+    if ((e = configure_one<1, MODE_ORDERED_COUNT>(per[1])) != cudaSuccess) return e;
+    if ((e = configure_one<1, MODE_ORDERED_EMIT>(per[1])) != cudaSuccess) return e;
+    if ((e = configure_one<2, MODE_ARRIVAL>(per[2])) != cudaSuccess) return e;
+    if ((e = configure_one<2, MODE_ORDERED_COUNT>(per[2])) != cudaSuccess) return e;
+    if ((e = configure_one<2, MODE_ORDERED_EMIT>(per[2])) != cudaSuccess) return e;
+    if ((e = configure_one<3, MODE_ARRIVAL>(per[3])) != cudaSuccess) return e;
+    if ((e = configure_one<3, MODE_ORDERED_COUNT>(per[3])) != cudaSuccess) return e;
+    if ((e = configure_one<3, MODE_ORDERED_EMIT>(per[3])) != cudaSuccess) return e;
     g_num_sms[device] = sms;
-    for (int c = N_CFG - 1; c >= 0; c--) { g_ctas_per_sm[device][1][c] = ext[c]; g_ctas_per_sm[device][0][c] = plain[c]; }
+    for (int x = 3; x >= 0; x--) for (int c = N_CFG - 1; c >= 0; c--) g_ctas_per_sm[device][x][c] = per[x][c];
     return cudaSuccess;
 }
 
-static cudaError_t choose_variant(int device, FrameArgs& a, bool* ext, uint32_t* smem_bytes, int* grid) {
+static cudaError_t choose_variant(int device, FrameArgs& a, int* ext, uint32_t* smem_bytes, int* grid) {
     cudaError_t e = frame_configure(device);
     if (e != cudaSuccess) return e;
-    *ext = a.insp != nullptr || a.interest != nullptr || a.tok_entry != nullptr || (a.xflags & XF_PRE_VERDICT);
+    *ext = ((a.insp != nullptr || a.tok_entry != nullptr || (a.xflags & XF_PRE_VERDICT)) ? X_INSPECT : 0) | (a.interest != nullptr ? X_INTEREST : 0);
     const bool cache = a.insp != nullptr && !(a.xflags & XF_PRE_VERDICT);
     const bool wide = (a.op & OP_NATS_PUB) != 0, bridge = (a.op & OP_BRIDGE) != 0;
     const int cfg = cache ? (wide ? 4 : (bridge ? 3 : 2)) : (wide ? 1 : 0);
     cfg_caps(cfg, &a.in_cap, &a.out_cap_s, smem_bytes);
-    *grid = g_num_sms[device] * g_ctas_per_sm[device][*ext ? 1 : 0][cfg];
+    *grid = g_num_sms[device] * g_ctas_per_sm[device][*ext][cfg];
     a.num_tiles = (a.n + TILE - 1) / TILE;
     if ((int)a.num_tiles < *grid) *grid = (int)a.num_tiles;
     return cudaSuccess;
 }
 
-template <bool EXT>
+template <int EXT>
 static void launch_variant(const FrameArgs& a, int grid, uint32_t smem_bytes, cudaStream_t stream) {
     if (a.op & OP_ORDERED) {
         k_frame_tiles<EXT, MODE_ORDERED_COUNT><<<grid, TILE, smem_bytes, stream>>>(a);
@@ -726,26 +742,30 @@ static cudaError_t clear_scratch(const FrameArgs& a, cudaStream_t stream) {
 cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     uint32_t smem_bytes;
     int grid;
-    bool ext;
+    int ext;
     cudaError_t e = choose_variant(device, a, &ext, &smem_bytes, &grid);
     if (e != cudaSuccess) return e;
     if ((e = clear_scratch(a, stream)) != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
-    if (ext) launch_variant<true>(a, grid, smem_bytes, stream);
-    else launch_variant<false>(a, grid, smem_bytes, stream);
+    switch (ext) {
+    case 0: launch_variant<0>(a, grid, smem_bytes, stream); break;
+    case 1: launch_variant<1>(a, grid, smem_bytes, stream); break;
+    case 2: launch_variant<2>(a, grid, smem_bytes, stream); break;
+    default: launch_variant<3>(a, grid, smem_bytes, stream); break;
+    }
     return cudaGetLastError();
 }
 
 cudaError_t frame_plan_launch(int device, FrameArgs a, cudaStream_t stream) {
     uint32_t smem_bytes;
     int grid;
-    bool ext;
+    int ext;
     a.xflags |= XF_ENTRY_IN_COUNT;
     cudaError_t e = choose_variant(device, a, &ext, &smem_bytes, &grid);
     if (e != cudaSuccess) return e;
     if ((e = clear_scratch(a, stream)) != cudaSuccess) return e;
     if (a.n == 0) return cudaSuccess;
-    k_frame_tiles<true, MODE_ORDERED_COUNT><<<grid, TILE, smem_bytes, stream>>>(a);
+    k_frame_tiles<X_INSPECT, MODE_ORDERED_COUNT><<<grid, TILE, smem_bytes, stream>>>(a);
     return cudaGetLastError();
 }
 

@@ -32,11 +32,11 @@ struct FrameArgs {
     uint32_t* subj_len;          // n or nullptr
     uint32_t* status;            // n
     // content inspection.  per_token mode is fused into the frame kernel (insp != nullptr).  streaming mode is a
-    // per-conversation walk in its own kernels (sse_stream.cu): the frame kernel then only leaves a 16-byte token
+    // per-conversation walk in its own kernels (sse_stream.cu): the frame kernel then only leaves a 32-byte token
     // entry per record (tok_entry != nullptr) and, for inline verdicts, a second frame pass reads the walk's
     // verdicts back (XF_PRE_VERDICT) instead of inspecting.
     const InspectDev* insp;
-    uint4* tok_entry;            // n or nullptr
+    uint4* tok_entry;            // 2n (one 32-byte entry per record) or nullptr
     uint32_t xflags;
     uint32_t* verdict;           // n
     int32_t* match;              // 2n: begin, end (byte offsets into the decoded token text)
@@ -119,7 +119,7 @@ cudaError_t frame_plan_launch(int device, FrameArgs a, cudaStream_t stream);
 struct StreamArgs {
     const InspectDev* insp;      // device descriptor
     const uint8_t* in;           // payload arena (tokens longer than 8 bytes or with escapes are read from it)
-    const uint4* tok_entry;      // n, written by the frame kernel
+    const uint4* tok_entry;      // 2n, written by the frame kernel
     const uint32_t* conv_slot;   // n
     uint32_t n, conv_slots;
     uint32_t* conv_state;        // [conv_slots] carried DFA state

@@ -596,8 +596,13 @@ template <class Src> SSE_HD void ld3u(const Src& s, uint32_t pos, uint32_t& w0, 
     w0 = funnel_r(x0, x1, shb); w1 = funnel_r(x1, x2, shb); w2 = funnel_r(x2, x3, shb);
 }
 
+// Hook called by parse_fast right after the conversation id has been scanned (absolute range [b, e) in s; `plain`: the
+// record is canonical so far and the id has no escape).  The interest lookup uses it to hash the id and put its first
+// table probe in flight while the rest of the record is still being parsed.
+struct NoHook { template <class Src> SSE_HD void operator()(const Src&, uint32_t, uint32_t, bool) const {} };
+
 // True iff the record is byte-for-byte what json.Marshal(TokenMessage) would emit.
-template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, Plan& pl) {
+template <class Src, class Hook> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, Plan& pl, Hook&& after_cid) {
     const bool go122 = (op & OP_GO122) != 0;
     bool ok = L >= 72;
     const uint32_t end = o + (ok ? L : 0u);                     // a too-short record runs through with an empty range
@@ -615,6 +620,7 @@ template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L
     pl.cid_b = 20;
     ok = scan_canon_string(s, pos, end, go122, cid_esc) && ok;
     pl.cid_e = pos - o;
+    after_cid(s, o + 20, pos, ok && !cid_esc);
     // ","token":"   (11 bytes)
     ld3u(s, pos, w0, w1, w2);
     d = (w0 ^ w4("\",\"t")) | (w1 ^ w4("oken")) | ((w2 ^ w4("\":\"\0")) & 0xFFFFFFu);
@@ -652,6 +658,8 @@ template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L
     pl.tok_esc = tok_esc ? 1u : 0u;
     return ok;
 }
+
+template <class Src> SSE_HD bool parse_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, Plan& pl) { return parse_fast(s, o, L, op, pl, NoHook()); }
 
 // --------------------------------------------------------------- general path ----
 SSE_HD bool is_ws(uint32_t c) { return c == ' ' || c == '\t' || c == '\r' || c == '\n'; }
@@ -860,11 +868,11 @@ SSE_HD bool fast_emit_ok(const Plan& pl, uint32_t op) {
 }
 
 // Pass 1, canonical records only.  false = not canonical (or fast path disabled): call plan_record().
-template <class Src>
+template <class Src, class Hook>
 SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, int64_t start_seq,
-                             Plan& pl, uint32_t& st, uint32_t& out_len) {
+                             Plan& pl, uint32_t& st, uint32_t& out_len, Hook&& after_cid) {
     pl.fast = 0;
-    if ((op & OP_NO_FAST) || !parse_fast(s, o, L, op, pl)) return false;
+    if ((op & OP_NO_FAST) || !parse_fast(s, o, L, op, pl, after_cid)) return false;
     if (!fast_emit_ok(pl, op)) return false;
     out_len = 0;
     if (!(op & OP_BRIDGE) && start_seq > 0 && pl.seq <= start_seq) { st = ST_FILTERED; return true; }   // sse_handler.go:143
@@ -872,6 +880,12 @@ SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, 
     if ((op & (OP_BRIDGE | OP_NATS_PUB)) == (OP_BRIDGE | OP_NATS_PUB)) out_len += 9 + dec_digits(L);   // "PUB " + " " + digits + CRLF, CRLF
     st = pl.done ? (ST_OK | ST_DONE) : ST_OK;
     return true;
+}
+
+template <class Src>
+SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, int64_t start_seq,
+                             Plan& pl, uint32_t& st, uint32_t& out_len) {
+    return plan_record_fast(s, o, L, op, start_seq, pl, st, out_len, NoHook());
 }
 
 // Pass 2 for records accepted by plan_record_fast(): header + verbatim payload (+ trailer).

@@ -6,14 +6,14 @@
 // size or time may hold any number of tokens of one conversation (bursts, catch-up after a reconnect), so the carried
 // DFA state makes the tokens of a conversation a sequential chain while different conversations stay independent.
 //
-// Pipeline (all on the caller's stream, after the frame kernel has left one 16-byte token entry per record):
-//   1. stable LSD radix sort of the record numbers by conversation slot (1-3 passes of <= 11 bits: per-tile digit
+// Pipeline (all on the caller's stream, after the frame kernel has left one 32-byte token entry per record):
+//   1. stable LSD radix sort of the record numbers by conversation slot (1-4 passes of <= 10 bits: per-tile digit
 //      histogram, exclusive scan, stable scatter with per-warp running offsets and match.any ranking) -- after it every
 //      conversation's records are contiguous and in arrival order;
 //   2. segment heads are compacted into a list;
 //   3. one lane per conversation walks its segment: carried state in a register, forward DFA in shared memory (the
-//      whole table when it fits), token bytes from the entry itself (<= 8 raw bytes, 90 % of the BASELINE tokens) or
-//      from the payload arena; only hits are written (verdict/match are cleared first); the state is committed once.
+//      whole table when it fits), token bytes from the entry itself (<= 24 raw bytes: every BASELINE token) or from
+//      the payload arena; the next record's entry is requested before the current one is walked; only hits are written (verdict/match are cleared first); the state is committed once.
 // No atomics on the conversation state, no limit on how often a conversation occurs in a batch.
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -27,8 +27,8 @@ namespace sse {
 namespace {
 
 constexpr int SORT_WARPS = 8, SORT_THREADS = SORT_WARPS * 32;
-constexpr uint32_t SORT_PER_WARP = 1024, SORT_TILE = SORT_WARPS * SORT_PER_WARP;     // keys per CTA
-constexpr uint32_t MAX_DIGIT_BITS = 11;
+constexpr uint32_t SORT_PER_WARP = 512, SORT_TILE = SORT_WARPS * SORT_PER_WARP;      // keys per CTA
+constexpr uint32_t MAX_DIGIT_BITS = 10;
 constexpr uint32_t SCAN_BLOCK = 4096;                                                // elements per scan CTA (1024 threads x 4)
 constexpr uint32_t WALK_THREADS = 256;
 constexpr uint32_t WALK_TABLE_MAX = 96 * 1024;                                       // bytes of transition rows kept on chip by the walk
@@ -45,7 +45,9 @@ SortPlan sort_plan(uint32_t conv_slots) {
 }
 
 // ---- 1a. per-tile digit histogram: hist[digit * num_tiles + tile] ----
-__global__ void __launch_bounds__(SORT_THREADS) k_radix_hist(const uint32_t* __restrict__ keys, uint32_t n, uint32_t shift, uint32_t digit_bits,
+// Keys come from the caller's conv_slot array in the first pass (record number = position) and from the previous
+// pass's (key, record number) pairs afterwards: `stride` is 1 or 2 words.
+__global__ void __launch_bounds__(SORT_THREADS) k_radix_hist(const uint32_t* __restrict__ keys, uint32_t stride, uint32_t n, uint32_t shift, uint32_t digit_bits,
                                                             uint32_t* __restrict__ hist, uint32_t num_tiles, uint32_t conv_slots,
                                                             uint32_t* bad_conv) {
     extern __shared__ uint32_t s_hist[];
@@ -55,7 +57,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_radix_hist(const uint32_t* __r
     const uint32_t lo = blockIdx.x * SORT_TILE, hi = min(n, lo + SORT_TILE);
     bool bad = false;
     for (uint32_t i = lo + threadIdx.x; i < hi; i += SORT_THREADS) {
-        const uint32_t k = keys[i];
+        const uint32_t k = keys[(size_t)i * stride];
         bad |= k >= conv_slots;
         atomicAdd(&s_hist[(k >> shift) & mask], 1u);
     }
@@ -123,9 +125,10 @@ __global__ void __launch_bounds__(1024) k_scan_apply(uint32_t* __restrict__ data
 }
 
 // ---- 1c. stable scatter: every warp owns SORT_PER_WARP consecutive keys and its own running offsets ----
-__global__ void __launch_bounds__(SORT_THREADS) k_radix_scatter(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ idx_in, uint32_t n,
+// Output: (key, record number) pairs, one 8-byte store each (the scattered stores are what bounds this kernel).
+__global__ void __launch_bounds__(SORT_THREADS) k_radix_scatter(const uint32_t* __restrict__ keys, const uint2* __restrict__ pairs_in, uint32_t n,
                                                                uint32_t shift, uint32_t digit_bits, const uint32_t* __restrict__ hist,
-                                                               uint32_t num_tiles, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out) {
+                                                               uint32_t num_tiles, uint2* __restrict__ pairs_out) {
     extern __shared__ uint32_t s_off[];                      // [SORT_WARPS][radix]
     const uint32_t radix = 1u << digit_bits, mask = radix - 1;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -133,7 +136,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_radix_scatter(const uint32_t* 
     __syncthreads();
     uint32_t* mine = s_off + warp * radix;
     const uint32_t w_lo = blockIdx.x * SORT_TILE + warp * SORT_PER_WARP, w_hi = min(n, w_lo + SORT_PER_WARP);
-    for (uint32_t i = w_lo + lane; i < w_hi; i += 32) atomicAdd(&mine[(keys[i] >> shift) & mask], 1u);
+    for (uint32_t i = w_lo + lane; i < w_hi; i += 32) atomicAdd(&mine[((pairs_in ? pairs_in[i].x : keys[i]) >> shift) & mask], 1u);
     __syncthreads();
     for (uint32_t d = threadIdx.x; d < radix; d += SORT_THREADS) {   // counts -> first output position of (warp, digit)
         uint32_t run = hist[(size_t)d * num_tiles + blockIdx.x];
@@ -144,8 +147,9 @@ __global__ void __launch_bounds__(SORT_THREADS) k_radix_scatter(const uint32_t* 
     for (uint32_t i0 = w_lo; i0 < w_hi; i0 += 32) {
         const uint32_t i = i0 + lane;
         const bool valid = i < w_hi;
-        const uint32_t k = valid ? keys[i] : 0;
-        const uint32_t d = valid ? ((k >> shift) & mask) : 0xFFFFFFFFu;
+        uint2 kv = make_uint2(0u, i);
+        if (valid) { if (pairs_in) kv = pairs_in[i]; else kv.x = keys[i]; }
+        const uint32_t d = valid ? ((kv.x >> shift) & mask) : 0xFFFFFFFFu;
         const uint32_t peers = __match_any_sync(0xFFFFFFFFu, d);
         const uint32_t rank = __popc(peers & ((1u << lane) - 1));
         uint32_t pos = 0;
@@ -153,23 +157,34 @@ __global__ void __launch_bounds__(SORT_THREADS) k_radix_scatter(const uint32_t* 
         __syncwarp();
         if (valid && rank == 0) mine[d] += __popc(peers);
         __syncwarp();
-        if (valid) { keys_out[pos] = k; idx_out[pos] = idx_in ? idx_in[i] : i; }
+        if (valid) pairs_out[pos] = kv;
     }
 }
 
 // ---- 2. segment heads ----
-__global__ void __launch_bounds__(256) k_segment_heads(const uint32_t* __restrict__ keys, uint32_t n, uint32_t* __restrict__ heads, uint32_t* n_heads) {
-    const uint32_t i = blockIdx.x * 256 + threadIdx.x, lane = threadIdx.x & 31;
-    const bool head = i < n && (i == 0 || keys[i] != keys[i - 1]);
+__global__ void __launch_bounds__(1024) k_segment_heads(const uint2* __restrict__ pairs, uint32_t n, uint32_t* __restrict__ heads, uint32_t* n_heads) {
+    __shared__ uint32_t s_cnt[33];
+    const uint32_t i = blockIdx.x * 1024 + threadIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool head = i < n && (i == 0 || pairs[i].x != pairs[i - 1].x);
     const uint32_t m = __ballot_sync(0xFFFFFFFFu, head);
-    uint32_t base = 0;
-    if (lane == 0 && m) base = atomicAdd(n_heads, (uint32_t)__popc(m));
-    base = __shfl_sync(0xFFFFFFFFu, base, 0);
-    if (head) heads[base + __popc(m & ((1u << lane) - 1))] = i;
+    if (lane == 0) s_cnt[warp] = (uint32_t)__popc(m);
+    __syncthreads();
+    if (warp == 0) {                                  // one atomic per CTA: the list keeps runs of 1024 positions in order
+        const uint32_t c = s_cnt[lane];
+        uint32_t incl = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= (uint32_t)d) incl += t; }
+        uint32_t base = 0;
+        if (lane == 31 && incl) base = atomicAdd(n_heads, incl);
+        base = __shfl_sync(0xFFFFFFFFu, base, 31);
+        s_cnt[lane] = base + incl - c;
+    }
+    __syncthreads();
+    if (head) heads[s_cnt[warp] + __popc(m & ((1u << lane) - 1))] = i;
 }
 
 // ---- 3. the walk: one lane per conversation ----
-__global__ void __launch_bounds__(WALK_THREADS) k_stream_walk(const StreamArgs a, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ idxs,
+__global__ void __launch_bounds__(WALK_THREADS) k_stream_walk(const StreamArgs a, const uint2* __restrict__ pairs,
                                                              const uint32_t* __restrict__ heads, const uint32_t* __restrict__ n_heads,
                                                              uint32_t n_cached) {
     extern __shared__ __align__(16) uint8_t s_tab[];
@@ -177,34 +192,48 @@ __global__ void __launch_bounds__(WALK_THREADS) k_stream_walk(const StreamArgs a
     uint32_t* s_eot = reinterpret_cast<uint32_t*>(s_cls + 256);
     uint16_t* s_rows = reinterpret_cast<uint16_t*>(s_eot + DFA_EOT_WORDS);
     const InspectDev& t = *a.insp;
-    const DfaDev& d = t.fwd;
-    for (uint32_t i = threadIdx.x; i < 256; i += WALK_THREADS) s_cls[i] = d.cls[i];
-    for (uint32_t i = threadIdx.x; i < n_cached * d.n_classes; i += WALK_THREADS) s_rows[i] = d.next[i];
-    if (d.n_states <= 32 * DFA_EOT_WORDS)
-        for (uint32_t w = threadIdx.x; w < DFA_EOT_WORDS; w += WALK_THREADS) {
-            uint32_t bits = 0;
-            for (uint32_t k = 0; k < 32 && 32 * w + k < d.n_states; k++) bits |= (d.acc_eot[32 * w + k] != 0 ? 1u : 0u) << k;
-            s_eot[w] = bits;
-        }
+    {   // table -> shared memory (descriptor fields first into registers: the descriptor itself lives in global memory)
+        const uint32_t* g_cls = reinterpret_cast<const uint32_t*>(t.fwd.cls);
+        const uint32_t* g_next = reinterpret_cast<const uint32_t*>(t.fwd.next);
+        const uint32_t* g_eot = t.fwd.acc_eot;
+        const uint32_t n_states = t.fwd.n_states, row_words = (n_cached * t.fwd.n_classes + 1) / 2;
+        for (uint32_t i = threadIdx.x; i < 64; i += WALK_THREADS) reinterpret_cast<uint32_t*>(s_cls)[i] = g_cls[i];
+        for (uint32_t i = threadIdx.x; i < row_words; i += WALK_THREADS) reinterpret_cast<uint32_t*>(s_rows)[i] = g_next[i];
+        if (n_states <= 32 * DFA_EOT_WORDS)
+            for (uint32_t w = threadIdx.x; w < DFA_EOT_WORDS; w += WALK_THREADS) {
+                uint32_t bits = 0;
+                for (uint32_t k = 0; k < 32 && 32 * w + k < n_states; k++) bits |= (g_eot[32 * w + k] != 0 ? 1u : 0u) << k;
+                s_eot[w] = bits;
+            }
+    }
     __syncthreads();
-    const DfaCache cache{s_cls, s_rows, n_cached, s_eot};
+    const DfaCache cache = make_dfa_cache(t, s_cls, s_rows, n_cached, s_eot);
     const PtrSrc arena{a.in};
     const uint32_t nh = *n_heads;
     for (uint32_t h = blockIdx.x * WALK_THREADS + threadIdx.x; h < nh; h += gridDim.x * WALK_THREADS) {
         uint32_t q = heads[h];
-        const uint32_t slot = keys[q];
+        uint2 cur = pairs[q];                                             // (conversation slot, record number)
+        const uint32_t slot = cur.x;
         if (slot >= a.conv_slots) continue;                               // reported through bad_conv by the sort
         uint32_t state = a.conv_state[slot];
-        for (; q < a.n && keys[q] == slot; q++) {
-            const uint32_t i = idxs[q];
-            const uint4 e = a.tok_entry[i];
-            if (!((e.y >> 24) & ENTRY_OK)) continue;                      // dropped or filtered before the hook: never inspected
-            const InspectResult r = stream_walk(t, cache, arena, e.x, e.y, e.z, e.w, state);
-            state = r.state;
-            if (r.verdict) {
-                a.verdict[i] = r.verdict;
-                reinterpret_cast<int2*>(a.match)[i] = make_int2(r.begin, r.end);
+        // software pipeline: while record q is walked, the entry of q+1 and the pair of q+2 are already on their way
+        // (the loads are speculative: any position below n holds a valid record number)
+        uint2 nxt = q + 1 < a.n ? pairs[q + 1] : make_uint2(~slot, 0u);
+        uint4 ea = a.tok_entry[2 * (size_t)cur.y], eb = a.tok_entry[2 * (size_t)cur.y + 1];
+        for (;;) {
+            const uint2 nxt2 = q + 2 < a.n ? pairs[q + 2] : make_uint2(~slot, 0u);
+            const uint4 na = a.tok_entry[2 * (size_t)nxt.y], nb = a.tok_entry[2 * (size_t)nxt.y + 1];
+            if ((ea.y >> 24) & ENTRY_OK) {                                // else: dropped or filtered before the hook, never inspected
+                const uint32_t e[ENTRY_WORDS] = {ea.x, ea.y, ea.z, ea.w, eb.x, eb.y, eb.z, eb.w};
+                const InspectResult r = stream_walk(t, cache, arena, e, state);
+                state = r.state;
+                if (r.verdict) {
+                    a.verdict[cur.y] = r.verdict;
+                    reinterpret_cast<int2*>(a.match)[cur.y] = make_int2(r.begin, r.end);
+                }
             }
+            if (nxt.x != slot) break;
+            q++; cur = nxt; nxt = nxt2; ea = na; eb = nb;
         }
         a.conv_state[slot] = state;
     }
@@ -251,7 +280,7 @@ cudaError_t stream_inspect_launch(int device, const StreamArgs& a, cudaStream_t 
     if (a.n == 0) return cudaSuccess;
     const uint32_t n = a.n;
     uint8_t* p = static_cast<uint8_t*>(a.scratch);
-    uint32_t* kA = carve(p, n); uint32_t* iA = carve(p, n); uint32_t* kB = carve(p, n); uint32_t* iB = carve(p, n);
+    uint2* pA = reinterpret_cast<uint2*>(carve(p, 2 * (size_t)n)); uint2* pB = reinterpret_cast<uint2*>(carve(p, 2 * (size_t)n));
     uint32_t* heads = carve(p, n);
     uint32_t* hist = carve(p, hist_words(n));
     uint32_t* block_sums = carve(p, hist_words(n) / SCAN_BLOCK + 2);
@@ -264,28 +293,28 @@ cudaError_t stream_inspect_launch(int device, const StreamArgs& a, cudaStream_t 
     const uint32_t radix = 1u << sp.digit_bits;
     const size_t m = (size_t)radix * num_tiles;
     const uint32_t nb = (uint32_t)((m + SCAN_BLOCK - 1) / SCAN_BLOCK);
-    const uint32_t* k_in = a.conv_slot;
-    const uint32_t* i_in = nullptr;
-    uint32_t* k_out = kA; uint32_t* i_out = iA;
+    const uint2* in = nullptr;
+    uint2* out = pA;
     for (uint32_t pass = 0; pass < sp.passes; pass++) {
         const uint32_t shift = pass * sp.digit_bits;
-        k_radix_hist<<<num_tiles, SORT_THREADS, radix * 4, stream>>>(k_in, n, shift, sp.digit_bits, hist, num_tiles, a.conv_slots,
+        const uint32_t* k_in = in ? reinterpret_cast<const uint32_t*>(in) : a.conv_slot;
+        k_radix_hist<<<num_tiles, SORT_THREADS, radix * 4, stream>>>(k_in, in ? 2u : 1u, n, shift, sp.digit_bits, hist, num_tiles, a.conv_slots,
                                                                       pass == 0 ? a.bad_conv : nullptr);
         k_scan_reduce<<<nb, 1024, 0, stream>>>(hist, m, block_sums);
         k_scan_block_sums<<<1, 1024, 0, stream>>>(block_sums, nb);
         k_scan_apply<<<nb, 1024, 0, stream>>>(hist, m, block_sums);
-        k_radix_scatter<<<num_tiles, SORT_THREADS, radix * 4 * SORT_WARPS, stream>>>(k_in, i_in, n, shift, sp.digit_bits, hist, num_tiles, k_out, i_out);
-        k_in = k_out; i_in = i_out;
-        k_out = (k_out == kA) ? kB : kA; i_out = (i_out == iA) ? iB : iA;
+        k_radix_scatter<<<num_tiles, SORT_THREADS, radix * 4 * SORT_WARPS, stream>>>(a.conv_slot, in, n, shift, sp.digit_bits, hist, num_tiles, out);
+        in = out;
+        out = (out == pA) ? pB : pA;
     }
-    k_segment_heads<<<(n + 255) / 256, 256, 0, stream>>>(k_in, n, heads, n_heads);
+    k_segment_heads<<<(n + 1023) / 1024, 1024, 0, stream>>>(in, n, heads, n_heads);
     uint32_t n_cached = a.dfa_states;
     if ((size_t)n_cached * a.dfa_classes * 2 > WALK_TABLE_MAX) n_cached = WALK_TABLE_MAX / (a.dfa_classes * 2);
     const size_t smem = 256 + 4 * DFA_EOT_WORDS + (((size_t)n_cached * a.dfa_classes * 2 + 15) & ~(size_t)15);
     int grid = (int)((n + WALK_THREADS - 1) / WALK_THREADS);
-    const int cap = g_sms[device] * 8;
+    const int cap = g_sms[device] * 6;
     if (grid > cap) grid = cap;
-    k_stream_walk<<<grid, WALK_THREADS, smem, stream>>>(a, k_in, i_in, heads, n_heads, n_cached);
+    k_stream_walk<<<grid, WALK_THREADS, smem, stream>>>(a, in, heads, n_heads, n_cached);
     return cudaGetLastError();
 }
 

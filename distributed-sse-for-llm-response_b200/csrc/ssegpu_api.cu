@@ -611,7 +611,7 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
         std::vector<uint32_t> init(ctx->cfg.conv_slots, ctx->insp_start_state);
         CU(cudaMemcpy(ctx->d_conv_state, init.data(), init.size() * 4, cudaMemcpyHostToDevice));
         if (mode == sse::INSPECT_STREAMING && !ctx->d_tok_entry) {     // token entries + sort scratch of the per-conversation walk
-            CU(cudaMalloc(&ctx->d_tok_entry, (size_t)ctx->cfg.max_records * 16 + 16));
+            CU(cudaMalloc(&ctx->d_tok_entry, (size_t)ctx->cfg.max_records * 32 + 32));
             CU(cudaMalloc(&ctx->d_stream_scratch, sse::stream_scratch_bytes(ctx->cfg.max_records)));
         }
     }

@@ -84,7 +84,7 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
     std::vector<uint32_t> eot_bits(DFA_EOT_WORDS, 0);
     if (c.forward.n_states <= 32 * DFA_EOT_WORDS)
         for (uint32_t st = 0; st < c.forward.n_states; st++) if (c.forward.acc_eot[st]) eot_bits[st >> 5] |= 1u << (st & 31);
-    DfaCache cache{c.forward.cls, c.forward.next.data(), c.forward.n_states < 20 ? c.forward.n_states : 20, eot_bits.data()};
+    DfaCache cache = make_dfa_cache(t, c.forward.cls, c.forward.next.data(), c.forward.n_states < 20 ? c.forward.n_states : 20, eot_bits.data());
     const bool streaming = mode == INSPECT_STREAMING;
     for (uint32_t i = 0; i < n; i++) {
         Plan pl;
@@ -100,11 +100,11 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
             // arrival order (which is record order here)
             const uint32_t flags = ((st & ST_CODE_MASK) == ST_OK ? ENTRY_OK : 0u) | ((fastp && !pl.tok_esc) ? 0u : ENTRY_DECODE) |
                                    ((st & ST_DONE) ? ENTRY_DONE : 0u);
-            uint32_t e[4];
+            uint32_t e[ENTRY_WORDS];
             make_token_entry(src, o + pl.tok_b, pl.tok_e - pl.tok_b, o + pl.tok_b, flags, e);
             if (!(flags & ENTRY_OK)) continue;
             const uint32_t slot = conv_slot[i];
-            r = stream_walk(t, cache, src, e[0], e[1], e[2], e[3], state[slot]);
+            r = stream_walk(t, cache, src, e, state[slot]);
             state[slot] = r.state;
         } else {
             if ((st & ST_CODE_MASK) != ST_OK) continue;
@@ -153,8 +153,11 @@ extern "C" int hc_interest(const hc_delta* d, uint32_t nd, const uint8_t* in, co
         hit[3 * i] = hit[3 * i + 1] = hit[3 * i + 2] = 0;
         if ((st & ST_CODE_MASK) == ST_OK) {
             InterestHit h{0, 0, 0};
-            if (!(fastp && !pl.cid_esc && interest_lookup_raw(dev, src, o + pl.cid_b, o + pl.cid_e, h)))
-                h = interest_lookup(dev, src, o + pl.cid_b, o + pl.cid_e);
+            const InterestFast fast = make_interest_fast(dev);
+            InterestPre pre;
+            interest_prepare(fast, src, o + pl.cid_b, o + pl.cid_e, fastp && !pl.cid_esc, pre);     // the kernel calls this from parse_fast's hook
+            if (pre.ready) interest_finish(fast, src, o + pl.cid_b, o + pl.cid_e, pre, h);
+            else h = interest_lookup(dev, src, o + pl.cid_b, o + pl.cid_e);
             hit[3 * i] = h.list_off; hit[3 * i + 1] = h.list_cnt; hit[3 * i + 2] = h.wild_mask;
             if (h.list_cnt == 0 && h.wild_mask == 0) st = ST_NO_INTEREST;
         }
