@@ -34,7 +34,8 @@ constexpr uint32_t DFA_CACHE_BYTES = 256 + 4 * DFA_EOT_WORDS + 2 * DFA_CACHE_ENT
 // walk (sse_stream.cu): word 0 = offset of the token literal's content in the payload arena, word 1 = its raw length
 // (24 bits, saturating) | flags << 24, words 2..7 = the first 24 raw bytes of the literal -- every BASELINE token, so the
 // walk needs the arena only for longer ones.
-enum : uint32_t { ENTRY_OK = 1u, ENTRY_DECODE = 2u, ENTRY_DONE = 4u, ENTRY_HUGE = 8u };
+enum : uint32_t { ENTRY_OK = 1u, ENTRY_DECODE = 2u, ENTRY_DONE = 4u, ENTRY_HUGE = 8u,
+                  ENTRY_CANON = 16u };   // with ENTRY_DECODE: the only escapes are the ones json.Marshal itself writes
 constexpr uint32_t ENTRY_LEN_MASK = 0xFFFFFFu;
 constexpr uint32_t ENTRY_WORDS = 8, ENTRY_INLINE = 24;
 constexpr uint32_t STREAM_BUF_WORDS = 16;            // the walk fetches tokens of up to 56 raw bytes from the arena in one round of word loads
@@ -187,6 +188,25 @@ SSE_HD_NOINLINE InspectResult inspect_token(const InspectDev& t, const Src& s, u
     return r;
 }
 
+// Walk over a token literal whose only escapes are the ones json.Marshal itself writes: two-character forms and
+// u00XX (one byte each), u2028 / u2029 (three bytes); raw UTF-8 passes through.
+template <bool STREAMING, class Src>
+SSE_HD void walk_canon_escaped(const DfaDev& d, const DfaCache& c, Walk& w, const Src& s, uint32_t tok_b, uint32_t tok_e) {
+    for (uint32_t pos = tok_b; pos < tok_e;) {
+        uint32_t ch = s.ld8(pos++);
+        if (ch == '\\') {
+            const uint32_t e = s.ld8(pos++);
+            if (e == 'u') {
+                const uint32_t r = (uint32_t)hex4(s, pos);
+                pos += 4;
+                if (r < 0x80) ch = r;
+                else { walk_byte<STREAMING>(d, c, w, 0xE0 | (r >> 12)); walk_byte<STREAMING>(d, c, w, 0x80 | ((r >> 6) & 0x3F)); ch = 0x80 | (r & 0x3F); }
+            } else ch = e == 'n' ? 10u : e == 'r' ? 13u : e == 't' ? 9u : e == 'b' ? 8u : e == 'f' ? 12u : e;
+        }
+        walk_byte<STREAMING>(d, c, w, ch);
+    }
+}
+
 // per_token mode, canonical record (what json.Marshal wrote): the token literal's content [tok_b, tok_e) sits in the
 // tile.  Without escapes its decoded text IS those bytes (word loads, funnel-shifted); with escapes (1.5 % of the
 // BASELINE tokens) the same walk runs over the decoded bytes.  Class map, end-of-text bitmap and hot rows are on
@@ -211,20 +231,7 @@ SSE_HD bool inspect_canon_token(const InspectDev& t, const DfaCache& c, const Sr
             for (uint32_t k = 0; k < m; k++, word >>= 8) walk_byte<false>(d, c, w, word & 0xFF);
         }
     } else {
-        // the escapes json.Marshal itself writes: two-character forms and u00XX (one byte each), u2028 / u2029 (three bytes)
-        for (uint32_t pos = tok_b; pos < tok_e;) {
-            uint32_t ch = s.ld8(pos++);
-            if (ch == '\\') {
-                const uint32_t e = s.ld8(pos++);
-                if (e == 'u') {
-                    const uint32_t r = (uint32_t)hex4(s, pos);
-                    pos += 4;
-                    if (r < 0x80) ch = r;
-                    else { walk_byte<false>(d, c, w, 0xE0 | (r >> 12)); walk_byte<false>(d, c, w, 0x80 | ((r >> 6) & 0x3F)); ch = 0x80 | (r & 0x3F); }
-                } else ch = e == 'n' ? 10u : e == 'r' ? 13u : e == 't' ? 9u : e == 'b' ? 8u : e == 'f' ? 12u : e;
-            }
-            walk_byte<false>(d, c, w, ch);
-        }
+        walk_canon_escaped<false>(d, c, w, s, tok_b, tok_e);
     }
     walk_eot<false>(d, c, w);
     if (w.win < 32) {
@@ -295,6 +302,7 @@ SSE_HD InspectResult stream_walk(const InspectDev& t, const DfaCache& c, const S
         }
         const PtrSrc local{reinterpret_cast<const uint8_t*>(buf)};
         if (!(flags & ENTRY_DECODE)) for (uint32_t k = 0; k < n; k++) walk_byte<true>(d, c, w, local.ld8(sh + k));
+        else if (flags & ENTRY_CANON) walk_canon_escaped<true>(d, c, w, local, sh, sh + n);
         else for_each_decoded_byte(local, sh, sh + n, [&](uint32_t b) { walk_byte<true>(d, c, w, b); });
     } else {
         uint32_t end = e[0] + n;

@@ -186,9 +186,10 @@ __device__ __noinline__ uint32_t measure_slow(const uint8_t* src_base, uint32_t 
 }
 // Token entry of record i for the streaming walk (sb + o = the record's first byte, abs_b its offset in the arena)
 __device__ __forceinline__ void store_token_entry(const FrameArgs& a, uint32_t i, const uint8_t* sb, uint32_t o, uint32_t abs_b, const Plan& pl,
-                                                  uint32_t st, bool raw_text) {
+                                                  uint32_t st, bool raw_text, bool canonical) {
     PtrSrc src{sb};
-    const uint32_t flags = ((st & ST_CODE_MASK) == ST_OK ? ENTRY_OK : 0u) | (raw_text ? 0u : ENTRY_DECODE) | ((st & ST_DONE) ? ENTRY_DONE : 0u);
+    const uint32_t flags = ((st & ST_CODE_MASK) == ST_OK ? ENTRY_OK : 0u) | (raw_text ? 0u : ENTRY_DECODE) | ((st & ST_DONE) ? ENTRY_DONE : 0u) |
+                           (canonical ? ENTRY_CANON : 0u);
     uint32_t e[ENTRY_WORDS];
     make_token_entry(src, o + pl.tok_b, pl.tok_e - pl.tok_b, abs_b + pl.tok_b, flags, e);
     a.tok_entry[2 * (size_t)i] = make_uint4(e[0], e[1], e[2], e[3]);
@@ -218,7 +219,7 @@ __device__ __noinline__ void ext_stage_slow(const FrameArgs& a, uint32_t i, cons
             reinterpret_cast<int2*>(a.match)[i] = make_int2(io.begin, io.end);
         }
     }
-    if (a.tok_entry != nullptr && write_entry) store_token_entry(a, i, sb, o, abs_b, *plp, *stp, false);
+    if (a.tok_entry != nullptr && write_entry) store_token_entry(a, i, sb, o, abs_b, *plp, *stp, false, false);
     if (a.interest != nullptr) {
         InterestHit h{0, 0, 0};
         if ((st & ST_CODE_MASK) == ST_OK) {
@@ -439,7 +440,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
             }
             // token entry for the streaming walk
             if ((EXT & X_INSPECT) && a.tok_entry != nullptr && canon && (MODE != MODE_ORDERED_COUNT || (a.xflags & XF_ENTRY_IN_COUNT)))
-                store_token_entry(a, r0 + tid, s_in, o, my_b, pl, st, !pl.tok_esc);
+                store_token_entry(a, r0 + tid, s_in, o, my_b, pl, st, !pl.tok_esc, true);
             // subject -> subscriber/interest table
             if (EXT & X_INTEREST) {
                 InterestHit h{0, 0, 0};

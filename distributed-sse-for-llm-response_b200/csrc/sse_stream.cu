@@ -191,6 +191,8 @@ __global__ void __launch_bounds__(WALK_THREADS) k_stream_walk(const StreamArgs a
     uint8_t* s_cls = s_tab;
     uint32_t* s_eot = reinterpret_cast<uint32_t*>(s_cls + 256);
     uint16_t* s_rows = reinterpret_cast<uint16_t*>(s_eot + DFA_EOT_WORDS);
+    const uint32_t nh = *n_heads;
+    if (blockIdx.x * WALK_THREADS >= nh) return;                          // the grid is sized for the worst case (every record its own conversation)
     const InspectDev& t = *a.insp;
     {   // table -> shared memory (descriptor fields first into registers: the descriptor itself lives in global memory)
         const uint32_t* g_cls = reinterpret_cast<const uint32_t*>(t.fwd.cls);
@@ -209,20 +211,21 @@ __global__ void __launch_bounds__(WALK_THREADS) k_stream_walk(const StreamArgs a
     __syncthreads();
     const DfaCache cache = make_dfa_cache(t, s_cls, s_rows, n_cached, s_eot);
     const PtrSrc arena{a.in};
-    const uint32_t nh = *n_heads;
     for (uint32_t h = blockIdx.x * WALK_THREADS + threadIdx.x; h < nh; h += gridDim.x * WALK_THREADS) {
         uint32_t q = heads[h];
         uint2 cur = pairs[q];                                             // (conversation slot, record number)
         const uint32_t slot = cur.x;
         if (slot >= a.conv_slots) continue;                               // reported through bad_conv by the sort
         uint32_t state = a.conv_state[slot];
-        // software pipeline: while record q is walked, the entry of q+1 and the pair of q+2 are already on their way
-        // (the loads are speculative: any position below n holds a valid record number)
-        uint2 nxt = q + 1 < a.n ? pairs[q + 1] : make_uint2(~slot, 0u);
+        // software pipeline: while record q is walked, the entries of q+1 and q+2 and the pair of q+3 are already on
+        // their way (the loads are speculative: any position below n holds a valid record number)
+        const uint2 none = make_uint2(~slot, 0u);
+        uint2 p1 = q + 1 < a.n ? pairs[q + 1] : none, p2 = q + 2 < a.n ? pairs[q + 2] : none;
         uint4 ea = a.tok_entry[2 * (size_t)cur.y], eb = a.tok_entry[2 * (size_t)cur.y + 1];
+        uint4 fa = a.tok_entry[2 * (size_t)p1.y], fb = a.tok_entry[2 * (size_t)p1.y + 1];
         for (;;) {
-            const uint2 nxt2 = q + 2 < a.n ? pairs[q + 2] : make_uint2(~slot, 0u);
-            const uint4 na = a.tok_entry[2 * (size_t)nxt.y], nb = a.tok_entry[2 * (size_t)nxt.y + 1];
+            const uint2 p3 = q + 3 < a.n ? pairs[q + 3] : none;
+            const uint4 ga = a.tok_entry[2 * (size_t)p2.y], gb = a.tok_entry[2 * (size_t)p2.y + 1];
             if ((ea.y >> 24) & ENTRY_OK) {                                // else: dropped or filtered before the hook, never inspected
                 const uint32_t e[ENTRY_WORDS] = {ea.x, ea.y, ea.z, ea.w, eb.x, eb.y, eb.z, eb.w};
                 const InspectResult r = stream_walk(t, cache, arena, e, state);
@@ -232,8 +235,8 @@ __global__ void __launch_bounds__(WALK_THREADS) k_stream_walk(const StreamArgs a
                     reinterpret_cast<int2*>(a.match)[cur.y] = make_int2(r.begin, r.end);
                 }
             }
-            if (nxt.x != slot) break;
-            q++; cur = nxt; nxt = nxt2; ea = na; eb = nb;
+            if (p1.x != slot) break;
+            q++; cur = p1; p1 = p2; p2 = p3; ea = fa; eb = fb; fa = ga; fb = gb;
         }
         a.conv_state[slot] = state;
     }

@@ -780,6 +780,56 @@ double sseo_bench_adapter(const uint8_t *in, const uint32_t *in_off, uint32_t n,
     return best;
 }
 
+/* The same baseline with its buffers prepared once: sseo_bench_new allocates and touches every worker's output buffer,
+ * sseo_bench_run times ONE pass of all workers (wall clock), sseo_bench_free releases.  bench.py's reference arm uses
+ * it so that a timed step pays no page faults for freshly malloc'ed output (the GPU arm's buffers are allocated once too). */
+struct sseo_bench {
+    int threads;
+    bench_job *jobs;
+    pthread_t *tid;
+};
+
+sseo_bench *sseo_bench_new(const uint8_t *in, const uint32_t *in_off, uint32_t n, int threads)
+{
+    if (threads < 1) threads = 1;
+    sseo_bench *b = (sseo_bench *)calloc(1, sizeof *b);
+    b->threads = threads;
+    b->jobs = (bench_job *)calloc((size_t)threads, sizeof(bench_job));
+    b->tid = (pthread_t *)calloc((size_t)threads, sizeof(pthread_t));
+    for (int t = 0; t < threads; t++) {
+        uint32_t lo = (uint32_t)((uint64_t)n * (uint64_t)t / (uint64_t)threads);
+        uint32_t hi = (uint32_t)((uint64_t)n * (uint64_t)(t + 1) / (uint64_t)threads);
+        uint64_t in_bytes = in_off[hi] - in_off[lo];
+        b->jobs[t].in = in; b->jobs[t].in_off = in_off; b->jobs[t].lo = lo; b->jobs[t].hi = hi;
+        b->jobs[t].out_cap = 2 * in_bytes + 64ull * (hi - lo) + (1u << 20);
+        b->jobs[t].out = (uint8_t *)malloc(b->jobs[t].out_cap);
+        if (!b->jobs[t].out) { sseo_bench_free(b); return NULL; }
+        memset(b->jobs[t].out, 0, b->jobs[t].out_cap);
+    }
+    return b;
+}
+
+double sseo_bench_run(sseo_bench *b, uint64_t *frames, uint64_t *out_bytes)
+{
+    struct timespec t0, t1;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    for (int t = 0; t < b->threads; t++) pthread_create(&b->tid[t], NULL, bench_worker, &b->jobs[t]);
+    for (int t = 0; t < b->threads; t++) pthread_join(b->tid[t], NULL);
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    uint64_t f = 0, by = 0;
+    for (int t = 0; t < b->threads; t++) { f += b->jobs[t].frames; by += b->jobs[t].bytes; }
+    if (frames) *frames = f;
+    if (out_bytes) *out_bytes = by;
+    return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+}
+
+void sseo_bench_free(sseo_bench *b)
+{
+    if (!b) return;
+    for (int t = 0; t < b->threads; t++) free(b->jobs[t].out);
+    free(b->jobs); free(b->tid); free(b);
+}
+
 /* hash/fnv New64a: the conversation -> GPU shard function. */
 uint64_t sseo_fnv1a64(const uint8_t *p, size_t n)
 {

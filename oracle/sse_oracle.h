@@ -104,6 +104,11 @@ int sseo_bridge_batch(const uint8_t *in, const uint32_t *in_off, uint32_t n, int
  * wall-clock seconds of one repetition; *frames / *out_bytes are per repetition. */
 double sseo_bench_adapter(const uint8_t *in, const uint32_t *in_off, uint32_t n,
                           int threads, int reps, uint64_t *frames, uint64_t *out_bytes);
+/* the same with buffers allocated and touched once, one timed pass per call (bench.py --impl reference) */
+typedef struct sseo_bench sseo_bench;
+sseo_bench *sseo_bench_new(const uint8_t *in, const uint32_t *in_off, uint32_t n, int threads);
+double sseo_bench_run(sseo_bench *b, uint64_t *frames, uint64_t *out_bytes);
+void sseo_bench_free(sseo_bench *b);
 
 /* ---- content inspection (oracle/sse_inspect_oracle.c; semantics in its header comment) ---- */
 typedef struct { uint32_t kind;   /* 0 literal, ASCII case-insensitive; 1 regex subset */

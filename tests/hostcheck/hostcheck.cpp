@@ -99,7 +99,7 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
             // as on the GPU: the frame pass leaves a token entry, the per-conversation walk consumes the entries in
             // arrival order (which is record order here)
             const uint32_t flags = ((st & ST_CODE_MASK) == ST_OK ? ENTRY_OK : 0u) | ((fastp && !pl.tok_esc) ? 0u : ENTRY_DECODE) |
-                                   ((st & ST_DONE) ? ENTRY_DONE : 0u);
+                                   ((st & ST_DONE) ? ENTRY_DONE : 0u) | (fastp ? ENTRY_CANON : 0u);
             uint32_t e[ENTRY_WORDS];
             make_token_entry(src, o + pl.tok_b, pl.tok_e - pl.tok_b, o + pl.tok_b, flags, e);
             if (!(flags & ENTRY_OK)) continue;

@@ -131,6 +131,27 @@ class Oracle:
         sec = self.lib.sseo_bench_adapter(_ptr(arena, u8p), _ptr(off, u32p), n, threads, reps, C.byref(frames), C.byref(nbytes))
         return sec, frames.value, nbytes.value
 
+    def bench_prepared(self, arena, off, threads):
+        """-> run() -> (seconds, frames, out_bytes) for one timed pass with warm, pre-touched buffers; close() frees them."""
+        lib = self.lib
+        lib.sseo_bench_new.restype = C.c_void_p
+        lib.sseo_bench_new.argtypes = [u8p, u32p, C.c_uint32, C.c_int]
+        lib.sseo_bench_run.restype = C.c_double
+        lib.sseo_bench_run.argtypes = [C.c_void_p, u64p, u64p]
+        lib.sseo_bench_free.argtypes = [C.c_void_p]
+        h = lib.sseo_bench_new(_ptr(arena, u8p), _ptr(off, u32p), len(off) - 1, threads)
+        assert h, "oracle: out of memory"
+
+        class Prepared:
+            def run(self_):
+                frames, nbytes = C.c_uint64(0), C.c_uint64(0)
+                sec = lib.sseo_bench_run(h, C.byref(frames), C.byref(nbytes))
+                return sec, frames.value, nbytes.value
+
+            def close(self_):
+                lib.sseo_bench_free(h)
+        return Prepared()
+
     def start_sequence(self, s):
         return self.lib.sseo_start_sequence(s.encode() if s is not None else None)
 
