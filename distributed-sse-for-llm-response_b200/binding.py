@@ -110,6 +110,14 @@ def load_library():
     lib.ssegpu_interest_subs.argtypes = [vp, u32p]
     lib.ssegpu_interest_wild_ids.restype = u32p
     lib.ssegpu_interest_wild_ids.argtypes = [vp, u32p]
+    lib.ssegpu_interest_version.restype = C.c_uint64
+    lib.ssegpu_interest_version.argtypes = [vp]
+    lib.ssegpu_batch_subs.restype = u32p
+    lib.ssegpu_batch_subs.argtypes = [vp, u32p]
+    lib.ssegpu_batch_wild_ids.restype = u32p
+    lib.ssegpu_batch_wild_ids.argtypes = [vp, u32p]
+    lib.ssegpu_batch_table_version.restype = C.c_uint64
+    lib.ssegpu_batch_table_version.argtypes = [vp]
     lib.ssegpu_sub_span.restype = u32p
     lib.ssegpu_sub_span.argtypes = [vp]
     lib.ssegpu_interest_bind.restype = C.c_int
@@ -197,6 +205,20 @@ class Batch:
         self.out = np.ctypeslib.as_array(lib.ssegpu_out_bytes(self.h), shape=(max(total, 1),))[:total]
         return self
 
+    def subs(self):
+        """subscriber-id arena of the table generation this batch was matched against (copy)"""
+        n = C.c_uint32(0)
+        p = self.owner.lib.ssegpu_batch_subs(self.h, C.byref(n))
+        return np.ctypeslib.as_array(p, shape=(max(n.value, 1),))[: n.value].copy() if n.value else np.zeros(0, np.uint32)
+
+    def wild_ids(self):
+        n = C.c_uint32(0)
+        p = self.owner.lib.ssegpu_batch_wild_ids(self.h, C.byref(n))
+        return np.ctypeslib.as_array(p, shape=(max(n.value, 1),))[: n.value].copy() if n.value else np.zeros(0, np.uint32)
+
+    def table_version(self):
+        return int(self.owner.lib.ssegpu_batch_table_version(self.h))
+
     def release(self):
         self.owner._check(self.owner.lib.ssegpu_batch_release(self.owner.ctx, self.h))
 
@@ -242,12 +264,15 @@ class SseGpu:
     def interest_subs(self):
         n = C.c_uint32(0)
         p = self.lib.ssegpu_interest_subs(self.ctx, C.byref(n))
-        return np.ctypeslib.as_array(p, shape=(max(n.value, 1),))[: n.value].copy()
+        return np.ctypeslib.as_array(p, shape=(max(n.value, 1),))[: n.value].copy() if n.value else np.zeros(0, np.uint32)
 
     def interest_wild_ids(self):
         n = C.c_uint32(0)
         p = self.lib.ssegpu_interest_wild_ids(self.ctx, C.byref(n))
         return np.ctypeslib.as_array(p, shape=(max(n.value, 1),))[: n.value].copy() if n.value else np.zeros(0, np.uint32)
+
+    def interest_version(self):
+        return int(self.lib.ssegpu_interest_version(self.ctx))
 
     def interest_bind(self, d_sub_span):
         self._check(self.lib.ssegpu_interest_bind(self.ctx, d_sub_span))

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <new>
 #include <thread>
@@ -36,8 +37,37 @@ enum SlotState { FREE = 0, ACQUIRED, SUBMITTED, DONE };
 
 }  // namespace
 
+// Device tables live in generations that are reference-counted by whoever may still read them: the context (the current
+// one) and every submitted batch until it is released.  Swapping a generation in needs no device-wide synchronisation:
+// the old one is freed, stream-ordered, when its last user lets go (cudaFreeAsync on the context's table stream).
+struct TableGen {                        // interest table
+    cudaStream_t stream = nullptr;
+    sse::InterestSlot* d_slots = nullptr; uint32_t* d_keys = nullptr; uint8_t* d_wild = nullptr; sse::InterestDev* d_desc = nullptr;
+    std::shared_ptr<std::vector<uint32_t>> subs;     // host arena the spans of this generation index (append-only, fixed address)
+    std::vector<uint32_t> wild_ids;
+    ~TableGen() {
+        if (d_slots) cudaFreeAsync(d_slots, stream);
+        if (d_keys) cudaFreeAsync(d_keys, stream);
+        if (d_wild) cudaFreeAsync(d_wild, stream);
+        if (d_desc) cudaFreeAsync(d_desc, stream);
+    }
+};
+struct InspGen {                         // inspection pattern tables
+    cudaStream_t stream = nullptr;
+    void* d_blob = nullptr; sse::InspectDev* d_desc = nullptr;
+    uint32_t mode = 0, start_state = 0, n_states = 0, n_classes = 0;
+    ~InspGen() {
+        if (d_blob) cudaFreeAsync(d_blob, stream);
+        if (d_desc) cudaFreeAsync(d_desc, stream);
+    }
+};
+struct SlotOp { uint32_t index, pad[15]; sse::InterestSlot image; };     // one changed slot of an incremental table update
+
 struct ssegpu_batch {
     ssegpu_ctx* ctx = nullptr;
+    std::shared_ptr<TableGen> tab;       // generations this batch was launched on (held until release)
+    std::shared_ptr<InspGen> insp;
+    uint64_t table_version = 0;
     int state = FREE;
     uint32_t n = 0, op = 0;
     uint64_t spec_out = 0;       // output bytes whose D2H copy was enqueued at submit
@@ -74,17 +104,26 @@ struct ssegpu_ctx {
     ssegpu_counters totals{};
     uint64_t launches = 0;
     // content inspection
-    void* d_insp_blob = nullptr;          // DFA tables
-    sse::InspectDev* d_insp = nullptr;    // descriptor with device pointers into the blob
-    uint32_t insp_mode = 0, insp_start_state = 0, insp_states = 0, insp_classes = 0;
+    std::shared_ptr<InspGen> insp;        // current pattern tables (nullptr: none loaded)
     uint32_t* d_conv_state = nullptr;
     // streaming mode: token entries + sort scratch of the per-conversation walk, shared by every batch of the context
     // (streaming batches run one after the other on the GPU: ev_stream orders them in submit order)
     uint4* d_tok_entry = nullptr; void* d_stream_scratch = nullptr;
     cudaEvent_t ev_stream = nullptr;
     // interest table
-    sse_interest::HostTable interest;
-    void* d_int_slots = nullptr; void* d_int_keys = nullptr; void* d_int_wild = nullptr; sse::InterestDev* d_interest = nullptr;
+    sse_interest::HostTable interest;     // authoritative subscriptions + host mirror of the current generation
+    std::shared_ptr<TableGen> tab;        // current device generation (nullptr: ssegpu_interest_apply not called yet)
+    uint64_t table_version = 0;           // successful ssegpu_interest_apply calls so far
+    // table updates are GPU work on their own stream, ordered against the batches by events: an update waits for the
+    // batches in flight that read the tables, later batches wait for the update (ev_table)
+    cudaStream_t table_stream = nullptr;
+    cudaEvent_t ev_table = nullptr;
+    static constexpr int kOpChunks = 64, kOpsPerChunk = 256, kLaunchEvents = 8;
+    SlotOp* h_ops = nullptr; SlotOp* d_ops = nullptr;            // pinned staging ring + device copy, kOpChunks x kOpsPerChunk
+    cudaEvent_t ev_chunk[kOpChunks] = {};
+    int next_chunk = 0;
+    cudaEvent_t ev_launch[kLaunchEvents] = {};                   // device-resident launches that read the tables
+    int next_launch_ev = 0;
     uint32_t* bound_hit = nullptr;
     const uint32_t* bound_conv = nullptr; uint32_t* bound_verdict = nullptr; int32_t* bound_match = nullptr;   // ssegpu_inspect_bind
 };
@@ -97,19 +136,20 @@ uint32_t launches_of(uint32_t op) { return (op & SSEGPU_OP_ORDERED) ? 3 : 1; }
 // Frame kernels plus, in streaming inspection mode, the per-conversation walk.  Streaming batches of one context run in
 // submit order (each waits for the previous one's walk): the carried DFA state of a conversation that has tokens in
 // two consecutive batches must be committed by the first before the second reads it.
-int launch_path(ssegpu_ctx* ctx, sse::FrameArgs a, const uint32_t* d_conv, cudaStream_t st, uint32_t* n_launches) {
+// The caller holds ctx->mu whenever the op reads tables (inspection, interest), from the snapshot of the generations to
+// the last enqueue: lock order is then GPU order, for batches among themselves and against table updates.
+int launch_path(ssegpu_ctx* ctx, sse::FrameArgs a, const uint32_t* d_conv, cudaStream_t st, const InspGen* insp, uint32_t* n_launches) {
     const bool inspect = (a.op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) != 0;
     *n_launches = a.n ? launches_of(a.op) : 0;
-    if (!inspect || ctx->insp_mode != sse::INSPECT_STREAMING) {
+    if (!inspect || insp->mode != sse::INSPECT_STREAMING) {
         CU(sse::frame_launch(ctx->cfg.device, a, st));
         return SSEGPU_OK;
     }
-    std::lock_guard<std::mutex> lk(ctx->mu);
     CU(cudaStreamWaitEvent(st, ctx->ev_stream, 0));
     sse::StreamArgs w{};
     w.insp = a.insp; w.in = a.in; w.tok_entry = ctx->d_tok_entry; w.conv_slot = d_conv; w.n = a.n; w.conv_slots = ctx->cfg.conv_slots;
     w.conv_state = ctx->d_conv_state; w.verdict = a.verdict; w.match = a.match; w.scratch = ctx->d_stream_scratch;
-    w.dfa_states = ctx->insp_states; w.dfa_classes = ctx->insp_classes;
+    w.dfa_states = insp->n_states; w.dfa_classes = insp->n_classes;
     sse::FrameArgs f = a;
     f.insp = nullptr; f.tok_entry = ctx->d_tok_entry;
     uint32_t bits = 1;
@@ -139,6 +179,22 @@ int launch_path(ssegpu_ctx* ctx, sse::FrameArgs a, const uint32_t* d_conv, cudaS
 
 // SSEGPU_OP_NATS_PUB is a bridge-mode framing; SSEGPU_OP_RESP belongs to the encoder
 bool bad_frame_op(uint32_t op) { return (op & SSEGPU_OP_RESP) || ((op & SSEGPU_OP_NATS_PUB) && !(op & SSEGPU_OP_BRIDGE)); }
+
+// With ctx->mu held: the generations `op` needs (SSEGPU_E_STATE if none has been loaded), and `st` made to wait for
+// the last table update.
+int acquire_tables(ssegpu_ctx* ctx, uint32_t op, cudaStream_t st, std::shared_ptr<TableGen>& tab, std::shared_ptr<InspGen>& insp) {
+    if (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) {
+        if (!ctx->insp) return SSEGPU_E_STATE;                        // ssegpu_patterns_load first
+        if (ctx->insp->mode == sse::INSPECT_STREAMING && (!ctx->d_conv_state || !ctx->d_tok_entry)) return SSEGPU_E_STATE;   // conv_slots was 0 at init
+        insp = ctx->insp;
+    }
+    if (op & SSEGPU_OP_MATCH) {
+        if (!ctx->tab) return SSEGPU_E_STATE;                         // ssegpu_interest_apply first
+        tab = ctx->tab;
+    }
+    CU(cudaStreamWaitEvent(st, ctx->ev_table, 0));
+    return SSEGPU_OK;
+}
 
 void add_rows(const uint8_t* hdr, ssegpu_counters* c, uint32_t n_records) {
     const unsigned long long* rows = reinterpret_cast<const unsigned long long*>(hdr + sse::SCRATCH_HDR);
@@ -307,6 +363,14 @@ int ssegpu_init(const ssegpu_config* cfg, ssegpu_ctx** out) {
         if (e != cudaSuccess) { rc = cuda_fail(e, "frame_configure"); break; }
         if ((e = sse::stream_configure(cfg->device)) != cudaSuccess) { rc = cuda_fail(e, "stream_configure"); break; }
         if ((e = cudaEventCreateWithFlags(&ctx->ev_stream, cudaEventDisableTiming)) != cudaSuccess) { rc = cuda_fail(e, "cudaEventCreate"); break; }
+        if ((e = cudaStreamCreateWithFlags(&ctx->table_stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(e, "cudaStreamCreate"); break; }
+        if ((e = cudaEventCreateWithFlags(&ctx->ev_table, cudaEventDisableTiming)) != cudaSuccess) { rc = cuda_fail(e, "cudaEventCreate"); break; }
+        for (int k = 0; k < ssegpu_ctx::kOpChunks && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&ctx->ev_chunk[k], cudaEventDisableTiming);
+        for (int k = 0; k < ssegpu_ctx::kLaunchEvents && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&ctx->ev_launch[k], cudaEventDisableTiming);
+        if (e != cudaSuccess) { rc = cuda_fail(e, "cudaEventCreate"); break; }
+        const size_t ops_bytes = sizeof(SlotOp) * ssegpu_ctx::kOpChunks * ssegpu_ctx::kOpsPerChunk;
+        if ((e = cudaHostAlloc(&ctx->h_ops, ops_bytes, cudaHostAllocDefault)) != cudaSuccess) { rc = cuda_fail(e, "cudaHostAlloc"); break; }
+        if ((e = cudaMalloc(&ctx->d_ops, ops_bytes)) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc"); break; }
         if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(e, "cudaStreamCreate"); break; }
         if ((e = cudaMalloc(&ctx->d_launch_scratch, sse::scratch_bytes_with_plan(cfg->max_records))) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc scratch"); break; }
         if ((e = cudaMalloc(&ctx->d_encode_scratch, sse::SCRATCH_HDR)) != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc scratch"); break; }
@@ -328,12 +392,21 @@ void ssegpu_destroy(ssegpu_ctx* ctx) {
     cudaSetDevice(ctx->cfg.device);
     for (ssegpu_batch* b : ctx->slots) if (b->stream) cudaStreamSynchronize(b->stream);   // own streams only: the GPU may be shared
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->table_stream) cudaStreamSynchronize(ctx->table_stream);
+    for (ssegpu_batch* b : ctx->slots) { b->tab.reset(); b->insp.reset(); }
+    ctx->tab.reset(); ctx->insp.reset();                                  // stream-ordered frees of the table generations
+    if (ctx->table_stream) cudaStreamSynchronize(ctx->table_stream);
     for (ssegpu_batch* b : ctx->slots) free_batch(b);
+    ctx->slots.clear();
     cudaFree(ctx->d_launch_scratch);
     cudaFree(ctx->d_encode_scratch);
-    cudaFree(ctx->d_int_slots); cudaFree(ctx->d_int_keys); cudaFree(ctx->d_int_wild); cudaFree(ctx->d_interest);
-    cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp); cudaFree(ctx->d_conv_state); cudaFree(ctx->d_tok_entry); cudaFree(ctx->d_stream_scratch);
+    cudaFree(ctx->d_conv_state); cudaFree(ctx->d_tok_entry); cudaFree(ctx->d_stream_scratch);
+    cudaFree(ctx->d_ops); cudaFreeHost(ctx->h_ops);
     if (ctx->ev_stream) cudaEventDestroy(ctx->ev_stream);
+    if (ctx->ev_table) cudaEventDestroy(ctx->ev_table);
+    for (cudaEvent_t e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->ev_launch) if (e) cudaEventDestroy(e);
+    if (ctx->table_stream) cudaStreamDestroy(ctx->table_stream);
     cudaFreeHost(ctx->h_launch_hdr);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -399,23 +472,23 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     a.status = b->d_status;
     sse::scratch_carve_split(b->d_block + b->ts_cap, n, a);
     a.plan = reinterpret_cast<uint32_t*>(b->d_block + b->plan_off);
-    const bool inspect = (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) != 0;
-    if (inspect) {
-        if (!ctx->d_insp) return SSEGPU_E_STATE;                  // ssegpu_patterns_load first
-        if (ctx->insp_mode == sse::INSPECT_STREAMING) {
-            if (!ctx->d_conv_state || !ctx->d_tok_entry) return SSEGPU_E_STATE;   // conv_slots was 0 at init
-            if (n) CU(cudaMemcpyAsync(b->d_conv, b->h_conv, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    // ops that read tables hold the context lock from the snapshot of the generations to the last enqueue (see launch_path)
+    const bool uses_tables = (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE | SSEGPU_OP_MATCH)) != 0;
+    std::unique_lock<std::mutex> lk(ctx->mu, std::defer_lock);
+    b->tab.reset(); b->insp.reset();
+    if (uses_tables) {
+        lk.lock();
+        const int rc = acquire_tables(ctx, op, st, b->tab, b->insp);
+        if (rc != SSEGPU_OK) return rc;
+        b->table_version = ctx->table_version;
+        if (b->insp) {
+            if (b->insp->mode == sse::INSPECT_STREAMING && n) CU(cudaMemcpyAsync(b->d_conv, b->h_conv, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+            a.insp = b->insp->d_desc; a.verdict = b->d_verdict; a.match = b->d_match;
         }
-        a.insp = ctx->d_insp;
-        a.verdict = b->d_verdict; a.match = b->d_match;
-    }
-    const bool match = (op & SSEGPU_OP_MATCH) != 0;
-    if (match) {
-        if (!ctx->d_interest) return SSEGPU_E_STATE;                  // ssegpu_interest_apply first
-        a.interest = ctx->d_interest; a.hit = b->d_hit;
+        if (b->tab) { a.interest = b->tab->d_desc; a.hit = b->d_hit; }
     }
     uint32_t n_launches = 0;
-    { const int rc = launch_path(ctx, a, b->d_conv, st, &n_launches); if (rc != SSEGPU_OK) return rc; }
+    { const int rc = launch_path(ctx, a, b->d_conv, st, b->insp.get(), &n_launches); if (rc != SSEGPU_OK) return rc; }
     // header, counters and every per-record result array of this batch: one copy
     CU(cudaMemcpyAsync(b->h_block, b->d_block + b->ts_cap, b->meta_bytes, cudaMemcpyDeviceToHost, st));
     // Speculative copy of the frames: a canonical record grows by 26 + digits(seq) bytes
@@ -425,11 +498,9 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     b->spec_out = spec;
     if (spec) CU(cudaMemcpyAsync(b->h_out, b->d_out, spec, cudaMemcpyDeviceToHost, st));
     CU(cudaEventRecord(b->ev_done, st));
-    {
-        std::lock_guard<std::mutex> lk(ctx->mu);
-        b->state = SUBMITTED;
-        ctx->launches += n_launches;
-    }
+    if (!uses_tables) lk.lock();
+    b->state = SUBMITTED;
+    ctx->launches += n_launches;
     return SSEGPU_OK;
 }
 
@@ -471,6 +542,7 @@ int ssegpu_batch_release(ssegpu_ctx* ctx, ssegpu_batch* b) {
     if (b->state == SUBMITTED) { int rc = ssegpu_batch_wait(ctx, b, 0); if (b->state == SUBMITTED) return rc; }   // still in flight: a CUDA error; data-level errors free the slot
     std::lock_guard<std::mutex> lk(ctx->mu);
     b->state = FREE;
+    b->tab.reset(); b->insp.reset();
     return SSEGPU_OK;
 }
 
@@ -496,20 +568,32 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
     a.subj_len = d_subj_len; a.status = d_status;
     sse::scratch_carve(ctx->d_launch_scratch, a);
     a.plan = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(ctx->d_launch_scratch) + ((sse::scratch_bytes(ctx->cfg.max_records) + 15) & ~(size_t)15));
-    if (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE)) {
-        if (!ctx->d_insp || !ctx->bound_verdict || !ctx->bound_match) return SSEGPU_E_STATE;
-        if (ctx->insp_mode == sse::INSPECT_STREAMING && (!ctx->bound_conv || !ctx->d_conv_state || !ctx->d_tok_entry)) return SSEGPU_E_STATE;
-        a.insp = ctx->d_insp;
-        a.verdict = ctx->bound_verdict; a.match = ctx->bound_match;
-    }
-    if (op & SSEGPU_OP_MATCH) {
-        if (!ctx->d_interest || !ctx->bound_hit) return SSEGPU_E_STATE;
-        a.interest = ctx->d_interest; a.hit = ctx->bound_hit;
-    }
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
+    const bool uses_tables = (op & (SSEGPU_OP_INSPECT | SSEGPU_OP_INSPECT_INLINE | SSEGPU_OP_MATCH)) != 0;
+    std::unique_lock<std::mutex> lk(ctx->mu, std::defer_lock);
+    std::shared_ptr<TableGen> tab;
+    std::shared_ptr<InspGen> insp;
+    if (uses_tables) {
+        lk.lock();
+        const int rc = acquire_tables(ctx, op, st, tab, insp);
+        if (rc != SSEGPU_OK) return rc;
+        if (insp) {
+            if (!ctx->bound_verdict || !ctx->bound_match || (insp->mode == sse::INSPECT_STREAMING && !ctx->bound_conv)) return SSEGPU_E_STATE;
+            a.insp = insp->d_desc; a.verdict = ctx->bound_verdict; a.match = ctx->bound_match;
+        }
+        if (tab) {
+            if (!ctx->bound_hit) return SSEGPU_E_STATE;
+            a.interest = tab->d_desc; a.hit = ctx->bound_hit;
+        }
+    }
     uint32_t n_launches = 0;
-    { const int rc = launch_path(ctx, a, ctx->bound_conv, st, &n_launches); if (rc != SSEGPU_OK) return rc; }
-    std::lock_guard<std::mutex> lk(ctx->mu);
+    { const int rc = launch_path(ctx, a, ctx->bound_conv, st, insp.get(), &n_launches); if (rc != SSEGPU_OK) return rc; }
+    if (uses_tables) {
+        // a table update issued after this call waits for this launch; the generations themselves stay alive at least until
+        // the next update has been ordered behind that event (they are only ever freed on the table stream)
+        cudaEvent_t ev = ctx->ev_launch[ctx->next_launch_ev++ % ssegpu_ctx::kLaunchEvents];
+        CU(cudaEventRecord(ev, st));
+    } else lk.lock();
     ctx->launches += n_launches;
     return SSEGPU_OK;
 }
@@ -554,6 +638,25 @@ int ssegpu_encode_launch_result(ssegpu_ctx* ctx, uint64_t* out_bytes) {
     return hdr[1] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
 }
 
+// ---- table updates ---------------------------------------------------------------------------
+// With ctx->mu held: the table stream waits for every batch and device-resident launch in flight that reads tables.
+static int table_stream_wait_users(ssegpu_ctx* ctx) {
+    for (ssegpu_batch* b : ctx->slots)
+        if (b->state == SUBMITTED && (b->tab || b->insp)) CU(cudaStreamWaitEvent(ctx->table_stream, b->ev_done, 0));
+    for (cudaEvent_t e : ctx->ev_launch) CU(cudaStreamWaitEvent(ctx->table_stream, e, 0));
+    CU(cudaStreamWaitEvent(ctx->table_stream, ctx->ev_stream, 0));
+    return SSEGPU_OK;
+}
+
+__global__ void k_interest_apply(const SlotOp* __restrict__ ops, uint32_t n, sse::InterestSlot* slots) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4* src = reinterpret_cast<const uint4*>(&ops[i].image);
+    uint4* dst = reinterpret_cast<uint4*>(slots + ops[i].index);
+    dst[1] = src[1]; dst[2] = src[2]; dst[3] = src[3];
+    dst[0] = src[0];                                              // tag and value last (no reader runs beside this kernel anyway)
+}
+
 // ---- content inspection --------------------------------------------------------------------
 int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n, uint32_t mode) {
     if (!ctx || !pats || mode > 1) return SSEGPU_E_INVAL;
@@ -574,16 +677,19 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
     for (const sse_inspect::Dfa* d : dfas)
         offs.push_back({put(d->cls, 256), put(d->next.data(), d->next.size() * 2), put(d->acc_imm.data(), d->acc_imm.size() * 4),
                         put(d->acc_del.data(), d->acc_del.size() * 4), put(d->acc_eot.data(), d->acc_eot.size() * 4)});
-    void* d_blob = nullptr;
-    sse::InspectDev* d_desc = nullptr;
-    // new tables are built beside the live ones; on any failure they are freed and the old set stays in force
-    auto fail = [&](cudaError_t e, const char* what) { cudaFree(d_blob); cudaFree(d_desc); return cuda_fail(e, what); };
-    cudaError_t ce;
-    if ((ce = cudaMalloc(&d_blob, blob.size())) != cudaSuccess) return fail(ce, "cudaMalloc tables");
-    if ((ce = cudaMemcpy(d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy tables");
+    blob.resize((blob.size() + 31) & ~(size_t)15);
+    // A new generation is built beside the live one (uploads on the table stream, which nothing else is using yet); on
+    // any failure it is dropped and the old set stays in force.  No device-wide synchronisation anywhere.
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto gen = std::make_shared<InspGen>();
+    gen->stream = ctx->table_stream;
+    gen->mode = mode; gen->start_state = c.forward.start[0]; gen->n_states = c.forward.n_states; gen->n_classes = c.forward.n_classes;
+    CU(cudaMallocAsync(&gen->d_blob, blob.size(), ctx->table_stream));
+    CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_desc), sizeof(sse::InspectDev), ctx->table_stream));
+    CU(cudaMemcpyAsync(gen->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice, ctx->table_stream));
     sse::InspectDev h{};
     auto fill = [&](sse::DfaDev& dd, const sse_inspect::Dfa& d, const Off& o) {
-        const uint8_t* base = static_cast<const uint8_t*>(d_blob);
+        const uint8_t* base = static_cast<const uint8_t*>(gen->d_blob);
         dd.cls = base + o.cls; dd.next = reinterpret_cast<const uint16_t*>(base + o.next);
         dd.acc_imm = reinterpret_cast<const uint32_t*>(base + o.imm); dd.acc_del = reinterpret_cast<const uint32_t*>(base + o.del);
         dd.acc_eot = reinterpret_cast<const uint32_t*>(base + o.eot);
@@ -599,32 +705,36 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
         h.fixed_len[i] = c.patterns[i].min_len == c.patterns[i].max_len ? c.patterns[i].min_len : 0;
         h.anchored_of[i] = c.anchored_of[i];
     }
-    if ((ce = cudaMalloc(&d_desc, sizeof h)) != cudaSuccess) return fail(ce, "cudaMalloc descriptor");
-    if ((ce = cudaMemcpy(d_desc, &h, sizeof h, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy descriptor");
-    if ((ce = cudaDeviceSynchronize()) != cudaSuccess) return fail(ce, "cudaDeviceSynchronize");   // no batch may still be using the old tables
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    cudaFree(ctx->d_insp_blob); cudaFree(ctx->d_insp);
-    ctx->d_insp_blob = d_blob; ctx->d_insp = d_desc; ctx->insp_mode = mode; ctx->insp_start_state = c.forward.start[0];
-    ctx->insp_states = c.forward.n_states; ctx->insp_classes = c.forward.n_classes;
+    CU(cudaMemcpyAsync(gen->d_desc, &h, sizeof h, cudaMemcpyHostToDevice, ctx->table_stream));
+    CU(cudaStreamSynchronize(ctx->table_stream));                 // the host buffers above are about to go out of scope (own stream only)
     if (ctx->cfg.conv_slots) {
+        // a new pattern set restarts every conversation (the carried states belong to the old DFA): once the batches in
+        // flight that still use the old one are through
         if (!ctx->d_conv_state) CU(cudaMalloc(&ctx->d_conv_state, (size_t)ctx->cfg.conv_slots * 4));
-        std::vector<uint32_t> init(ctx->cfg.conv_slots, ctx->insp_start_state);
-        CU(cudaMemcpy(ctx->d_conv_state, init.data(), init.size() * 4, cudaMemcpyHostToDevice));
         if (mode == sse::INSPECT_STREAMING && !ctx->d_tok_entry) {     // token entries + sort scratch of the per-conversation walk
             CU(cudaMalloc(&ctx->d_tok_entry, (size_t)ctx->cfg.max_records * 32 + 32));
             CU(cudaMalloc(&ctx->d_stream_scratch, sse::stream_scratch_bytes(ctx->cfg.max_records)));
         }
+        { const int rc = table_stream_wait_users(ctx); if (rc != SSEGPU_OK) return rc; }
+        std::vector<uint32_t> init(ctx->cfg.conv_slots, gen->start_state);
+        CU(cudaMemcpyAsync(ctx->d_conv_state, init.data(), init.size() * 4, cudaMemcpyHostToDevice, ctx->table_stream));
+        CU(cudaStreamSynchronize(ctx->table_stream));
     }
+    CU(cudaEventRecord(ctx->ev_table, ctx->table_stream));
+    ctx->insp = gen;                                                  // the old generation goes when its last batch is released
     return SSEGPU_OK;
 }
 
 int ssegpu_conv_reset(ssegpu_ctx* ctx) {
     if (!ctx) return SSEGPU_E_INVAL;
-    if (!ctx->d_conv_state) return SSEGPU_OK;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!ctx->d_conv_state || !ctx->insp) return SSEGPU_OK;
     CU(cudaSetDevice(ctx->cfg.device));
-    CU(cudaDeviceSynchronize());
-    std::vector<uint32_t> init(ctx->cfg.conv_slots, ctx->insp_start_state);
-    CU(cudaMemcpy(ctx->d_conv_state, init.data(), init.size() * 4, cudaMemcpyHostToDevice));
+    { const int rc = table_stream_wait_users(ctx); if (rc != SSEGPU_OK) return rc; }
+    std::vector<uint32_t> init(ctx->cfg.conv_slots, ctx->insp->start_state);
+    CU(cudaMemcpyAsync(ctx->d_conv_state, init.data(), init.size() * 4, cudaMemcpyHostToDevice, ctx->table_stream));
+    CU(cudaStreamSynchronize(ctx->table_stream));
+    CU(cudaEventRecord(ctx->ev_table, ctx->table_stream));
     return SSEGPU_OK;
 }
 
@@ -636,57 +746,113 @@ int ssegpu_inspect_bind(ssegpu_ctx* ctx, const uint32_t* d_conv_slot, uint32_t* 
 }
 
 // ---- subscriber / interest table ---------------------------------------------------------------
-int ssegpu_interest_apply(ssegpu_ctx* ctx, const ssegpu_sub_delta* d, uint32_t n) {
-    if (!ctx || (n && !d)) return SSEGPU_E_INVAL;
-    CU(cudaSetDevice(ctx->cfg.device));
-    std::string err;
-    for (uint32_t i = 0; i < n; i++) {
-        if (!d[i].subject) return SSEGPU_E_INVAL;
-        std::string subj(d[i].subject, d[i].subject_len);
-        if (d[i].op == 0) { if (!ctx->interest.add(subj, d[i].sub_id, err)) { snprintf(g_cuda_err, sizeof g_cuda_err, "%s", err.c_str()); return SSEGPU_E_TOOBIG; } }
-        else if (d[i].op == 1) ctx->interest.del(subj, d[i].sub_id);
-        else return SSEGPU_E_INVAL;
-    }
+// A new device generation from the host table's flattened form (with ctx->mu held).
+static int interest_rebuild(ssegpu_ctx* ctx) {
     sse_interest::HostTable& t = ctx->interest;
     t.flatten();
-    void *ds = nullptr, *dk = nullptr, *dw = nullptr;
-    sse::InterestDev* dd = nullptr;
-    // the new table is built beside the live one; on a CUDA failure it is freed and the device keeps the old version
-    // (the host-side table already holds the deltas: the next successful apply uploads them)
-    auto fail = [&](cudaError_t e, const char* what) { cudaFree(ds); cudaFree(dk); cudaFree(dw); cudaFree(dd); return cuda_fail(e, what); };
-    cudaError_t ce;
-    if ((ce = cudaMalloc(&ds, t.slots.size() * sizeof(sse::InterestSlot))) != cudaSuccess) return fail(ce, "cudaMalloc interest slots");
-    if ((ce = cudaMalloc(&dk, t.keys.size() * 4)) != cudaSuccess) return fail(ce, "cudaMalloc interest keys");
-    if ((ce = cudaMalloc(&dw, t.wild_bytes.size())) != cudaSuccess) return fail(ce, "cudaMalloc wildcards");
-    if ((ce = cudaMalloc(&dd, sizeof(sse::InterestDev))) != cudaSuccess) return fail(ce, "cudaMalloc descriptor");
-    if ((ce = cudaMemcpy(ds, t.slots.data(), t.slots.size() * sizeof(sse::InterestSlot), cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy interest slots");
-    if ((ce = cudaMemcpy(dk, t.keys.data(), t.keys.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy interest keys");
-    if ((ce = cudaMemcpy(dw, t.wild_bytes.data(), t.wild_bytes.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy wildcards");
+    auto gen = std::make_shared<TableGen>();
+    gen->stream = ctx->table_stream;
+    gen->subs = t.subs; gen->wild_ids = t.wild_ids;
+    cudaStream_t ts = ctx->table_stream;
+    CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_slots), t.slots.size() * sizeof(sse::InterestSlot), ts));
+    CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_keys), t.keys.size() * 4, ts));
+    CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_wild), t.wild_bytes.size(), ts));
+    CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_desc), sizeof(sse::InterestDev), ts));
+    CU(cudaMemcpyAsync(gen->d_slots, t.slots.data(), t.slots.size() * sizeof(sse::InterestSlot), cudaMemcpyHostToDevice, ts));
+    CU(cudaMemcpyAsync(gen->d_keys, t.keys.data(), t.keys.size() * 4, cudaMemcpyHostToDevice, ts));
+    CU(cudaMemcpyAsync(gen->d_wild, t.wild_bytes.data(), t.wild_bytes.size(), cudaMemcpyHostToDevice, ts));
     sse::InterestDev h{};
-    h.slots = static_cast<const sse::InterestSlot*>(ds); h.keys = static_cast<const uint32_t*>(dk);
+    h.slots = gen->d_slots; h.keys = gen->d_keys;
     h.wild_single = t.wild_single; h.wild_generic = t.wild_generic;
     h.mask = (uint32_t)t.slots.size() - 1; h.n_wild = (uint32_t)t.wild_ids.size();
-    h.wild_bytes = static_cast<const uint8_t*>(dw);
+    h.wild_bytes = gen->d_wild;
     for (size_t i = 0; i < t.wild_off.size(); i++) h.wild_off[i] = t.wild_off[i];
-    if ((ce = cudaMemcpy(dd, &h, sizeof h, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(ce, "cudaMemcpy descriptor");
-    if ((ce = cudaDeviceSynchronize()) != cudaSuccess) return fail(ce, "cudaDeviceSynchronize");   // versioned swap: no batch may still read the old table
+    CU(cudaMemcpyAsync(gen->d_desc, &h, sizeof h, cudaMemcpyHostToDevice, ts));
+    CU(cudaStreamSynchronize(ts));                                // own stream only: the uploads came from pageable host memory
+    CU(cudaEventRecord(ctx->ev_table, ts));
+    ctx->tab = gen;                                               // batches in flight keep the old generation alive until they are released
+    return SSEGPU_OK;
+}
+
+int ssegpu_interest_apply(ssegpu_ctx* ctx, const ssegpu_sub_delta* d, uint32_t n) {
+    if (!ctx || (n && !d)) return SSEGPU_E_INVAL;
+    for (uint32_t i = 0; i < n; i++) if (!d[i].subject || d[i].op > 1) return SSEGPU_E_INVAL;
+    CU(cudaSetDevice(ctx->cfg.device));
     std::lock_guard<std::mutex> lk(ctx->mu);
-    cudaFree(ctx->d_int_slots); cudaFree(ctx->d_int_keys); cudaFree(ctx->d_int_wild); cudaFree(ctx->d_interest);
-    ctx->d_int_slots = ds; ctx->d_int_keys = dk; ctx->d_int_wild = dw; ctx->d_interest = dd;
+    sse_interest::HostTable& t = ctx->interest;
+    std::string err;
+    bool rebuild = !ctx->tab || !t.flattened;
+    for (uint32_t i = 0; i < n; i++) {
+        std::string subj(d[i].subject, d[i].subject_len);
+        const int ch = d[i].op == 0 ? t.add(subj, d[i].sub_id, err) : t.del(subj, d[i].sub_id);
+        if (ch < 0) {                                             // the deltas before this one stay applied
+            snprintf(g_cuda_err, sizeof g_cuda_err, "%s", err.c_str());
+            if (interest_rebuild(ctx) == SSEGPU_OK) ctx->table_version++;
+            return SSEGPU_E_TOOBIG;
+        }
+        if (ch == 2) rebuild = true;                              // the wildcard list lives in the descriptor: new generation
+        else if (ch == 1 && !rebuild && !t.sync_subject(subj)) rebuild = true;
+    }
+    if (!rebuild && t.dirty.size() > (size_t)ssegpu_ctx::kOpsPerChunk) rebuild = true;
+    if (rebuild) {
+        const int rc = interest_rebuild(ctx);
+        if (rc == SSEGPU_OK) ctx->table_version++;
+        return rc;
+    }
+    if (!t.dirty.empty()) {
+        // in place: the changed slots go to the device through a pinned staging chunk and a small kernel on the table
+        // stream, which first waits for the batches in flight; batches submitted from now on wait for it (ev_table)
+        const int chunk = ctx->next_chunk++ % ssegpu_ctx::kOpChunks;
+        CU(cudaEventSynchronize(ctx->ev_chunk[chunk]));           // the chunk's previous use (kOpChunks updates ago) has been consumed
+        SlotOp* h = ctx->h_ops + (size_t)chunk * ssegpu_ctx::kOpsPerChunk;
+        SlotOp* dv = ctx->d_ops + (size_t)chunk * ssegpu_ctx::kOpsPerChunk;
+        const uint32_t m = (uint32_t)t.dirty.size();
+        for (uint32_t k = 0; k < m; k++) { h[k].index = t.dirty[k]; h[k].image = t.slots[t.dirty[k]]; }
+        t.dirty.clear();
+        { const int rc = table_stream_wait_users(ctx); if (rc != SSEGPU_OK) return rc; }
+        CU(cudaMemcpyAsync(dv, h, sizeof(SlotOp) * m, cudaMemcpyHostToDevice, ctx->table_stream));
+        k_interest_apply<<<(m + 127) / 128, 128, 0, ctx->table_stream>>>(dv, m, ctx->tab->d_slots);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(ctx->ev_chunk[chunk], ctx->table_stream));
+        CU(cudaEventRecord(ctx->ev_table, ctx->table_stream));
+    }
+    ctx->table_version++;
     return SSEGPU_OK;
 }
 
 const uint32_t* ssegpu_interest_subs(ssegpu_ctx* ctx, uint32_t* count) {
     if (!ctx) return nullptr;
-    if (count) *count = (uint32_t)ctx->interest.subs.size();
-    return ctx->interest.subs.data();
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (count) *count = (uint32_t)ctx->interest.subs->size();
+    return ctx->interest.subs->data();
 }
 
 const uint32_t* ssegpu_interest_wild_ids(ssegpu_ctx* ctx, uint32_t* count) {
     if (!ctx) return nullptr;
+    std::lock_guard<std::mutex> lk(ctx->mu);
     if (count) *count = (uint32_t)ctx->interest.wild_ids.size();
     return ctx->interest.wild_ids.data();
 }
+
+uint64_t ssegpu_interest_version(ssegpu_ctx* ctx) {
+    if (!ctx) return 0;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return ctx->table_version;
+}
+
+const uint32_t* ssegpu_batch_subs(const ssegpu_batch* b, uint32_t* count) {
+    if (!b || !b->tab) { if (count) *count = 0; return nullptr; }
+    if (count) *count = (uint32_t)b->tab->subs->size();
+    return b->tab->subs->data();
+}
+
+const uint32_t* ssegpu_batch_wild_ids(const ssegpu_batch* b, uint32_t* count) {
+    if (!b || !b->tab) { if (count) *count = 0; return nullptr; }
+    if (count) *count = (uint32_t)b->tab->wild_ids.size();
+    return b->tab->wild_ids.data();
+}
+
+uint64_t ssegpu_batch_table_version(const ssegpu_batch* b) { return b ? b->table_version : 0; }
 
 int ssegpu_interest_bind(ssegpu_ctx* ctx, uint32_t* d_sub_span) {
     if (!ctx) return SSEGPU_E_INVAL;

@@ -173,6 +173,8 @@ int ssegpu_counters_get(ssegpu_ctx *ctx, ssegpu_counters *out);
  * mode; INT32_MIN with SSEGPU_VERDICT_BEGIN_UNKNOWN for variable-length patterns whose start is not recoverable). */
 typedef struct { uint32_t kind; uint32_t action; const char *text; } ssegpu_pattern;
 #define SSEGPU_VERDICT_BEGIN_UNKNOWN 0x10000u
+/* Safe while batches are in flight: the new tables become a new generation, batches already submitted finish on the old
+ * one (freed when the last of them is released), later ones use the new one.  Restarts every conversation slot. */
 int ssegpu_patterns_load(ssegpu_ctx *ctx, const ssegpu_pattern *patterns, uint32_t n, uint32_t mode);
 int ssegpu_conv_reset(ssegpu_ctx *ctx);                        /* every conversation slot back to the start state */
 const uint32_t *ssegpu_verdict(const ssegpu_batch *b);         /* n  */
@@ -184,13 +186,27 @@ int ssegpu_inspect_bind(ssegpu_ctx *ctx, const uint32_t *d_conv_slot, uint32_t *
 /* Replaces, for this path, the subscription matching that the reference delegates to nats.go / nats-server:
  * nc.Subscribe("chat.<id>.tokens", cb) per connection (sse_handler.go:133-135, :314-316), wildcard consumers such
  * as chat.*.tokens (docs/security-inspection-patterns.md:110,268).  NATS subject rules: '.'-separated tokens, '*' = one
- * token, '>' = the rest.  ssegpu_interest_apply adds (op 0) / removes (op 1) (subject, subscriber id) pairs and swaps
- * the device table in (synchronous).  With SSEGPU_OP_MATCH every record gets three words in ssegpu_sub_span():
- * [3i] offset and [3i+1] count of its subscriber ids inside ssegpu_interest_subs(), [3i+2] bit mask over
- * ssegpu_interest_wild_ids() of the wildcard subscriptions that match.  At most 32 wildcard subscriptions. */
+ * token, '>' = the rest.  ssegpu_interest_apply adds (op 0) / removes (op 1) (subject, subscriber id) pairs.  The
+ * reference does one such change per HTTP connect / disconnect (sse_handler.go:133-135, :166-169), so a call is cheap:
+ * a literal subscription changes ONE slot of the device table in place (a small copy + kernel on the context's table
+ * stream, ordered by events: after the batches in flight that read the table, before the batches submitted later --
+ * no device-wide synchronisation, the call does not wait for the GPU); the table is rebuilt as a new generation only
+ * when its slots are half full, its id arena is full, or the wildcard list changes.  Safe to call from any thread
+ * while other threads submit: every batch sees exactly the deltas of the calls that returned before its submit
+ * (ssegpu_batch_table_version = number of successful calls it saw).
+ * With SSEGPU_OP_MATCH every record gets three words in ssegpu_sub_span(): [3i] offset and [3i+1] count of its subscriber
+ * ids inside ssegpu_batch_subs(), [3i+2] bit mask over ssegpu_batch_wild_ids() of the wildcard subscriptions that
+ * match.  At most 32 wildcard subscriptions. */
 typedef struct { uint32_t op; uint32_t sub_id; const char *subject; uint32_t subject_len; } ssegpu_sub_delta;
 int ssegpu_interest_apply(ssegpu_ctx *ctx, const ssegpu_sub_delta *deltas, uint32_t n);
-const uint32_t *ssegpu_interest_subs(ssegpu_ctx *ctx, uint32_t *count);      /* host copy, valid until the next apply */
+uint64_t ssegpu_interest_version(ssegpu_ctx *ctx);                           /* successful applies so far */
+/* The subscriber-id arena / wildcard ids of the table generation a batch was matched against: valid from wait to release
+ * of that batch, whatever ssegpu_interest_apply does meanwhile. */
+const uint32_t *ssegpu_batch_subs(const ssegpu_batch *b, uint32_t *count);
+const uint32_t *ssegpu_batch_wild_ids(const ssegpu_batch *b, uint32_t *count);
+uint64_t ssegpu_batch_table_version(const ssegpu_batch *b);
+/* The same for the CURRENT generation (for ssegpu_frame_launch users): valid until the next ssegpu_interest_apply. */
+const uint32_t *ssegpu_interest_subs(ssegpu_ctx *ctx, uint32_t *count);
 const uint32_t *ssegpu_interest_wild_ids(ssegpu_ctx *ctx, uint32_t *count);
 const uint32_t *ssegpu_sub_span(const ssegpu_batch *b);                      /* 3n */
 int ssegpu_interest_bind(ssegpu_ctx *ctx, uint32_t *d_sub_span);             /* buffer used by ssegpu_frame_launch */

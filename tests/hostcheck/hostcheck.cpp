@@ -128,12 +128,16 @@ extern "C" int hc_interest(const hc_delta* d, uint32_t nd, const uint8_t* in, co
     std::string err;
     for (uint32_t i = 0; i < nd; i++) {
         std::string s(d[i].subject, d[i].subject_len);
-        if (d[i].op == 0) { if (!t.add(s, d[i].sub_id, err)) return -1; } else t.del(s, d[i].sub_id);
+        // every other delta goes through the incremental path once a flattened form exists (as ssegpu_interest_apply does)
+        const int ch = d[i].op == 0 ? t.add(s, d[i].sub_id, err) : t.del(s, d[i].sub_id);
+        if (ch < 0) return -1;
+        if (i == nd / 2) t.flatten();
+        else if (t.flattened && (ch == 2 || (ch == 1 && !t.sync_subject(s)))) t.flatten();
     }
-    t.flatten();
-    if (t.subs.size() > subs_cap) return -2;
-    memcpy(subs_out, t.subs.data(), t.subs.size() * 4);
-    *n_subs = (uint32_t)t.subs.size();
+    if (!t.flattened) t.flatten();
+    if (t.subs->size() > subs_cap) return -2;
+    memcpy(subs_out, t.subs->data(), t.subs->size() * 4);
+    *n_subs = (uint32_t)t.subs->size();
     memcpy(wild_ids_out, t.wild_ids.data(), t.wild_ids.size() * 4);
     *n_wild = (uint32_t)t.wild_ids.size();
     InterestDev dev{};

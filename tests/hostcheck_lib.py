@@ -60,7 +60,7 @@ def interest(lib, deltas, arena, off):
     arr = (HcDelta * len(deltas))(*[HcDelta(o, i, s, len(s)) for o, i, s in deltas])
     hit = np.zeros(3 * n, dtype=np.uint32)
     status = np.zeros(n, dtype=np.uint32)
-    subs = np.zeros(len(deltas) + 1, dtype=np.uint32)
+    subs = np.zeros(64 * len(deltas) + 65536, dtype=np.uint32)     # the arena is append-only between rebuilds
     wild = np.zeros(64, dtype=np.uint32)
     ns, nw = C.c_uint32(0), C.c_uint32(0)
     rc = lib.hc_interest(arr, len(deltas), _ptr(arena, u8p), _ptr(off, u32p), n, _ptr(hit, u32p), _ptr(status, u32p),

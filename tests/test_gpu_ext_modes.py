@@ -294,3 +294,37 @@ def test_interest_table_at_config3_shape(pkg, oracle):
                 assert got[i] == (want[i] if int(r["status"][i]) & 0xF == 0 else b"")
     finally:
         eng.close()
+
+
+def test_streaming_batches_on_different_ring_slots_run_in_submit_order(pkg, oracle):
+    """A conversation with tokens in two batches that are in flight together: the second batch must start from the state the
+    first one commits (streaming batches of a context execute in submit order), so a pattern split across them is found."""
+    insp = oracle.inspector(SET_B)
+    n_conv = 2000
+    eng = pkg.SseGpu(device=0, max_records=1 << 13, max_in_bytes=2 << 20, ring_slots=4, conv_slots=n_conv)
+    try:
+        eng.load_patterns(SET_B, pkg.INSPECT_STREAMING)
+        halves = [("my pass", "word is"), ("ignore pre", "vious now"), ("sec", "ret"), ("plain ", "text")]
+        for rep in range(5):
+            first = [mg.canon("conv-%d" % c, halves[c % 4][0], 2 * rep + 1, False, 5) for c in range(n_conv)]
+            second = [mg.canon("conv-%d" % c, halves[c % 4][1], 2 * rep + 2, True, 5) for c in range(n_conv)]
+            conv = np.arange(n_conv, dtype=np.uint32)
+            slots = []
+            for payloads in (first, second):                      # both submitted before either is waited for
+                arena, off = oracle.pack(payloads)
+                b = eng.acquire()
+                b.fill(arena, off, None, conv)
+                b.submit(n_conv, pkg.OP_INSPECT)
+                slots.append(b)
+            v1 = slots[0].wait().verdict.copy()
+            v2 = slots[1].wait().verdict.copy()
+            for b in slots:
+                b.release()
+            assert not v1.any()
+            for c in range(n_conv):
+                a, z = halves[c % 4]
+                text = (a + z).encode()
+                assert int(v2[c]) == insp.stream(text, len(a), len(text), True)[0], (rep, c)
+            assert (v2[0::4] != 0).all() and (v2[3::4] == 0).all()
+    finally:
+        eng.close()
