@@ -481,26 +481,40 @@ def run_gpu(args):
         h2d += a16(nbytes) + 32 + 4 * (m + 1)
         d2h += 4160 + a16(8 * (m + 1)) + 2 * a16(4 * m + 4) + nbytes + 32 * m + 16 * ((m + 127) // 128)
 
-    def e2e_step():
+    def e2e_step(flags=0):
         for b in slots:
-            b.submit(b.n, op)
+            b.submit(b.n, op | flags)
         frames = 0
         for b in slots:
             b.wait()
             frames += b.n
         return frames
 
-    for _ in range(2):
-        e2e_step()
-    torch.cuda.synchronize()
-    if use_dist:
-        dist.barrier()
-    t0 = time.perf_counter()
-    e2e_frames = 0
-    for _ in range(args.steps):
-        e2e_frames += e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
+    def e2e_timed(flags=0):
+        for _ in range(2):
+            e2e_step(flags)
+        torch.cuda.synchronize()
+        if use_dist:
+            dist.barrier()
+        t0 = time.perf_counter()
+        frames = 0
+        for _ in range(args.steps):
+            frames += e2e_step(flags)
+        torch.cuda.synchronize()
+        return frames, time.perf_counter() - t0
+
+    # SSEGPU_OP_HEADER_ONLY egress first (the default mode runs last so that the spot check below sees its output): the GPU
+    # returns only the header of every Go-marshalled frame; the host still holds the payload in the pinned input slot and
+    # appends it when it writes to the connection (host/adapter_host.cpp does, tests/test_gpu_adapter_host.py checks the bytes)
+    _, e2e_hdr_s = e2e_timed(pkg.OP_HEADER_ONLY)
+    hdr = slots[0]
+    assert int(hdr.status[0]) & pkg.ST_HEADER_ONLY
+    hdr_frame0 = hdr.out[int(hdr.out_off[0]):int(hdr.out_off[0]) + int(hdr.out_len[0])].tobytes() + \
+        arena[int(off[0]):int(off[1])].tobytes() + b"\n\n"
+    d2h_hdr = sum(4160 + ((8 * (b.n + 1) + 15) & ~15) + 2 * ((4 * b.n + 4 + 15) & ~15) + 32 * b.n + 16 * ((b.n + 127) // 128) for b in slots)
+    e2e_frames, e2e_s = e2e_timed()
+    first = slots[0]
+    assert hdr_frame0 == first.out[int(first.out_off[0]):int(first.out_off[0]) + int(first.out_len[0])].tobytes()
     clocks = sampler.stop() if rank == 0 else None
     # spot check the e2e output of the last step against the device-resident arm
     last = slots[-1]
@@ -526,7 +540,7 @@ def run_gpu(args):
 
     # ---------------- gather over ranks ----------------
     tot = torch.tensor([float(n), float(in_bytes), float(out_bytes), float(e2e_frames)], dtype=torch.float64, device="cuda")
-    mx = torch.tensor([dev_ms, kern_ms, e2e_s], dtype=torch.float64, device="cuda")
+    mx = torch.tensor([dev_ms, kern_ms, e2e_s, e2e_hdr_s], dtype=torch.float64, device="cuda")
     if use_dist:
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -551,6 +565,10 @@ def run_gpu(args):
             "e2e": {"value": e2e_all / mx[2], "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "batches_per_step": nb, "records_per_batch": E2E_BATCH, "ms_per_step": 1e3 * mx[2] / args.steps,
                     "bytes_per_sec": (in_all + out_all) * args.steps / mx[2]},
+            "e2e_header_only": {"value": e2e_all / mx[3], "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h_hdr),
+                                "ms_per_step": 1e3 * mx[3] / args.steps,
+                                "note": "SSEGPU_OP_HEADER_ONLY: only frame headers + offsets + status cross back; the host appends the payload it "
+                                        "still holds in the pinned input slot when it writes to the connection"},
             "gpu_launches": int(launches), "gpu_launches_e2e": int(e2e_launches),
             "roofline": {"bound": "hbm", "kernel": "k_frame_tiles", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "peak_source": which, "frac_of_8000_datasheet": achieved / 8000.0, "traffic": measured_traffic("k_frame_tiles", n),

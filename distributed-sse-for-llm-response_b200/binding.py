@@ -7,14 +7,14 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 OP_ADAPTER, OP_BRIDGE, OP_GO122, OP_NO_FAST, OP_ORDERED, OP_INSPECT, OP_INSPECT_INLINE, OP_MATCH = 0, 1, 2, 4, 8, 16, 32, 64
-OP_NATS_PUB, OP_RESP = 128, 256
+OP_NATS_PUB, OP_RESP, OP_HEADER_ONLY = 128, 256, 512
 ST_NO_INTEREST = 5
 INSPECT_PER_TOKEN, INSPECT_STREAMING = 0, 1
 KIND_LITERAL, KIND_REGEX = 0, 1
 ACT_ALLOW, ACT_REDACT, ACT_DROP, ACT_ALERT = 0, 1, 2, 3
 VERDICT_BEGIN_UNKNOWN = 0x10000
 ST_OK, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_INSPECT_DROP = 0, 1, 2, 3, 4
-ST_CODE_MASK, ST_DONE, ST_REDACTED = 0xF, 0x100, 0x200
+ST_CODE_MASK, ST_DONE, ST_REDACTED, ST_HEADER_ONLY = 0xF, 0x100, 0x200, 0x400
 E_OVERFLOW, E_AGAIN, E_CONVSLOT, E_PATTERN = -6, -4, -9, -10
 
 u8p, u32p, u64p, i64p = (C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_int64))

@@ -429,7 +429,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
                             sp.cid_esc = pl.cid_esc; sp.tok_esc = pl.tok_esc;  // the general decoder does not note escapes; same literal ranges
                             len = measure_slow(s_in, o, L, &sp, a.op);
                             pl = sp;
-                            st |= ST_REDACTED;
+                            st = (st & ~ST_HEADER_ONLY) | ST_REDACTED;                 // a re-marshalled record goes out whole
                         }
                     }
                 }

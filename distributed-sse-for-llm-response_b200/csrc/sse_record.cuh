@@ -39,11 +39,11 @@ namespace sse {
 enum : uint32_t {
     ST_OK = 0, ST_ERR_SYNTAX = 1, ST_ERR_TYPE = 2, ST_FILTERED = 3, ST_INSPECT_DROP = 4, ST_NO_INTEREST = 5,
     ST_PENDING = 0xE,            // internal: left to the tail phase of the tile kernel, never visible to the caller
-    ST_CODE_MASK = 0xF, ST_DONE = 0x100, ST_REDACTED = 0x200,
+    ST_CODE_MASK = 0xF, ST_DONE = 0x100, ST_REDACTED = 0x200, ST_HEADER_ONLY = 0x400,
 };
 // op flags (mirrors include/ssegpu.h)
 enum : uint32_t { OP_BRIDGE = 1u, OP_GO122 = 2u, OP_NO_FAST = 4u, OP_ORDERED = 8u, OP_INSPECT = 16u, OP_INSPECT_INLINE = 32u, OP_MATCH = 64u,
-                  OP_NATS_PUB = 128u, OP_RESP = 256u };
+                  OP_NATS_PUB = 128u, OP_RESP = 256u, OP_HEADER_ONLY = 512u };
 
 constexpr uint32_t MAX_NESTING = 10000;            // encoding/json scanner.go maxNestingDepth
 constexpr uint32_t NEST_WORDS = MAX_NESTING / 32 + 1;
@@ -879,6 +879,10 @@ SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, 
     out_len = (op & OP_BRIDGE) ? 12 + (pl.cid_e - pl.cid_b) + L : 26 + pl.seq_n + L;
     if ((op & (OP_BRIDGE | OP_NATS_PUB)) == (OP_BRIDGE | OP_NATS_PUB)) out_len += 9 + dec_digits(L);   // "PUB " + " " + digits + CRLF, CRLF
     st = pl.done ? (ST_OK | ST_DONE) : ST_OK;
+    if (op & OP_HEADER_ONLY) {      // the payload (which IS the JSON) and the trailer stay with the host: only what precedes them is produced
+        out_len -= L + ((op & OP_BRIDGE) ? ((op & OP_NATS_PUB) ? 2u : 0u) : 2u);
+        st |= ST_HEADER_ONLY;
+    }
     return true;
 }
 
@@ -891,6 +895,7 @@ SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, 
 // Pass 2 for records accepted by plan_record_fast(): header + verbatim payload (+ trailer).
 template <class Src, class W>
 SSE_HD void emit_record_fast(const Src& s, uint32_t o, uint32_t L, const Plan& pl, uint32_t op, W& w, uint32_t* subj_len) {
+    const bool body = !(op & OP_HEADER_ONLY);
     if (op & OP_BRIDGE) {
         const bool pub = (op & OP_NATS_PUB) != 0;
         if (pub) { w.put32(w4("PUB ")); SSE_PUT_LIT_NF(w, "chat."); }   // nats.go publish(): PUB <subject> <#bytes>CRLF<payload>CRLF
@@ -899,15 +904,19 @@ SSE_HD void emit_record_fast(const Src& s, uint32_t o, uint32_t L, const Plan& p
         SSE_PUT_LIT_NF(w, ".tokens");
         if (subj_len) *subj_len = 12 + (pl.cid_e - pl.cid_b);
         if (pub) { w.put_n_nf(' ', 1); put_int(w, (int64_t)L); w.put_n_nf(w4("\r\n\0\0"), 2); }
-        put_copy_t<true>(s, o, L, w);                     // main.go:161
-        if (pub) w.put_n_nf(w4("\r\n\0\0"), 2);
+        if (body) {
+            put_copy_t<true>(s, o, L, w);                 // main.go:161
+            if (pub) w.put_n_nf(w4("\r\n\0\0"), 2);
+        }
     } else {
         w.put32(w4("even"));                              // sse_handler.go:212-213
         SSE_PUT_LIT_NF(w, "t: token\nid: ");
         put_copy_t<true>(s, o + pl.seq_b, pl.seq_n, w);   // canonical literal == fmt %d
         SSE_PUT_LIT_NF(w, "\ndata: ");                    // :214
-        put_copy_t<true>(s, o, L, w);
-        w.put_n_nf(w4("\n\n\0\0"), 2);
+        if (body) {
+            put_copy_t<true>(s, o, L, w);
+            w.put_n_nf(w4("\n\n\0\0"), 2);
+        }
     }
     w.finish();
 }

@@ -493,7 +493,8 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
     CU(cudaMemcpyAsync(b->h_block, b->d_block + b->ts_cap, b->meta_bytes, cudaMemcpyDeviceToHost, st));
     // Speculative copy of the frames: a canonical record grows by 26 + digits(seq) bytes
     // (28 + len("chat..tokens")=40ish in bridge mode); anything beyond is fetched in wait().
-    uint64_t spec = in_total + (uint64_t)n * ((op & SSEGPU_OP_BRIDGE) ? ((op & SSEGPU_OP_NATS_PUB) ? 96 : 80) : 32) + 16ull * ((n + sse::TILE - 1) / sse::TILE);
+    uint64_t spec = ((op & SSEGPU_OP_HEADER_ONLY) ? 0 : in_total) + (uint64_t)n * ((op & SSEGPU_OP_BRIDGE) ? ((op & SSEGPU_OP_NATS_PUB) ? 96 : 80) : 32) +
+                    16ull * ((n + sse::TILE - 1) / sse::TILE);
     if (spec > ctx->out_cap) spec = ctx->out_cap;
     b->spec_out = spec;
     if (spec) CU(cudaMemcpyAsync(b->h_out, b->d_out, spec, cudaMemcpyDeviceToHost, st));
@@ -612,7 +613,7 @@ int ssegpu_frame_launch_result(ssegpu_ctx* ctx, ssegpu_counters* out) {
 int ssegpu_encode_launch(ssegpu_ctx* ctx, const void* d_cid, const uint32_t* d_cid_off, const void* d_tok, const uint32_t* d_tok_off,
                          const int64_t* d_seq, const uint8_t* d_done, const int64_t* d_ts, uint32_t n, uint32_t op,
                          void* d_out, uint64_t out_cap, uint64_t* d_out_off, uint32_t* d_out_len, uint32_t* d_chan_len, void* stream) {
-    if (!ctx || !d_out_off || (op & ~(uint32_t)(SSEGPU_OP_BRIDGE | SSEGPU_OP_GO122 | SSEGPU_OP_RESP))) return SSEGPU_E_INVAL;
+    if (!ctx || !d_out_off || (op & ~(uint32_t)(SSEGPU_OP_BRIDGE | SSEGPU_OP_GO122 | SSEGPU_OP_RESP))) return SSEGPU_E_INVAL;   // (no SSEGPU_OP_HEADER_ONLY here: the encoder's output IS the payload)
     if (n && (!d_cid || !d_cid_off || !d_tok || !d_tok_off || !d_seq || !d_done || !d_ts || !d_out || !d_out_len)) return SSEGPU_E_INVAL;
     if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
     if ((reinterpret_cast<uintptr_t>(d_cid) | reinterpret_cast<uintptr_t>(d_tok) | reinterpret_cast<uintptr_t>(d_out)) & 15) return SSEGPU_E_INVAL;

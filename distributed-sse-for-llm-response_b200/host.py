@@ -28,6 +28,7 @@ def _lib():
         lib.ssehost_flush.argtypes = [vp]
         lib.ssehost_take.argtypes = [vp, C.c_uint64, C.c_char_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_int)]
         lib.ssehost_stats.argtypes = [vp, C.POINTER(C.c_uint64)]
+        lib.ssehost_set_header_only.argtypes = [vp, C.c_int]
         _LIB = lib
     return _LIB
 
@@ -43,6 +44,10 @@ class AdapterHost:
     def _check(self, rc):
         if rc != 0:
             raise SseGpuError(rc, self.engine.lib.ssegpu_strerror(rc).decode())
+
+    def set_header_only(self, on=True):
+        """SSEGPU_OP_HEADER_ONLY egress: the GPU returns frame headers only, the coalescing loop adds the payload it still holds"""
+        self._check(self.lib.ssehost_set_header_only(self.h, int(on)))
 
     def connect(self, conn_id, conversation_id, last_event_id=None, chat=False):
         self._check(self.lib.ssehost_connect(self.h, conn_id, conversation_id, last_event_id, int(chat)))

@@ -50,6 +50,7 @@ struct ssehost {
     uint64_t delivered = 0;        // sse_messages_delivered_total
     uint64_t dropped_bad = 0, filtered = 0, after_close = 0;
     std::string err;
+    bool header_only = false;      // SSEGPU_OP_HEADER_ONLY egress (ssehost_set_header_only)
 };
 
 extern "C" {
@@ -126,7 +127,7 @@ int ssehost_on_message(ssehost* h, uint64_t conn_id, const uint8_t* data, uint32
 int ssehost_flush(ssehost* h) {
     if (!h) return SSEGPU_E_INVAL;
     if (!h->cur || h->n == 0) return SSEGPU_OK;
-    int rc = ssegpu_batch_submit(h->ctx, h->cur, h->n, SSEGPU_OP_ADAPTER, /*use_filter=*/1);
+    int rc = ssegpu_batch_submit(h->ctx, h->cur, h->n, SSEGPU_OP_ADAPTER | (h->header_only ? SSEGPU_OP_HEADER_ONLY : 0u), /*use_filter=*/1);
     if (rc == SSEGPU_OK) rc = ssegpu_batch_wait(h->ctx, h->cur, 0);
     if (rc == SSEGPU_OK) {
         const uint8_t* out = ssegpu_out_bytes(h->cur);
@@ -140,6 +141,11 @@ int ssehost_flush(ssehost* h) {
             if (code == SSEGPU_ST_FILTERED) { h->filtered++; continue; }          // sse_handler.go:143-145
             if (code != SSEGPU_ST_OK) { h->dropped_bad++; continue; }             // :137-140 log + drop
             c.pending.append(reinterpret_cast<const char*>(out + off[i]), len[i]);
+            if (st[i] & SSEGPU_ST_HEADER_ONLY) {      // Go-marshalled record: its JSON is the payload, which never left this batch's pinned input
+                const uint32_t* in_off = ssegpu_in_off(h->cur);
+                c.pending.append(reinterpret_cast<const char*>(ssegpu_in_bytes(h->cur) + in_off[i]), in_off[i + 1] - in_off[i]);
+                c.pending.append("\n\n", 2);
+            }
             c.frames++;
             h->delivered++;                                                       // messagesDelivered.Inc(), :217
             if (st[i] & SSEGPU_ST_DONE) c.closed = true;                          // :220-226 return after the done frame
@@ -164,6 +170,14 @@ int ssehost_take(ssehost* h, uint64_t conn_id, uint8_t* buf, uint64_t cap, uint6
         if (!c.pending.empty()) { memcpy(buf, c.pending.data(), c.pending.size()); c.writes++; }
         c.pending.clear();
     }
+    return SSEGPU_OK;
+}
+
+// Egress without the bytes the host already has (SSEGPU_OP_HEADER_ONLY): the GPU returns only each frame's header, the
+// coalescing loop above appends the payload from the pinned input slot and the blank line.
+int ssehost_set_header_only(ssehost* h, int on) {
+    if (!h) return SSEGPU_E_INVAL;
+    h->header_only = on != 0;
     return SSEGPU_OK;
 }
 

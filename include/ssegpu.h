@@ -58,6 +58,7 @@ typedef enum {
 #define SSEGPU_ST_CODE_MASK     0xFu
 #define SSEGPU_ST_DONE          0x100u
 #define SSEGPU_ST_REDACTED      0x200u
+#define SSEGPU_ST_HEADER_ONLY   0x400u /* SSEGPU_OP_HEADER_ONLY: the output slice holds only what precedes the payload */
 
 /* ---- op flags for submit / launch -------------------------------------------------- */
 #define SSEGPU_OP_ADAPTER   0u   /* SSE frame: event/id/data lines (sse_handler.go:211-214, :427-430) */
@@ -80,6 +81,14 @@ typedef enum {
 #define SSEGPU_OP_RESP      256u /* ssegpu_encode_launch only: each record is the RESP2 command go-redis writes for
                                   * rdb.Publish(ctx, channel, payload) (llm-stream-proxy/main.go:244):
                                   * "*3\r\n$7\r\npublish\r\n$<n>\r\n<channel>\r\n$<m>\r\n<payload>\r\n"; implies the channel. */
+#define SSEGPU_OP_HEADER_ONLY 512u /* egress without the bytes the host already has.  A record that is exactly what json.Marshal writes
+                                  * (the proxy's and the load generator's output, counted in fast_path) re-marshals to itself, so its
+                                  * frame is header + the payload itself + trailer.  With this flag such a record's output slice is only the
+                                  * header -- "event: token\nid: <seq>\ndata: " (bridge: the subject, with SSEGPU_OP_NATS_PUB the whole
+                                  * "PUB <subject> <#bytes>\r\n" line) -- and its status carries SSEGPU_ST_HEADER_ONLY: the host writes
+                                  * out[off:off+len] + payload (still in the batch's in_bytes) + "\n\n" (bridge: nothing, PUB: "\r\n").
+                                  * Every other record (re-marshalled, redacted) comes back whole, without the status bit.  Cuts the
+                                  * device-to-host traffic of a Go-marshalled stream from ~180 to ~45 bytes per record. */
 #define SSEGPU_OP_ORDERED   8u   /* lay the frames out back to back in record order (the arena then equals the
                                     sequential Go output byte for byte); costs a second decode pass.  Default: frames
                                     land in completion order -- the Go-marshalled records of a tile of 128 consecutive

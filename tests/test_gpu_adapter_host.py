@@ -16,12 +16,16 @@ from __graft_entry__ import load_package  # noqa: E402
 pytestmark = pytest.mark.gpu
 
 
-def test_replay_streams_match_reference_model():
+@pytest.mark.parametrize("header_only", [False, True])
+def test_replay_streams_match_reference_model(header_only):
+    """header_only: SSEGPU_OP_HEADER_ONLY egress -- the GPU returns only the frame headers of Go-marshalled records and the
+    coalescing loop appends the payload it still holds; the byte streams must not change."""
     pkg = load_package()
     rng = random.Random(3)
     n_conn, n_tok = 120, 40
     eng = pkg.SseGpu(device=0, max_records=512, max_in_bytes=512 * 160, ring_slots=2)
     host = pkg.host.AdapterHost(eng, 512, 512 * 160)
+    host.set_header_only(header_only)
     try:
         conns = []
         for c in range(n_conn):

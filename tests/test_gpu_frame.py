@@ -432,3 +432,39 @@ def test_api_error_paths(pkg, oracle):
     with pytest.raises(pkg.SseGpuError) as err:              # no such device
         pkg.SseGpu(device=63, max_records=16, max_in_bytes=4096)
     assert err.value.code == -2
+
+
+@pytest.mark.parametrize("op", [0, 8, 1, 1 | 8, 1 | 128, 1 | 128 | 8])
+def test_header_only_egress_reassembles_to_the_same_bytes(pkg, eng, oracle, golden, op):
+    """SSEGPU_OP_HEADER_ONLY: a record that is exactly json.Marshal's output comes back as its header only (status bit
+    SSEGPU_ST_HEADER_ONLY); header + payload + trailer must be the frame the full mode and the oracle produce."""
+    rng = random.Random(5)
+    payloads = [bytes.fromhex(c["in"]) for c in golden]
+    arena0, off0 = pkg.workload.generate(1, 300, 7)
+    payloads += [arena0[off0[i]:off0[i + 1]].tobytes() for i in range(len(off0) - 1)]
+    rng.shuffle(payloads)
+    arena, off = oracle.pack(payloads)
+    n = len(payloads)
+    if op & 128:
+        want_out, want_off, want_subj, want_status = oracle.bridge_pub(arena, off)
+    elif op & 1:
+        want_out, want_off, want_subj, want_status = oracle.bridge(arena, off)
+    else:
+        want_out, want_off, want_status = oracle.adapter(arena, off)
+    want = slices(want_out, want_off)
+    out, out_off, status, subj = run_batch(eng, arena, off, None, op | pkg.OP_HEADER_ONLY)
+    got = slices(out, out_off)
+    trailer = b"\r\n" if op & 128 else (b"" if op & 1 else b"\n\n")
+    n_hdr = 0
+    for i in range(n):
+        st = int(status[i])
+        assert (st & ~0x400) == int(want_status[i]), i
+        if st & 0x400:
+            n_hdr += 1
+            assert got[i] + payloads[i] + trailer == want[i], i
+        else:
+            assert got[i] == want[i], i
+        if op & 1 and (st & 0xF) == 0:
+            k = 4 if op & 128 else 0
+            assert want[i][k:k + int(subj[i])].startswith(b"chat.") and int(subj[i]) == int(want_subj[i])
+    assert n_hdr >= 2100
