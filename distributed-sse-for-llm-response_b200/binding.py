@@ -11,6 +11,7 @@ OP_NATS_PUB, OP_RESP, OP_HEADER_ONLY = 128, 256, 512
 ST_NO_INTEREST = 5
 INSPECT_PER_TOKEN, INSPECT_STREAMING = 0, 1
 KIND_LITERAL, KIND_REGEX = 0, 1
+WIRE_NATS, WIRE_RESP = 0, 1
 ACT_ALLOW, ACT_REDACT, ACT_DROP, ACT_ALERT = 0, 1, 2, 3
 VERDICT_BEGIN_UNKNOWN = 0x10000
 ST_OK, ST_ERR_SYNTAX, ST_ERR_TYPE, ST_FILTERED, ST_INSPECT_DROP = 0, 1, 2, 3, 4
@@ -132,6 +133,10 @@ def load_library():
     lib.ssegpu_verdict.argtypes = [vp]
     lib.ssegpu_match.restype = C.POINTER(C.c_int32)
     lib.ssegpu_match.argtypes = [vp]
+    lib.ssegpu_split_launch.restype = C.c_int
+    lib.ssegpu_split_launch.argtypes = [vp, C.c_uint32, vp, vp, C.c_uint32, vp, C.c_uint64, vp, C.c_uint32, vp, vp, vp, vp, vp, vp, vp]
+    lib.ssegpu_split_result.restype = C.c_int
+    lib.ssegpu_split_result.argtypes = [vp, u32p, u64p]
     lib.ssegpu_frame_launch_static.restype = C.c_int
     lib.ssegpu_frame_launch_static.argtypes = [C.c_int, vp, vp, vp, C.c_uint32, C.c_uint32, vp, C.c_uint64, vp, vp, vp, vp, vp]
     lib.ssegpu_static_last_error.restype = C.c_char_p
@@ -320,6 +325,20 @@ class SseGpu:
         if rc not in (0, E_OVERFLOW):
             self._check(rc)
         return rc, used.value
+
+    def split_launch(self, proto, d_buf, d_buf_off, n_conn, d_arena, arena_cap, d_in_off, max_msgs, d_msg_conn, d_msg_sid, d_msg_subj,
+                     d_conn_consumed, d_conn_status, d_conn_pings, stream=0):
+        """ssegpu_split_launch: NATS MSG / RESP push bytes of many connections -> packed payload arena; raw device addresses"""
+        self._check(self.lib.ssegpu_split_launch(self.ctx, proto, d_buf or None, d_buf_off, n_conn, d_arena, arena_cap, d_in_off, max_msgs,
+                                                 d_msg_conn or None, d_msg_sid or None, d_msg_subj or None, d_conn_consumed or None,
+                                                 d_conn_status or None, d_conn_pings or None, stream or None))
+
+    def split_result(self):
+        n, used = C.c_uint32(0), C.c_uint64(0)
+        rc = self.lib.ssegpu_split_result(self.ctx, C.byref(n), C.byref(used))
+        if rc not in (0, E_OVERFLOW):
+            self._check(rc)
+        return rc, n.value, used.value
 
     def launch_count(self):
         return int(self.lib.ssegpu_launch_count(self.ctx))

@@ -109,6 +109,25 @@ inline void scratch_carve_split(void* hdr_base, uint32_t n, FrameArgs& a) {
     a.zero_bytes = tiles * 8 + scratch_readback_bytes();
 }
 
+// ---- receiving side of the wire protocols (sse_wire.cu): socket bytes -> packed payload arena ----
+struct WireArgs {
+    uint32_t proto;              // WIRE_NATS / WIRE_RESP
+    const uint8_t* buf;          // every connection's unread socket bytes, back to back
+    const uint32_t* buf_off;     // n_conn + 1
+    uint32_t n_conn, max_msgs;
+    uint8_t* arena; uint64_t arena_cap;   // out: packed payloads (+48 readable bytes), 16-byte aligned: the frame kernel's input
+    uint32_t* in_off;            // out: max_msgs + 1
+    uint32_t* msg_conn;          // out per delivery: connection index
+    uint64_t* msg_sid;           // out per delivery: NATS subscription id (0 for RESP)
+    uint32_t* msg_subj;          // out per delivery: (offset into buf, length) of the subject / channel
+    uint32_t* conn_consumed; uint32_t* conn_status; uint32_t* conn_pings;   // out per connection
+    // scratch (carved by wire_split_launch)
+    uint32_t* totals;            // [0] deliveries, [1] payload bytes, [2] overflow flag
+    uint32_t* cnt_msgs; uint32_t* cnt_bytes; uint32_t* msg_src;
+};
+size_t wire_scratch_bytes(uint32_t n_conn, uint32_t max_msgs);
+cudaError_t wire_split_launch(WireArgs a, void* scratch, cudaStream_t stream);
+
 cudaError_t frame_configure(int device);
 cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream);
 // the counting pass of ordered mode on its own: decodes, leaves token entries (XF_ENTRY_IN_COUNT) and emits nothing --

@@ -116,6 +116,7 @@ struct ssegpu_ctx {
     uint64_t table_version = 0;           // successful ssegpu_interest_apply calls so far
     // table updates are GPU work on their own stream, ordered against the batches by events: an update waits for the
     // batches in flight that read the tables, later batches wait for the update (ev_table)
+    void* d_wire_scratch = nullptr; size_t wire_scratch_cap = 0;     // ssegpu_split_launch
     cudaStream_t table_stream = nullptr;
     cudaEvent_t ev_table = nullptr;
     static constexpr int kOpChunks = 64, kOpsPerChunk = 256, kLaunchEvents = 8;
@@ -401,7 +402,7 @@ void ssegpu_destroy(ssegpu_ctx* ctx) {
     cudaFree(ctx->d_launch_scratch);
     cudaFree(ctx->d_encode_scratch);
     cudaFree(ctx->d_conv_state); cudaFree(ctx->d_tok_entry); cudaFree(ctx->d_stream_scratch);
-    cudaFree(ctx->d_ops); cudaFreeHost(ctx->h_ops);
+    cudaFree(ctx->d_ops); cudaFreeHost(ctx->h_ops); cudaFree(ctx->d_wire_scratch);
     if (ctx->ev_stream) cudaEventDestroy(ctx->ev_stream);
     if (ctx->ev_table) cudaEventDestroy(ctx->ev_table);
     for (cudaEvent_t e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
@@ -860,6 +861,44 @@ int ssegpu_interest_bind(ssegpu_ctx* ctx, uint32_t* d_sub_span) {
     std::lock_guard<std::mutex> lk(ctx->mu);
     ctx->bound_hit = d_sub_span;
     return SSEGPU_OK;
+}
+
+// ---- receiving side of the wire protocols ------------------------------------------------------
+int ssegpu_split_launch(ssegpu_ctx* ctx, uint32_t proto, const void* d_buf, const uint32_t* d_buf_off, uint32_t n_conn, void* d_arena,
+                        uint64_t arena_cap, uint32_t* d_in_off, uint32_t max_msgs, uint32_t* d_msg_conn, uint64_t* d_msg_sid,
+                        uint32_t* d_msg_subj, uint32_t* d_conn_consumed, uint32_t* d_conn_status, uint32_t* d_conn_pings, void* stream) {
+    if (!ctx || proto > SSEGPU_WIRE_RESP || !d_buf_off || !d_in_off || !d_arena || (reinterpret_cast<uintptr_t>(d_arena) & 15)) return SSEGPU_E_INVAL;
+    if (n_conn && (!d_buf || !d_msg_conn || !d_msg_sid || !d_msg_subj || !d_conn_consumed || !d_conn_status || !d_conn_pings)) return SSEGPU_E_INVAL;
+    CU(cudaSetDevice(ctx->cfg.device));
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    const size_t need = sse::wire_scratch_bytes(n_conn, max_msgs);
+    if (need > ctx->wire_scratch_cap) {                      // grows on demand (first call, or a larger box of connections)
+        cudaStream_t st0 = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
+        CU(cudaStreamSynchronize(st0));
+        cudaFree(ctx->d_wire_scratch);
+        ctx->d_wire_scratch = nullptr; ctx->wire_scratch_cap = 0;
+        CU(cudaMalloc(&ctx->d_wire_scratch, need * 2));
+        ctx->wire_scratch_cap = need * 2;
+    }
+    sse::WireArgs a{};
+    a.proto = proto; a.buf = static_cast<const uint8_t*>(d_buf); a.buf_off = d_buf_off; a.n_conn = n_conn; a.max_msgs = max_msgs;
+    a.arena = static_cast<uint8_t*>(d_arena); a.arena_cap = arena_cap; a.in_off = d_in_off;
+    a.msg_conn = d_msg_conn; a.msg_sid = d_msg_sid; a.msg_subj = d_msg_subj;
+    a.conn_consumed = d_conn_consumed; a.conn_status = d_conn_status; a.conn_pings = d_conn_pings;
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
+    CU(sse::wire_split_launch(a, ctx->d_wire_scratch, st));
+    ctx->launches += n_conn ? 4 : 0;
+    return SSEGPU_OK;
+}
+
+int ssegpu_split_result(ssegpu_ctx* ctx, uint32_t* n_msgs, uint64_t* arena_bytes) {
+    if (!ctx || !ctx->d_wire_scratch) return SSEGPU_E_STATE;
+    CU(cudaSetDevice(ctx->cfg.device));
+    uint32_t t[4];
+    CU(cudaMemcpy(t, ctx->d_wire_scratch, sizeof t, cudaMemcpyDeviceToHost));
+    if (n_msgs) *n_msgs = t[0];
+    if (arena_bytes) *arena_bytes = t[1];
+    return t[2] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
 }
 
 uint64_t ssegpu_launch_count(ssegpu_ctx* ctx) {

@@ -254,6 +254,29 @@ int ssegpu_encode_launch(ssegpu_ctx *ctx, const void *d_cid, const uint32_t *d_c
 /* After the stream has been synchronised: bytes of d_out used; SSEGPU_E_OVERFLOW if out_cap was too small. */
 int ssegpu_encode_launch_result(ssegpu_ctx *ctx, uint64_t *out_bytes);
 
+/* ---- receiving side of the wire protocols (row N4): socket bytes -> the packed arena the frame launch reads ----------- */
+/* Replaces, batched over every connection of the box, the read side of the two client libraries the reference uses:
+ * nats.go's parser, which turns "MSG <subject> <sid> [reply] <#bytes>\r\n<payload>\r\n" into the msg.Data the adapter's
+ * callback gets (sse_handler.go:135, :316), and go-redis's reader, which turns the RESP push
+ * "*4 $8 pmessage $.. <pattern> $.. <channel> $.. <payload>" (or *3 message) into the msg.Payload of the bridge loop
+ * (redis-nats-bridge/main.go:115, :127, :142).  Neither library is vendored: layouts restated from the protocol specs, PARITY
+ * UNPINNED.  Connection c's unread bytes are d_buf[d_buf_off[c] .. d_buf_off[c+1]).  Every COMPLETE delivery's payload
+ * is copied, in connection order, into d_arena (16-byte aligned; d_in_off[0..n_msgs] are its offsets: exactly the input
+ * of ssegpu_frame_launch); per delivery d_msg_conn = connection index, d_msg_sid = NATS subscription id (0 for RESP),
+ * d_msg_subj[2i], [2i+1] = offset (into d_buf) and length of the subject / channel.  Per connection d_conn_consumed =
+ * bytes used (an incomplete trailing message stays in the socket buffer), d_conn_status = 0, or bit 0: protocol
+ * violation at that offset, bit 1: a -ERR line was seen; d_conn_pings = PING lines (the host owes that many PONGs).
+ * All pointers are device memory of this context's GPU.  Asynchronous on stream (NULL = the context's). */
+#define SSEGPU_WIRE_NATS 0u
+#define SSEGPU_WIRE_RESP 1u
+int ssegpu_split_launch(ssegpu_ctx *ctx, uint32_t proto, const void *d_buf, const uint32_t *d_buf_off, uint32_t n_conn,
+                        void *d_arena, uint64_t arena_cap, uint32_t *d_in_off, uint32_t max_msgs, uint32_t *d_msg_conn,
+                        uint64_t *d_msg_sid, uint32_t *d_msg_subj, uint32_t *d_conn_consumed, uint32_t *d_conn_status,
+                        uint32_t *d_conn_pings, void *stream);
+/* After the stream has been synchronised: deliveries found and arena bytes used; SSEGPU_E_OVERFLOW (nothing written)
+ * if max_msgs or arena_cap was too small. */
+int ssegpu_split_result(ssegpu_ctx *ctx, uint32_t *n_msgs, uint64_t *arena_bytes);
+
 /* Number of kernel launches this context has issued so far (bench.py "gpu_launches"). */
 uint64_t ssegpu_launch_count(ssegpu_ctx *ctx);
 

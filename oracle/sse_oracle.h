@@ -126,6 +126,13 @@ void sseo_inspect_stream(const sseo_inspector *I, const uint8_t *stream, uint32_
 /* fnv1a64 of the conversation id: the shard function. */
 uint64_t sseo_fnv1a64(const uint8_t *p, size_t n);
 
+/* ---- receiving side of the wire protocols (oracle/sse_wire_oracle.c; row N4, parity unpinned) ---- */
+typedef struct { uint32_t payload_off, payload_len, subj_off, subj_len; uint64_t sid; uint32_t conn, pad; } sseo_wire_msg;
+typedef struct { uint32_t n_msgs, payload_bytes, consumed, status, pings; } sseo_wire_conn;
+uint32_t sseo_wire_split(uint32_t proto, const uint8_t *buf, const uint32_t *buf_off, uint32_t n_conn, sseo_wire_msg **msgs,
+                         uint32_t *unused, sseo_wire_conn *conns);
+void sseo_free(void *p);
+
 #ifdef __cplusplus
 }
 #endif

@@ -195,3 +195,21 @@ extern "C" int hc_encode(const uint8_t* cid, const uint32_t* cid_off, const uint
     out_off[n] = w;
     return 0;
 }
+
+// ---- wire splitter: the product's per-connection walk on the CPU (test double) ----
+#include "sse_wire.cuh"
+struct hc_wire_msg { uint32_t payload_off, payload_len, subj_off, subj_len; uint64_t sid; uint32_t conn, pad; };
+struct hc_wire_conn { uint32_t n_msgs, payload_bytes, consumed, status, pings; };
+extern "C" uint32_t hc_wire_split(uint32_t proto, const uint8_t* buf, const uint32_t* buf_off, uint32_t n_conn, hc_wire_msg* msgs, uint32_t cap,
+                                  hc_wire_conn* conns) {
+    PtrSrc src{buf};
+    uint32_t n = 0;
+    for (uint32_t c = 0; c < n_conn; c++) {
+        const WireConn r = wire_walk(proto, src, buf_off[c], buf_off[c + 1], [&](uint32_t, const WireMsg& m) {
+            if (n < cap) msgs[n] = hc_wire_msg{m.payload_off, m.payload_len, m.subj_off, m.subj_len, m.sid, c, 0};
+            n++;
+        });
+        conns[c] = hc_wire_conn{r.n_msgs, r.payload_bytes, r.consumed, r.status, r.pings};
+    }
+    return n;
+}
