@@ -137,6 +137,10 @@ def load_library():
     lib.ssegpu_split_launch.argtypes = [vp, C.c_uint32, vp, vp, C.c_uint32, vp, C.c_uint64, vp, C.c_uint32, vp, vp, vp, vp, vp, vp, vp]
     lib.ssegpu_split_result.restype = C.c_int
     lib.ssegpu_split_result.argtypes = [vp, u32p, u64p]
+    lib.ssegpu_chunk_decode_launch.restype = C.c_int
+    lib.ssegpu_chunk_decode_launch.argtypes = [vp, vp, vp, C.c_uint32, vp, C.c_uint64, vp, vp, vp, C.c_uint32, vp, vp]
+    lib.ssegpu_chunk_decode_result.restype = C.c_int
+    lib.ssegpu_chunk_decode_result.argtypes = [vp, u32p, u64p]
     lib.ssegpu_frame_launch_static.restype = C.c_int
     lib.ssegpu_frame_launch_static.argtypes = [C.c_int, vp, vp, vp, C.c_uint32, C.c_uint32, vp, C.c_uint64, vp, vp, vp, vp, vp]
     lib.ssegpu_static_last_error.restype = C.c_char_p
@@ -336,6 +340,18 @@ class SseGpu:
     def split_result(self):
         n, used = C.c_uint32(0), C.c_uint64(0)
         rc = self.lib.ssegpu_split_result(self.ctx, C.byref(n), C.byref(used))
+        if rc not in (0, E_OVERFLOW):
+            self._check(rc)
+        return rc, n.value, used.value
+
+    def chunk_decode_launch(self, d_lines, d_line_off, n_lines, d_tok, tok_cap, d_tok_off, d_done, d_msg_line, max_msgs, d_line_status, stream=0):
+        """ssegpu_chunk_decode_launch: vLLM stream lines -> the encoder's token columns; raw device addresses"""
+        self._check(self.lib.ssegpu_chunk_decode_launch(self.ctx, d_lines or None, d_line_off, n_lines, d_tok, tok_cap, d_tok_off, d_done or None,
+                                                        d_msg_line or None, max_msgs, d_line_status or None, stream or None))
+
+    def chunk_decode_result(self):
+        n, used = C.c_uint32(0), C.c_uint64(0)
+        rc = self.lib.ssegpu_chunk_decode_result(self.ctx, C.byref(n), C.byref(used))
         if rc not in (0, E_OVERFLOW):
             self._check(rc)
         return rc, n.value, used.value

@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libssegpu.so")
-SOURCES = ["sse_kernels.cu", "sse_stream.cu", "sse_wire.cu", "sse_encode.cu", "ssegpu_api.cu", "ssegpu_static.cu"]
+SOURCES = ["sse_kernels.cu", "sse_stream.cu", "sse_wire.cu", "sse_chunk.cu", "sse_encode.cu", "ssegpu_api.cu", "ssegpu_static.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "--shared", "-cudart", "shared", "--threads", "4"]
 

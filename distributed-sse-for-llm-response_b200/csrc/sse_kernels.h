@@ -128,6 +128,25 @@ struct WireArgs {
 size_t wire_scratch_bytes(uint32_t n_conn, uint32_t max_msgs);
 cudaError_t wire_split_launch(WireArgs a, void* scratch, cudaStream_t stream);
 
+cudaError_t scan_exclusive_u32(uint32_t* data, size_t m, uint32_t* block_sums, cudaStream_t stream);   // sse_stream.cu
+
+// ---- decode half of row N3 (sse_chunk.cu): vLLM stream lines -> token columns for the encoder ----
+struct ChunkArgs {
+    const uint8_t* lines;        // SSE lines of the vLLM response bodies, back to back (each with 8 readable bytes behind it is not needed: reads stay inside the line)
+    const uint32_t* line_off;    // n_lines + 1
+    uint32_t n_lines, max_msgs;
+    uint8_t* tok; uint64_t tok_cap;   // out: decoded token texts, packed (+32 readable bytes): the encoder's d_tok
+    uint32_t* tok_off;           // out: max_msgs + 1
+    uint8_t* done;               // out per message: 1 for the "[DONE]" sentinel
+    uint32_t* msg_line;          // out per message: the line it came from
+    uint32_t* line_status;       // out per line: CHUNK_* word
+    // scratch (carved by chunk_decode_launch)
+    uint32_t* totals;            // [0] messages, [1] token bytes, [2] overflow flag, [3..4] the last line's own counts
+    uint32_t* cnt_msgs; uint32_t* cnt_bytes; uint32_t* block_sums;
+};
+size_t chunk_scratch_bytes(uint32_t n_lines);
+cudaError_t chunk_decode_launch(ChunkArgs a, void* scratch, cudaStream_t stream);
+
 cudaError_t frame_configure(int device);
 cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream);
 // the counting pass of ordered mode on its own: decodes, leaves token entries (XF_ENTRY_IN_COUNT) and emits nothing --

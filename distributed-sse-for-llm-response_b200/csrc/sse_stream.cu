@@ -255,6 +255,16 @@ size_t hist_words(uint32_t n) { return ((size_t)(n + SORT_TILE - 1) / SORT_TILE)
 
 }  // namespace
 
+// exclusive scan of data[0, m) in place; block_sums: m / 4096 + 2 words of scratch
+cudaError_t scan_exclusive_u32(uint32_t* data, size_t m, uint32_t* block_sums, cudaStream_t stream) {
+    if (m == 0) return cudaSuccess;
+    const uint32_t nb = (uint32_t)((m + SCAN_BLOCK - 1) / SCAN_BLOCK);
+    k_scan_reduce<<<nb, 1024, 0, stream>>>(data, m, block_sums);
+    k_scan_block_sums<<<1, 1024, 0, stream>>>(block_sums, nb);
+    k_scan_apply<<<nb, 1024, 0, stream>>>(data, m, block_sums);
+    return cudaGetLastError();
+}
+
 size_t stream_scratch_bytes(uint32_t n) {
     const size_t a = ((size_t)n * 4 + 255) & ~(size_t)255;
     const size_t h = (hist_words(n) * 4 + 255) & ~(size_t)255;

@@ -117,6 +117,7 @@ struct ssegpu_ctx {
     // table updates are GPU work on their own stream, ordered against the batches by events: an update waits for the
     // batches in flight that read the tables, later batches wait for the update (ev_table)
     void* d_wire_scratch = nullptr; size_t wire_scratch_cap = 0;     // ssegpu_split_launch
+    void* d_chunk_scratch = nullptr; size_t chunk_scratch_cap = 0;   // ssegpu_chunk_decode_launch
     cudaStream_t table_stream = nullptr;
     cudaEvent_t ev_table = nullptr;
     static constexpr int kOpChunks = 64, kOpsPerChunk = 256, kLaunchEvents = 8;
@@ -402,7 +403,7 @@ void ssegpu_destroy(ssegpu_ctx* ctx) {
     cudaFree(ctx->d_launch_scratch);
     cudaFree(ctx->d_encode_scratch);
     cudaFree(ctx->d_conv_state); cudaFree(ctx->d_tok_entry); cudaFree(ctx->d_stream_scratch);
-    cudaFree(ctx->d_ops); cudaFreeHost(ctx->h_ops); cudaFree(ctx->d_wire_scratch);
+    cudaFree(ctx->d_ops); cudaFreeHost(ctx->h_ops); cudaFree(ctx->d_wire_scratch); cudaFree(ctx->d_chunk_scratch);
     if (ctx->ev_stream) cudaEventDestroy(ctx->ev_stream);
     if (ctx->ev_table) cudaEventDestroy(ctx->ev_table);
     for (cudaEvent_t e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
@@ -875,7 +876,7 @@ int ssegpu_split_launch(ssegpu_ctx* ctx, uint32_t proto, const void* d_buf, cons
     if (need > ctx->wire_scratch_cap) {                      // grows on demand (first call, or a larger box of connections)
         cudaStream_t st0 = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
         CU(cudaStreamSynchronize(st0));
-        cudaFree(ctx->d_wire_scratch);
+        cudaFree(ctx->d_wire_scratch); cudaFree(ctx->d_chunk_scratch);
         ctx->d_wire_scratch = nullptr; ctx->wire_scratch_cap = 0;
         CU(cudaMalloc(&ctx->d_wire_scratch, need * 2));
         ctx->wire_scratch_cap = need * 2;
@@ -898,6 +899,41 @@ int ssegpu_split_result(ssegpu_ctx* ctx, uint32_t* n_msgs, uint64_t* arena_bytes
     CU(cudaMemcpy(t, ctx->d_wire_scratch, sizeof t, cudaMemcpyDeviceToHost));
     if (n_msgs) *n_msgs = t[0];
     if (arena_bytes) *arena_bytes = t[1];
+    return t[2] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
+}
+
+// ---- decode half of row N3 ----------------------------------------------------------------------
+int ssegpu_chunk_decode_launch(ssegpu_ctx* ctx, const void* d_lines, const uint32_t* d_line_off, uint32_t n_lines, void* d_tok, uint64_t tok_cap,
+                               uint32_t* d_tok_off, uint8_t* d_done, uint32_t* d_msg_line, uint32_t max_msgs, uint32_t* d_line_status, void* stream) {
+    if (!ctx || !d_line_off || !d_tok || !d_tok_off || (reinterpret_cast<uintptr_t>(d_tok) & 15)) return SSEGPU_E_INVAL;
+    if (n_lines && (!d_lines || !d_done || !d_msg_line || !d_line_status)) return SSEGPU_E_INVAL;
+    CU(cudaSetDevice(ctx->cfg.device));
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
+    const size_t need = sse::chunk_scratch_bytes(n_lines);
+    if (need > ctx->chunk_scratch_cap) {
+        CU(cudaStreamSynchronize(st));
+        cudaFree(ctx->d_chunk_scratch);
+        ctx->d_chunk_scratch = nullptr; ctx->chunk_scratch_cap = 0;
+        CU(cudaMalloc(&ctx->d_chunk_scratch, need * 2));
+        ctx->chunk_scratch_cap = need * 2;
+    }
+    sse::ChunkArgs a{};
+    a.lines = static_cast<const uint8_t*>(d_lines); a.line_off = d_line_off; a.n_lines = n_lines; a.max_msgs = max_msgs;
+    a.tok = static_cast<uint8_t*>(d_tok); a.tok_cap = tok_cap; a.tok_off = d_tok_off; a.done = d_done; a.msg_line = d_msg_line;
+    a.line_status = d_line_status;
+    CU(sse::chunk_decode_launch(a, ctx->d_chunk_scratch, st));
+    ctx->launches += n_lines ? 9 : 0;
+    return SSEGPU_OK;
+}
+
+int ssegpu_chunk_decode_result(ssegpu_ctx* ctx, uint32_t* n_msgs, uint64_t* tok_bytes) {
+    if (!ctx || !ctx->d_chunk_scratch) return SSEGPU_E_STATE;
+    CU(cudaSetDevice(ctx->cfg.device));
+    uint32_t t[4];
+    CU(cudaMemcpy(t, ctx->d_chunk_scratch, sizeof t, cudaMemcpyDeviceToHost));
+    if (n_msgs) *n_msgs = t[0];
+    if (tok_bytes) *tok_bytes = t[1];
     return t[2] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
 }
 

@@ -277,6 +277,25 @@ int ssegpu_split_launch(ssegpu_ctx *ctx, uint32_t proto, const void *d_buf, cons
  * if max_msgs or arena_cap was too small. */
 int ssegpu_split_result(ssegpu_ctx *ctx, uint32_t *n_msgs, uint64_t *arena_bytes);
 
+/* ---- decode half of row N3: the proxy's read of the vLLM stream ---------------------------------------------------- */
+/* Replaces, batched over the lines of many chats' response bodies, the loop body of streamFromLLM
+ * (src/llm-stream-proxy/main.go:188-226): strings.TrimSpace, the "data: " filter, the "[DONE]" line, json.Unmarshal into
+ * StreamChunk (main.go:45-53; a line that does not decode is skipped), then per choice: a non-empty delta.content is a
+ * token message, a non-nil finish_reason ends the stream with the "[DONE]" sentinel.  Line i is d_lines[d_line_off[i] ..
+ * d_line_off[i+1]).  Out: d_line_status[i] = kind (0 skipped, 1 chunk, 2 "[DONE]" line) | SSEGPU_CHUNK_ENDS (the reference
+ * stops reading that chat after this line: the host drops the chat's later lines) | SSEGPU_CHUNK_TOO_MANY (more than 16
+ * choices in one line: not decoded, told apart from a skip); the messages the lines publish, in line order: decoded token
+ * text d_tok[d_tok_off[m] .. d_tok_off[m+1]) (16-byte aligned arena), d_done[m] (1 = sentinel), d_msg_line[m] -- d_tok,
+ * d_tok_off and d_done are columns of ssegpu_encode_launch; conversation id, sequence (sequence++ per token, sentinel =
+ * sequence + 1) and timestamp are per-chat state the host fills in.  PARITY UNPINNED (no test in the reference). */
+#define SSEGPU_CHUNK_ENDS     0x100u
+#define SSEGPU_CHUNK_TOO_MANY 0x200u
+int ssegpu_chunk_decode_launch(ssegpu_ctx *ctx, const void *d_lines, const uint32_t *d_line_off, uint32_t n_lines, void *d_tok,
+                               uint64_t tok_cap, uint32_t *d_tok_off, uint8_t *d_done, uint32_t *d_msg_line, uint32_t max_msgs,
+                               uint32_t *d_line_status, void *stream);
+/* After the stream has been synchronised: messages and token bytes; SSEGPU_E_OVERFLOW (nothing written) if too small. */
+int ssegpu_chunk_decode_result(ssegpu_ctx *ctx, uint32_t *n_msgs, uint64_t *tok_bytes);
+
 /* Number of kernel launches this context has issued so far (bench.py "gpu_launches"). */
 uint64_t ssegpu_launch_count(ssegpu_ctx *ctx);
 

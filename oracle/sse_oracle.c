@@ -837,3 +837,203 @@ uint64_t sseo_fnv1a64(const uint8_t *p, size_t n)
     for (size_t i = 0; i < n; i++) { h ^= p[i]; h *= 0x100000001b3ull; }
     return h;
 }
+
+/* ---------------------------------------------------------------- row N3, decode half ----
+ * The proxy's read of the vLLM stream: src/llm-stream-proxy/main.go:188-226 with StreamChunk of main.go:45-53.
+ * PARITY UNPINNED (the reference has no test for it).  Written the way the Go code reads: TrimSpace, prefix test,
+ * "[DONE]", json.Unmarshal into a materialised struct (choices as a heap slice with Go's growth rule, strings
+ * unquoted into their own buffers), then the loop over the choices. */
+typedef struct { uint8_t *content; uint32_t content_len; int has_finish; } o_choice;
+typedef struct { o_choice *v; uint32_t len, cap; int type_err; } o_chunk;
+
+static int go_is_space(uint32_t r)
+{
+    if (r == ' ' || (r >= 9 && r <= 13) || r == 0x85 || r == 0xA0 || r == 0x1680 || (r >= 0x2000 && r <= 0x200A)) return 1;
+    return r == 0x2028 || r == 0x2029 || r == 0x202F || r == 0x205F || r == 0x3000;
+}
+static void trim_space(const uint8_t *p, size_t *b, size_t *e)
+{
+    while (*b < *e) {                                           /* TrimLeftFunc: decode runes from the front */
+        uint32_t r;
+        int n = utf8_decode(p + *b, *e - *b, &r);
+        if (!(n >= 1 && go_is_space(r) && !(r == 0xFFFD && n == 1))) break;
+        *b += (size_t)n;
+    }
+    while (*e > *b) {                                           /* TrimRightFunc: utf8.DecodeLastRune */
+        size_t s = *e - 1;
+        size_t lim = *e - *b >= 4 ? *e - 4 : *b;
+        while (s > lim && (p[s] & 0xC0) == 0x80) s--;
+        uint32_t r;
+        int n = utf8_decode(p + s, *e - s, &r);
+        if (s + (size_t)n != *e) { r = p[*e - 1]; s = *e - 1; if (r >= 0x80) break; }   /* not one whole rune at the end: invalid byte, not a space */
+        if (!go_is_space(r)) break;
+        *e = s;
+    }
+}
+static int key_is(const uint8_t *lit, size_t n, const char *upper)
+{
+    uint8_t *k = (uint8_t *)malloc(n + 4);
+    uint32_t kl = unquote(lit, n, k), i = 0;
+    size_t L = strlen(upper), j = 0;
+    int ok = 1;
+    while (i < kl) {
+        uint32_t r;
+        i += (uint32_t)utf8_decode(k + i, kl - i, &r);
+        if (j >= L || fold_rune(r) != (uint32_t)(uint8_t)upper[j]) { ok = 0; break; }
+        j++;
+    }
+    free(k);
+    return ok && j == L;
+}
+static size_t ws(const uint8_t *p, size_t i) { while (is_ws(p[i])) i++; return i; }
+static size_t str_end(const uint8_t *p, size_t i) { for (i++; p[i] != '"'; i++) if (p[i] == '\\') i++; return i + 1; }
+
+static size_t decode_delta(const uint8_t *p, size_t i, o_choice *c, int *type_err)
+{
+    if (p[i] == 'n') return i + 4;
+    if (p[i] != '{') { *type_err = 1; return skip_value(p, i); }
+    i = ws(p, i + 1);
+    if (p[i] == '}') return i + 1;
+    for (;;) {
+        size_t ke = str_end(p, i);
+        int is_content = key_is(p + i + 1, ke - i - 2, "CONTENT");
+        i = ws(p, ws(p, ke) + 1);
+        if (is_content && p[i] == '"') {
+            size_t se = str_end(p, i);
+            free(c->content);
+            c->content = (uint8_t *)malloc(3 * (se - i) + 4);
+            c->content_len = unquote(p + i + 1, se - i - 2, c->content);
+            i = se;
+        } else {
+            if (is_content && p[i] != 'n') *type_err = 1;
+            i = skip_value(p, i);
+        }
+        i = ws(p, i);
+        if (p[i] == ',') { i = ws(p, i + 1); continue; }
+        return i + 1;
+    }
+}
+static size_t decode_choice(const uint8_t *p, size_t i, o_choice *c, int *type_err)
+{
+    if (p[i] == 'n') return i + 4;
+    if (p[i] != '{') { *type_err = 1; return skip_value(p, i); }
+    i = ws(p, i + 1);
+    if (p[i] == '}') return i + 1;
+    for (;;) {
+        size_t ke = str_end(p, i);
+        int is_delta = key_is(p + i + 1, ke - i - 2, "DELTA"), is_fin = key_is(p + i + 1, ke - i - 2, "FINISH_REASON");
+        i = ws(p, ws(p, ke) + 1);
+        if (is_delta) i = decode_delta(p, i, c, type_err);
+        else if (is_fin) {
+            if (p[i] == '"') c->has_finish = 1;
+            else if (p[i] == 'n') c->has_finish = 0;
+            else *type_err = 1;
+            i = skip_value(p, i);
+        } else i = skip_value(p, i);
+        i = ws(p, i);
+        if (p[i] == ',') { i = ws(p, i + 1); continue; }
+        return i + 1;
+    }
+}
+static void chunk_free(o_chunk *ch) { for (uint32_t k = 0; k < ch->cap; k++) free(ch->v[k].content); free(ch->v); ch->v = NULL; ch->len = ch->cap = 0; }
+
+static void decode_chunk(const uint8_t *p, o_chunk *ch)
+{
+    size_t i = ws(p, 0);
+    if (p[i] == 'n') return;
+    if (p[i] != '{') { ch->type_err = 1; return; }
+    i = ws(p, i + 1);
+    if (p[i] == '}') return;
+    for (;;) {
+        size_t ke = str_end(p, i);
+        int is_choices = key_is(p + i + 1, ke - i - 2, "CHOICES");
+        i = ws(p, ws(p, ke) + 1);
+        if (is_choices && p[i] == '[') {                         /* decode.go array() into a slice */
+            uint32_t n = 0;
+            i = ws(p, i + 1);
+            if (p[i] == ']') i++;
+            else for (;;) {
+                if (n >= ch->cap) {                              /* grow: new backing array, the first len elements move over */
+                    uint32_t nc = ch->cap + ch->cap / 2;
+                    if (nc < 4) nc = 4;
+                    o_choice *nv = (o_choice *)calloc(nc, sizeof *nv);
+                    for (uint32_t k = 0; k < ch->len; k++) { nv[k] = ch->v[k]; ch->v[k].content = NULL; }
+                    for (uint32_t k = 0; k < ch->cap; k++) free(ch->v[k].content);
+                    free(ch->v);
+                    ch->v = nv; ch->cap = nc;
+                }
+                if (n >= ch->len) ch->len = n + 1;
+                i = decode_choice(p, i, &ch->v[n], &ch->type_err);
+                n++;
+                i = ws(p, i);
+                if (p[i] == ',') { i = ws(p, i + 1); continue; }
+                i++;
+                break;
+            }
+            if (n < ch->len) ch->len = n;
+            if (n == 0) chunk_free(ch);                          /* v.Set(reflect.MakeSlice(v.Type(), 0, 0)) */
+        } else if (is_choices && p[i] == 'n') { chunk_free(ch); i += 4; }
+        else {
+            if (is_choices) ch->type_err = 1;
+            i = skip_value(p, i);
+        }
+        i = ws(p, i);
+        if (p[i] == ',') { i = ws(p, i + 1); continue; }
+        return;
+    }
+}
+
+/* One line.  Appends the messages it publishes to (tok, tok_off, done) starting at message *n_msgs / byte *w, returns
+ * the status word (kind | 0x100 ends the stream). */
+static uint32_t chunk_line(const uint8_t *line, size_t len, uint8_t *tok, uint32_t *tok_off, uint8_t *done, uint32_t *n_msgs, size_t *w)
+{
+    size_t b = 0, e = len;
+    trim_space(line, &b, &e);
+    if (e - b < 6 || memcmp(line + b, "data: ", 6) != 0) return 0;
+    b += 6;
+    if (e - b == 6 && memcmp(line + b, "[DONE]", 6) == 0) {
+        tok_off[*n_msgs] = (uint32_t)*w; done[*n_msgs] = 1; (*n_msgs)++;
+        memcpy(tok + *w, "[DONE]", 6); *w += 6;
+        return 2 | 0x100;
+    }
+    if (!json_valid(line + b, e - b)) return 0;
+    uint8_t *doc = (uint8_t *)malloc(e - b + 8);                /* NUL-terminated copy: the walkers above run to delimiters */
+    memcpy(doc, line + b, e - b);
+    memset(doc + (e - b), 0, 8);
+    o_chunk ch = {0, 0, 0, 0};
+    decode_chunk(doc, &ch);
+    uint32_t st = 0;
+    if (!ch.type_err) {
+        st = 1;
+        for (uint32_t k = 0; k < ch.len; k++) {
+            if (ch.v[k].content_len) {
+                tok_off[*n_msgs] = (uint32_t)*w; done[*n_msgs] = 0; (*n_msgs)++;
+                memcpy(tok + *w, ch.v[k].content, ch.v[k].content_len); *w += ch.v[k].content_len;
+            }
+            if (ch.v[k].has_finish) {
+                tok_off[*n_msgs] = (uint32_t)*w; done[*n_msgs] = 1; (*n_msgs)++;
+                memcpy(tok + *w, "[DONE]", 6); *w += 6;
+                st |= 0x100;
+                break;
+            }
+        }
+    }
+    chunk_free(&ch);
+    free(doc);
+    return st;
+}
+
+/* tok must hold 3 x the input bytes + 6 per line; tok_off/done/msg_line one entry per possible message (<= bytes/8 + lines) */
+uint32_t sseo_chunk_decode(const uint8_t *lines, const uint32_t *line_off, uint32_t n_lines, uint8_t *tok, uint32_t *tok_off,
+                           uint8_t *done, uint32_t *msg_line, uint32_t *line_status)
+{
+    uint32_t n = 0;
+    size_t w = 0;
+    for (uint32_t i = 0; i < n_lines; i++) {
+        const uint32_t before = n;
+        line_status[i] = chunk_line(lines + line_off[i], line_off[i + 1] - line_off[i], tok, tok_off, done, &n, &w);
+        for (uint32_t k = before; k < n; k++) msg_line[k] = i;
+    }
+    tok_off[n] = (uint32_t)w;
+    return n;
+}

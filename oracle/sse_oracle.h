@@ -133,6 +133,10 @@ uint32_t sseo_wire_split(uint32_t proto, const uint8_t *buf, const uint32_t *buf
                          uint32_t *unused, sseo_wire_conn *conns);
 void sseo_free(void *p);
 
+/* ---- row N3, decode half: vLLM stream lines -> token messages (src/llm-stream-proxy/main.go:188-226; parity unpinned) ---- */
+uint32_t sseo_chunk_decode(const uint8_t *lines, const uint32_t *line_off, uint32_t n_lines, uint8_t *tok, uint32_t *tok_off,
+                           uint8_t *done, uint32_t *msg_line, uint32_t *line_status);
+
 #ifdef __cplusplus
 }
 #endif

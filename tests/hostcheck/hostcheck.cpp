@@ -213,3 +213,29 @@ extern "C" uint32_t hc_wire_split(uint32_t proto, const uint8_t* buf, const uint
     }
     return n;
 }
+
+// ---- vLLM stream-chunk decoder: the product's per-line logic on the CPU (test double) ----
+#include "sse_chunk.cuh"
+extern "C" uint32_t hc_chunk_decode(const uint8_t* lines, const uint32_t* line_off, uint32_t n_lines, uint8_t* tok, uint32_t* tok_off, uint8_t* done,
+                                    uint32_t* msg_line, uint32_t* line_status) {
+    std::vector<uint32_t> nest(NEST_WORDS);
+    PtrSrc src{lines};
+    uint32_t n = 0, w = 0;
+    for (uint32_t i = 0; i < n_lines; i++) {
+        ChunkEvents ev;
+        const uint32_t st = chunk_line(src, line_off[i], line_off[i + 1], ev, nest.data());
+        line_status[i] = st;
+        if (st & CHUNK_TOO_MANY) continue;
+        if ((st & CHUNK_KIND_MASK) == CHUNK_DATA)
+            for (uint32_t k = 0; k < ev.len; k++) {
+                if (!(ev.ch[k].has_content && ev.ch[k].ce > ev.ch[k].cb)) continue;
+                tok_off[n] = w; done[n] = 0; msg_line[n] = i;
+                if (chunk_content_bytes(src, ev.ch[k]) == 0) return 0xFFFFFFFFu;
+                for_each_decoded_byte(src, ev.ch[k].cb, ev.ch[k].ce, [&](uint32_t b) { tok[w++] = (uint8_t)b; });
+                n++;
+            }
+        if (st & CHUNK_ENDS) { tok_off[n] = w; done[n] = 1; msg_line[n] = i; memcpy(tok + w, "[DONE]", 6); w += 6; n++; }
+    }
+    tok_off[n] = w;
+    return n;
+}

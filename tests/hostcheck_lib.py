@@ -21,7 +21,7 @@ def load():
     so = os.path.join(HC_DIR, "libhostcheck.so")
     srcs = [os.path.join(HC_DIR, "hostcheck.cpp"), os.path.join(CSRC, "sse_record.cuh"), os.path.join(CSRC, "sse_inspect.cuh"),
             os.path.join(CSRC, "inspect_compile.hpp"), os.path.join(CSRC, "sse_interest.cuh"), os.path.join(CSRC, "interest_table.hpp"),
-            os.path.join(CSRC, "sse_wire.cuh")]
+            os.path.join(CSRC, "sse_wire.cuh"), os.path.join(CSRC, "sse_chunk.cuh")]
     if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-fPIC", "-shared", "-I", CSRC, "-o", so, srcs[0]])
     lib = C.CDLL(so)
