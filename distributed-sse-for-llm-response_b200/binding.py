@@ -137,6 +137,10 @@ def load_library():
     lib.ssegpu_split_launch.argtypes = [vp, C.c_uint32, vp, vp, C.c_uint32, vp, C.c_uint64, vp, C.c_uint32, vp, vp, vp, vp, vp, vp, vp]
     lib.ssegpu_split_result.restype = C.c_int
     lib.ssegpu_split_result.argtypes = [vp, u32p, u64p]
+    lib.ssegpu_fanout_launch.restype = C.c_int
+    lib.ssegpu_fanout_launch.argtypes = [vp, vp, C.c_uint32, vp, vp, C.c_uint64, vp, vp]
+    lib.ssegpu_fanout_result.restype = C.c_int
+    lib.ssegpu_fanout_result.argtypes = [vp, u64p]
     lib.ssegpu_chunk_decode_launch.restype = C.c_int
     lib.ssegpu_chunk_decode_launch.argtypes = [vp, vp, vp, C.c_uint32, vp, C.c_uint64, vp, vp, vp, C.c_uint32, vp, vp]
     lib.ssegpu_chunk_decode_result.restype = C.c_int
@@ -343,6 +347,17 @@ class SseGpu:
         if rc not in (0, E_OVERFLOW):
             self._check(rc)
         return rc, n.value, used.value
+
+    def fanout_launch(self, d_sub_span, n, d_pair_sub, d_pair_rec, max_pairs, d_rec_off, stream=0):
+        """ssegpu_fanout_launch: spans of OP_MATCH -> flat (subscriber id, record) pairs; raw device addresses"""
+        self._check(self.lib.ssegpu_fanout_launch(self.ctx, d_sub_span or None, n, d_pair_sub or None, d_pair_rec or None, max_pairs, d_rec_off, stream or None))
+
+    def fanout_result(self):
+        n = C.c_uint64(0)
+        rc = self.lib.ssegpu_fanout_result(self.ctx, C.byref(n))
+        if rc not in (0, E_OVERFLOW):
+            self._check(rc)
+        return rc, n.value
 
     def chunk_decode_launch(self, d_lines, d_line_off, n_lines, d_tok, tok_cap, d_tok_off, d_done, d_msg_line, max_msgs, d_line_status, stream=0):
         """ssegpu_chunk_decode_launch: vLLM stream lines -> the encoder's token columns; raw device addresses"""

@@ -43,9 +43,13 @@ enum SlotState { FREE = 0, ACQUIRED, SUBMITTED, DONE };
 struct TableGen {                        // interest table
     cudaStream_t stream = nullptr;
     sse::InterestSlot* d_slots = nullptr; uint32_t* d_keys = nullptr; uint8_t* d_wild = nullptr; sse::InterestDev* d_desc = nullptr;
+    uint32_t* d_subs = nullptr;                      // device copy of the id arena (ssegpu_fanout_launch expands spans from it)
+    uint32_t* d_wild_ids = nullptr;                  // 32 words
     std::shared_ptr<std::vector<uint32_t>> subs;     // host arena the spans of this generation index (append-only, fixed address)
     std::vector<uint32_t> wild_ids;
     ~TableGen() {
+        if (d_subs) cudaFreeAsync(d_subs, stream);
+        if (d_wild_ids) cudaFreeAsync(d_wild_ids, stream);
         if (d_slots) cudaFreeAsync(d_slots, stream);
         if (d_keys) cudaFreeAsync(d_keys, stream);
         if (d_wild) cudaFreeAsync(d_wild, stream);
@@ -118,6 +122,7 @@ struct ssegpu_ctx {
     // batches in flight that read the tables, later batches wait for the update (ev_table)
     void* d_wire_scratch = nullptr; size_t wire_scratch_cap = 0;     // ssegpu_split_launch
     void* d_chunk_scratch = nullptr; size_t chunk_scratch_cap = 0;   // ssegpu_chunk_decode_launch
+    void* d_fanout_scratch = nullptr;                                // ssegpu_fanout_launch
     cudaStream_t table_stream = nullptr;
     cudaEvent_t ev_table = nullptr;
     static constexpr int kOpChunks = 64, kOpsPerChunk = 256, kLaunchEvents = 8;
@@ -403,7 +408,7 @@ void ssegpu_destroy(ssegpu_ctx* ctx) {
     cudaFree(ctx->d_launch_scratch);
     cudaFree(ctx->d_encode_scratch);
     cudaFree(ctx->d_conv_state); cudaFree(ctx->d_tok_entry); cudaFree(ctx->d_stream_scratch);
-    cudaFree(ctx->d_ops); cudaFreeHost(ctx->h_ops); cudaFree(ctx->d_wire_scratch); cudaFree(ctx->d_chunk_scratch);
+    cudaFree(ctx->d_ops); cudaFreeHost(ctx->h_ops); cudaFree(ctx->d_wire_scratch); cudaFree(ctx->d_chunk_scratch); cudaFree(ctx->d_fanout_scratch);
     if (ctx->ev_stream) cudaEventDestroy(ctx->ev_stream);
     if (ctx->ev_table) cudaEventDestroy(ctx->ev_table);
     for (cudaEvent_t e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
@@ -651,8 +656,10 @@ static int table_stream_wait_users(ssegpu_ctx* ctx) {
     return SSEGPU_OK;
 }
 
-__global__ void k_interest_apply(const SlotOp* __restrict__ ops, uint32_t n, sse::InterestSlot* slots) {
+__global__ void k_interest_apply(const SlotOp* __restrict__ ops, uint32_t n, sse::InterestSlot* slots, const uint32_t* __restrict__ new_ids,
+                                 uint32_t n_ids, uint32_t* subs_tail) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint32_t k = i; k < n_ids; k += gridDim.x * blockDim.x) subs_tail[k] = new_ids[k];      // the arena's new tail (nothing refers to it yet)
     if (i >= n) return;
     const uint4* src = reinterpret_cast<const uint4*>(&ops[i].image);
     uint4* dst = reinterpret_cast<uint4*>(slots + ops[i].index);
@@ -761,6 +768,15 @@ static int interest_rebuild(ssegpu_ctx* ctx) {
     CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_keys), t.keys.size() * 4, ts));
     CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_wild), t.wild_bytes.size(), ts));
     CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_desc), sizeof(sse::InterestDev), ts));
+    CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_subs), (t.subs->capacity() + 4) * 4, ts));
+    CU(cudaMallocAsync(reinterpret_cast<void**>(&gen->d_wild_ids), sse::INTEREST_MAX_WILD * 4, ts));
+    if (!t.subs->empty()) CU(cudaMemcpyAsync(gen->d_subs, t.subs->data(), t.subs->size() * 4, cudaMemcpyHostToDevice, ts));
+    {
+        uint32_t w[sse::INTEREST_MAX_WILD] = {0};
+        for (size_t k = 0; k < t.wild_ids.size(); k++) w[k] = t.wild_ids[k];
+        CU(cudaMemcpyAsync(gen->d_wild_ids, w, sizeof w, cudaMemcpyHostToDevice, ts));
+        CU(cudaStreamSynchronize(ts));
+    }
     CU(cudaMemcpyAsync(gen->d_slots, t.slots.data(), t.slots.size() * sizeof(sse::InterestSlot), cudaMemcpyHostToDevice, ts));
     CU(cudaMemcpyAsync(gen->d_keys, t.keys.data(), t.keys.size() * 4, cudaMemcpyHostToDevice, ts));
     CU(cudaMemcpyAsync(gen->d_wild, t.wild_bytes.data(), t.wild_bytes.size(), cudaMemcpyHostToDevice, ts));
@@ -785,6 +801,7 @@ int ssegpu_interest_apply(ssegpu_ctx* ctx, const ssegpu_sub_delta* d, uint32_t n
     sse_interest::HostTable& t = ctx->interest;
     std::string err;
     bool rebuild = !ctx->tab || !t.flattened;
+    const size_t arena_before = t.subs->size();
     for (uint32_t i = 0; i < n; i++) {
         std::string subj(d[i].subject, d[i].subject_len);
         const int ch = d[i].op == 0 ? t.add(subj, d[i].sub_id, err) : t.del(subj, d[i].sub_id);
@@ -796,7 +813,9 @@ int ssegpu_interest_apply(ssegpu_ctx* ctx, const ssegpu_sub_delta* d, uint32_t n
         if (ch == 2) rebuild = true;                              // the wildcard list lives in the descriptor: new generation
         else if (ch == 1 && !rebuild && !t.sync_subject(subj)) rebuild = true;
     }
-    if (!rebuild && t.dirty.size() > (size_t)ssegpu_ctx::kOpsPerChunk) rebuild = true;
+    // slot images and the arena's new tail travel together in one pinned staging chunk
+    const size_t new_ids = rebuild ? 0 : t.subs->size() - arena_before;
+    if (!rebuild && t.dirty.size() * sizeof(SlotOp) + new_ids * 4 > sizeof(SlotOp) * (size_t)ssegpu_ctx::kOpsPerChunk) rebuild = true;
     if (rebuild) {
         const int rc = interest_rebuild(ctx);
         if (rc == SSEGPU_OK) ctx->table_version++;
@@ -812,9 +831,11 @@ int ssegpu_interest_apply(ssegpu_ctx* ctx, const ssegpu_sub_delta* d, uint32_t n
         const uint32_t m = (uint32_t)t.dirty.size();
         for (uint32_t k = 0; k < m; k++) { h[k].index = t.dirty[k]; h[k].image = t.slots[t.dirty[k]]; }
         t.dirty.clear();
+        if (new_ids) memcpy(h + m, t.subs->data() + arena_before, new_ids * 4);
         { const int rc = table_stream_wait_users(ctx); if (rc != SSEGPU_OK) return rc; }
-        CU(cudaMemcpyAsync(dv, h, sizeof(SlotOp) * m, cudaMemcpyHostToDevice, ctx->table_stream));
-        k_interest_apply<<<(m + 127) / 128, 128, 0, ctx->table_stream>>>(dv, m, ctx->tab->d_slots);
+        CU(cudaMemcpyAsync(dv, h, sizeof(SlotOp) * m + new_ids * 4, cudaMemcpyHostToDevice, ctx->table_stream));
+        k_interest_apply<<<(m + 127) / 128, 128, 0, ctx->table_stream>>>(dv, m, ctx->tab->d_slots, reinterpret_cast<const uint32_t*>(dv + m), (uint32_t)new_ids,
+                                                                        ctx->tab->d_subs + arena_before);
         CU(cudaGetLastError());
         CU(cudaEventRecord(ctx->ev_chunk[chunk], ctx->table_stream));
         CU(cudaEventRecord(ctx->ev_table, ctx->table_stream));
@@ -864,6 +885,74 @@ int ssegpu_interest_bind(ssegpu_ctx* ctx, uint32_t* d_sub_span) {
     return SSEGPU_OK;
 }
 
+// ---- fan-out expansion ----------------------------------------------------------------------------
+// (record, subscriber) pairs from the spans OP_MATCH left: counts -> exclusive scan -> one thread per PAIR (binary search
+// for its record in the offsets), so a record with 1 024 subscribers costs no more per pair than one with a single one.
+__global__ void k_fanout_count(const uint32_t* __restrict__ span, uint32_t n, uint32_t* __restrict__ cnt, uint32_t* last) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t c = span[3 * (size_t)i + 1] + __popc(span[3 * (size_t)i + 2]);
+    cnt[i] = c;
+    if (i == n - 1) *last = c;
+}
+__global__ void k_fanout_totals(const uint32_t* rec_off, uint32_t n, uint64_t max_pairs, uint32_t* totals, uint32_t* rec_off_n) {
+    const uint32_t total = rec_off[n - 1] + totals[3];
+    totals[0] = total; totals[2] = total > max_pairs ? 1u : 0u;
+    *rec_off_n = total;
+}
+__global__ void k_fanout_emit(const uint32_t* __restrict__ span, const uint32_t* __restrict__ rec_off, uint32_t n, const uint32_t* __restrict__ subs,
+                              const uint32_t* __restrict__ wild_ids, const uint32_t* totals, uint32_t* __restrict__ pair_sub, uint32_t* __restrict__ pair_rec) {
+    if (totals[2]) return;
+    const uint32_t total = totals[0];
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+        uint32_t lo = 0, hi = n;                                  // last record whose offset is <= t
+        while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (rec_off[mid] <= t) lo = mid; else hi = mid; }
+        const uint32_t k = t - rec_off[lo], off = span[3 * (size_t)lo], cnt = span[3 * (size_t)lo + 1];
+        uint32_t id;
+        if (k < cnt) id = subs[off + k];
+        else {                                                    // the (k - cnt)-th set bit of the wildcard mask
+            uint32_t mask = span[3 * (size_t)lo + 2];
+            for (uint32_t j = k - cnt; j; j--) mask &= mask - 1;
+            id = wild_ids[__ffs((int)mask) - 1];
+        }
+        pair_sub[t] = id; pair_rec[t] = lo;
+    }
+}
+
+int ssegpu_fanout_launch(ssegpu_ctx* ctx, const uint32_t* d_sub_span, uint32_t n, uint32_t* d_pair_sub, uint32_t* d_pair_rec, uint64_t max_pairs,
+                         uint32_t* d_rec_off, void* stream) {
+    if (!ctx || !d_rec_off || (n && (!d_sub_span || !d_pair_sub || !d_pair_rec))) return SSEGPU_E_INVAL;
+    if (n > ctx->cfg.max_records) return SSEGPU_E_TOOBIG;
+    CU(cudaSetDevice(ctx->cfg.device));
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!ctx->tab) return SSEGPU_E_STATE;
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
+    if (!ctx->d_fanout_scratch) CU(cudaMalloc(&ctx->d_fanout_scratch, ((size_t)ctx->cfg.max_records / 4096 + 16) * 4 + 64));
+    uint32_t* totals = static_cast<uint32_t*>(ctx->d_fanout_scratch);
+    uint32_t* block_sums = totals + 8;
+    CU(cudaStreamWaitEvent(st, ctx->ev_table, 0));
+    CU(cudaMemsetAsync(totals, 0, 32, st));
+    if (n == 0) { CU(cudaMemsetAsync(d_rec_off, 0, 4, st)); return SSEGPU_OK; }
+    k_fanout_count<<<(n + 255) / 256, 256, 0, st>>>(d_sub_span, n, d_rec_off, totals + 3);
+    CU(sse::scan_exclusive_u32(d_rec_off, n, block_sums, st));
+    k_fanout_totals<<<1, 1, 0, st>>>(d_rec_off, n, max_pairs, totals, d_rec_off + n);
+    k_fanout_emit<<<148 * 8, 256, 0, st>>>(d_sub_span, d_rec_off, n, ctx->tab->d_subs, ctx->tab->d_wild_ids, totals, d_pair_sub, d_pair_rec);
+    CU(cudaGetLastError());
+    cudaEvent_t ev = ctx->ev_launch[ctx->next_launch_ev++ % ssegpu_ctx::kLaunchEvents];     // a later table update waits for this reader
+    CU(cudaEventRecord(ev, st));
+    ctx->launches += 6;
+    return SSEGPU_OK;
+}
+
+int ssegpu_fanout_result(ssegpu_ctx* ctx, uint64_t* n_pairs) {
+    if (!ctx || !ctx->d_fanout_scratch) return SSEGPU_E_STATE;
+    CU(cudaSetDevice(ctx->cfg.device));
+    uint32_t t[4];
+    CU(cudaMemcpy(t, ctx->d_fanout_scratch, sizeof t, cudaMemcpyDeviceToHost));
+    if (n_pairs) *n_pairs = t[0];
+    return t[2] ? SSEGPU_E_OVERFLOW : SSEGPU_OK;
+}
+
 // ---- receiving side of the wire protocols ------------------------------------------------------
 int ssegpu_split_launch(ssegpu_ctx* ctx, uint32_t proto, const void* d_buf, const uint32_t* d_buf_off, uint32_t n_conn, void* d_arena,
                         uint64_t arena_cap, uint32_t* d_in_off, uint32_t max_msgs, uint32_t* d_msg_conn, uint64_t* d_msg_sid,
@@ -876,7 +965,7 @@ int ssegpu_split_launch(ssegpu_ctx* ctx, uint32_t proto, const void* d_buf, cons
     if (need > ctx->wire_scratch_cap) {                      // grows on demand (first call, or a larger box of connections)
         cudaStream_t st0 = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
         CU(cudaStreamSynchronize(st0));
-        cudaFree(ctx->d_wire_scratch); cudaFree(ctx->d_chunk_scratch);
+        cudaFree(ctx->d_wire_scratch); cudaFree(ctx->d_chunk_scratch); cudaFree(ctx->d_fanout_scratch);
         ctx->d_wire_scratch = nullptr; ctx->wire_scratch_cap = 0;
         CU(cudaMalloc(&ctx->d_wire_scratch, need * 2));
         ctx->wire_scratch_cap = need * 2;

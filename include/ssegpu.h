@@ -219,6 +219,15 @@ const uint32_t *ssegpu_interest_subs(ssegpu_ctx *ctx, uint32_t *count);
 const uint32_t *ssegpu_interest_wild_ids(ssegpu_ctx *ctx, uint32_t *count);
 const uint32_t *ssegpu_sub_span(const ssegpu_batch *b);                      /* 3n */
 int ssegpu_interest_bind(ssegpu_ctx *ctx, uint32_t *d_sub_span);             /* buffer used by ssegpu_frame_launch */
+/* Fan-out expansion (BASELINE config 3/4: one Subscribe per connection, sse_handler.go:133-135, so a popular subject has
+ * many): turns the spans of n records (d_sub_span as SSEGPU_OP_MATCH left it, device memory) into the flat list of
+ * deliveries, d_pair_sub[k] = subscriber id, d_pair_rec[k] = record index, sorted by record (literal subscribers in span
+ * order, then the matching wildcard subscriptions); d_rec_off[0..n] = first pair of every record.  One thread per pair, so
+ * a record with 1 024 subscribers is as cheap per delivery as one with a single one.  Uses the CURRENT table generation:
+ * call it before the next ssegpu_interest_apply that follows the match launch.  Asynchronous on stream. */
+int ssegpu_fanout_launch(ssegpu_ctx *ctx, const uint32_t *d_sub_span, uint32_t n_records, uint32_t *d_pair_sub, uint32_t *d_pair_rec,
+                         uint64_t max_pairs, uint32_t *d_rec_off, void *stream);
+int ssegpu_fanout_result(ssegpu_ctx *ctx, uint64_t *n_pairs);               /* after sync; SSEGPU_E_OVERFLOW if max_pairs was too small */
 
 /* ---- device-resident launch (kernel-level path, used by the bench and the parity tests) -- */
 /* Same computation as submit, on buffers that already live in this context's GPU memory.

@@ -328,3 +328,59 @@ def test_streaming_batches_on_different_ring_slots_run_in_submit_order(pkg, orac
             assert (v2[0::4] != 0).all() and (v2[3::4] == 0).all()
     finally:
         eng.close()
+
+
+def test_fanout_expansion_of_match_spans(pkg, oracle):
+    """ssegpu_fanout_launch: (subscriber, record) pairs from the spans of an OP_MATCH launch, literal subscribers in list order
+    then the matching wildcard subscriptions; also after in-place table updates (the device copy of the id arena grows with them)."""
+    import torch
+    rng = random.Random(91)
+    n_subj = 3000
+    subs_of = {j: [] for j in range(n_subj)}
+    deltas, sid = [], 1
+    for j in range(n_subj):
+        fan = 0 if rng.random() < 0.1 else (1 if rng.random() < 0.7 else rng.randrange(2, 600))
+        for _ in range(fan):
+            deltas.append((0, sid, b"chat.subj-%d.tokens" % j))
+            subs_of[j].append(sid)
+            sid += 1
+    deltas += [(0, 900001, b"chat.*.tokens"), (0, 900002, b"chat.*.control"), (0, 900003, b"chat.>")]
+    eng = pkg.SseGpu(device=0, max_records=1 << 15, max_in_bytes=8 << 20)
+    try:
+        eng.interest_apply(deltas)
+        for step in range(3):
+            if step:                                    # a few in-place updates between launches
+                for _ in range(40):
+                    j = rng.randrange(n_subj)
+                    if subs_of[j] and rng.random() < 0.4:
+                        x = subs_of[j].pop(rng.randrange(len(subs_of[j])))
+                        eng.interest_apply([(1, x, b"chat.subj-%d.tokens" % j)])
+                    else:
+                        eng.interest_apply([(0, sid, b"chat.subj-%d.tokens" % j)])
+                        subs_of[j].append(sid)
+                        sid += 1
+            picks = [rng.randrange(n_subj + 50) for _ in range(20000)]
+            arena, off = oracle.pack([mg.canon("subj-%d" % j, " t", k, False, 5) for k, j in enumerate(picks)])
+            db = DevBuffers(torch, arena, off)
+            db.launch(eng, pkg.OP_BRIDGE | pkg.OP_MATCH)
+            n = db.n
+            cap = 4_000_000
+            d_sub, d_rec = torch.zeros(cap, dtype=torch.int32, device="cuda"), torch.zeros(cap, dtype=torch.int32, device="cuda")
+            d_roff = torch.zeros(n + 1, dtype=torch.int32, device="cuda")
+            eng.fanout_launch(db.d_hit.data_ptr(), n, d_sub.data_ptr(), d_rec.data_ptr(), cap, d_roff.data_ptr())
+            torch.cuda.synchronize()
+            rc, total = eng.fanout_result()
+            assert rc == 0
+            roff, ps, pr = d_roff.cpu().numpy(), d_sub.cpu().numpy()[:total], d_rec.cpu().numpy()[:total]
+            assert int(roff[n]) == total and np.array_equal(pr, np.repeat(np.arange(n), np.diff(roff)))
+            wild = eng.interest_wild_ids().tolist()
+            for i in list(range(0, n, 97)) + [int(x) for x in np.argsort(-np.diff(roff))[:20]]:
+                j = picks[i]
+                got = ps[int(roff[i]):int(roff[i + 1])].tolist()
+                lit = subs_of.get(j, [])
+                assert sorted(got[: len(lit)]) == sorted(lit) and sorted(got[len(lit):]) == sorted(w for w in wild if w in (900001, 900003)), (step, i, j)
+            assert total > 200000
+            rc, _ = (eng.fanout_launch(db.d_hit.data_ptr(), n, d_sub.data_ptr(), d_rec.data_ptr(), 1000, d_roff.data_ptr()), torch.cuda.synchronize(), eng.fanout_result())[2]
+            assert rc == -6
+    finally:
+        eng.close()
