@@ -107,7 +107,7 @@ for seed in range(a.first_seed, a.first_seed + a.seeds):
                 assert got[int(i)] == b"", (seed, op, int(i))
         checked += len(payloads)
     # interest table over a sample of the batch's own (decoded) conversation ids
-    cids = sorted({m_i["cid"] for st_i, m_i in decoded.values() if st_i == 0 and m_i["cid"] and "." not in m_i["cid"] and " " not in m_i["cid"]})[:1500]
+    cids = sorted({m_i["cid"] for st_i, m_i in decoded.values() if st_i == 0 and m_i["cid"] and all(ch.isalnum() or ch in "_-" for ch in m_i["cid"])})[:1500]   # ("*", ">", "a.b" would be wildcards / several tokens)
     eng.interest_apply([(0, k + 1, b"chat." + c.encode("utf-8") + b".tokens") for k, c in enumerate(cids)])
     b_out, b_off, b_subj, b_status = oracle.bridge(arena, off)
     b_want = slices(b_out, b_off)
