@@ -1,0 +1,8 @@
+set -x
+P=gpurun_out
+python tools/prof_target.py match > $P/p.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_frame_tiles -s 4 -c 1 -o $P/r02_ncu_match python tools/prof_target.py match > $P/n.log 2>&1
+python tools/prof_target.py stream > $P/p.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:"k_stream_walk|k_radix_scatter" -s 9 -c 2 -o $P/r02_ncu_stream python tools/prof_target.py stream > $P/n.log 2>&1
+python tools/bench_encode.py --steps 3 > $P/p.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_encode_messages -s 3 -c 1 -o $P/r02_ncu_encode python tools/bench_encode.py --steps 3 > $P/n.log 2>&1
+python bench.py --steps 3 --warmup 3 --no-extras > $P/p.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $P/r02_launches_bench.csv python bench.py --steps 3 --warmup 3 --no-extras > $P/n.log 2>&1
+python tools/prof_target.py stream > $P/p.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -s 52 -c 26 --csv --log-file $P/r02_launches_stream.csv python tools/prof_target.py stream > $P/n.log 2>&1
+ls -la $P/*.ncu-rep $P/*.csv
