@@ -89,26 +89,53 @@ __device__ __forceinline__ void st_relaxed_u64(uint64_t* p, uint64_t v) {
 // stays a single pass.
 constexpr int MODE_ARRIVAL = 0, MODE_ORDERED_COUNT = 1, MODE_ORDERED_EMIT = 2;
 
-__global__ void __launch_bounds__(1024) k_scan_tile_totals(uint64_t* tile_state, uint32_t num_tiles, uint64_t* out_total, uint32_t* ticket) {
-    __shared__ uint64_t warp_sums[32];
+// Tile totals -> exclusive prefixes, in place, in two small launches of one CTA per 1024 tiles: block sums first (parked in
+// out_off[0 .. blocks), which nothing has written yet and the emit pass overwrites afterwards), then every CTA adds up
+// the sums of the blocks in front of it and scans its own 1024 totals.  (One CTA scanning all 78 125 tiles of the
+// BASELINE batch took 82 us between the two passes.)
+constexpr uint32_t SCAN_BLOCK = 1024;
+__device__ __forceinline__ uint64_t block_reduce_u64(uint64_t v, uint64_t* warp_sums) {
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+    __syncthreads();                                   // warp_sums may still be read from a previous use
+    if (lane == 0) warp_sums[warp] = v;
+    __syncthreads();
+    uint64_t t = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < SCAN_BLOCK / 32; w++) t += warp_sums[w];
+    return t;
+}
+__global__ void __launch_bounds__(SCAN_BLOCK) k_tile_block_sums(const uint64_t* tile_state, uint32_t num_tiles, uint64_t* block_sums) {
+    __shared__ uint64_t warp_sums[SCAN_BLOCK / 32];
+    const uint32_t i = blockIdx.x * SCAN_BLOCK + threadIdx.x;
+    const uint64_t t = block_reduce_u64(i < num_tiles ? tile_state[i] : 0, warp_sums);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = t;
+}
+__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_tile_totals(uint64_t* tile_state, uint32_t num_tiles, const uint64_t* block_sums,
+                                                                 uint64_t* out_total, uint32_t* ticket) {
+    __shared__ uint64_t warp_sums[SCAN_BLOCK / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t per = (num_tiles + 1023) / 1024;
-    const uint32_t lo = min(num_tiles, tid * per), hi = min(num_tiles, lo + per);
-    uint64_t sum = 0;
-    for (uint32_t i = lo; i < hi; i++) sum += tile_state[i];
-    uint64_t incl = sum;
+    uint64_t before = 0;
+    for (uint32_t b = tid; b < blockIdx.x; b += SCAN_BLOCK) before += block_sums[b];
+    before = block_reduce_u64(before, warp_sums);
+    const uint32_t i = blockIdx.x * SCAN_BLOCK + tid;
+    const uint64_t mine = i < num_tiles ? tile_state[i] : 0;
+    uint64_t incl = mine;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-        uint64_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-        if (lane >= d) incl += v;
+        const uint64_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= (uint32_t)d) incl += v;
     }
+    __syncthreads();
     if (lane == 31) warp_sums[warp] = incl;
     __syncthreads();
     uint64_t wpre = 0, total = 0;
-    for (uint32_t w = 0; w < 32; w++) { const uint64_t v = warp_sums[w]; if (w < warp) wpre += v; total += v; }
-    uint64_t run = wpre + incl - sum;
-    for (uint32_t i = lo; i < hi; i++) { const uint64_t v = tile_state[i]; tile_state[i] = run; run += v; }
-    if (tid == 0) { *out_total = total; *ticket = 0; }         // pass B hands the tiles out again from 0
+#pragma unroll
+    for (uint32_t w = 0; w < SCAN_BLOCK / 32; w++) { const uint64_t v = warp_sums[w]; if (w < warp) wpre += v; total += v; }
+    if (i < num_tiles) tile_state[i] = before + wpre + incl - mine;
+    if (tid == 0 && blockIdx.x == gridDim.x - 1) *out_total = before + total;
+    if (tid == 0 && blockIdx.x == 0) *ticket = 0;               // pass B hands the tiles out again from 0
 }
 
 // ---------------------------------------------------------------------- kernel ----
@@ -120,6 +147,7 @@ constexpr uint32_t PLAN_REDO = 0xFFFFFFFFu;             // FrameArgs::plan: deco
 struct TileSmem {
     uint64_t mbar;
     uint64_t base;           // global byte offset of the tile's output
+    uint64_t obase;          // ordered emit pass: the same, known as soon as the tile is claimed (k_scan_tile_totals)
     uint32_t tile, tb, te, in_total;
     uint32_t npend;          // records of this tile left to the tail phase (later: fill of the tail's list)
     uint32_t wsum[TILE / 32];
@@ -148,10 +176,12 @@ __device__ __noinline__ uint32_t emit_slow(const uint8_t* src_base, uint32_t o, 
 }
 
 // tid 0: claim bookkeeping for tile t -- tile byte range + TMA load into s_in
-__device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t t, uint64_t& c_in) {
+__device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t t, uint64_t& c_in, bool want_base = false) {
     ts->tile = t;
     ts->npend = 0;
     if (t < a.num_tiles) {
+        uint64_t ob = 0;
+        if (want_base) ob = a.tile_state[t];                // requested first: in flight while the TMA load is set up
         const uint32_t r0 = t * TILE;
         const uint32_t nrec = min((uint32_t)TILE, a.n - r0);
         // offsets come from the host: clamp them so that nothing below can leave the arena, and say so
@@ -166,6 +196,7 @@ __device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uin
             tma_load_1d(s_in, a.in + abase, bytes, &ts->mbar);
         }
         c_in += te - tb;
+        if (want_base) ts->obase = ob;
     }
 }
 
@@ -231,44 +262,6 @@ __device__ __noinline__ void ext_stage_slow(const FrameArgs& a, uint32_t i, cons
     *plp = pl; *stp = st; *lenp = len;
 }
 
-__device__ __forceinline__ uint4 lds128(const uint8_t* p) { return *reinterpret_cast<const uint4*>(p); }
-
-// Staging tile (bytes [0,total) of s_out) -> out[g0, g0+total): coalesced 16-byte stores for the
-// 16-byte aligned interior, byte-shifted by r = (-g0) mod 16 on the fly (r is tile-uniform, so
-// the word part of the shift is a template parameter chosen once per tile).
-template <int Q>
-__device__ __forceinline__ void copy_chunks(uint4* __restrict__ dst, const uint8_t* s_out, uint32_t nchunk, uint32_t b, uint32_t tid) {
-    for (uint32_t i = tid; i < nchunk; i += TILE) {
-        const uint4 A = lds128(s_out + 16 * i), B = lds128(s_out + 16 * i + 16);
-        uint4 y;
-        if (Q == 0) { y.x = __funnelshift_r(A.x, A.y, b); y.y = __funnelshift_r(A.y, A.z, b); y.z = __funnelshift_r(A.z, A.w, b); y.w = __funnelshift_r(A.w, B.x, b); }
-        if (Q == 1) { y.x = __funnelshift_r(A.y, A.z, b); y.y = __funnelshift_r(A.z, A.w, b); y.z = __funnelshift_r(A.w, B.x, b); y.w = __funnelshift_r(B.x, B.y, b); }
-        if (Q == 2) { y.x = __funnelshift_r(A.z, A.w, b); y.y = __funnelshift_r(A.w, B.x, b); y.z = __funnelshift_r(B.x, B.y, b); y.w = __funnelshift_r(B.y, B.z, b); }
-        if (Q == 3) { y.x = __funnelshift_r(A.w, B.x, b); y.y = __funnelshift_r(B.x, B.y, b); y.z = __funnelshift_r(B.y, B.z, b); y.w = __funnelshift_r(B.z, B.w, b); }
-        dst[i] = y;
-    }
-}
-__device__ __forceinline__ void copy_out(uint8_t* __restrict__ out, const uint8_t* s_out, uint64_t g0, uint32_t total, uint32_t tid) {
-    const uint64_t g1 = g0 + total;
-    const uint64_t ga = (g0 + 15) & ~15ull, gb = g1 & ~15ull;
-    if (ga >= gb) {
-        for (uint32_t i = tid; i < total; i += TILE) out[g0 + i] = s_out[i];
-        return;
-    }
-    const uint32_t r = (uint32_t)(ga - g0), b = (r & 3u) * 8;
-    const uint32_t nchunk = (uint32_t)((gb - ga) >> 4);
-    uint4* dst = reinterpret_cast<uint4*>(out + ga);
-    switch (r >> 2) {                          // tile-uniform: no divergence
-    case 0:  copy_chunks<0>(dst, s_out, nchunk, b, tid); break;
-    case 1:  copy_chunks<1>(dst, s_out, nchunk, b, tid); break;
-    case 2:  copy_chunks<2>(dst, s_out, nchunk, b, tid); break;
-    default: copy_chunks<3>(dst, s_out, nchunk, b, tid); break;
-    }
-    const uint32_t tail = (uint32_t)(g1 - gb);
-    if (tid < r) out[g0 + tid] = s_out[tid];
-    if (tid >= 32 && tid - 32 < tail) out[gb + (tid - 32)] = s_out[total - tail + (tid - 32)];
-}
-
 // EXT is a compile-time switch so that the plain framing kernel carries none of the registers of the optional
 // stages (per-token content inspection, interest lookup, token entries for the streaming walk).
 constexpr int X_INSPECT = 1, X_INTEREST = 2;    // compile-time set of optional stages (each variant pays only for its own registers)
@@ -310,7 +303,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
     if (tid == 0) {
         mbar_init(&ts->mbar, 1);
         ts->in_total = a.in_off[a.n];
-        setup_tile(a, ts, s_in, atomicAdd(a.ticket, 1u), c_in);
+        setup_tile(a, ts, s_in, atomicAdd(a.ticket, 1u), c_in, MODE == MODE_ORDERED_EMIT);
     }
 
     for (;;) {
@@ -484,7 +477,12 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
             continue;
         }
         constexpr bool ordered = MODE == MODE_ORDERED_EMIT;
-        const bool smem_out = total <= a.out_cap_smem();                      // tile-uniform
+        // Ordered emit pass: the tile's arena offset is already known (k_scan_tile_totals), so the staging tile is laid
+        // out at the same position modulo 16 as the arena bytes it becomes; its 16-byte aligned interior then leaves as
+        // ONE TMA bulk store like an arrival-mode tile, and only the <= 15 bytes at either end are stored by threads.
+        const uint64_t obase = ordered ? ts->obase : 0;                       // read before (D); setup_tile rewrites it after (D)
+        const uint32_t shift = ordered ? (uint32_t)obase & 15u : 0u;
+        const bool smem_out = total + (ordered ? 16u : 0u) <= a.out_cap_smem();   // tile-uniform
         // arrival-order placement: every tile owns a 16-byte aligned slice of the arena, so its staging
         // tile leaves as ONE TMA bulk store; the <=15 pad bytes after its last frame are zeroed.
         const uint32_t alloc = ordered ? total : ((total + 15u) & ~15u);
@@ -494,7 +492,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
         }
         if (tid == 0) {
             c_out += total;
-            if (ordered) ts->base = a.tile_state[tile];                       // exclusive prefix from k_scan_tile_totals
+            if (ordered) ts->base = obase;                                    // exclusive prefix from k_scan_tile_totals
             else ts->base = atomicAdd(a.cursor, (unsigned long long)alloc);   // nothing to wait for
         }
         const uint32_t local = wpre + incl - len;
@@ -507,19 +505,17 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
                 if (fastp) {
                     PtrSrc src{s_in};
                     Ptr32Dst d{s_out};
-                    Writer<Ptr32Dst, true> w(d, local);
+                    Writer<Ptr32Dst, true> w(d, local + shift);
                     emit_record_fast(src, o, L, pl, a.op, w, &subj);
                 } else {
                     Plan sp = pl;
-                    subj = emit_slow(sb, o, L, &sp, a.op, s_out, (uint64_t)local);
+                    subj = emit_slow(sb, o, L, &sp, a.op, s_out, (uint64_t)(local + shift));
                 }
             }
-            if (!ordered) {
-                if (tid < alloc - total) s_out[total + tid] = 0;
-                fence_proxy_async_smem();                                     // staging writes -> visible to the TMA store
-            }
+            if (!ordered && tid < alloc - total) s_out[total + tid] = 0;
+            fence_proxy_async_smem();                                         // staging writes -> visible to the TMA store
             __syncthreads();                                                  // (D) s_in free, staging tile complete, base visible
-            if (tid == 0) setup_tile(a, ts, s_in, next_t, c_in);              // next tile's TMA load flies during the copy-out
+            if (tid == 0) setup_tile(a, ts, s_in, next_t, c_in, ordered);     // next tile's TMA load flies during the copy-out
         } else {
             // ---- oversize tile: emit straight into the arena ---------------------------
             __syncthreads();                                                  // (D')
@@ -533,7 +529,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
             }
             if (fits && tid < alloc - total) a.out[base + total + tid] = 0;       // pad of an aligned tile
             __syncthreads();                                                  // (E') s_in free
-            if (tid == 0) setup_tile(a, ts, s_in, next_t, c_in);
+            if (tid == 0) setup_tile(a, ts, s_in, next_t, c_in, ordered);
         }
         if (active) {
             if (code == ST_OK) { c_ok++; c_fast += fastp ? 1u : 0u; if (st & ST_DONE) c_done++; }
@@ -547,8 +543,17 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
         }
         if (tid == 0 && !fits) atomicExch(a.overflow, 1u);
         if (smem_out && fits && total != 0) {
-            if (ordered) copy_out(a.out, s_out, base, total, tid);
-            else if (tid == 0) { tma_store_1d(a.out + base, s_out, alloc); bulk_commit(); }
+            if (ordered) {
+                const uint64_t g1 = base + total, ga = (base + 15) & ~15ull, gb = g1 & ~15ull;
+                if (ga < gb) {
+                    const uint32_t head = (uint32_t)(ga - base), tail = (uint32_t)(g1 - gb);
+                    if (tid == 0) { tma_store_1d(a.out + ga, s_out + shift + head, (uint32_t)(gb - ga)); bulk_commit(); }
+                    if (tid >= 32 && tid - 32 < head) a.out[base + (tid - 32)] = s_out[shift + (tid - 32)];
+                    if (tid >= 64 && tid - 64 < tail) a.out[gb + (tid - 64)] = s_out[shift + (total - tail) + (tid - 64)];
+                } else {
+                    for (uint32_t i = tid; i < total; i += TILE) a.out[base + i] = s_out[shift + i];
+                }
+            } else if (tid == 0) { tma_store_1d(a.out + base, s_out, alloc); bulk_commit(); }
         }
     }
 
@@ -659,10 +664,18 @@ static void cfg_caps(int cfg, uint32_t* ic, uint32_t* oc, uint32_t* smem) {
     *oc = TILE * (cfg == 2 ? 184 : ((cfg == 1 || cfg == 4) ? 224 : 192));
     *smem = *ic + 32 + *oc + 48 + (uint32_t)sizeof(TileSmem) + (cache ? DFA_CACHE_BYTES : 0u);
 }
+// The counting pass of ordered mode never stages a frame: launched with out_cap_s = 0 it needs the input tile only, and
+// more CTAs fit an SM.
+static uint32_t count_smem(int cfg) {
+    uint32_t ic, oc, sm;
+    cfg_caps(cfg, &ic, &oc, &sm);
+    return sm - oc;
+}
 
 static std::mutex g_cfg_mu;             // the cache below is filled once per device, from whichever thread launches first
 static int g_num_sms[64];
 static int g_ctas_per_sm[64][4][N_CFG]; // [device][ext][cfg]; 0 = device not configured yet
+static int g_count_ctas_per_sm[64][4][N_CFG];   // the same for the counting pass of ordered mode
 
 template <int EXT, int MODE>
 static cudaError_t configure_one(int* per_sm /* [N_CFG] */) {
@@ -676,7 +689,21 @@ static cudaError_t configure_one(int* per_sm /* [N_CFG] */) {
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<EXT, MODE>, TILE, sm);
         if (e != cudaSuccess) return e;
         per = per < 1 ? 1 : per;
-        per_sm[c] = per_sm[c] == 0 ? per : min(per_sm[c], per);      // the three modes of one launch share a grid
+        per_sm[c] = per_sm[c] == 0 ? per : min(per_sm[c], per);      // arrival and emit pass: one table
+    }
+    return cudaSuccess;
+}
+template <int EXT>
+static cudaError_t configure_count(int* per_sm /* [N_CFG] */) {
+    uint32_t sm_max = 0;
+    for (int c = 0; c < N_CFG; c++) sm_max = max(sm_max, count_smem(c));
+    cudaError_t e = cudaFuncSetAttribute(k_frame_tiles<EXT, MODE_ORDERED_COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_max);
+    if (e != cudaSuccess) return e;
+    for (int c = 0; c < N_CFG; c++) {
+        int per = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_frame_tiles<EXT, MODE_ORDERED_COUNT>, TILE, count_smem(c));
+        if (e != cudaSuccess) return e;
+        per_sm[c] = per < 1 ? 1 : per;
     }
     return cudaSuccess;
 }
@@ -687,25 +714,27 @@ cudaError_t frame_configure(int device) {
     int sms = 0;
     cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     if (e != cudaSuccess) return e;
-    int per[4][N_CFG] = {};
+    int per[4][N_CFG] = {}, cnt[4][N_CFG] = {};
     if ((e = configure_one<0, MODE_ARRIVAL>(per[0])) != cudaSuccess) return e;
-    if ((e = configure_one<0, MODE_ORDERED_COUNT>(per[0])) != cudaSuccess) return e;
     if ((e = configure_one<0, MODE_ORDERED_EMIT>(per[0])) != cudaSuccess) return e;
+    if ((e = configure_count<0>(cnt[0])) != cudaSuccess) return e;
     if ((e = configure_one<1, MODE_ARRIVAL>(per[1])) != cudaSuccess) return e;
-    if ((e = configure_one<1, MODE_ORDERED_COUNT>(per[1])) != cudaSuccess) return e;
     if ((e = configure_one<1, MODE_ORDERED_EMIT>(per[1])) != cudaSuccess) return e;
+    if ((e = configure_count<1>(cnt[1])) != cudaSuccess) return e;
     if ((e = configure_one<2, MODE_ARRIVAL>(per[2])) != cudaSuccess) return e;
-    if ((e = configure_one<2, MODE_ORDERED_COUNT>(per[2])) != cudaSuccess) return e;
     if ((e = configure_one<2, MODE_ORDERED_EMIT>(per[2])) != cudaSuccess) return e;
+    if ((e = configure_count<2>(cnt[2])) != cudaSuccess) return e;
     if ((e = configure_one<3, MODE_ARRIVAL>(per[3])) != cudaSuccess) return e;
-    if ((e = configure_one<3, MODE_ORDERED_COUNT>(per[3])) != cudaSuccess) return e;
     if ((e = configure_one<3, MODE_ORDERED_EMIT>(per[3])) != cudaSuccess) return e;
+    if ((e = configure_count<3>(cnt[3])) != cudaSuccess) return e;
     g_num_sms[device] = sms;
+    for (int x = 3; x >= 0; x--) for (int c = N_CFG - 1; c >= 0; c--) g_count_ctas_per_sm[device][x][c] = cnt[x][c];
     for (int x = 3; x >= 0; x--) for (int c = N_CFG - 1; c >= 0; c--) g_ctas_per_sm[device][x][c] = per[x][c];
     return cudaSuccess;
 }
 
-static cudaError_t choose_variant(int device, FrameArgs& a, int* ext, uint32_t* smem_bytes, int* grid) {
+struct CountLaunch { int grid; uint32_t smem; };
+static cudaError_t choose_variant(int device, FrameArgs& a, int* ext, uint32_t* smem_bytes, int* grid, CountLaunch* cl = nullptr) {
     cudaError_t e = frame_configure(device);
     if (e != cudaSuccess) return e;
     *ext = ((a.insp != nullptr || a.tok_entry != nullptr || (a.xflags & XF_PRE_VERDICT)) ? X_INSPECT : 0) | (a.interest != nullptr ? X_INTEREST : 0);
@@ -716,14 +745,23 @@ static cudaError_t choose_variant(int device, FrameArgs& a, int* ext, uint32_t* 
     *grid = g_num_sms[device] * g_ctas_per_sm[device][*ext][cfg];
     a.num_tiles = (a.n + TILE - 1) / TILE;
     if ((int)a.num_tiles < *grid) *grid = (int)a.num_tiles;
+    if (cl) {
+        cl->grid = min((int)a.num_tiles, g_num_sms[device] * g_count_ctas_per_sm[device][*ext][cfg]);
+        cl->smem = count_smem(cfg);
+    }
     return cudaSuccess;
 }
 
 template <int EXT>
-static void launch_variant(const FrameArgs& a, int grid, uint32_t smem_bytes, cudaStream_t stream) {
+static void launch_variant(const FrameArgs& a, int grid, uint32_t smem_bytes, const CountLaunch& cl, cudaStream_t stream) {
     if (a.op & OP_ORDERED) {
-        k_frame_tiles<EXT, MODE_ORDERED_COUNT><<<grid, TILE, smem_bytes, stream>>>(a);
-        k_scan_tile_totals<<<1, 1024, 0, stream>>>(a.tile_state, a.num_tiles, a.out_off + a.n, a.ticket);
+        FrameArgs ac = a;
+        ac.out_cap_s = 0;
+        k_frame_tiles<EXT, MODE_ORDERED_COUNT><<<cl.grid, TILE, cl.smem, stream>>>(ac);
+        const uint32_t nb = (a.num_tiles + SCAN_BLOCK - 1) / SCAN_BLOCK;
+        uint64_t* block_sums = a.out_off;                 // free until the emit pass; nb <= n, so out_off[n] is not among them
+        k_tile_block_sums<<<nb, SCAN_BLOCK, 0, stream>>>(a.tile_state, a.num_tiles, block_sums);
+        k_scan_tile_totals<<<nb, SCAN_BLOCK, 0, stream>>>(a.tile_state, a.num_tiles, block_sums, a.out_off + a.n, a.ticket);
         k_frame_tiles<EXT, MODE_ORDERED_EMIT><<<grid, TILE, smem_bytes, stream>>>(a);
     } else {
         k_frame_tiles<EXT, MODE_ARRIVAL><<<grid, TILE, smem_bytes, stream>>>(a);
@@ -744,15 +782,16 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     uint32_t smem_bytes;
     int grid;
     int ext;
-    cudaError_t e = choose_variant(device, a, &ext, &smem_bytes, &grid);
+    CountLaunch cl;
+    cudaError_t e = choose_variant(device, a, &ext, &smem_bytes, &grid, &cl);
     if (e != cudaSuccess) return e;
     if ((e = clear_scratch(a, stream)) != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
     switch (ext) {
-    case 0: launch_variant<0>(a, grid, smem_bytes, stream); break;
-    case 1: launch_variant<1>(a, grid, smem_bytes, stream); break;
-    case 2: launch_variant<2>(a, grid, smem_bytes, stream); break;
-    default: launch_variant<3>(a, grid, smem_bytes, stream); break;
+    case 0: launch_variant<0>(a, grid, smem_bytes, cl, stream); break;
+    case 1: launch_variant<1>(a, grid, smem_bytes, cl, stream); break;
+    case 2: launch_variant<2>(a, grid, smem_bytes, cl, stream); break;
+    default: launch_variant<3>(a, grid, smem_bytes, cl, stream); break;
     }
     return cudaGetLastError();
 }
@@ -762,11 +801,13 @@ cudaError_t frame_plan_launch(int device, FrameArgs a, cudaStream_t stream) {
     int grid;
     int ext;
     a.xflags |= XF_ENTRY_IN_COUNT;
-    cudaError_t e = choose_variant(device, a, &ext, &smem_bytes, &grid);
+    CountLaunch cl;
+    cudaError_t e = choose_variant(device, a, &ext, &smem_bytes, &grid, &cl);
     if (e != cudaSuccess) return e;
     if ((e = clear_scratch(a, stream)) != cudaSuccess) return e;
     if (a.n == 0) return cudaSuccess;
-    k_frame_tiles<X_INSPECT, MODE_ORDERED_COUNT><<<grid, TILE, smem_bytes, stream>>>(a);
+    a.out_cap_s = 0;
+    k_frame_tiles<X_INSPECT, MODE_ORDERED_COUNT><<<cl.grid, TILE, cl.smem, stream>>>(a);
     return cudaGetLastError();
 }
 
