@@ -144,6 +144,8 @@ __global__ void __launch_bounds__(SCAN_BLOCK) k_scan_tile_totals(uint64_t* tile_
 #endif
 constexpr uint32_t PREFETCH_WAVES = SSE_PREFETCH_WAVES;
 constexpr uint32_t PLAN_REDO = 0xFFFFFFFFu;             // FrameArgs::plan: decode this record again in the emit pass
+constexpr uint32_t PLAN_HOLE = 0xFFFFFFFEu;             // emit pass -> its tail: this record's frame is still to be written
+constexpr uint32_t DEFER_MAX_PER_WARP = 9;              // more such records than this in a warp: decoded inline, where the tile is on chip
 struct TileSmem {
     uint64_t mbar;
     uint64_t base;           // global byte offset of the tile's output
@@ -266,7 +268,7 @@ __device__ __noinline__ void ext_stage_slow(const FrameArgs& a, uint32_t i, cons
 // stages (per-token content inspection, interest lookup, token entries for the streaming walk).
 constexpr int X_INSPECT = 1, X_INTEREST = 2;    // compile-time set of optional stages (each variant pays only for its own registers)
 template <int EXT, int MODE>
-__global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_constant__ FrameArgs a) {
+__global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0) ? 8 : 640 / TILE) k_frame_tiles(const __grid_constant__ FrameArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* s_in = smem;                                   // in_cap + 32 (word reads run up to 24 bytes past a record)
     uint8_t* s_out = smem + a.in_cap + 32;                  // out_cap_s + 48
@@ -350,21 +352,32 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
         // ONE such record makes its whole warp -- and at the next barrier its CTA -- wait ten times as long as a
         // canonical tile takes (measured: 1 % of them cost 7x).
         constexpr bool DEFER = MODE == MODE_ARRIVAL;
-        constexpr uint32_t DEFER_MAX_PER_WARP = 9;
         Plan pl;
         uint32_t st = ST_OK, len = 0;
         const uint32_t o = my_b - abase, L = my_e - my_b;
         const uint8_t* sb = smem_in ? s_in : a.in + abase;                    // where this tile's bytes are read from
         bool fastp = false;
         bool planned = false;
-        if (MODE == MODE_ORDERED_EMIT && !EXT && a.plan && active && smem_in) {
-            const uint32_t pw = a.plan[r0 + tid];                             // left by the count pass
-            if (pw != PLAN_REDO) {
+        // Ordered mode with plan words (no optional stages): both passes leave the records that are not canonical to
+        // their tail phases too.  The count pass's tail adds their lengths to the tile totals before the scan; the emit
+        // pass places such a record as a hole of the known length and its tail writes the frame into it.
+        const bool defer_ordered = (MODE == MODE_ORDERED_COUNT || MODE == MODE_ORDERED_EMIT) && !EXT && a.plan != nullptr;   // launch-uniform
+        bool hole = false;
+        if (MODE == MODE_ORDERED_EMIT && defer_ordered) {
+            uint32_t pw = 0;
+            if (active) {
+                pw = a.plan[r0 + tid];                                        // left by the count pass
                 st = a.status[r0 + tid]; len = a.out_len[r0 + tid];
+            }
+            const bool redo = active && pw == PLAN_REDO;
+            const uint32_t nredo = __popc(__ballot_sync(0xFFFFFFFFu, redo));
+            if (redo && nredo < DEFER_MAX_PER_WARP) { hole = true; planned = true; a.plan[r0 + tid] = PLAN_HOLE; }
+            else if (active && !redo && smem_in) {
                 pl.fast = 1; pl.cid_b = 20; pl.seq_b = pw & 0x3FFFu; pl.cid_e = (pw >> 14) & 0x3FFFu; pl.seq_n = pw >> 28;
                 pl.done = (st & ST_DONE) ? 1u : 0u; pl.cid_esc = 0; pl.tok_esc = 0; pl.tok_redacted = 0;
                 fastp = true; planned = true;
-            }
+            } else { st = ST_OK; len = 0; }                                   // decoded again below
+            if (lane == 0 && nredo && nredo < DEFER_MAX_PER_WARP) atomicAdd(&ts->npend, nredo);
         }
         InterestPre ipre{0, 0, 0, 0, 0, 0};
         if (active && smem_in && !planned) {
@@ -376,9 +389,9 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
         }
         // A few such records in a warp: deferred (the tail phase runs them densely).  Many of
         // them: decoded here, where the tile is in shared memory (22 ns per warp however many of its lanes take part).
-        const bool slow = active && !fastp;
+        const bool slow = active && !fastp && !hole;
         const uint32_t nslow = __popc(__ballot_sync(0xFFFFFFFFu, slow));
-        const bool defer = DEFER && nslow < DEFER_MAX_PER_WARP;      // warp-uniform
+        const bool defer = (DEFER || (MODE == MODE_ORDERED_COUNT && defer_ordered)) && nslow < DEFER_MAX_PER_WARP;      // warp-uniform
         if (slow) {
             if (defer) { st = ST_PENDING; len = 0; }
             else {                   // separate Plan object: taking pl's address would push the hot path's plan into local memory
@@ -471,7 +484,9 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
                 a.out_len[r0 + tid] = len;
             }
             if (tid == 0) {
-                a.tile_state[tile] = total;
+                uint64_t w = total;
+                if (ts->npend) { w |= (uint64_t)my_chain << 32; my_chain = tile + 1; }   // tiles with records left to the tail, chained
+                a.tile_state[tile] = w;
                 setup_tile(a, ts, s_in, next_t, c_in);                        // every thread is past (B): the tile has been consumed
             }
             continue;
@@ -486,7 +501,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
         // arrival-order placement: every tile owns a 16-byte aligned slice of the arena, so its staging
         // tile leaves as ONE TMA bulk store; the <=15 pad bytes after its last frame are zeroed.
         const uint32_t alloc = ordered ? total : ((total + 15u) & ~15u);
-        if (DEFER && tid == 0 && ts->npend) {          // chain this tile to the CTA's list of tiles with records left over
+        if ((DEFER || MODE == MODE_ORDERED_EMIT) && tid == 0 && ts->npend) {   // chain this tile to the CTA's list of tiles with records left over
             a.tile_state[tile] = (uint64_t)ts->npend | ((uint64_t)my_chain << 32);
             my_chain = tile + 1;
         }
@@ -501,7 +516,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
 
         if (smem_out) {
             // ---- pass 2 into the staging tile; the global offset is not needed yet ------
-            if (active && code == ST_OK) {
+            if (active && code == ST_OK && !hole) {
                 if (fastp) {
                     PtrSrc src{s_in};
                     Ptr32Dst d{s_out};
@@ -523,7 +538,7 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
         const uint64_t base = ts->base;
         const bool fits = base + alloc <= a.out_cap;
         if (!smem_out) {
-            if (active && code == ST_OK && fits) {
+            if (active && code == ST_OK && fits && !hole) {
                 Plan sp = pl;
                 subj = emit_slow(sb, o, L, &sp, a.op, a.out, base + local);
             }
@@ -557,7 +572,10 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
         }
     }
 
-    if (tid == 0) bulk_wait0();
+    if (tid == 0) {
+        bulk_wait0();
+        if (MODE == MODE_ORDERED_EMIT) asm volatile("fence.proxy.async;" ::: "memory");   // the tail writes into tiles stored by TMA
+    }
     unsigned long long* row = a.counters + (size_t)(blockIdx.x % CTR_ROWS) * CTR_COLS;
 
     // ---- tail: the records this CTA left over --------------------------------------------------
@@ -566,6 +584,79 @@ __global__ void __launch_bounds__(TILE, 640 / TILE) k_frame_tiles(const __grid_c
     // stages -- runs over them one record per lane, 128 at a time, straight from and to global memory.  Each warp
     // takes a 16-byte aligned slice of the arena from the same cursor, so such a frame simply lives somewhere else in
     // the arena (out_off/out_len address it like any other).
+    if (MODE == MODE_ORDERED_COUNT && !EXT && a.plan != nullptr) {
+        // Count pass: lengths and statuses of the records left over; each length is added to its tile's total (the
+        // chain link in the upper half of the tile word is cleared as the chain is walked, the scan wants plain totals).
+        uint32_t* s_list = reinterpret_cast<uint32_t*>(s_in);
+        __syncthreads();
+        if (tid == 0) { ts->tile = my_chain; ts->npend = 0; }
+        __syncthreads();
+        uint32_t t1 = ts->tile;
+        const uint32_t in_total = ts->in_total;
+        while (t1 != 0) {
+            uint32_t cnt = 0;
+            while (t1 != 0 && cnt < (uint32_t)TILE) {
+                const uint32_t t = t1 - 1, i = t * TILE + tid;
+                if (i < a.n && (a.status[i] & ST_CODE_MASK) == ST_PENDING) s_list[atomicAdd(&ts->npend, 1u)] = i;
+                t1 = (uint32_t)(a.tile_state[t] >> 32);
+                __syncthreads();
+                if (tid == 0) a.tile_state[t] &= 0xFFFFFFFFull;
+                cnt = ts->npend;
+            }
+            __syncthreads();                                                  // links cleared before any length is added
+            for (uint32_t g = 0; g < cnt; g += TILE) {
+                if (g + tid < cnt) {
+                    const uint32_t i = s_list[g + tid];
+                    const uint32_t b = min(a.in_off[i], in_total), e = min(max(a.in_off[i + 1], b), in_total);
+                    Plan pl;
+                    uint32_t len = 0;
+                    const uint32_t st = plan_slow(a.in, b, e - b, a.op, a.start_seq ? a.start_seq[i] : 0, &pl, &len);
+                    a.status[i] = st;
+                    a.out_len[i] = len;
+                    if (len) atomicAdd(reinterpret_cast<unsigned long long*>(&a.tile_state[i / TILE]), (unsigned long long)len);
+                }
+            }
+            __syncthreads();
+            if (tid == 0) ts->npend = 0;
+            __syncthreads();
+        }
+    }
+    if (MODE == MODE_ORDERED_EMIT && !EXT && a.plan != nullptr) {
+        // Emit pass: the frames of the records placed as holes, written where the main loop put them.
+        uint32_t* s_list = reinterpret_cast<uint32_t*>(s_out);
+        __syncthreads();                                                      // the last tile's bulk store is complete (bulk_wait0 above)
+        if (tid == 0) { ts->tile = my_chain; ts->npend = 0; }
+        __syncthreads();
+        uint32_t t1 = ts->tile;
+        const uint32_t in_total = ts->in_total;
+        while (t1 != 0) {
+            uint32_t cnt = 0;
+            while (t1 != 0 && cnt < (uint32_t)TILE) {
+                const uint32_t t = t1 - 1, i = t * TILE + tid;
+                if (i < a.n && a.plan[i] == PLAN_HOLE) s_list[atomicAdd(&ts->npend, 1u)] = i;
+                t1 = (uint32_t)(a.tile_state[t] >> 32);
+                __syncthreads();
+                cnt = ts->npend;
+            }
+            for (uint32_t g = 0; g < cnt; g += TILE) {
+                if (g + tid < cnt) {
+                    const uint32_t i = s_list[g + tid];
+                    const uint32_t b = min(a.in_off[i], in_total), e = min(max(a.in_off[i + 1], b), in_total);
+                    Plan pl;
+                    uint32_t len = 0;
+                    const uint32_t st = plan_slow(a.in, b, e - b, a.op, a.start_seq ? a.start_seq[i] : 0, &pl, &len);
+                    const uint64_t at = a.out_off[i];
+                    if ((st & ST_CODE_MASK) == ST_OK && len != 0 && at + len <= a.out_cap) {
+                        const uint32_t subj = emit_slow(a.in, b, e - b, &pl, a.op, a.out, at);
+                        if (a.subj_len) a.subj_len[i] = subj;
+                    }
+                }
+            }
+            __syncthreads();
+            if (tid == 0) ts->npend = 0;
+            __syncthreads();
+        }
+    }
     if (MODE == MODE_ARRIVAL) {
         uint32_t* s_list = reinterpret_cast<uint32_t*>(s_out);
         __syncthreads();                                                      // every thread has read the loop's last ts->tile
