@@ -735,6 +735,16 @@ template <class Src> SSE_HD bool parse_int64(const Src& s, uint32_t b, uint32_t 
 // decode.go object(): field whose name equals the unquoted key exactly, else under simple
 // case folding (fold.go foldName).  Only {K,k,U+212A} and {S,s,U+017F} fold onto ASCII.
 template <class Src> SSE_HD int match_field(const Src& s, uint32_t b, uint32_t e) {
+    // the exact names first, compared as words (what every producer that uses the struct tags sends); a name that
+    // matches exactly is also the one the folded comparison below would find
+    {
+        const uint32_t n = e - b, w0 = ld32u(s, b);
+        if (n == 5 && w0 == w4("toke") && s.ld8(b + 4) == 'n') return 1;
+        if (n == 4 && w0 == w4("done")) return 3;
+        if (n == 8 && w0 == w4("sequ") && ld32u(s, b + 4) == w4("ence")) return 2;
+        if (n == 9 && w0 == w4("time") && ld32u(s, b + 4) == w4("stam") && s.ld8(b + 8) == 'p') return 4;
+        if (n == 15 && w0 == w4("conv") && ld32u(s, b + 4) == w4("ersa") && ld32u(s, b + 8) == w4("tion") && ld32u(s, b + 11) == w4("n_id")) return 0;
+    }
     uint32_t alive = 0x1F, k = 0;
     while (b < e && alive) {
         uint32_t r = next_rune(s, b, e);

@@ -100,7 +100,7 @@ def func_of(key):
     return f
 
 
-fn_incl, site = {}, {}
+fn_incl, site, fn_static = {}, {}, {}
 for k in range(n):
     ie_k, s_k = int(body[k][ie]), int(body[k][smp])
     seen = set()
@@ -111,6 +111,11 @@ for k in range(n):
             a = fn_incl.setdefault(fn, [0, 0])
             a[0] += ie_k
             a[1] += s_k
+            fn_static[fn] = fn_static.get(fn, 0) + 1
+if "--static" in sys.argv:
+    print("---- static SASS instructions per function (inclusive of what is inlined into it), of %d ----" % n)
+    for fn, c in sorted(fn_static.items(), key=lambda kv: -kv[1])[:30]:
+        print("%6d  %s" % (c, fn))
     if chains[k]:
         outer = chains[k][-1]
         a = site.setdefault(outer, [0, 0])
