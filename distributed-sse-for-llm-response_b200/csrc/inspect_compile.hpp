@@ -208,6 +208,9 @@ struct Dfa {
     uint8_t cls[256];                           // byte -> class
     std::vector<uint16_t> next;                 // [state][class]; 0xFFFF = dead; bit 15 = target state reports a match
     std::vector<uint32_t> acc_imm, acc_del, acc_eot;
+    // per state: the fewest further bytes after which anything can be reported (0 = at end of text in this state),
+    // saturating at 15.  A walk that has fewer bytes left than that can stop.
+    std::vector<uint8_t> dist;
 };
 
 namespace detail {
@@ -305,6 +308,21 @@ inline bool build_dfa(const Nfa& nfa, const std::vector<uint32_t>& starts, bool 
     // loads the accept masks only when something fired
     for (uint16_t& nx : out.next)
         if (nx != 0xFFFF && (out.acc_imm[nx] | out.acc_del[nx])) nx |= 0x8000;
+    std::vector<uint32_t> dist(out.n_states, INF);
+    for (uint32_t st = 0; st < out.n_states; st++) if (out.acc_eot[st]) dist[st] = 0;
+    for (bool changed = true; changed;) {
+        changed = false;
+        for (uint32_t st = 0; st < out.n_states; st++)
+            for (uint32_t c = 0; c < out.n_classes; c++) {
+                const uint16_t nx = out.next[(size_t)st * out.n_classes + c];
+                if (nx == 0xFFFF) continue;
+                const uint32_t t = nx & 0x7FFF;
+                const uint32_t cand = (nx & 0x8000) ? 1u : (dist[t] == INF ? INF : dist[t] + 1);
+                if (cand < dist[st]) { dist[st] = cand; changed = true; }
+            }
+    }
+    out.dist.resize(out.n_states);
+    for (uint32_t st = 0; st < out.n_states; st++) out.dist[st] = (uint8_t)(dist[st] > 15 ? 15 : dist[st]);
     return true;
 }
 

@@ -47,6 +47,7 @@ struct DfaDev {
     const uint32_t* acc_del;
     const uint32_t* acc_eot;
     uint32_t n_classes, start0, start1, n_states;
+    const uint8_t* dist;       // per state: fewest further bytes before anything can be reported (saturates at 15); may be null
 };
 
 struct InspectDev {
@@ -86,17 +87,26 @@ struct InspectResult { uint32_t verdict; int32_t begin, end; uint32_t state; };
 // DFA (subset construction numbers states breadth-first from the start state, so these are the states ordinary
 // text lives in).  On the host it simply points at the full tables.
 // next/n_classes/n_states/min_len repeat fields of the (global-memory) descriptor so that the walk finds them in registers.
+// "Packed" on-chip rows (per_token mode, DFAs of up to 2048 states) carry, in bits 11..14 of each transition, the target
+// state's `dist`: the walk learns from the transition it has just loaded whether the rest of the token is long enough
+// for anything to be reported, and stops when it is not.
+constexpr uint32_t DFA_PACK_MAX_STATES = 2048, DFA_PACK_SHIFT = 11;
 struct DfaCache {
     const uint8_t* cls; const uint16_t* rows; uint32_t n_cached; const uint32_t* eot_bits;
     const uint16_t* next; uint32_t n_classes, n_states, start0, min_len;
+    uint32_t cmask, nmask;     // on-chip rows: state bits, dist bits (0 = rows are not packed)
 };
-SSE_HD DfaCache make_dfa_cache(const InspectDev& t, const uint8_t* cls, const uint16_t* rows, uint32_t n_cached, const uint32_t* eot_bits) {
-    return DfaCache{cls, rows, n_cached, eot_bits, t.fwd.next, t.fwd.n_classes, t.fwd.n_states, t.fwd.start0, t.min_len};
+SSE_HD bool dfa_rows_packable(const DfaDev& d) { return d.dist != nullptr && d.n_states <= DFA_PACK_MAX_STATES; }
+SSE_HD uint16_t dfa_pack_row(const DfaDev& d, uint16_t nx) { return (uint16_t)(nx | ((uint32_t)d.dist[nx & 0x7FFFu] << DFA_PACK_SHIFT)); }
+SSE_HD DfaCache make_dfa_cache(const InspectDev& t, const uint8_t* cls, const uint16_t* rows, uint32_t n_cached, const uint32_t* eot_bits,
+                               bool packed = false) {
+    return DfaCache{cls, rows, n_cached, eot_bits, t.fwd.next, t.fwd.n_classes, t.fwd.n_states, t.fwd.start0, t.min_len,
+                    packed ? (1u << DFA_PACK_SHIFT) - 1u : 0x7FFFu, packed ? 15u : 0u};
 }
 
 // State of one walk.  per_token: the lowest-numbered pattern wins, with its first (= smallest) end; streaming: the
 // first match to become decidable wins, ties to the lowest id.
-struct Walk { uint32_t st, idx, seen, win, win_end; };
+struct Walk { uint32_t st, idx, seen, win, win_end, need; };   // need: bytes that must still follow for anything to be reported (packed rows)
 
 template <bool STREAMING> SSE_HD void walk_event(Walk& w, uint32_t mask, uint32_t e) {
     if (STREAMING) {
@@ -110,8 +120,8 @@ template <bool STREAMING> SSE_HD void walk_event(Walk& w, uint32_t mask, uint32_
 template <bool STREAMING> SSE_HD void walk_byte(const DfaDev& d, const DfaCache& c, Walk& w, uint32_t byte) {
     const uint32_t k = w.st * c.n_classes + c.cls[byte];
     uint32_t nx;
-    if (w.st < c.n_cached) nx = c.rows[k]; else nx = c.next[k];     // the unanchored forward DFA has no dead state
-    w.st = nx & 0x7FFF;
+    if (w.st < c.n_cached) { nx = c.rows[k]; w.need = (nx >> DFA_PACK_SHIFT) & c.nmask; w.st = nx & c.cmask; }
+    else { nx = c.next[k]; w.need = 0; w.st = nx & 0x7FFF; }       // the unanchored forward DFA has no dead state
     if (nx & 0x8000) {                                             // the target state reports a match: rare
         walk_event<STREAMING>(w, d.acc_del[w.st], w.idx);
         walk_event<STREAMING>(w, d.acc_imm[w.st], w.idx + 1);
@@ -228,7 +238,10 @@ SSE_HD bool inspect_canon_token(const InspectDev& t, const DfaCache& c, const Sr
             uint32_t word = funnel_r(lo, hi, shb);
             lo = hi;
             const uint32_t m = n - i < 4 ? n - i : 4;
-            for (uint32_t k = 0; k < m; k++, word >>= 8) walk_byte<false>(d, c, w, word & 0xFF);
+            for (uint32_t k = 0; k < m; k++, word >>= 8) {
+                walk_byte<false>(d, c, w, word & 0xFF);
+                if (n - w.idx < w.need) { i = n; break; }          // too few bytes left for any pattern to complete
+            }
         }
     } else {
         walk_canon_escaped<false>(d, c, w, s, tok_b, tok_e);

@@ -291,14 +291,15 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         const DfaDev& d = a.insp->fwd;
         const uint32_t nc = min(d.n_states, DFA_CACHE_ENTRIES / d.n_classes);
         for (uint32_t i = tid; i < 256; i += TILE) s_cls[i] = d.cls[i];
-        for (uint32_t i = tid; i < nc * d.n_classes; i += TILE) s_rows[i] = d.next[i];
+        const bool packed = dfa_rows_packable(d);
+        for (uint32_t i = tid; i < nc * d.n_classes; i += TILE) s_rows[i] = packed ? dfa_pack_row(d, d.next[i]) : d.next[i];
         if (d.n_states <= 32 * DFA_EOT_WORDS)
             for (uint32_t w = tid; w < DFA_EOT_WORDS; w += TILE) {
                 uint32_t bits = 0;
                 for (uint32_t k = 0; k < 32 && 32 * w + k < d.n_states; k++) bits |= (d.acc_eot[32 * w + k] != 0 ? 1u : 0u) << k;
                 s_eot[w] = bits;
             }
-        dcache = make_dfa_cache(*a.insp, s_cls, s_rows, nc, s_eot);
+        dcache = make_dfa_cache(*a.insp, s_cls, s_rows, nc, s_eot, packed);
     }
     InterestFast ifast{nullptr, 0, 0, 0};
     if (EXT & X_INTEREST) ifast = make_interest_fast(*a.interest);

@@ -680,13 +680,14 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
     // flatten every DFA into one blob: cls[256] | next u16[] | acc_imm | acc_del | acc_eot, 16-byte aligned pieces
     std::vector<uint8_t> blob;
     auto put = [&](const void* p, size_t bytes) { size_t off = (blob.size() + 15) & ~(size_t)15; blob.resize(off + bytes); memcpy(blob.data() + off, p, bytes); return off; };
-    struct Off { size_t cls, next, imm, del, eot; };
+    struct Off { size_t cls, next, imm, del, eot, dist; };
     std::vector<const sse_inspect::Dfa*> dfas{&c.forward};
     for (auto& d : c.anchored) dfas.push_back(&d);
     std::vector<Off> offs;
     for (const sse_inspect::Dfa* d : dfas)
         offs.push_back({put(d->cls, 256), put(d->next.data(), d->next.size() * 2), put(d->acc_imm.data(), d->acc_imm.size() * 4),
-                        put(d->acc_del.data(), d->acc_del.size() * 4), put(d->acc_eot.data(), d->acc_eot.size() * 4)});
+                        put(d->acc_del.data(), d->acc_del.size() * 4), put(d->acc_eot.data(), d->acc_eot.size() * 4),
+                        put(d->dist.data(), d->dist.size())});
     blob.resize((blob.size() + 31) & ~(size_t)15);
     // A new generation is built beside the live one (uploads on the table stream, which nothing else is using yet); on
     // any failure it is dropped and the old set stays in force.  No device-wide synchronisation anywhere.
@@ -703,6 +704,7 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
         dd.cls = base + o.cls; dd.next = reinterpret_cast<const uint16_t*>(base + o.next);
         dd.acc_imm = reinterpret_cast<const uint32_t*>(base + o.imm); dd.acc_del = reinterpret_cast<const uint32_t*>(base + o.del);
         dd.acc_eot = reinterpret_cast<const uint32_t*>(base + o.eot);
+        dd.dist = base + o.dist;
         dd.n_classes = d.n_classes; dd.start0 = d.start[0]; dd.start1 = d.start[1]; dd.n_states = d.n_states;
     };
     fill(h.fwd, c.forward, offs[0]);

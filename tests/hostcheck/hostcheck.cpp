@@ -62,6 +62,7 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
     auto fill = [](DfaDev& dd, const sse_inspect::Dfa& d) {
         dd.cls = d.cls; dd.next = d.next.data(); dd.acc_imm = d.acc_imm.data(); dd.acc_del = d.acc_del.data();
         dd.acc_eot = d.acc_eot.data(); dd.n_classes = d.n_classes; dd.start0 = d.start[0]; dd.start1 = d.start[1]; dd.n_states = d.n_states;
+        dd.dist = d.dist.data();
     };
     fill(t.fwd, c.forward);
     if (c.anchored.size() > INSPECT_MAX_ANCHORED) return -2;
@@ -84,7 +85,12 @@ extern "C" int hc_inspect(const hc_pattern* pats, uint32_t n_pats, uint32_t mode
     std::vector<uint32_t> eot_bits(DFA_EOT_WORDS, 0);
     if (c.forward.n_states <= 32 * DFA_EOT_WORDS)
         for (uint32_t st = 0; st < c.forward.n_states; st++) if (c.forward.acc_eot[st]) eot_bits[st >> 5] |= 1u << (st & 31);
-    DfaCache cache = make_dfa_cache(t, c.forward.cls, c.forward.next.data(), c.forward.n_states < 20 ? c.forward.n_states : 20, eot_bits.data());
+    // per_token mode: packed rows as in the frame kernel (the walk stops when the rest of the token is too short for any match)
+    const uint32_t n_cached = c.forward.n_states < 20 ? c.forward.n_states : 20;
+    const bool packed = mode != INSPECT_STREAMING && dfa_rows_packable(t.fwd);
+    std::vector<uint16_t> rows(c.forward.next.begin(), c.forward.next.begin() + (size_t)n_cached * c.forward.n_classes);
+    if (packed) for (uint16_t& nx : rows) nx = dfa_pack_row(t.fwd, nx);
+    DfaCache cache = make_dfa_cache(t, c.forward.cls, rows.data(), n_cached, eot_bits.data(), packed);
     const bool streaming = mode == INSPECT_STREAMING;
     for (uint32_t i = 0; i < n; i++) {
         Plan pl;

@@ -1,3 +1,3 @@
 set -x
-export SSEGPU_LIB=$PWD/tools/exp/libssegpu_B.so
-for p in 1 10 100; do timeout 200 python tools/time_kernel.py --op 0 --noncanon $p 2>&1 | tail -1; done
+timeout 900 python -m pytest tests/test_gpu_inspect.py tests/test_gpu_ext_modes.py -m gpu -x -q > gpurun_out/r02_gputest_i3.log 2>&1; tail -3 gpurun_out/r02_gputest_i3.log
+for w in inspect inspect_ab; do timeout 200 python tools/prof_target.py $w > gpurun_out/r02_i3_$w.log 2>&1; tail -1 gpurun_out/r02_i3_$w.log; done

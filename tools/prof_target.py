@@ -108,7 +108,7 @@ if a.what == "chunk":
         rc, n_lines, n, int(loff[-1]), used, float(np.mean(ms)), min(ms), n_lines / min(ms) / 1e3, int(loff[-1]) / min(ms) / 1e6))
     eng.close()
     sys.exit(0)
-shape = {"inspect": (100_000, 32), "inspect_ab": (100_000, 32), "stream": (100_000, 32), "match": (100_000, 16), "bridge": (100_000, 16),
+shape = {"inspect": (100_000, 32), "inspect_ab": (100_000, 32), "inspect_none": (100_000, 32), "plain32": (100_000, 32), "stream": (100_000, 32), "match": (100_000, 16), "bridge": (100_000, 16),
          "ordered": (10_000, 1000), "plain": (10_000, 1000)}[a.what]
 n_conv, n_tok = a.conv or shape[0], a.tok or shape[1]
 arena, off = pkg.workload.generate(1, n_conv, n_tok)
@@ -117,8 +117,9 @@ eng = pkg.SseGpu(device=0, max_records=n, max_in_bytes=1 << 20, conv_slots=n_con
 db = DevBatch(arena, off, extra_cap=96)
 d_conv = 0
 op = 0
-if a.what in ("inspect", "inspect_ab", "stream"):
-    eng.load_patterns(SET_A if a.what == "inspect" else SET_A + SET_B, pkg.INSPECT_STREAMING if a.what == "stream" else pkg.INSPECT_PER_TOKEN)
+if a.what in ("inspect", "inspect_ab", "stream", "inspect_none"):
+    # inspect_none: one pattern longer than any token, so that every walk is skipped -- what the variant costs before it walks a byte
+    eng.load_patterns([(0, 3, b"a pattern that is longer than every token of the workload")] if a.what == "inspect_none" else SET_A if a.what == "inspect" else SET_A + SET_B, pkg.INSPECT_STREAMING if a.what == "stream" else pkg.INSPECT_PER_TOKEN)
     op = pkg.OP_INSPECT
     if a.what == "stream":
         conv = torch.from_numpy(np.tile(np.arange(n_conv, dtype=np.int32), n_tok)).cuda()
