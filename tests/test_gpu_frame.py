@@ -126,11 +126,12 @@ def test_nats_pub_needs_bridge_mode(pkg, eng, oracle):
 
 
 @pytest.mark.parametrize("pct", [0.05, 1.0, 20.0])
-@pytest.mark.parametrize("op", [0, 1, 1 | 128, 8])
+@pytest.mark.parametrize("op", [0, 1, 1 | 128, 8, 8 | 1, 8 | 1 | 128])
 def test_sparse_non_canonical_records_in_canonical_traffic(pkg, eng, oracle, pct, op):
     """Mostly Go-marshalled traffic with a few records that need the general decoder (a "Token" key, a payload with a
     space after the brace, a syntax error, a type error): in arrival mode the tile kernel leaves them to its tail phase
-    when they are few in their warp -- statuses, frames, counters and the arena invariants must not notice."""
+    when they are few in their warp, in ordered mode both passes do (the count pass's tail adds their lengths to the tile
+    totals, the emit pass leaves holes that its tail fills) -- statuses, frames, counters and the arena invariants must not notice."""
     n_conv, n_tok = 2000, 30
     arena, off = pkg.workload.generate(1, n_conv, n_tok)
     n = n_conv * n_tok
