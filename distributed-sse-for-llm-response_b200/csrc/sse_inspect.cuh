@@ -26,7 +26,7 @@ enum : uint32_t { ACT_ALLOW = 0, ACT_REDACT = 1, ACT_DROP = 2, ACT_ALERT = 3 };
 // lowest-numbered states.  Subset construction numbers states breadth-first from the start state, so ordinary text
 // lives in the first few dozen (measured on the BASELINE token stream: 99.7 % of all steps in states < 32, 99.99 % in
 // states < 48); the other rows are read through L1/L2.
-constexpr uint32_t DFA_CACHE_ENTRIES = 1008;          // u16 transitions kept on chip (with five tiles per SM the shared memory is full to within 24 bytes)
+constexpr uint32_t DFA_CACHE_ENTRIES = 992;           // u16 transitions kept on chip (with five tiles per SM the shared memory is full to within 8 bytes)
 constexpr uint32_t DFA_EOT_WORDS = 32;
 constexpr uint32_t DFA_CACHE_BYTES = 256 + 4 * DFA_EOT_WORDS + 2 * DFA_CACHE_ENTRIES;
 
@@ -98,6 +98,11 @@ struct DfaCache {
 };
 SSE_HD bool dfa_rows_packable(const DfaDev& d) { return d.dist != nullptr && d.n_states <= DFA_PACK_MAX_STATES; }
 SSE_HD uint16_t dfa_pack_row(const DfaDev& d, uint16_t nx) { return (uint16_t)(nx | ((uint32_t)d.dist[nx & 0x7FFFu] << DFA_PACK_SHIFT)); }
+SSE_HD DfaCache make_dfa_cache(const uint16_t* next, uint32_t n_classes, uint32_t n_states, uint32_t start0, uint32_t min_len, const uint8_t* cls,
+                               const uint16_t* rows, uint32_t n_cached, const uint32_t* eot_bits, bool packed) {
+    return DfaCache{cls, rows, n_cached, eot_bits, next, n_classes, n_states, start0, min_len,
+                    packed ? (1u << DFA_PACK_SHIFT) - 1u : 0x7FFFu, packed ? 15u : 0u};
+}
 SSE_HD DfaCache make_dfa_cache(const InspectDev& t, const uint8_t* cls, const uint16_t* rows, uint32_t n_cached, const uint32_t* eot_bits,
                                bool packed = false) {
     return DfaCache{cls, rows, n_cached, eot_bits, t.fwd.next, t.fwd.n_classes, t.fwd.n_states, t.fwd.start0, t.min_len,

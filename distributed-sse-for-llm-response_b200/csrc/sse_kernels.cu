@@ -153,6 +153,10 @@ struct TileSmem {
     uint32_t tile, tb, te, in_total;
     uint32_t npend;          // records of this tile left to the tail phase (later: fill of the tail's list)
     uint32_t wsum[TILE / 32];
+    // the CTA's share of the launch counters (ok, syntax, type, filtered, done, fast; bytes in / out): kept here, not in
+    // eight registers of every thread across the whole persistent loop
+    uint32_t ctr[6];
+    unsigned long long c_in, c_out;
 };
 
 // Out-of-line general path (generic pointers: the tile may sit in shared or in global memory).
@@ -178,7 +182,7 @@ __device__ __noinline__ uint32_t emit_slow(const uint8_t* src_base, uint32_t o, 
 }
 
 // tid 0: claim bookkeeping for tile t -- tile byte range + TMA load into s_in
-__device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t t, uint64_t& c_in, bool want_base = false) {
+__device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t t, bool want_base = false) {
     ts->tile = t;
     ts->npend = 0;
     if (t < a.num_tiles) {
@@ -197,7 +201,7 @@ __device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uin
             mbar_expect_tx(&ts->mbar, bytes);
             tma_load_1d(s_in, a.in + abase, bytes, &ts->mbar);
         }
-        c_in += te - tb;
+        ts->c_in += te - tb;
         if (want_base) ts->obase = ob;
     }
 }
@@ -275,8 +279,10 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
     TileSmem* ts = reinterpret_cast<TileSmem*>(s_out + a.out_cap_s + 48);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // Launch counters: the variants with optional stages sit at the register cap and keep their counts in shared memory
+    // (ts->ctr, one ballot per kind and tile); the plain kernel has the registers and counts per thread.
+    constexpr bool SMEM_CTR = EXT != 0;
     uint32_t c_ok = 0, c_syn = 0, c_typ = 0, c_fil = 0, c_done = 0, c_fast = 0;
-    uint64_t c_in = 0, c_out = 0;
     uint32_t parity = 0;
     uint32_t my_chain = 0;                                  // tid 0: last tile (+1) of this CTA that left records to the tail phase
 
@@ -289,24 +295,31 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         uint32_t* s_eot = reinterpret_cast<uint32_t*>(s_cls + 256);
         uint16_t* s_rows = reinterpret_cast<uint16_t*>(s_eot + DFA_EOT_WORDS);
         const DfaDev& d = a.insp->fwd;
-        const uint32_t nc = min(d.n_states, DFA_CACHE_ENTRIES / d.n_classes);
+        // the descriptor's scalars come from the kernel parameters (a.dfa), not from the descriptor in global memory
+        const uint32_t n_states = a.dfa.n_states, n_classes = a.dfa.n_classes;
+        const uint32_t nc = min(n_states, DFA_CACHE_ENTRIES / n_classes);
+        const bool packed = a.dfa.dist != nullptr && n_states <= DFA_PACK_MAX_STATES;
         for (uint32_t i = tid; i < 256; i += TILE) s_cls[i] = d.cls[i];
-        const bool packed = dfa_rows_packable(d);
-        for (uint32_t i = tid; i < nc * d.n_classes; i += TILE) s_rows[i] = packed ? dfa_pack_row(d, d.next[i]) : d.next[i];
-        if (d.n_states <= 32 * DFA_EOT_WORDS)
+        for (uint32_t i = tid; i < nc * n_classes; i += TILE) {
+            const uint16_t nx = a.dfa.next[i];
+            s_rows[i] = packed ? (uint16_t)(nx | ((uint32_t)a.dfa.dist[nx & 0x7FFFu] << DFA_PACK_SHIFT)) : nx;
+        }
+        if (n_states <= 32 * DFA_EOT_WORDS)
             for (uint32_t w = tid; w < DFA_EOT_WORDS; w += TILE) {
                 uint32_t bits = 0;
-                for (uint32_t k = 0; k < 32 && 32 * w + k < d.n_states; k++) bits |= (d.acc_eot[32 * w + k] != 0 ? 1u : 0u) << k;
+                for (uint32_t k = 0; k < 32 && 32 * w + k < n_states; k++) bits |= (d.acc_eot[32 * w + k] != 0 ? 1u : 0u) << k;
                 s_eot[w] = bits;
             }
-        dcache = make_dfa_cache(*a.insp, s_cls, s_rows, nc, s_eot, packed);
+        dcache = make_dfa_cache(a.dfa.next, n_classes, n_states, a.dfa.start0, a.dfa.min_len, s_cls, s_rows, nc, s_eot, packed);
     }
     InterestFast ifast{nullptr, 0, 0, 0};
-    if (EXT & X_INTEREST) ifast = make_interest_fast(*a.interest);
+    if (EXT & X_INTEREST) ifast = InterestFast{a.itab.slots, a.itab.mask, a.itab.wild_single, a.itab.wild_generic};
     if (tid == 0) {
         mbar_init(&ts->mbar, 1);
         ts->in_total = a.in_off[a.n];
-        setup_tile(a, ts, s_in, atomicAdd(a.ticket, 1u), c_in, MODE == MODE_ORDERED_EMIT);
+        for (int k = 0; k < 6; k++) ts->ctr[k] = 0;
+        ts->c_in = 0; ts->c_out = 0;
+        setup_tile(a, ts, s_in, atomicAdd(a.ticket, 1u), MODE == MODE_ORDERED_EMIT);
     }
 
     for (;;) {
@@ -488,7 +501,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
                 uint64_t w = total;
                 if (ts->npend) { w |= (uint64_t)my_chain << 32; my_chain = tile + 1; }   // tiles with records left to the tail, chained
                 a.tile_state[tile] = w;
-                setup_tile(a, ts, s_in, next_t, c_in);                        // every thread is past (B): the tile has been consumed
+                setup_tile(a, ts, s_in, next_t);                        // every thread is past (B): the tile has been consumed
             }
             continue;
         }
@@ -507,7 +520,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             my_chain = tile + 1;
         }
         if (tid == 0) {
-            c_out += total;
+            ts->c_out += total;
             if (ordered) ts->base = obase;                                    // exclusive prefix from k_scan_tile_totals
             else ts->base = atomicAdd(a.cursor, (unsigned long long)alloc);   // nothing to wait for
         }
@@ -531,7 +544,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             if (!ordered && tid < alloc - total) s_out[total + tid] = 0;
             fence_proxy_async_smem();                                         // staging writes -> visible to the TMA store
             __syncthreads();                                                  // (D) s_in free, staging tile complete, base visible
-            if (tid == 0) setup_tile(a, ts, s_in, next_t, c_in, ordered);     // next tile's TMA load flies during the copy-out
+            if (tid == 0) setup_tile(a, ts, s_in, next_t, ordered);     // next tile's TMA load flies during the copy-out
         } else {
             // ---- oversize tile: emit straight into the arena ---------------------------
             __syncthreads();                                                  // (D')
@@ -545,17 +558,36 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             }
             if (fits && tid < alloc - total) a.out[base + total + tid] = 0;       // pad of an aligned tile
             __syncthreads();                                                  // (E') s_in free
-            if (tid == 0) setup_tile(a, ts, s_in, next_t, c_in, ordered);
+            if (tid == 0) setup_tile(a, ts, s_in, next_t, ordered);
         }
         if (active) {
-            if (code == ST_OK) { c_ok++; c_fast += fastp ? 1u : 0u; if (st & ST_DONE) c_done++; }
-            else if (code == ST_ERR_SYNTAX) c_syn++;
-            else if (code == ST_ERR_TYPE) c_typ++;
-            else if (code == ST_FILTERED) c_fil++;
             a.out_off[r0 + tid] = base + local;
             a.out_len[r0 + tid] = len;
             a.status[r0 + tid] = st;
             if (a.subj_len) a.subj_len[r0 + tid] = subj;
+        }
+        if (!SMEM_CTR) {
+            if (active) {
+                if (code == ST_OK) { c_ok++; c_fast += fastp ? 1u : 0u; if (st & ST_DONE) c_done++; }
+                else if (code == ST_ERR_SYNTAX) c_syn++;
+                else if (code == ST_ERR_TYPE) c_typ++;
+                else if (code == ST_FILTERED) c_fil++;
+            }
+        } else {   // counters: one ballot per kind, lane 0 adds the warp's counts to the CTA's words
+            const bool okr = active && code == ST_OK;
+            const uint32_t m_ok = __ballot_sync(0xFFFFFFFFu, okr), m_fast = __ballot_sync(0xFFFFFFFFu, okr && fastp);
+            const uint32_t m_done = __ballot_sync(0xFFFFFFFFu, okr && (st & ST_DONE) != 0);
+            const uint32_t m_other = __ballot_sync(0xFFFFFFFFu, active && !okr && code != ST_PENDING);
+            if (lane == 0) {
+                if (m_ok) atomicAdd(&ts->ctr[0], (uint32_t)__popc(m_ok));
+                if (m_fast) atomicAdd(&ts->ctr[5], (uint32_t)__popc(m_fast));
+                if (m_done) atomicAdd(&ts->ctr[4], (uint32_t)__popc(m_done));
+            }
+            if (m_other && active) {                         // rare: dropped / filtered records
+                if (code == ST_ERR_SYNTAX) atomicAdd(&ts->ctr[1], 1u);
+                else if (code == ST_ERR_TYPE) atomicAdd(&ts->ctr[2], 1u);
+                else if (code == ST_FILTERED) atomicAdd(&ts->ctr[3], 1u);
+            }
         }
         if (tid == 0 && !fits) atomicExch(a.overflow, 1u);
         if (smem_out && fits && total != 0) {
@@ -703,10 +735,10 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
                     a.out_len[i] = len;
                     a.status[i] = st;
                     if (a.subj_len) a.subj_len[i] = subj;
-                    if (code == ST_OK) { c_ok++; if (st & ST_DONE) c_done++; }
-                    else if (code == ST_ERR_SYNTAX) c_syn++;
-                    else if (code == ST_ERR_TYPE) c_typ++;
-                    else if (code == ST_FILTERED) c_fil++;
+                    if (code == ST_OK) { atomicAdd(&ts->ctr[0], 1u); if (st & ST_DONE) atomicAdd(&ts->ctr[4], 1u); }
+                    else if (code == ST_ERR_SYNTAX) atomicAdd(&ts->ctr[1], 1u);
+                    else if (code == ST_ERR_TYPE) atomicAdd(&ts->ctr[2], 1u);
+                    else if (code == ST_FILTERED) atomicAdd(&ts->ctr[3], 1u);
                 }
                 if (fits && lane < alloc - total) a.out[base + total + lane] = 0;
                 if (lane == 0 && total) atomicAdd(&row[7], (unsigned long long)total);
@@ -719,17 +751,21 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
     }
 
     // ---- counters: one row per CTA slot, summed by the host --------------------------
-    uint32_t vals[6] = {c_ok, c_syn, c_typ, c_fil, c_done, c_fast};
+    if (!SMEM_CTR) {
+        uint32_t vals[6] = {c_ok, c_syn, c_typ, c_fil, c_done, c_fast};
 #pragma unroll
-    for (int k = 0; k < 6; k++) {
-        uint32_t v = vals[k];
+        for (int k = 0; k < 6; k++) {
+            uint32_t v = vals[k];
 #pragma unroll
-        for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o2);
-        if (lane == 0 && v) atomicAdd(&row[k], (unsigned long long)v);
+            for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o2);
+            if (lane == 0 && v) atomicAdd(&ts->ctr[k], v);
+        }
     }
+    __syncthreads();
+    if (tid < 6) { const uint32_t v = ts->ctr[tid]; if (v) atomicAdd(&row[tid], (unsigned long long)v); }
     if (tid == 0 && MODE != MODE_ORDERED_COUNT) {
-        if (c_in) atomicAdd(&row[6], (unsigned long long)c_in);
-        if (c_out) atomicAdd(&row[7], (unsigned long long)c_out);
+        if (ts->c_in) atomicAdd(&row[6], ts->c_in);
+        if (ts->c_out) atomicAdd(&row[7], ts->c_out);
         if (MODE == MODE_ARRIVAL) {     // the CTA that finishes last publishes the arena's total size as out_off[n]
             __threadfence();
             if (atomicAdd(a.done_ctas, 1u) == gridDim.x - 1) {

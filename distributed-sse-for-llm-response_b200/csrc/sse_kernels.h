@@ -20,6 +20,14 @@ constexpr size_t SCRATCH_HDR = 64;   // [0] ticket u32, [4] overflow u32, [8] cu
 enum : uint32_t { XF_PRE_VERDICT = 1u,       // verdict[] already holds this batch's verdicts: apply them (inline mode), do not inspect
                   XF_ENTRY_IN_COUNT = 2u };  // write tok_entry in ordered mode's counting pass too (it runs alone, as a planning pass)
 
+// Scalars of the interest table's descriptor, passed by value: kernel-parameter (constant) space instead of registers
+// held across the whole persistent loop.  Constant for the lifetime of a table generation.
+struct InterestSlot;
+struct InterestUniform { const InterestSlot* slots; uint32_t mask, wild_single, wild_generic; };
+
+// The same for the forward DFA of the content inspection (insp->fwd, insp->min_len).
+struct DfaUniform { const uint16_t* next; const uint8_t* dist; uint32_t n_classes, n_states, start0, min_len; };
+
 struct FrameArgs {
     const uint8_t* in;           // packed payload arena, 16-byte aligned, 32 readable bytes after the last record
     const uint32_t* in_off;      // n+1
@@ -36,12 +44,14 @@ struct FrameArgs {
     // entry per record (tok_entry != nullptr) and, for inline verdicts, a second frame pass reads the walk's
     // verdicts back (XF_PRE_VERDICT) instead of inspecting.
     const InspectDev* insp;
+    DfaUniform dfa;              // with insp: what insp->fwd and insp->min_len say (filled by the caller from its host copy)
     uint4* tok_entry;            // 2n (one 32-byte entry per record) or nullptr
     uint32_t xflags;
     uint32_t* verdict;           // n
     int32_t* match;              // 2n: begin, end (byte offsets into the decoded token text)
     // subscriber/interest table (nullptr = off): per record (CSR offset, count, wildcard mask)
     const InterestDev* interest;
+    InterestUniform itab;        // with interest: the same fields of *interest (filled by the caller from its host copy)
     uint32_t* hit;               // 3n
     // scratch: one device allocation of scratch_bytes(n), zeroed by frame_launch
     void* scratch_base;

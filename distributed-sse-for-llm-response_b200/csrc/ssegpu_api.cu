@@ -45,6 +45,7 @@ struct TableGen {                        // interest table
     sse::InterestSlot* d_slots = nullptr; uint32_t* d_keys = nullptr; uint8_t* d_wild = nullptr; sse::InterestDev* d_desc = nullptr;
     uint32_t* d_subs = nullptr;                      // device copy of the id arena (ssegpu_fanout_launch expands spans from it)
     uint32_t* d_wild_ids = nullptr;                  // 32 words
+    sse::InterestUniform uni{};                      // host copy of the descriptor's scalars, passed to the frame kernel by value
     std::shared_ptr<std::vector<uint32_t>> subs;     // host arena the spans of this generation index (append-only, fixed address)
     std::vector<uint32_t> wild_ids;
     ~TableGen() {
@@ -60,6 +61,7 @@ struct InspGen {                         // inspection pattern tables
     cudaStream_t stream = nullptr;
     void* d_blob = nullptr; sse::InspectDev* d_desc = nullptr;
     uint32_t mode = 0, start_state = 0, n_states = 0, n_classes = 0;
+    sse::DfaUniform dfa{};               // host copy of the forward DFA's descriptor scalars, passed to the frame kernel by value
     ~InspGen() {
         if (d_blob) cudaFreeAsync(d_blob, stream);
         if (d_desc) cudaFreeAsync(d_desc, stream);
@@ -490,9 +492,9 @@ int ssegpu_batch_submit(ssegpu_ctx* ctx, ssegpu_batch* b, uint32_t n, uint32_t o
         b->table_version = ctx->table_version;
         if (b->insp) {
             if (b->insp->mode == sse::INSPECT_STREAMING && n) CU(cudaMemcpyAsync(b->d_conv, b->h_conv, (size_t)n * 4, cudaMemcpyHostToDevice, st));
-            a.insp = b->insp->d_desc; a.verdict = b->d_verdict; a.match = b->d_match;
+            a.insp = b->insp->d_desc; a.dfa = b->insp->dfa; a.verdict = b->d_verdict; a.match = b->d_match;
         }
-        if (b->tab) { a.interest = b->tab->d_desc; a.hit = b->d_hit; }
+        if (b->tab) { a.interest = b->tab->d_desc; a.itab = b->tab->uni; a.hit = b->d_hit; }
     }
     uint32_t n_launches = 0;
     { const int rc = launch_path(ctx, a, b->d_conv, st, b->insp.get(), &n_launches); if (rc != SSEGPU_OK) return rc; }
@@ -587,11 +589,11 @@ int ssegpu_frame_launch(ssegpu_ctx* ctx, const void* d_in, const uint32_t* d_in_
         if (rc != SSEGPU_OK) return rc;
         if (insp) {
             if (!ctx->bound_verdict || !ctx->bound_match || (insp->mode == sse::INSPECT_STREAMING && !ctx->bound_conv)) return SSEGPU_E_STATE;
-            a.insp = insp->d_desc; a.verdict = ctx->bound_verdict; a.match = ctx->bound_match;
+            a.insp = insp->d_desc; a.dfa = insp->dfa; a.verdict = ctx->bound_verdict; a.match = ctx->bound_match;
         }
         if (tab) {
             if (!ctx->bound_hit) return SSEGPU_E_STATE;
-            a.interest = tab->d_desc; a.hit = ctx->bound_hit;
+            a.interest = tab->d_desc; a.itab = tab->uni; a.hit = ctx->bound_hit;
         }
     }
     uint32_t n_launches = 0;
@@ -717,6 +719,7 @@ int ssegpu_patterns_load(ssegpu_ctx* ctx, const ssegpu_pattern* pats, uint32_t n
         h.fixed_len[i] = c.patterns[i].min_len == c.patterns[i].max_len ? c.patterns[i].min_len : 0;
         h.anchored_of[i] = c.anchored_of[i];
     }
+    gen->dfa = sse::DfaUniform{h.fwd.next, h.fwd.dist, h.fwd.n_classes, h.fwd.n_states, h.fwd.start0, h.min_len};
     CU(cudaMemcpyAsync(gen->d_desc, &h, sizeof h, cudaMemcpyHostToDevice, ctx->table_stream));
     CU(cudaStreamSynchronize(ctx->table_stream));                 // the host buffers above are about to go out of scope (own stream only)
     if (ctx->cfg.conv_slots) {
@@ -788,6 +791,7 @@ static int interest_rebuild(ssegpu_ctx* ctx) {
     h.mask = (uint32_t)t.slots.size() - 1; h.n_wild = (uint32_t)t.wild_ids.size();
     h.wild_bytes = gen->d_wild;
     for (size_t i = 0; i < t.wild_off.size(); i++) h.wild_off[i] = t.wild_off[i];
+    gen->uni = sse::InterestUniform{h.slots, h.mask, h.wild_single, h.wild_generic};
     CU(cudaMemcpyAsync(gen->d_desc, &h, sizeof h, cudaMemcpyHostToDevice, ts));
     CU(cudaStreamSynchronize(ts));                                // own stream only: the uploads came from pageable host memory
     CU(cudaEventRecord(ctx->ev_table, ts));

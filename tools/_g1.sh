@@ -1,5 +1,2 @@
-set -x
-timeout 1700 python -m pytest tests -m gpu -x -q > gpurun_out/r02_gputest_full2.log 2>&1; tail -4 gpurun_out/r02_gputest_full2.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
-timeout 900 python bench.py > gpurun_out/r02_bench_v2.json 2> gpurun_out/r02_bench_v2.err; tail -c 600 gpurun_out/r02_bench_v2.json
-timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/r02_bench_v2_reference_arm.json 2>/dev/null; tail -c 400 gpurun_out/r02_bench_v2_reference_arm.json
+timeout 1200 python -m pytest tests/test_gpu_frame.py tests/test_gpu_inspect.py tests/test_gpu_ext_modes.py tests/test_gpu_interest.py tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -2
+for w in plain plain32 inspect_none inspect_ab match bridge ordered stream; do timeout 200 python tools/prof_target.py $w 2>&1 | tail -1; done
