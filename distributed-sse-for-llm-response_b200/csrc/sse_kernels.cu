@@ -157,6 +157,7 @@ struct TileSmem {
     // eight registers of every thread across the whole persistent loop
     uint32_t ctr[6];
     unsigned long long c_in, c_out;
+    uint32_t next_t, my_chain;   // thread 0's loop state: the tile claimed for the next trip; last tile (+1) of this CTA that left records to the tail phase
 };
 
 // Out-of-line general path (generic pointers: the tile may sit in shared or in global memory).
@@ -284,7 +285,6 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
     constexpr bool SMEM_CTR = EXT != 0;
     uint32_t c_ok = 0, c_syn = 0, c_typ = 0, c_fil = 0, c_done = 0, c_fast = 0;
     uint32_t parity = 0;
-    uint32_t my_chain = 0;                                  // tid 0: last tile (+1) of this CTA that left records to the tail phase
 
     // EXT, fused per-token inspection: on-chip copy of the forward DFA's byte-class map, end-of-text bitmap and hottest rows
     const bool pre_verdict = (EXT & X_INSPECT) && (a.xflags & XF_PRE_VERDICT) != 0;          // launch-uniform
@@ -318,6 +318,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         mbar_init(&ts->mbar, 1);
         ts->in_total = a.in_off[a.n];
         for (int k = 0; k < 6; k++) ts->ctr[k] = 0;
+        ts->my_chain = 0;
         ts->c_in = 0; ts->c_out = 0;
         setup_tile(a, ts, s_in, atomicAdd(a.ticket, 1u), MODE == MODE_ORDERED_EMIT);
     }
@@ -326,8 +327,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         __syncthreads();                                                      // (A) tile info visible; s_out free
         const uint32_t tile = ts->tile;
         if (tile >= a.num_tiles) break;
-        uint32_t next_t = 0;
-        if (tid == 0) next_t = atomicAdd(a.ticket, 1u);                       // claimed early, used after (D)
+        if (tid == 0) ts->next_t = atomicAdd(a.ticket, 1u);                   // claimed early, used after (D)
         const uint32_t r0 = tile * TILE;
         const uint32_t nrec = min((uint32_t)TILE, a.n - r0);
         const uint32_t tb = ts->tb, te = ts->te;
@@ -499,9 +499,9 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             }
             if (tid == 0) {
                 uint64_t w = total;
-                if (ts->npend) { w |= (uint64_t)my_chain << 32; my_chain = tile + 1; }   // tiles with records left to the tail, chained
+                if (ts->npend) { w |= (uint64_t)ts->my_chain << 32; ts->my_chain = tile + 1; }   // tiles with records left to the tail, chained
                 a.tile_state[tile] = w;
-                setup_tile(a, ts, s_in, next_t);                        // every thread is past (B): the tile has been consumed
+                setup_tile(a, ts, s_in, ts->next_t);                        // every thread is past (B): the tile has been consumed
             }
             continue;
         }
@@ -516,8 +516,8 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         // tile leaves as ONE TMA bulk store; the <=15 pad bytes after its last frame are zeroed.
         const uint32_t alloc = ordered ? total : ((total + 15u) & ~15u);
         if ((DEFER || MODE == MODE_ORDERED_EMIT) && tid == 0 && ts->npend) {   // chain this tile to the CTA's list of tiles with records left over
-            a.tile_state[tile] = (uint64_t)ts->npend | ((uint64_t)my_chain << 32);
-            my_chain = tile + 1;
+            a.tile_state[tile] = (uint64_t)ts->npend | ((uint64_t)ts->my_chain << 32);
+            ts->my_chain = tile + 1;
         }
         if (tid == 0) {
             ts->c_out += total;
@@ -544,7 +544,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             if (!ordered && tid < alloc - total) s_out[total + tid] = 0;
             fence_proxy_async_smem();                                         // staging writes -> visible to the TMA store
             __syncthreads();                                                  // (D) s_in free, staging tile complete, base visible
-            if (tid == 0) setup_tile(a, ts, s_in, next_t, ordered);     // next tile's TMA load flies during the copy-out
+            if (tid == 0) setup_tile(a, ts, s_in, ts->next_t, ordered);     // next tile's TMA load flies during the copy-out
         } else {
             // ---- oversize tile: emit straight into the arena ---------------------------
             __syncthreads();                                                  // (D')
@@ -558,7 +558,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             }
             if (fits && tid < alloc - total) a.out[base + total + tid] = 0;       // pad of an aligned tile
             __syncthreads();                                                  // (E') s_in free
-            if (tid == 0) setup_tile(a, ts, s_in, next_t, ordered);
+            if (tid == 0) setup_tile(a, ts, s_in, ts->next_t, ordered);
         }
         if (active) {
             a.out_off[r0 + tid] = base + local;
@@ -622,7 +622,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         // chain link in the upper half of the tile word is cleared as the chain is walked, the scan wants plain totals).
         uint32_t* s_list = reinterpret_cast<uint32_t*>(s_in);
         __syncthreads();
-        if (tid == 0) { ts->tile = my_chain; ts->npend = 0; }
+        if (tid == 0) { ts->tile = ts->my_chain; ts->npend = 0; }
         __syncthreads();
         uint32_t t1 = ts->tile;
         const uint32_t in_total = ts->in_total;
@@ -658,7 +658,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         // Emit pass: the frames of the records placed as holes, written where the main loop put them.
         uint32_t* s_list = reinterpret_cast<uint32_t*>(s_out);
         __syncthreads();                                                      // the last tile's bulk store is complete (bulk_wait0 above)
-        if (tid == 0) { ts->tile = my_chain; ts->npend = 0; }
+        if (tid == 0) { ts->tile = ts->my_chain; ts->npend = 0; }
         __syncthreads();
         uint32_t t1 = ts->tile;
         const uint32_t in_total = ts->in_total;
@@ -693,7 +693,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
     if (MODE == MODE_ARRIVAL) {
         uint32_t* s_list = reinterpret_cast<uint32_t*>(s_out);
         __syncthreads();                                                      // every thread has read the loop's last ts->tile
-        if (tid == 0) { ts->tile = my_chain; ts->npend = 0; }
+        if (tid == 0) { ts->tile = ts->my_chain; ts->npend = 0; }
         __syncthreads();
         uint32_t t1 = ts->tile;                                               // CTA-uniform
         const uint32_t in_total = ts->in_total;
