@@ -361,10 +361,17 @@ template <bool NF, class Src, class W> SSE_HD void put_copy_t(const Src& s, uint
         const uint32_t shb = (sp & 3u) * 8;
         uint32_t lo = s.ld32a(a);
         uint32_t i = 0;
-        for (; i + 4 <= nw; i += 4) {
+        for (; i + 8 <= nw; i += 8) {                // eight words per trip: no register shuffling between the halves
+            const uint32_t h0 = s.ld32a(a + 4), h1 = s.ld32a(a + 8), h2 = s.ld32a(a + 12), h3 = s.ld32a(a + 16);
+            const uint32_t h4 = s.ld32a(a + 20), h5 = s.ld32a(a + 24), h6 = s.ld32a(a + 28), h7 = s.ld32a(a + 32);
+            w.store_words4(funnel_r(lo, h0, shb), funnel_r(h0, h1, shb), funnel_r(h1, h2, shb), funnel_r(h2, h3, shb));
+            w.store_words4(funnel_r(h3, h4, shb), funnel_r(h4, h5, shb), funnel_r(h5, h6, shb), funnel_r(h6, h7, shb));
+            lo = h7; a += 32;
+        }
+        if (i + 4 <= nw) {
             const uint32_t h0 = s.ld32a(a + 4), h1 = s.ld32a(a + 8), h2 = s.ld32a(a + 12), h3 = s.ld32a(a + 16);
             w.store_words4(funnel_r(lo, h0, shb), funnel_r(h0, h1, shb), funnel_r(h1, h2, shb), funnel_r(h2, h3, shb));
-            lo = h3; a += 16;
+            lo = h3; a += 16; i += 4;
         }
         const uint32_t r = nw - i;
         const uint32_t h0 = s.ld32a(a + 4), h1 = s.ld32a(a + 8), h2 = s.ld32a(a + 12);
@@ -374,6 +381,16 @@ template <bool NF, class Src, class W> SSE_HD void put_copy_t(const Src& s, uint
     if (n) { if (NF) w.put_n_nf(ld32u(s, sp), n); else w.put_n(ld32u(s, sp), n); }
 }
 template <class Src, class W> SSE_HD void put_copy(const Src& s, uint32_t sp, uint32_t n, W& w) { put_copy_t<false>(s, sp, n, w); }
+template <class Src> SSE_HD void ld3u(const Src& s, uint32_t pos, uint32_t& w0, uint32_t& w1, uint32_t& w2);
+// the same for at most 12 bytes (a canonical sequence literal has 1..9), after the first flush: three unaligned word
+// loads and three puts instead of the alignment prologue / word loop / tail of the general copy
+template <class Src, class W> SSE_HD void put_copy_small_nf(const Src& s, uint32_t sp, uint32_t n, W& w) {
+    uint32_t w0, w1, w2;
+    ld3u(s, sp, w0, w1, w2);
+    w.put_n_nf(w0, n < 4 ? n : 4);
+    if (n > 4) w.put_n_nf(w1, n < 8 ? n - 4 : 4);
+    if (n > 8) w.put_n_nf(w2, n - 8);
+}
 
 // ------------------------------------------------------------------ emission ----
 // Writes the record's output (SSE frame, or bridge subject+JSON) at w.pos.  With a counting
@@ -921,7 +938,7 @@ SSE_HD void emit_record_fast(const Src& s, uint32_t o, uint32_t L, const Plan& p
     } else {
         w.put32(w4("even"));                              // sse_handler.go:212-213
         SSE_PUT_LIT_NF(w, "t: token\nid: ");
-        put_copy_t<true>(s, o + pl.seq_b, pl.seq_n, w);   // canonical literal == fmt %d
+        put_copy_small_nf(s, o + pl.seq_b, pl.seq_n, w);  // canonical literal == fmt %d (1..9 bytes on this path)
         SSE_PUT_LIT_NF(w, "\ndata: ");                    // :214
         if (body) {
             put_copy_t<true>(s, o, L, w);

@@ -153,3 +153,10 @@ if "--lost" in sys.argv:
 print("---- per innermost line ----")
 for key, (i, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
     print("%5.1f%% inst %5.1f%% smp  %-28s %s" % (100.0 * i / tot_i, 100.0 * s / max(tot_s, 1), "%s:%d" % key if key else "?", src_line(key)))
+if "--sass" in sys.argv:          # --sass <function>: the SASS rows inlined from that function, with executed counts per record
+    want = sys.argv[sys.argv.index("--sass") + 1]
+    nrec = float(sys.argv[sys.argv.index("--records") + 1]) if "--records" in sys.argv else 1.0
+    print("---- SASS of %s (warp-instructions executed / record count %g) ----" % (want, nrec))
+    for k in range(n):
+        if any(func_of(fr) == want for fr in chains[k]):
+            print("%8.3f  %-12s %s" % (int(body[k][ie]) / nrec, "%s:%d" % lines[k][0] if lines[k][0] else "?", lines[k][1]))
