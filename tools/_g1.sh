@@ -1,3 +1,3 @@
-timeout 1200 python -m pytest tests/test_gpu_frame.py tests/test_gpu_encode.py -m gpu -x -q 2>&1 | tail -2
-for w in plain plain32 inspect_ab match bridge ordered; do timeout 200 python tools/prof_target.py $w 2>&1 | tail -1; done
-timeout 300 python tools/bench_encode.py 2>&1 | tail -2
+timeout 1700 python -m pytest tests -m gpu -x -q > gpurun_out/r02_gputest_full3.log 2>&1; tail -3 gpurun_out/r02_gputest_full3.log
+timeout 900 python tests/soak_fuzz.py --seeds 24 --records 200000 --first-seed 100 > gpurun_out/r02_soak2.log 2>&1; tail -2 gpurun_out/r02_soak2.log
+timeout 900 python bench.py > gpurun_out/r02_bench_v3.json 2> gpurun_out/r02_bench_v3.err; tail -c 300 gpurun_out/r02_bench_v3.json
