@@ -143,6 +143,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) k_scan_tile_totals(uint64_t* tile_
 #define SSE_PREFETCH_WAVES 1
 #endif
 constexpr uint32_t PREFETCH_WAVES = SSE_PREFETCH_WAVES;
+// A full tile's TILE + 1 record offsets (in_off[r0 .. r0 + TILE]) come into shared memory as a second bulk copy on the
+// payload's mbarrier: the threads then read their offsets on chip instead of waiting for a global load at the top of
+// every tile.  OFF_BYTES = (TILE + 1) words rounded up to the 16 bytes a bulk copy moves.
+constexpr uint32_t OFF_BYTES = ((TILE + 1) * 4 + 15) & ~15u;
 constexpr uint32_t PLAN_REDO = 0xFFFFFFFFu;             // FrameArgs::plan: decode this record again in the emit pass
 constexpr uint32_t PLAN_HOLE = 0xFFFFFFFEu;             // emit pass -> its tail: this record's frame is still to be written
 constexpr uint32_t DEFER_MAX_PER_WARP = 9;              // more such records than this in a warp: decoded inline, where the tile is on chip
@@ -157,6 +161,7 @@ struct TileSmem {
     // eight registers of every thread across the whole persistent loop
     uint32_t ctr[6];
     unsigned long long c_in, c_out;
+    uint32_t off_smem, pad_[3];  // this tile's record offsets arrived with the payload (s_off), not to be loaded from global memory
     uint32_t next_t, my_chain;   // thread 0's loop state: the tile claimed for the next trip; last tile (+1) of this CTA that left records to the tail phase
 };
 
@@ -186,6 +191,7 @@ __device__ __noinline__ uint32_t emit_slow(const uint8_t* src_base, uint32_t o, 
 __device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t t, bool want_base = false) {
     ts->tile = t;
     ts->npend = 0;
+    ts->off_smem = 0;
     if (t < a.num_tiles) {
         uint64_t ob = 0;
         if (want_base) ob = a.tile_state[t];                // requested first: in flight while the TMA load is set up
@@ -199,8 +205,14 @@ __device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uin
         const uint32_t abase = tb & ~15u;
         const uint32_t bytes = (te - abase + 15u) & ~15u;
         if (bytes != 0 && bytes <= a.in_cap) {
-            mbar_expect_tx(&ts->mbar, bytes);
+            // the offsets ride along when all OFF_BYTES of them exist (every tile but the batch's last one or two)
+            const bool with_off = a.off_tma && (size_t)r0 * 4 + OFF_BYTES <= ((size_t)a.n + 1) * 4;
+            mbar_expect_tx(&ts->mbar, bytes + (with_off ? OFF_BYTES : 0u));
             tma_load_1d(s_in, a.in + abase, bytes, &ts->mbar);
+            if (with_off) {
+                tma_load_1d(reinterpret_cast<uint8_t*>(ts + 1), a.in_off + r0, OFF_BYTES, &ts->mbar);
+                ts->off_smem = 1;
+            }
         }
         ts->c_in += te - tb;
         if (want_base) ts->obase = ob;
@@ -291,7 +303,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
     const bool inspect_fused = (EXT & X_INSPECT) && a.insp != nullptr && !pre_verdict;
     DfaCache dcache{nullptr, nullptr, 0, nullptr, nullptr, 0, 0, 0, 0};
     if (inspect_fused) {
-        uint8_t* s_cls = reinterpret_cast<uint8_t*>(ts + 1);
+        uint8_t* s_cls = reinterpret_cast<uint8_t*>(ts + 1) + OFF_BYTES;
         uint32_t* s_eot = reinterpret_cast<uint32_t*>(s_cls + 256);
         uint16_t* s_rows = reinterpret_cast<uint16_t*>(s_eot + DFA_EOT_WORDS);
         const DfaDev& d = a.insp->fwd;
@@ -349,16 +361,22 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         uint32_t my_b = 0, my_e = 0;
         int64_t my_start = 0;
         const bool active = tid < nrec;
+        const bool off_smem = ts->off_smem != 0;                              // tile-uniform
         if (active) {
-            my_b = a.in_off[r0 + tid];
-            my_e = a.in_off[r0 + tid + 1];
+            if (!off_smem) { my_b = a.in_off[r0 + tid]; my_e = a.in_off[r0 + tid + 1]; }
+            if (a.start_seq) my_start = a.start_seq[r0 + tid];
+        }
+        if (smem_in && in_bytes != 0) { mbar_wait(&ts->mbar, parity); parity ^= 1; }
+        if (active) {
+            if (off_smem) {
+                const uint32_t* s_off = reinterpret_cast<const uint32_t*>(ts + 1);
+                my_b = s_off[tid]; my_e = s_off[tid + 1];
+            }
             if (my_b < tb || my_e > te || my_b > my_e) {                     // malformed offsets: clamp into the tile
                 atomicExch(a.bad_offsets, 1u);
                 my_e = min(max(my_e, tb), te); my_b = min(max(my_b, tb), my_e);
             }
-            if (a.start_seq) my_start = a.start_seq[r0 + tid];
         }
-        if (smem_in && in_bytes != 0) { mbar_wait(&ts->mbar, parity); parity ^= 1; }
 
         // ---- pass 1: decode + filter, output length --------------------------------
         // Arrival mode: a record that is not canonical is left to the tail phase of this CTA, which runs the general
@@ -779,19 +797,20 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
 // ---------------------------------------------------------------------- launch ----
 // Shared memory per CTA: a tile of TILE records is ~17 KB in / ~21 KB out at the BASELINE workload; the caps leave
 // ~15% slack.  Tiles that exceed them take the direct global-memory path inside the same kernel.
-//   cfg 0  160 B in / 192 B out per record                      5 CTAs per SM (the SM's shared memory is then full)
+//   cfg 0  160 B in / 188 B out per record                      5 CTAs per SM (the SM's shared memory is then full)
 //   cfg 1  "wide": NATS PUB framing adds ~60 bytes per record (subject + protocol line): 224 B out
 //   cfg 2  fused per-token inspection of adapter frames: the on-chip DFA part (2.4 KB) has to fit beside five tiles
-//          per SM, so the caps shrink to 152 B in / 184 B out per record (~10 % slack at the BASELINE shape)
+//          per SM, so the caps shrink to 150 B in / 181 B out per record (~10 % slack at the BASELINE shape)
 //   cfg 3  fused inspection of bridge records (subject + payload ~182 B: the narrow cap would overflow): full caps, 4 CTAs per SM
 //   cfg 4  fused inspection + NATS PUB framing
 constexpr int N_CFG = 5;
 static void cfg_caps(int cfg, uint32_t* ic, uint32_t* oc, uint32_t* smem) {
     const bool cache = cfg >= 2;
-    *ic = TILE * (cfg == 2 ? 152 : 160);
-    *oc = TILE * (cfg == 2 ? 184 : ((cfg == 1 || cfg == 4) ? 224 : 192));
-    *smem = *ic + 32 + *oc + 48 + (uint32_t)sizeof(TileSmem) + (cache ? DFA_CACHE_BYTES : 0u);
+    *ic = TILE * (cfg == 2 ? 150 : 160);
+    *oc = TILE * (cfg == 2 ? 181 : (cfg == 0 ? 188 : ((cfg == 1 || cfg == 4) ? 224 : 192)));
+    *smem = *ic + 32 + *oc + 48 + (uint32_t)sizeof(TileSmem) + OFF_BYTES + (cache ? DFA_CACHE_BYTES : 0u);
 }
+static_assert(sizeof(TileSmem) % 16 == 0, "the record offsets behind TileSmem are the target of a bulk copy");
 // The counting pass of ordered mode never stages a frame: launched with out_cap_s = 0 it needs the input tile only, and
 // more CTAs fit an SM.
 static uint32_t count_smem(int cfg) {
@@ -915,6 +934,7 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     if ((e = clear_scratch(a, stream)) != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
+    a.off_tma = (reinterpret_cast<uintptr_t>(a.in_off) & 15) == 0 ? 1u : 0u;
     switch (ext) {
     case 0: launch_variant<0>(a, grid, smem_bytes, cl, stream); break;
     case 1: launch_variant<1>(a, grid, smem_bytes, cl, stream); break;
@@ -934,6 +954,7 @@ cudaError_t frame_plan_launch(int device, FrameArgs a, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     if ((e = clear_scratch(a, stream)) != cudaSuccess) return e;
     if (a.n == 0) return cudaSuccess;
+    a.off_tma = (reinterpret_cast<uintptr_t>(a.in_off) & 15) == 0 ? 1u : 0u;
     a.out_cap_s = 0;
     k_frame_tiles<X_INSPECT, MODE_ORDERED_COUNT><<<cl.grid, TILE, cl.smem, stream>>>(a);
     return cudaGetLastError();
