@@ -161,8 +161,11 @@ struct TileSmem {
     // eight registers of every thread across the whole persistent loop
     uint32_t ctr[6];
     unsigned long long c_in, c_out;
-    uint32_t off_smem, pad_[3];  // this tile's record offsets arrived with the payload (s_off), not to be loaded from global memory
-    uint32_t next_t, my_chain;   // thread 0's loop state: the tile claimed for the next trip; last tile (+1) of this CTA that left records to the tail phase
+    uint32_t off_smem;           // this tile's record offsets arrived with the payload (s_off), not to be loaded from global memory
+    // thread 0's loop state.  Tiles are claimed two trips ahead so that nothing on the way to a tile's TMA load waits for
+    // memory after the barrier: next_t is the next trip's tile, ntb / nte its byte range (loaded during this trip's
+    // decode), next2 the tile after that; my_chain: last tile (+1) of this CTA that left records to the tail phase.
+    uint32_t next_t, next2, ntb, nte, my_chain;
 };
 
 // Out-of-line general path (generic pointers: the tile may sit in shared or in global memory).
@@ -188,7 +191,8 @@ __device__ __noinline__ uint32_t emit_slow(const uint8_t* src_base, uint32_t o, 
 }
 
 // tid 0: claim bookkeeping for tile t -- tile byte range + TMA load into s_in
-__device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t t, bool want_base = false) {
+// (tb, te) = in_off[first record of t], in_off[one past its last record], loaded by the caller
+__device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t t, uint32_t tb, uint32_t te, bool want_base = false) {
     ts->tile = t;
     ts->npend = 0;
     ts->off_smem = 0;
@@ -196,10 +200,8 @@ __device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uin
         uint64_t ob = 0;
         if (want_base) ob = a.tile_state[t];                // requested first: in flight while the TMA load is set up
         const uint32_t r0 = t * TILE;
-        const uint32_t nrec = min((uint32_t)TILE, a.n - r0);
         // offsets come from the host: clamp them so that nothing below can leave the arena, and say so
         const uint32_t in_total = ts->in_total;
-        uint32_t tb = a.in_off[r0], te = a.in_off[r0 + nrec];
         if (te > in_total || tb > te) { atomicExch(a.bad_offsets, 1u); te = min(te, in_total); tb = min(tb, te); }
         ts->tb = tb; ts->te = te;
         const uint32_t abase = tb & ~15u;
@@ -332,14 +334,31 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         for (int k = 0; k < 6; k++) ts->ctr[k] = 0;
         ts->my_chain = 0;
         ts->c_in = 0; ts->c_out = 0;
-        setup_tile(a, ts, s_in, atomicAdd(a.ticket, 1u), MODE == MODE_ORDERED_EMIT);
+        const uint32_t t0 = atomicAdd(a.ticket, 1u);
+        uint32_t b0 = 0, e0 = 0;
+        if (t0 < a.num_tiles) { b0 = a.in_off[t0 * TILE]; e0 = a.in_off[min((t0 + 1) * TILE, a.n)]; }
+        setup_tile(a, ts, s_in, t0, b0, e0, MODE == MODE_ORDERED_EMIT);
+        ts->next_t = atomicAdd(a.ticket, 1u);
     }
+    // thread 0, after the barrier behind which the current tile's input is no longer needed: next tile's bookkeeping + TMA
+    // load, from what was parked in shared memory during the decode -- no memory round trip between the barriers
+    auto advance = [&]() {
+        setup_tile(a, ts, s_in, ts->next_t, ts->ntb, ts->nte, MODE == MODE_ORDERED_EMIT);
+        ts->next_t = ts->next2;
+    };
 
     for (;;) {
         __syncthreads();                                                      // (A) tile info visible; s_out free
         const uint32_t tile = ts->tile;
         if (tile >= a.num_tiles) break;
-        if (tid == 0) ts->next_t = atomicAdd(a.ticket, 1u);                   // claimed early, used after (D)
+        // thread 0: the tile after next is claimed and the next tile's byte range requested now; the results are parked in
+        // shared memory after the decode (nothing waits for them here)
+        uint32_t claim = 0, nb = 0, ne = 0;
+        if (tid == 0) {
+            const uint32_t nt = ts->next_t;
+            claim = atomicAdd(a.ticket, 1u);
+            if (nt < a.num_tiles) { nb = a.in_off[nt * TILE]; ne = a.in_off[min((nt + 1) * TILE, a.n)]; }
+        }
         const uint32_t r0 = tile * TILE;
         const uint32_t nrec = min((uint32_t)TILE, a.n - r0);
         const uint32_t tb = ts->tb, te = ts->te;
@@ -502,7 +521,10 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             if (lane >= d) incl += v;
         }
         if (lane == 31) ts->wsum[warp] = incl;
-        if (tid == 0) bulk_wait_read0();                                      // previous tile's bulk store has finished reading s_out
+        if (tid == 0) {
+            ts->next2 = claim; ts->ntb = nb; ts->nte = ne;
+            bulk_wait_read0();                                                // previous tile's bulk store has finished reading s_out
+        }
         __syncthreads();                                                      // (B)
         uint32_t wpre = 0, total = 0;
 #pragma unroll
@@ -519,7 +541,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
                 uint64_t w = total;
                 if (ts->npend) { w |= (uint64_t)ts->my_chain << 32; ts->my_chain = tile + 1; }   // tiles with records left to the tail, chained
                 a.tile_state[tile] = w;
-                setup_tile(a, ts, s_in, ts->next_t);                        // every thread is past (B): the tile has been consumed
+                advance();                        // every thread is past (B): the tile has been consumed
             }
             continue;
         }
@@ -562,7 +584,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             if (!ordered && tid < alloc - total) s_out[total + tid] = 0;
             fence_proxy_async_smem();                                         // staging writes -> visible to the TMA store
             __syncthreads();                                                  // (D) s_in free, staging tile complete, base visible
-            if (tid == 0) setup_tile(a, ts, s_in, ts->next_t, ordered);     // next tile's TMA load flies during the copy-out
+            if (tid == 0) advance();     // next tile's TMA load flies during the copy-out
         } else {
             // ---- oversize tile: emit straight into the arena ---------------------------
             __syncthreads();                                                  // (D')
@@ -576,7 +598,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             }
             if (fits && tid < alloc - total) a.out[base + total + tid] = 0;       // pad of an aligned tile
             __syncthreads();                                                  // (E') s_in free
-            if (tid == 0) setup_tile(a, ts, s_in, ts->next_t, ordered);
+            if (tid == 0) advance();
         }
         if (active) {
             a.out_off[r0 + tid] = base + local;
