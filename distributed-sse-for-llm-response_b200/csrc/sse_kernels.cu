@@ -154,18 +154,20 @@ struct TileSmem {
     uint64_t mbar;
     uint64_t base;           // global byte offset of the tile's output
     uint64_t obase;          // ordered emit pass: the same, known as soon as the tile is claimed (k_scan_tile_totals)
-    uint32_t tile, tb, te, in_total;
-    uint32_t npend;          // records of this tile left to the tail phase (later: fill of the tail's list)
-    uint32_t wsum[TILE / 32];
+    // Per-tile bookkeeping, double-buffered by the trip's parity: thread 0 parks the NEXT tile's entry during the current
+    // trip's decode (before barrier (B)), so every thread finds it at the top of the next trip without another barrier.
+    // npend: records of the tile left to the tail phase.
+    struct Meta { uint32_t tile, tb, te, npend; } meta[2];
+    uint32_t in_total;
+    uint32_t wsum[2][TILE / 32];   // double-buffered too: the counting pass has one barrier per tile
     // the CTA's share of the launch counters (ok, syntax, type, filtered, done, fast; bytes in / out): kept here, not in
     // eight registers of every thread across the whole persistent loop
     uint32_t ctr[6];
     unsigned long long c_in, c_out;
-    uint32_t off_smem;           // this tile's record offsets arrived with the payload (s_off), not to be loaded from global memory
     // thread 0's loop state.  Tiles are claimed two trips ahead so that nothing on the way to a tile's TMA load waits for
     // memory after the barrier: next_t is the next trip's tile, ntb / nte its byte range (loaded during this trip's
     // decode), next2 the tile after that; my_chain: last tile (+1) of this CTA that left records to the tail phase.
-    uint32_t next_t, next2, ntb, nte, my_chain;
+    uint32_t next_t, next2, my_chain, pad_[3];
 };
 
 // Out-of-line general path (generic pointers: the tile may sit in shared or in global memory).
@@ -190,35 +192,43 @@ __device__ __noinline__ uint32_t emit_slow(const uint8_t* src_base, uint32_t o, 
     return subj;
 }
 
-// tid 0: claim bookkeeping for tile t -- tile byte range + TMA load into s_in
-// (tb, te) = in_off[first record of t], in_off[one past its last record], loaded by the caller
-__device__ __forceinline__ void setup_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t t, uint32_t tb, uint32_t te, bool want_base = false) {
-    ts->tile = t;
-    ts->npend = 0;
-    ts->off_smem = 0;
+// Does a tile's payload come by TMA, and do its record offsets ride along?  (Every thread evaluates this for the
+// current tile; thread 0 for the tile it loads.)
+struct TileShape { uint32_t abase, bytes; bool smem_in, with_off; };
+__device__ __forceinline__ TileShape tile_shape(const FrameArgs& a, uint32_t t, uint32_t tb, uint32_t te) {
+    TileShape sh;
+    sh.abase = tb & ~15u;
+    sh.bytes = (te - sh.abase + 15u) & ~15u;
+    sh.smem_in = sh.bytes <= a.in_cap;
+    // the offsets ride along when all OFF_BYTES of them exist (every tile but the batch's last one or two)
+    sh.with_off = sh.smem_in && sh.bytes != 0 && a.off_tma && (size_t)t * TILE * 4 + OFF_BYTES <= ((size_t)a.n + 1) * 4;
+    return sh;
+}
+// thread 0, during the decode of the current tile: bookkeeping entry of tile t, whose byte range (tb, te) =
+// in_off[first record], in_off[one past the last record] the caller has loaded
+__device__ __forceinline__ void park_tile(const FrameArgs& a, TileSmem* ts, uint32_t slot, uint32_t t, uint32_t tb, uint32_t te) {
     if (t < a.num_tiles) {
-        uint64_t ob = 0;
-        if (want_base) ob = a.tile_state[t];                // requested first: in flight while the TMA load is set up
-        const uint32_t r0 = t * TILE;
         // offsets come from the host: clamp them so that nothing below can leave the arena, and say so
         const uint32_t in_total = ts->in_total;
         if (te > in_total || tb > te) { atomicExch(a.bad_offsets, 1u); te = min(te, in_total); tb = min(tb, te); }
-        ts->tb = tb; ts->te = te;
-        const uint32_t abase = tb & ~15u;
-        const uint32_t bytes = (te - abase + 15u) & ~15u;
-        if (bytes != 0 && bytes <= a.in_cap) {
-            // the offsets ride along when all OFF_BYTES of them exist (every tile but the batch's last one or two)
-            const bool with_off = a.off_tma && (size_t)r0 * 4 + OFF_BYTES <= ((size_t)a.n + 1) * 4;
-            mbar_expect_tx(&ts->mbar, bytes + (with_off ? OFF_BYTES : 0u));
-            tma_load_1d(s_in, a.in + abase, bytes, &ts->mbar);
-            if (with_off) {
-                tma_load_1d(reinterpret_cast<uint8_t*>(ts + 1), a.in_off + r0, OFF_BYTES, &ts->mbar);
-                ts->off_smem = 1;
-            }
-        }
-        ts->c_in += te - tb;
-        if (want_base) ts->obase = ob;
     }
+    ts->meta[slot].tile = t; ts->meta[slot].tb = tb; ts->meta[slot].te = te; ts->meta[slot].npend = 0;
+}
+// thread 0, once the input buffer is free: TMA load of the parked tile (payload and, when they all exist, its offsets)
+__device__ __forceinline__ void launch_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t slot, bool want_base) {
+    const uint32_t t = ts->meta[slot].tile;
+    if (t >= a.num_tiles) return;
+    uint64_t ob = 0;
+    if (want_base) ob = a.tile_state[t];                    // requested first: in flight while the TMA load is set up
+    const uint32_t tb = ts->meta[slot].tb, te = ts->meta[slot].te;
+    const TileShape sh = tile_shape(a, t, tb, te);
+    if (sh.smem_in && sh.bytes != 0) {
+        mbar_expect_tx(&ts->mbar, sh.bytes + (sh.with_off ? OFF_BYTES : 0u));
+        tma_load_1d(s_in, a.in + sh.abase, sh.bytes, &ts->mbar);
+        if (sh.with_off) tma_load_1d(reinterpret_cast<uint8_t*>(ts + 1), a.in_off + (size_t)t * TILE, OFF_BYTES, &ts->mbar);
+    }
+    ts->c_in += te - tb;
+    if (want_base) ts->obase = ob;
 }
 
 // Inspection of one record's token text, general case (out of line, generic pointers): records that are not
@@ -337,34 +347,32 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         const uint32_t t0 = atomicAdd(a.ticket, 1u);
         uint32_t b0 = 0, e0 = 0;
         if (t0 < a.num_tiles) { b0 = a.in_off[t0 * TILE]; e0 = a.in_off[min((t0 + 1) * TILE, a.n)]; }
-        setup_tile(a, ts, s_in, t0, b0, e0, MODE == MODE_ORDERED_EMIT);
+        park_tile(a, ts, 0, t0, b0, e0);
+        launch_tile(a, ts, s_in, 0, MODE == MODE_ORDERED_EMIT);
         ts->next_t = atomicAdd(a.ticket, 1u);
     }
-    // thread 0, after the barrier behind which the current tile's input is no longer needed: next tile's bookkeeping + TMA
-    // load, from what was parked in shared memory during the decode -- no memory round trip between the barriers
-    auto advance = [&]() {
-        setup_tile(a, ts, s_in, ts->next_t, ts->ntb, ts->nte, MODE == MODE_ORDERED_EMIT);
-        ts->next_t = ts->next2;
-    };
+    __syncthreads();                                                          // the first tile's entry is visible
 
-    for (;;) {
-        __syncthreads();                                                      // (A) tile info visible; s_out free
-        const uint32_t tile = ts->tile;
+    // Barriers per tile: (B) behind the decode, (D) behind the staging (the counting pass of ordered mode: (B) only).
+    // Nothing is needed at the top: the tile's entry was parked before the previous trip's (B).
+    for (uint32_t trip = 0;; trip++) {
+        const uint32_t slot = trip & 1u;
+        const uint32_t tile = ts->meta[slot].tile;
         if (tile >= a.num_tiles) break;
         // thread 0: the tile after next is claimed and the next tile's byte range requested now; the results are parked in
         // shared memory after the decode (nothing waits for them here)
-        uint32_t claim = 0, nb = 0, ne = 0;
+        uint32_t claim = 0, nb = 0, ne = 0, nt = 0;
         if (tid == 0) {
-            const uint32_t nt = ts->next_t;
+            nt = ts->next_t;
             claim = atomicAdd(a.ticket, 1u);
             if (nt < a.num_tiles) { nb = a.in_off[nt * TILE]; ne = a.in_off[min((nt + 1) * TILE, a.n)]; }
         }
         const uint32_t r0 = tile * TILE;
         const uint32_t nrec = min((uint32_t)TILE, a.n - r0);
-        const uint32_t tb = ts->tb, te = ts->te;
-        const uint32_t abase = tb & ~15u;
-        const uint32_t in_bytes = (te - abase + 15u) & ~15u;
-        const bool smem_in = in_bytes <= a.in_cap;
+        const uint32_t tb = ts->meta[slot].tb, te = ts->meta[slot].te;
+        const TileShape shape = tile_shape(a, tile, tb, te);
+        const uint32_t abase = shape.abase, in_bytes = shape.bytes;
+        const bool smem_in = shape.smem_in;
 
         // One wave ahead: the payload bytes of tile (tile + gridDim.x) are pulled into L2 now, so that the TMA load of
         // whichever CTA gets that tile pays an L2 hit instead of a DRAM round trip.  The bytes in flight towards DRAM are
@@ -380,7 +388,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         uint32_t my_b = 0, my_e = 0;
         int64_t my_start = 0;
         const bool active = tid < nrec;
-        const bool off_smem = ts->off_smem != 0;                              // tile-uniform
+        const bool off_smem = shape.with_off;                                 // tile-uniform
         if (active) {
             if (!off_smem) { my_b = a.in_off[r0 + tid]; my_e = a.in_off[r0 + tid + 1]; }
             if (a.start_seq) my_start = a.start_seq[r0 + tid];
@@ -428,7 +436,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
                 pl.done = (st & ST_DONE) ? 1u : 0u; pl.cid_esc = 0; pl.tok_esc = 0; pl.tok_redacted = 0;
                 fastp = true; planned = true;
             } else { st = ST_OK; len = 0; }                                   // decoded again below
-            if (lane == 0 && nredo && nredo < DEFER_MAX_PER_WARP) atomicAdd(&ts->npend, nredo);
+            if (lane == 0 && nredo && nredo < DEFER_MAX_PER_WARP) atomicAdd(&ts->meta[slot].npend, nredo);
         }
         InterestPre ipre{0, 0, 0, 0, 0, 0};
         if (active && smem_in && !planned) {
@@ -453,7 +461,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
                 pl = sp;
             }
         }
-        if (defer && lane == 0 && nslow) atomicAdd(&ts->npend, nslow);
+        if (defer && lane == 0 && nslow) atomicAdd(&ts->meta[slot].npend, nslow);
 
         if (pf) {
             const uint32_t in_total = ts->in_total;
@@ -520,15 +528,16 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
             if (lane >= d) incl += v;
         }
-        if (lane == 31) ts->wsum[warp] = incl;
+        if (lane == 31) ts->wsum[slot][warp] = incl;
         if (tid == 0) {
-            ts->next2 = claim; ts->ntb = nb; ts->nte = ne;
+            park_tile(a, ts, slot ^ 1u, nt, nb, ne);                          // the next trip's tile: visible behind (B)
+            ts->next2 = claim;
             bulk_wait_read0();                                                // previous tile's bulk store has finished reading s_out
         }
         __syncthreads();                                                      // (B)
         uint32_t wpre = 0, total = 0;
 #pragma unroll
-        for (int w = 0; w < TILE / 32; w++) { uint32_t v = ts->wsum[w]; if (w < (int)warp) wpre += v; total += v; }
+        for (int w = 0; w < TILE / 32; w++) { uint32_t v = ts->wsum[slot][w]; if (w < (int)warp) wpre += v; total += v; }
         if (MODE == MODE_ORDERED_COUNT) {        // pass A of ordered mode: only the tile's byte count is wanted
             if (!EXT && a.plan && active) {      // what the emit pass needs of a canonical record, so that it does not decode it again
                 uint32_t pw = PLAN_REDO;
@@ -539,9 +548,9 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             }
             if (tid == 0) {
                 uint64_t w = total;
-                if (ts->npend) { w |= (uint64_t)ts->my_chain << 32; ts->my_chain = tile + 1; }   // tiles with records left to the tail, chained
+                if (ts->meta[slot].npend) { w |= (uint64_t)ts->my_chain << 32; ts->my_chain = tile + 1; }   // tiles with records left to the tail, chained
                 a.tile_state[tile] = w;
-                advance();                        // every thread is past (B): the tile has been consumed
+                launch_tile(a, ts, s_in, slot ^ 1u, false); ts->next_t = ts->next2;   // every thread is past (B): the tile has been consumed
             }
             continue;
         }
@@ -555,8 +564,8 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         // arrival-order placement: every tile owns a 16-byte aligned slice of the arena, so its staging
         // tile leaves as ONE TMA bulk store; the <=15 pad bytes after its last frame are zeroed.
         const uint32_t alloc = ordered ? total : ((total + 15u) & ~15u);
-        if ((DEFER || MODE == MODE_ORDERED_EMIT) && tid == 0 && ts->npend) {   // chain this tile to the CTA's list of tiles with records left over
-            a.tile_state[tile] = (uint64_t)ts->npend | ((uint64_t)ts->my_chain << 32);
+        if ((DEFER || MODE == MODE_ORDERED_EMIT) && tid == 0 && ts->meta[slot].npend) {   // chain this tile to the CTA's list of tiles with records left over
+            a.tile_state[tile] = (uint64_t)ts->meta[slot].npend | ((uint64_t)ts->my_chain << 32);
             ts->my_chain = tile + 1;
         }
         if (tid == 0) {
@@ -584,7 +593,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             if (!ordered && tid < alloc - total) s_out[total + tid] = 0;
             fence_proxy_async_smem();                                         // staging writes -> visible to the TMA store
             __syncthreads();                                                  // (D) s_in free, staging tile complete, base visible
-            if (tid == 0) advance();     // next tile's TMA load flies during the copy-out
+            if (tid == 0) { launch_tile(a, ts, s_in, slot ^ 1u, ordered); ts->next_t = ts->next2; }   // next tile's TMA load flies during the copy-out
         } else {
             // ---- oversize tile: emit straight into the arena ---------------------------
             __syncthreads();                                                  // (D')
@@ -598,7 +607,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             }
             if (fits && tid < alloc - total) a.out[base + total + tid] = 0;       // pad of an aligned tile
             __syncthreads();                                                  // (E') s_in free
-            if (tid == 0) advance();
+            if (tid == 0) { launch_tile(a, ts, s_in, slot ^ 1u, ordered); ts->next_t = ts->next2; }
         }
         if (active) {
             a.out_off[r0 + tid] = base + local;
@@ -662,19 +671,19 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         // chain link in the upper half of the tile word is cleared as the chain is walked, the scan wants plain totals).
         uint32_t* s_list = reinterpret_cast<uint32_t*>(s_in);
         __syncthreads();
-        if (tid == 0) { ts->tile = ts->my_chain; ts->npend = 0; }
+        if (tid == 0) { ts->meta[0].tile = ts->my_chain; ts->meta[0].npend = 0; }
         __syncthreads();
-        uint32_t t1 = ts->tile;
+        uint32_t t1 = ts->meta[0].tile;
         const uint32_t in_total = ts->in_total;
         while (t1 != 0) {
             uint32_t cnt = 0;
             while (t1 != 0 && cnt < (uint32_t)TILE) {
                 const uint32_t t = t1 - 1, i = t * TILE + tid;
-                if (i < a.n && (a.status[i] & ST_CODE_MASK) == ST_PENDING) s_list[atomicAdd(&ts->npend, 1u)] = i;
+                if (i < a.n && (a.status[i] & ST_CODE_MASK) == ST_PENDING) s_list[atomicAdd(&ts->meta[0].npend, 1u)] = i;
                 t1 = (uint32_t)(a.tile_state[t] >> 32);
                 __syncthreads();
                 if (tid == 0) a.tile_state[t] &= 0xFFFFFFFFull;
-                cnt = ts->npend;
+                cnt = ts->meta[0].npend;
             }
             __syncthreads();                                                  // links cleared before any length is added
             for (uint32_t g = 0; g < cnt; g += TILE) {
@@ -690,7 +699,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
                 }
             }
             __syncthreads();
-            if (tid == 0) ts->npend = 0;
+            if (tid == 0) ts->meta[0].npend = 0;
             __syncthreads();
         }
     }
@@ -698,18 +707,18 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         // Emit pass: the frames of the records placed as holes, written where the main loop put them.
         uint32_t* s_list = reinterpret_cast<uint32_t*>(s_out);
         __syncthreads();                                                      // the last tile's bulk store is complete (bulk_wait0 above)
-        if (tid == 0) { ts->tile = ts->my_chain; ts->npend = 0; }
+        if (tid == 0) { ts->meta[0].tile = ts->my_chain; ts->meta[0].npend = 0; }
         __syncthreads();
-        uint32_t t1 = ts->tile;
+        uint32_t t1 = ts->meta[0].tile;
         const uint32_t in_total = ts->in_total;
         while (t1 != 0) {
             uint32_t cnt = 0;
             while (t1 != 0 && cnt < (uint32_t)TILE) {
                 const uint32_t t = t1 - 1, i = t * TILE + tid;
-                if (i < a.n && a.plan[i] == PLAN_HOLE) s_list[atomicAdd(&ts->npend, 1u)] = i;
+                if (i < a.n && a.plan[i] == PLAN_HOLE) s_list[atomicAdd(&ts->meta[0].npend, 1u)] = i;
                 t1 = (uint32_t)(a.tile_state[t] >> 32);
                 __syncthreads();
-                cnt = ts->npend;
+                cnt = ts->meta[0].npend;
             }
             for (uint32_t g = 0; g < cnt; g += TILE) {
                 if (g + tid < cnt) {
@@ -726,25 +735,25 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
                 }
             }
             __syncthreads();
-            if (tid == 0) ts->npend = 0;
+            if (tid == 0) ts->meta[0].npend = 0;
             __syncthreads();
         }
     }
     if (MODE == MODE_ARRIVAL) {
         uint32_t* s_list = reinterpret_cast<uint32_t*>(s_out);
-        __syncthreads();                                                      // every thread has read the loop's last ts->tile
-        if (tid == 0) { ts->tile = ts->my_chain; ts->npend = 0; }
+        __syncthreads();                                                      // every thread has left the loop
+        if (tid == 0) { ts->meta[0].tile = ts->my_chain; ts->meta[0].npend = 0; }
         __syncthreads();
-        uint32_t t1 = ts->tile;                                               // CTA-uniform
+        uint32_t t1 = ts->meta[0].tile;                                               // CTA-uniform
         const uint32_t in_total = ts->in_total;
         while (t1 != 0) {
             uint32_t cnt = 0;
             while (t1 != 0 && cnt < (uint32_t)TILE) {                         // gather until there is a full group
                 const uint32_t t = t1 - 1, i = t * TILE + tid;
-                if (i < a.n && (a.status[i] & ST_CODE_MASK) == ST_PENDING) s_list[atomicAdd(&ts->npend, 1u)] = i;
+                if (i < a.n && (a.status[i] & ST_CODE_MASK) == ST_PENDING) s_list[atomicAdd(&ts->meta[0].npend, 1u)] = i;
                 t1 = (uint32_t)(a.tile_state[t] >> 32);
                 __syncthreads();
-                cnt = ts->npend;
+                cnt = ts->meta[0].npend;
             }
             for (uint32_t g = 0; g < cnt; g += TILE) {
                 const bool act = g + tid < cnt;
@@ -785,7 +794,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
                 if (lane == 0 && !fits) atomicExch(a.overflow, 1u);
             }
             __syncthreads();
-            if (tid == 0) ts->npend = 0;
+            if (tid == 0) ts->meta[0].npend = 0;
             __syncthreads();
         }
     }
