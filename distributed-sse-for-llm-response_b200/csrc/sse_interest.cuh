@@ -145,7 +145,7 @@ SSE_HD_NOINLINE InterestHit interest_lookup(const InterestDev& t, const Src& s, 
 // The descriptor fields the fast lane needs are held in registers (InterestFast), not re-read from the descriptor.
 struct InterestFast { const InterestSlot* slots; uint32_t mask, wild_single, wild_generic; };
 SSE_HD InterestFast make_interest_fast(const InterestDev& t) { return InterestFast{t.slots, t.mask, t.wild_single, t.wild_generic}; }
-struct InterestPre { uint32_t ready, hash, q0, q1, q2, q3; };     // ready 0: the general routine must take over
+struct InterestPre { uint32_t hash, q0, q1, q2, q3; };     // hash 0 (never a key's hash): the general routine must take over
 
 SSE_HD void slot_head(const InterestSlot* e, uint32_t& q0, uint32_t& q1, uint32_t& q2, uint32_t& q3) {
 #if defined(__CUDA_ARCH__)
@@ -161,7 +161,7 @@ SSE_HD void slot_head(const InterestSlot* e, uint32_t& q0, uint32_t& q1, uint32_
 template <class Src>
 SSE_HD void interest_prepare(const InterestFast& t, const Src& s, uint32_t cid_b, uint32_t cid_e, bool plain, InterestPre& pre) {
     const uint32_t len = cid_e - cid_b;
-    pre.ready = 0; pre.hash = 0; pre.q0 = pre.q1 = pre.q2 = pre.q3 = 0;
+    pre.hash = 0; pre.q0 = pre.q1 = pre.q2 = pre.q3 = 0;
     if (!plain || len == 0 || len > INTEREST_INLINE_KEY || t.wild_generic) return;
     const uint32_t a = cid_b & ~3u, shb = (cid_b & 3u) * 8, nw = (len + 3) >> 2;
     uint32_t lo = s.ld32a(a), dots = 0, hash = key_hash_init(len);
@@ -175,7 +175,6 @@ SSE_HD void interest_prepare(const InterestFast& t, const Src& s, uint32_t cid_b
         hash = key_hash_step(hash, w);
     }
     if (dots) return;
-    pre.ready = 1;
     pre.hash = key_hash_fin(hash);
     if (t.slots) slot_head(t.slots + (pre.hash & t.mask), pre.q0, pre.q1, pre.q2, pre.q3);
 }

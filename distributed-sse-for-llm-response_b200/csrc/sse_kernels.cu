@@ -438,7 +438,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             } else { st = ST_OK; len = 0; }                                   // decoded again below
             if (lane == 0 && nredo && nredo < DEFER_MAX_PER_WARP) atomicAdd(&ts->meta[slot].npend, nredo);
         }
-        InterestPre ipre{0, 0, 0, 0, 0, 0};
+        InterestPre ipre{0, 0, 0, 0, 0};
         if (active && smem_in && !planned) {
             PtrSrc src{s_in};
             if (EXT & X_INTEREST)                  // the id is hashed and its first table probe requested inside the parse
@@ -510,7 +510,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             if (EXT & X_INTEREST) {
                 InterestHit h{0, 0, 0};
                 if (canon && (st & ST_CODE_MASK) == ST_OK) {
-                    if (ipre.ready) { PtrSrc src{s_in}; interest_finish(ifast, src, o + pl.cid_b, o + pl.cid_e, ipre, h); }
+                    if (ipre.hash) { PtrSrc src{s_in}; interest_finish(ifast, src, o + pl.cid_b, o + pl.cid_e, ipre, h); }
                     else h = interest_slow(a, s_in, o, pl.cid_b, pl.cid_e);
                     if (h.list_cnt == 0 && h.wild_mask == 0) { st = ST_NO_INTEREST; len = 0; }   // nobody subscribed: nothing to frame
                 }

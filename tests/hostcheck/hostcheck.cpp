@@ -166,7 +166,7 @@ extern "C" int hc_interest(const hc_delta* d, uint32_t nd, const uint8_t* in, co
             const InterestFast fast = make_interest_fast(dev);
             InterestPre pre;
             interest_prepare(fast, src, o + pl.cid_b, o + pl.cid_e, fastp && !pl.cid_esc, pre);     // the kernel calls this from parse_fast's hook
-            if (pre.ready) interest_finish(fast, src, o + pl.cid_b, o + pl.cid_e, pre, h);
+            if (pre.hash) interest_finish(fast, src, o + pl.cid_b, o + pl.cid_e, pre, h);
             else h = interest_lookup(dev, src, o + pl.cid_b, o + pl.cid_e);
             hit[3 * i] = h.list_off; hit[3 * i + 1] = h.list_cnt; hit[3 * i + 2] = h.wild_mask;
             if (h.list_cnt == 0 && h.wild_mask == 0) st = ST_NO_INTEREST;

@@ -180,6 +180,46 @@ def test_tile_boundaries(pkg, eng, oracle, n, op):
     assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
 
 
+@pytest.mark.parametrize("op", [0, 8, 1])
+@pytest.mark.parametrize("shift", [0, 1, 2, 3])
+def test_offset_array_alignment(pkg, oracle, op, shift):
+    """The kernel brings a tile's record offsets on chip with a bulk copy when the offset array is 16-byte aligned and loads
+    them per thread otherwise: a device-resident launch with in_off at every word alignment, several tiles and a ragged last one."""
+    import torch
+    n = 128 * 9 + 77
+    arena, off = pkg.workload.generate(1, 50, (n + 49) // 50)
+    off = off[: n + 1].copy()
+    if op & 1:
+        want_out, want_off, want_subj, want_status = oracle.bridge(arena, off)
+    else:
+        want_out, want_off, want_status = oracle.adapter(arena, off)
+    eng = pkg.SseGpu(device=0, max_records=n, max_in_bytes=int(off[n]) + 64)
+    try:
+        d_in = torch.from_numpy(arena).cuda()
+        d_off_buf = torch.zeros(n + 1 + 8, dtype=torch.int32, device="cuda")
+        d_off = d_off_buf[shift: shift + n + 1]
+        d_off.copy_(torch.from_numpy(off.view(np.int32)))
+        assert d_off.data_ptr() % 16 == 4 * shift
+        cap = int(off[n]) + 64 * n
+        d_out = torch.zeros(cap, dtype=torch.uint8, device="cuda")
+        d_out_off = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
+        d_out_len = torch.zeros(n, dtype=torch.int32, device="cuda")
+        d_subj = torch.zeros(n, dtype=torch.int32, device="cuda")
+        d_status = torch.zeros(n, dtype=torch.int32, device="cuda")
+        stream = torch.cuda.Stream()
+        torch.cuda.synchronize()
+        eng.frame_launch(d_in.data_ptr(), d_off.data_ptr(), 0, n, op, d_out.data_ptr(), cap, d_out_off.data_ptr(), d_out_len.data_ptr(),
+                         d_subj.data_ptr(), d_status.data_ptr(), stream.cuda_stream)
+        torch.cuda.synchronize()
+        rc, c = eng.launch_result()
+        assert rc == 0 and c["frames"] == n
+        out, out_off = normalise(d_out.cpu().numpy(), d_out_off.cpu().numpy().astype(np.uint64), d_out_len.cpu().numpy().astype(np.uint32), bool(op & 8))
+        assert np.array_equal(d_status.cpu().numpy().astype(np.uint32), want_status)
+        assert np.array_equal(out_off, want_off) and np.array_equal(out[: int(want_off[n])], want_out)
+    finally:
+        eng.close()
+
+
 def test_empty_and_ragged_records(pkg, eng, oracle):
     payloads = [b"", b"", b"null", b"", b"x" * 5, b"", mg.canon("c", "t", 1, False, 2), b""] * 40 + [b""] * 300
     arena, off = oracle.pack(payloads)
