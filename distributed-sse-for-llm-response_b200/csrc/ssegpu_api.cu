@@ -139,8 +139,8 @@ struct ssegpu_ctx {
 
 namespace {
 
-// kernels per frame launch: ordered = count pass, tile scan, emit pass; arrival = the tile kernel
-uint32_t launches_of(uint32_t op) { return (op & SSEGPU_OP_ORDERED) ? 3 : 1; }
+// kernels per frame launch: ordered = count pass, tile scan (two launches), emit pass; arrival = the tile kernel
+uint32_t launches_of(uint32_t op) { return (op & SSEGPU_OP_ORDERED) ? 4 : 1; }
 
 // Frame kernels plus, in streaming inspection mode, the per-conversation walk.  Streaming batches of one context run in
 // submit order (each waits for the previous one's walk): the carried DFA state of a conversation that has tokens in
