@@ -147,8 +147,14 @@ constexpr uint32_t PREFETCH_WAVES = SSE_PREFETCH_WAVES;
 // payload's mbarrier: the threads then read their offsets on chip instead of waiting for a global load at the top of
 // every tile.  OFF_BYTES = (TILE + 1) words rounded up to the 16 bytes a bulk copy moves.
 constexpr uint32_t OFF_BYTES = ((TILE + 1) * 4 + 15) & ~15u;
-constexpr uint32_t PLAN_REDO = 0xFFFFFFFFu;             // FrameArgs::plan: decode this record again in the emit pass
+// FrameArgs::plan, one word per record, left by the counting pass of ordered mode for the emit pass.  A canonical
+// record: where its sequence literal starts (13 bits), where its id ends (11), the literal's digits (4), done, filtered
+// -- everything its frame depends on besides the payload itself, so the emit pass neither decodes it again nor loads its
+// status and length.  The reserved values:
+constexpr uint32_t PLAN_REDO = 0xFFFFFFFFu;             // decode this record again in the emit pass (status / out_len hold the counting pass's result)
 constexpr uint32_t PLAN_HOLE = 0xFFFFFFFEu;             // emit pass -> its tail: this record's frame is still to be written
+constexpr uint32_t PLAN_PENDING = 0xFFFFFFFDu;          // counting pass -> its tail: not decoded yet
+constexpr uint32_t PLAN_BYTES = TILE * 4;               // a full tile's plan words reach the emit pass by bulk copy, like the offsets
 constexpr uint32_t DEFER_MAX_PER_WARP = 9;              // more such records than this in a warp: decoded inline, where the tile is on chip
 struct TileSmem {
     uint64_t mbar;
@@ -215,7 +221,7 @@ __device__ __forceinline__ void park_tile(const FrameArgs& a, TileSmem* ts, uint
     ts->meta[slot].tile = t; ts->meta[slot].tb = tb; ts->meta[slot].te = te; ts->meta[slot].npend = 0;
 }
 // thread 0, once the input buffer is free: TMA load of the parked tile (payload and, when they all exist, its offsets)
-__device__ __forceinline__ void launch_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t slot, bool want_base) {
+__device__ __forceinline__ void launch_tile(const FrameArgs& a, TileSmem* ts, uint8_t* s_in, uint32_t slot, bool want_base, bool want_plan = false) {
     const uint32_t t = ts->meta[slot].tile;
     if (t >= a.num_tiles) return;
     uint64_t ob = 0;
@@ -223,9 +229,11 @@ __device__ __forceinline__ void launch_tile(const FrameArgs& a, TileSmem* ts, ui
     const uint32_t tb = ts->meta[slot].tb, te = ts->meta[slot].te;
     const TileShape sh = tile_shape(a, t, tb, te);
     if (sh.smem_in && sh.bytes != 0) {
-        mbar_expect_tx(&ts->mbar, sh.bytes + (sh.with_off ? OFF_BYTES : 0u));
+        const bool with_plan = want_plan && sh.with_off && a.plan_tma;
+        mbar_expect_tx(&ts->mbar, sh.bytes + (sh.with_off ? OFF_BYTES : 0u) + (with_plan ? PLAN_BYTES : 0u));
         tma_load_1d(s_in, a.in + sh.abase, sh.bytes, &ts->mbar);
         if (sh.with_off) tma_load_1d(reinterpret_cast<uint8_t*>(ts + 1), a.in_off + (size_t)t * TILE, OFF_BYTES, &ts->mbar);
+        if (with_plan) tma_load_1d(reinterpret_cast<uint8_t*>(ts + 1) + OFF_BYTES, a.plan + (size_t)t * TILE, PLAN_BYTES, &ts->mbar);
     }
     ts->c_in += te - tb;
     if (want_base) ts->obase = ob;
@@ -348,7 +356,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         uint32_t b0 = 0, e0 = 0;
         if (t0 < a.num_tiles) { b0 = a.in_off[t0 * TILE]; e0 = a.in_off[min((t0 + 1) * TILE, a.n)]; }
         park_tile(a, ts, 0, t0, b0, e0);
-        launch_tile(a, ts, s_in, 0, MODE == MODE_ORDERED_EMIT);
+        launch_tile(a, ts, s_in, 0, MODE == MODE_ORDERED_EMIT, MODE == MODE_ORDERED_EMIT && !EXT && a.plan != nullptr);
         ts->next_t = atomicAdd(a.ticket, 1u);
     }
     __syncthreads();                                                          // the first tile's entry is visible
@@ -424,18 +432,22 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         bool hole = false;
         if (MODE == MODE_ORDERED_EMIT && defer_ordered) {
             uint32_t pw = 0;
-            if (active) {
-                pw = a.plan[r0 + tid];                                        // left by the count pass
-                st = a.status[r0 + tid]; len = a.out_len[r0 + tid];
+            if (active) {                                                     // left by the count pass; on chip with the payload when the tile is full
+                if (off_smem && a.plan_tma) pw = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(ts + 1) + OFF_BYTES)[tid];
+                else pw = a.plan[r0 + tid];
             }
-            const bool redo = active && pw == PLAN_REDO;
+            const bool redo = active && pw >= PLAN_PENDING;
             const uint32_t nredo = __popc(__ballot_sync(0xFFFFFFFFu, redo));
-            if (redo && nredo < DEFER_MAX_PER_WARP) { hole = true; planned = true; a.plan[r0 + tid] = PLAN_HOLE; }
-            else if (active && !redo && smem_in) {
-                pl.fast = 1; pl.cid_b = 20; pl.seq_b = pw & 0x3FFFu; pl.cid_e = (pw >> 14) & 0x3FFFu; pl.seq_n = pw >> 28;
-                pl.done = (st & ST_DONE) ? 1u : 0u; pl.cid_esc = 0; pl.tok_esc = 0; pl.tok_redacted = 0;
+            if (redo && nredo < DEFER_MAX_PER_WARP) {
+                hole = true; planned = true;
+                st = a.status[r0 + tid]; len = a.out_len[r0 + tid];           // the counting pass's tail decoded it
+                a.plan[r0 + tid] = PLAN_HOLE;
+            } else if (active && !redo && smem_in) {
+                pl.fast = 1; pl.cid_b = 20; pl.seq_b = pw & 0x1FFFu; pl.cid_e = (pw >> 13) & 0x7FFu; pl.seq_n = (pw >> 24) & 0xFu;
+                pl.done = (pw >> 28) & 1u; pl.cid_esc = 0; pl.tok_esc = 0; pl.tok_redacted = 0;
+                fast_status_len(a.op, L, pl.cid_e - pl.cid_b, pl.seq_n, pl.done != 0, ((pw >> 29) & 1u) != 0, st, len);
                 fastp = true; planned = true;
-            } else { st = ST_OK; len = 0; }                                   // decoded again below
+            }                                                                 // else: decoded again below
             if (lane == 0 && nredo && nredo < DEFER_MAX_PER_WARP) atomicAdd(&ts->meta[slot].npend, nredo);
         }
         InterestPre ipre{0, 0, 0, 0, 0};
@@ -541,10 +553,11 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
         if (MODE == MODE_ORDERED_COUNT) {        // pass A of ordered mode: only the tile's byte count is wanted
             if (!EXT && a.plan && active) {      // what the emit pass needs of a canonical record, so that it does not decode it again
                 uint32_t pw = PLAN_REDO;
-                if (fastp && pl.seq_b < (1u << 14) && pl.cid_e < (1u << 14)) pw = pl.seq_b | (pl.cid_e << 14) | (pl.seq_n << 28);
+                if (fastp && pl.seq_b < (1u << 13) && pl.cid_e < (1u << 11))
+                    pw = pl.seq_b | (pl.cid_e << 13) | (pl.seq_n << 24) | (pl.done << 28) | ((st & ST_CODE_MASK) == ST_FILTERED ? 1u << 29 : 0u);
+                else if (st == ST_PENDING) pw = PLAN_PENDING;
                 a.plan[r0 + tid] = pw;
-                a.status[r0 + tid] = st;
-                a.out_len[r0 + tid] = len;
+                if (pw == PLAN_REDO) { a.status[r0 + tid] = st; a.out_len[r0 + tid] = len; }   // decoded here: what a hole in the emit pass needs
             }
             if (tid == 0) {
                 uint64_t w = total;
@@ -593,7 +606,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             if (!ordered && tid < alloc - total) s_out[total + tid] = 0;
             fence_proxy_async_smem();                                         // staging writes -> visible to the TMA store
             __syncthreads();                                                  // (D) s_in free, staging tile complete, base visible
-            if (tid == 0) { launch_tile(a, ts, s_in, slot ^ 1u, ordered); ts->next_t = ts->next2; }   // next tile's TMA load flies during the copy-out
+            if (tid == 0) { launch_tile(a, ts, s_in, slot ^ 1u, ordered, ordered && !EXT && a.plan != nullptr); ts->next_t = ts->next2; }   // next tile's TMA load flies during the copy-out
         } else {
             // ---- oversize tile: emit straight into the arena ---------------------------
             __syncthreads();                                                  // (D')
@@ -607,7 +620,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             }
             if (fits && tid < alloc - total) a.out[base + total + tid] = 0;       // pad of an aligned tile
             __syncthreads();                                                  // (E') s_in free
-            if (tid == 0) { launch_tile(a, ts, s_in, slot ^ 1u, ordered); ts->next_t = ts->next2; }
+            if (tid == 0) { launch_tile(a, ts, s_in, slot ^ 1u, ordered, ordered && !EXT && a.plan != nullptr); ts->next_t = ts->next2; }
         }
         if (active) {
             a.out_off[r0 + tid] = base + local;
@@ -679,7 +692,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
             uint32_t cnt = 0;
             while (t1 != 0 && cnt < (uint32_t)TILE) {
                 const uint32_t t = t1 - 1, i = t * TILE + tid;
-                if (i < a.n && (a.status[i] & ST_CODE_MASK) == ST_PENDING) s_list[atomicAdd(&ts->meta[0].npend, 1u)] = i;
+                if (i < a.n && a.plan[i] == PLAN_PENDING) s_list[atomicAdd(&ts->meta[0].npend, 1u)] = i;
                 t1 = (uint32_t)(a.tile_state[t] >> 32);
                 __syncthreads();
                 if (tid == 0) a.tile_state[t] &= 0xFFFFFFFFull;
@@ -695,6 +708,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
                     const uint32_t st = plan_slow(a.in, b, e - b, a.op, a.start_seq ? a.start_seq[i] : 0, &pl, &len);
                     a.status[i] = st;
                     a.out_len[i] = len;
+                    a.plan[i] = PLAN_REDO;
                     if (len) atomicAdd(reinterpret_cast<unsigned long long*>(&a.tile_state[i / TILE]), (unsigned long long)len);
                 }
             }
@@ -828,7 +842,7 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
 // ---------------------------------------------------------------------- launch ----
 // Shared memory per CTA: a tile of TILE records is ~17 KB in / ~21 KB out at the BASELINE workload; the caps leave
 // ~15% slack.  Tiles that exceed them take the direct global-memory path inside the same kernel.
-//   cfg 0  160 B in / 188 B out per record                      5 CTAs per SM (the SM's shared memory is then full)
+//   cfg 0  160 B in / 184 B out per record                      5 CTAs per SM (the SM's shared memory is then full)
 //   cfg 1  "wide": NATS PUB framing adds ~60 bytes per record (subject + protocol line): 224 B out
 //   cfg 2  fused per-token inspection of adapter frames: the on-chip DFA part (2.4 KB) has to fit beside five tiles
 //          per SM, so the caps shrink to 150 B in / 181 B out per record (~10 % slack at the BASELINE shape)
@@ -838,8 +852,9 @@ constexpr int N_CFG = 5;
 static void cfg_caps(int cfg, uint32_t* ic, uint32_t* oc, uint32_t* smem) {
     const bool cache = cfg >= 2;
     *ic = TILE * (cfg == 2 ? 150 : 160);
-    *oc = TILE * (cfg == 2 ? 181 : (cfg == 0 ? 188 : ((cfg == 1 || cfg == 4) ? 224 : 192)));
-    *smem = *ic + 32 + *oc + 48 + (uint32_t)sizeof(TileSmem) + OFF_BYTES + (cache ? DFA_CACHE_BYTES : 0u);
+    *oc = TILE * (cfg == 2 ? 181 : (cfg == 0 ? 184 : ((cfg == 1 || cfg == 4) ? 224 : 192)));
+    // behind the offsets: the plan words of ordered mode's emit pass (variants without inspection), or the DFA part
+    *smem = *ic + 32 + *oc + 48 + (uint32_t)sizeof(TileSmem) + OFF_BYTES + (cache ? DFA_CACHE_BYTES : PLAN_BYTES);
 }
 static_assert(sizeof(TileSmem) % 16 == 0, "the record offsets behind TileSmem are the target of a bulk copy");
 // The counting pass of ordered mode never stages a frame: launched with out_cap_s = 0 it needs the input tile only, and
@@ -966,6 +981,7 @@ cudaError_t frame_launch(int device, FrameArgs a, cudaStream_t stream) {
     if ((e = clear_scratch(a, stream)) != cudaSuccess) return e;
     if (a.n == 0) return cudaMemsetAsync(a.out_off, 0, sizeof(uint64_t), stream);
     a.off_tma = (reinterpret_cast<uintptr_t>(a.in_off) & 15) == 0 ? 1u : 0u;
+    a.plan_tma = (a.off_tma && a.plan != nullptr && (reinterpret_cast<uintptr_t>(a.plan) & 15) == 0) ? 1u : 0u;
     switch (ext) {
     case 0: launch_variant<0>(a, grid, smem_bytes, cl, stream); break;
     case 1: launch_variant<1>(a, grid, smem_bytes, cl, stream); break;

@@ -67,6 +67,7 @@ struct FrameArgs {
     void* zero_base = nullptr;   // what frame_launch clears before the launch (default: scratch_base, scratch_bytes(n))
     size_t zero_bytes = 0;
     uint32_t keep_bad_conv = 0;  // the clear leaves the bad_conv word alone (set by the streaming walk in front of this frame pass)
+    uint32_t plan_tma = 0;       // filled by frame_launch: the same for the plan words (ordered mode's emit pass)
     uint32_t off_tma = 0;        // filled by frame_launch: in_off is 16-byte aligned, a tile's offsets may ride along with its payload (TMA)
     // filled by frame_launch
     uint32_t num_tiles, in_cap, out_cap_s;

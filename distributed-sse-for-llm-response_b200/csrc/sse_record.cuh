@@ -894,6 +894,20 @@ SSE_HD bool fast_emit_ok(const Plan& pl, uint32_t op) {
     return pl.fast && !((op & OP_BRIDGE) && pl.cid_esc);
 }
 
+// Status word and output length of a canonical record from the few facts its frame depends on (the emit pass of
+// ordered mode recomputes them from the plan word the counting pass left, instead of loading them).
+SSE_HD void fast_status_len(uint32_t op, uint32_t L, uint32_t cid_len, uint32_t seq_n, bool done, bool filtered, uint32_t& st, uint32_t& out_len) {
+    out_len = 0;
+    if (filtered) { st = ST_FILTERED; return; }
+    out_len = (op & OP_BRIDGE) ? 12 + cid_len + L : 26 + seq_n + L;
+    if ((op & (OP_BRIDGE | OP_NATS_PUB)) == (OP_BRIDGE | OP_NATS_PUB)) out_len += 9 + dec_digits(L);   // "PUB " + " " + digits + CRLF, CRLF
+    st = done ? (ST_OK | ST_DONE) : ST_OK;
+    if (op & OP_HEADER_ONLY) {      // the payload (which IS the JSON) and the trailer stay with the host: only what precedes them is produced
+        out_len -= L + ((op & OP_BRIDGE) ? ((op & OP_NATS_PUB) ? 2u : 0u) : 2u);
+        st |= ST_HEADER_ONLY;
+    }
+}
+
 // Pass 1, canonical records only.  false = not canonical (or fast path disabled): call plan_record().
 template <class Src, class Hook>
 SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, int64_t start_seq,
@@ -901,15 +915,8 @@ SSE_HD bool plan_record_fast(const Src& s, uint32_t o, uint32_t L, uint32_t op, 
     pl.fast = 0;
     if ((op & OP_NO_FAST) || !parse_fast(s, o, L, op, pl, after_cid)) return false;
     if (!fast_emit_ok(pl, op)) return false;
-    out_len = 0;
-    if (!(op & OP_BRIDGE) && start_seq > 0 && pl.seq <= start_seq) { st = ST_FILTERED; return true; }   // sse_handler.go:143
-    out_len = (op & OP_BRIDGE) ? 12 + (pl.cid_e - pl.cid_b) + L : 26 + pl.seq_n + L;
-    if ((op & (OP_BRIDGE | OP_NATS_PUB)) == (OP_BRIDGE | OP_NATS_PUB)) out_len += 9 + dec_digits(L);   // "PUB " + " " + digits + CRLF, CRLF
-    st = pl.done ? (ST_OK | ST_DONE) : ST_OK;
-    if (op & OP_HEADER_ONLY) {      // the payload (which IS the JSON) and the trailer stay with the host: only what precedes them is produced
-        out_len -= L + ((op & OP_BRIDGE) ? ((op & OP_NATS_PUB) ? 2u : 0u) : 2u);
-        st |= ST_HEADER_ONLY;
-    }
+    const bool filtered = !(op & OP_BRIDGE) && start_seq > 0 && pl.seq <= start_seq;                      // sse_handler.go:143
+    fast_status_len(op, L, pl.cid_e - pl.cid_b, pl.seq_n, pl.done != 0, filtered, st, out_len);
     return true;
 }
 

@@ -267,8 +267,8 @@ int alloc_batch(ssegpu_ctx* ctx, ssegpu_batch** out) {
     CU(cudaMalloc(&b->d_conv, n * 4 + 4));
     b->ts_cap = (((n + sse::TILE - 1) / sse::TILE) * 8 + 15) & ~(size_t)15;
     const size_t meta_cap = sse::scratch_readback_bytes() + (n + 1) * 8 + n * (4 + 4 + 4 + 4 + 8 + 12) + 8 * 16;
-    CU(cudaMalloc(&b->d_block, b->ts_cap + meta_cap + n * 4 + 16));      // + the ordered-mode plan words (device only)
-    b->plan_off = b->ts_cap + meta_cap;
+    CU(cudaMalloc(&b->d_block, b->ts_cap + meta_cap + n * 4 + 32));      // + the ordered-mode plan words (device only)
+    b->plan_off = (b->ts_cap + meta_cap + 15) & ~(size_t)15;     // 16-byte aligned: the emit pass fetches a tile's plan words by bulk copy
     CU(cudaHostAlloc(&b->h_block, meta_cap, cudaHostAllocDefault));
     memset(b->h_block, 0, meta_cap);
     layout_results(b, (uint32_t)n, ~0u);
