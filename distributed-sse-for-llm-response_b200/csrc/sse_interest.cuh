@@ -189,9 +189,28 @@ SSE_HD void interest_finish(const InterestFast& t, const Src& s, uint32_t cid_b,
         if (q0 == 0) return;                                         // empty slot: nobody subscribed to this id
         if (q0 == pre.hash && q1 == len) {
             // the key words sit in the slot itself (second sector prefetched by slot_head): word-wise against the id in the tile
-            const uint32_t* key = t.slots[p].key;
             const uint32_t a = cid_b & ~3u, shb = (cid_b & 3u) * 8;
-            uint32_t lo = s.ld32a(a), diff = 0, k = 0;
+            uint32_t lo = s.ld32a(a), diff = 0;
+#if defined(__CUDA_ARCH__)
+            // all twelve key words requested at once (three 16-byte loads), then compared from registers: a loop of
+            // dependent 4-byte loads left one L1 round trip per word exposed
+            const uint4* kp = reinterpret_cast<const uint4*>(t.slots[p].key);
+            const uint4 ka = kp[0], kb = kp[1], kc = kp[2];
+            const uint32_t kw[INTEREST_INLINE_KEY / 4] = {ka.x, ka.y, ka.z, ka.w, kb.x, kb.y, kb.z, kb.w, kc.x, kc.y, kc.z, kc.w};
+            const uint32_t rem = len - 4 * (nw - 1);                 // 1..4 bytes in the last word
+#pragma unroll
+            for (uint32_t k = 0; k < INTEREST_INLINE_KEY / 4; k++) {
+                if (k < nw) {                                        // (words past the id are not loaded)
+                    const uint32_t hi = s.ld32a(a + 4 * k + 4);
+                    uint32_t w = funnel_r(lo, hi, shb);
+                    if (k + 1 == nw) w &= 0xFFFFFFFFu >> (8 * (4 - rem));
+                    diff |= w ^ kw[k];
+                    lo = hi;
+                }
+            }
+#else
+            const uint32_t* key = t.slots[p].key;
+            uint32_t k = 0;
             for (; k + 1 < nw; k++) {
                 const uint32_t hi = s.ld32a(a + 4 * k + 4);
                 diff |= funnel_r(lo, hi, shb) ^ key[k];
@@ -199,6 +218,7 @@ SSE_HD void interest_finish(const InterestFast& t, const Src& s, uint32_t cid_b,
             }
             const uint32_t rem = len - 4 * k;                        // 1..4 bytes in the last word
             diff |= (funnel_r(lo, s.ld32a(a + 4 * k + 4), shb) & (0xFFFFFFFFu >> (8 * (4 - rem)))) ^ key[k];
+#endif
             if (diff == 0) { h.list_off = q2; h.list_cnt = q3; return; }
         }
         p = (p + 1) & t.mask;

@@ -1,3 +1,2 @@
-set -x
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/r02_bench_v5_2gpu.json 2> gpurun_out/r02_bench_v5_2gpu.err; tail -c 300 gpurun_out/r02_bench_v5_2gpu.json
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --impl reference --gpus 2 --steps 3 --warmup 1 2>/dev/null | tail -c 300
+timeout 900 python -m pytest tests/test_gpu_interest.py tests/test_gpu_churn.py tests/test_gpu_ext_modes.py -m gpu -x -q 2>&1 | tail -2
+for w in match bridge; do timeout 200 python tools/prof_target.py $w 2>&1 | tail -1; done
