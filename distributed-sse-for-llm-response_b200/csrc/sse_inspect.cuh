@@ -125,7 +125,10 @@ template <bool STREAMING> SSE_HD void walk_event(Walk& w, uint32_t mask, uint32_
 template <bool STREAMING> SSE_HD void walk_byte(const DfaDev& d, const DfaCache& c, Walk& w, uint32_t byte) {
     const uint32_t k = w.st * c.n_classes + c.cls[byte];
     uint32_t nx;
-    if (w.st < c.n_cached) { nx = c.rows[k]; w.need = (nx >> DFA_PACK_SHIFT) & c.nmask; w.st = nx & c.cmask; }
+    if (STREAMING) {                                               // rows are never packed here, and a carried walk never stops early
+        nx = w.st < c.n_cached ? c.rows[k] : c.next[k];
+        w.st = nx & 0x7FFF;
+    } else if (w.st < c.n_cached) { nx = c.rows[k]; w.need = (nx >> DFA_PACK_SHIFT) & c.nmask; w.st = nx & c.cmask; }
     else { nx = c.next[k]; w.need = 0; w.st = nx & 0x7FFF; }       // the unanchored forward DFA has no dead state
     if (nx & 0x8000) {                                             // the target state reports a match: rare
         walk_event<STREAMING>(w, d.acc_del[w.st], w.idx);
