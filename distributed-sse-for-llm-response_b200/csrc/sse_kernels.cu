@@ -362,7 +362,17 @@ __global__ void __launch_bounds__(TILE, (MODE == MODE_ORDERED_COUNT && EXT == 0)
     __syncthreads();                                                          // the first tile's entry is visible
 
     // Barriers per tile: (B) behind the decode, (D) behind the staging (the counting pass of ordered mode: (B) only).
-    // Nothing is needed at the top: the tile's entry was parked before the previous trip's (B).
+    // Nothing is needed at the top: the tile's entry was parked before the previous trip's (B).  What keeps a fast warp of
+    // trip k+1 off a slow warp of trip k:
+    //   meta[slot], wsum[slot]   written before (B) of the trip that uses them next; the slot's previous user (two trips
+    //                            back) was read before that trip's (B), which every thread has passed since;
+    //   s_in, the offsets, plan  overwritten by the TMA load thread 0 issues behind (D) (behind (B) in the counting pass),
+    //                            i.e. after every thread has finished reading them; readers of the new contents wait on
+    //                            the mbarrier, whose phase cannot complete before thread 0's arrive.expect_tx;
+    //   s_out                    written behind (B); the previous tile's bulk store has finished reading it (thread 0's
+    //                            bulk_wait_read0 in front of (B));
+    //   base / obase             written by thread 0 behind (B) / (D), read behind the following barrier, rewritten only
+    //                            after the next (B) / (D), by which time every reader has arrived there.
     for (uint32_t trip = 0;; trip++) {
         const uint32_t slot = trip & 1u;
         const uint32_t tile = ts->meta[slot].tile;
