@@ -24,13 +24,16 @@ __global__ void __launch_bounds__(128) k_chunk_count(const ChunkArgs a) {
     ChunkEvents ev;
     const uint32_t st = chunk_line_dev(a.lines, a.line_off[i], a.line_off[i + 1], &ev);
     const PtrSrc src{a.lines};
-    uint32_t msgs = 0, bytes = 0;
+    uint32_t msgs = 0, bytes = 0, cb = 0, ce = 0;
     if (!(st & CHUNK_TOO_MANY)) {
         if ((st & CHUNK_KIND_MASK) == CHUNK_DATA)
             for (uint32_t k = 0; k < ev.len; k++)
-                if (ev.ch[k].has_content && ev.ch[k].ce > ev.ch[k].cb) { msgs++; bytes += chunk_content_bytes(src, ev.ch[k]); }
+                if (ev.ch[k].has_content && ev.ch[k].ce > ev.ch[k].cb) { msgs++; bytes += chunk_content_bytes(src, ev.ch[k]); cb = ev.ch[k].cb; ce = ev.ch[k].ce; }
+        // the usual line carries one delta: its content span is left for the emit pass, which then does not decode the line again
+        if (msgs != 1) cb = ce = 0;
         if (st & CHUNK_ENDS) { msgs++; bytes += 6; }
     }
+    a.span[2 * (size_t)i] = cb; a.span[2 * (size_t)i + 1] = ce;
     a.line_status[i] = st; a.cnt_msgs[i] = msgs; a.cnt_bytes[i] = bytes;
     if (i == a.n_lines - 1) { a.totals[3] = msgs; a.totals[4] = bytes; }
 }
@@ -50,7 +53,12 @@ __global__ void __launch_bounds__(128) k_chunk_emit(const ChunkArgs a) {
     if ((st & CHUNK_TOO_MANY) || !((st & CHUNK_ENDS) || (st & CHUNK_KIND_MASK) == CHUNK_DATA)) return;
     uint32_t m = a.cnt_msgs[i], w = a.cnt_bytes[i];
     const PtrSrc src{a.lines};
-    if ((st & CHUNK_KIND_MASK) == CHUNK_DATA) {
+    const uint32_t cb = a.span[2 * (size_t)i], ce = a.span[2 * (size_t)i + 1];
+    if ((st & CHUNK_KIND_MASK) == CHUNK_DATA && ce > cb) {              // one delta with content: span known from the count pass
+        a.tok_off[m] = w; a.done[m] = 0; a.msg_line[m] = i;
+        for_each_decoded_byte(src, cb, ce, [&](uint32_t b) { a.tok[w++] = (uint8_t)b; });
+        m++;
+    } else if ((st & CHUNK_KIND_MASK) == CHUNK_DATA) {
         ChunkEvents ev;
         chunk_line_dev(a.lines, a.line_off[i], a.line_off[i + 1], &ev);
         for (uint32_t k = 0; k < ev.len; k++) {
@@ -69,13 +77,14 @@ __global__ void __launch_bounds__(128) k_chunk_emit(const ChunkArgs a) {
 
 }  // namespace
 
-size_t chunk_scratch_bytes(uint32_t n_lines) { return ((size_t)n_lines * 2 + (size_t)n_lines / 4096 + 32) * 4; }
+size_t chunk_scratch_bytes(uint32_t n_lines) { return ((size_t)n_lines * 4 + (size_t)n_lines / 4096 + 32) * 4; }
 
 cudaError_t chunk_decode_launch(ChunkArgs a, void* scratch, cudaStream_t stream) {
     uint32_t* p = static_cast<uint32_t*>(scratch);
     a.totals = p; p += 8;
     a.cnt_msgs = p; p += a.n_lines;
     a.cnt_bytes = p; p += a.n_lines;
+    a.span = p; p += 2 * (size_t)a.n_lines;
     a.block_sums = p;
     cudaError_t e = cudaMemsetAsync(a.totals, 0, 32, stream);
     if (e != cudaSuccess) return e;

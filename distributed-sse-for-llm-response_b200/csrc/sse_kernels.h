@@ -134,7 +134,7 @@ struct WireArgs {
     uint32_t* msg_subj;          // out per delivery: (offset into buf, length) of the subject / channel
     uint32_t* conn_consumed; uint32_t* conn_status; uint32_t* conn_pings;   // out per connection
     // scratch (carved by wire_split_launch)
-    uint32_t* totals;            // [0] deliveries, [1] payload bytes, [2] overflow flag
+    uint32_t* totals;            // [0] deliveries, [1] payload bytes, [2] overflow flag, [4..5] the last connection's own counts
     uint32_t* cnt_msgs; uint32_t* cnt_bytes; uint32_t* msg_src;
 };
 size_t wire_scratch_bytes(uint32_t n_conn, uint32_t max_msgs);
@@ -155,6 +155,7 @@ struct ChunkArgs {
     // scratch (carved by chunk_decode_launch)
     uint32_t* totals;            // [0] messages, [1] token bytes, [2] overflow flag, [3..4] the last line's own counts
     uint32_t* cnt_msgs; uint32_t* cnt_bytes; uint32_t* block_sums;
+    uint32_t* span;              // 2 per line: content span of a line with exactly one delta (count pass -> emit pass), else 0, 0
 };
 size_t chunk_scratch_bytes(uint32_t n_lines);
 cudaError_t chunk_decode_launch(ChunkArgs a, void* scratch, cudaStream_t stream);

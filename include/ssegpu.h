@@ -275,7 +275,8 @@ int ssegpu_encode_launch_result(ssegpu_ctx *ctx, uint64_t *out_bytes);
  * d_msg_subj[2i], [2i+1] = offset (into d_buf) and length of the subject / channel.  Per connection d_conn_consumed =
  * bytes used (an incomplete trailing message stays in the socket buffer), d_conn_status = 0, or bit 0: protocol
  * violation at that offset, bit 1: a -ERR line was seen; d_conn_pings = PING lines (the host owes that many PONGs).
- * All pointers are device memory of this context's GPU.  Asynchronous on stream (NULL = the context's). */
+ * All pointers are device memory of this context's GPU; d_buf with 8 readable bytes behind the last connection's bytes
+ * (payloads are copied word-wise).  Asynchronous on stream (NULL = the context's). */
 #define SSEGPU_WIRE_NATS 0u
 #define SSEGPU_WIRE_RESP 1u
 int ssegpu_split_launch(ssegpu_ctx *ctx, uint32_t proto, const void *d_buf, const uint32_t *d_buf_off, uint32_t n_conn,

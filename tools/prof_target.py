@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Short single-kernel runs for ncu: a few launches of ONE mode of the frame kernel on a device-resident batch.
 
-  python tools/prof_target.py inspect|inspect_ab|stream|match|bridge|ordered|plain|wire|chunk [--launches K] [--conv N] [--tok T]
+  python tools/prof_target.py inspect|inspect_ab|stream|match|fanout|bridge|ordered|plain|wire|chunk [--launches K] [--conv N] [--tok T]
 
 inspect     config-2 shape, Set A, per-token      (k_frame_tiles<true,0>)
 inspect_ab  config-2 shape, Set A+B, per-token
@@ -108,7 +108,7 @@ if a.what == "chunk":
         rc, n_lines, n, int(loff[-1]), used, float(np.mean(ms)), min(ms), n_lines / min(ms) / 1e3, int(loff[-1]) / min(ms) / 1e6))
     eng.close()
     sys.exit(0)
-shape = {"inspect": (100_000, 32), "inspect_ab": (100_000, 32), "inspect_none": (100_000, 32), "plain32": (100_000, 32), "stream": (100_000, 32), "match": (100_000, 16), "bridge": (100_000, 16),
+shape = {"fanout": (100_000, 16), "inspect": (100_000, 32), "inspect_ab": (100_000, 32), "inspect_none": (100_000, 32), "plain32": (100_000, 32), "stream": (100_000, 32), "match": (100_000, 16), "bridge": (100_000, 16),
          "ordered": (10_000, 1000), "plain": (10_000, 1000)}[a.what]
 n_conv, n_tok = a.conv or shape[0], a.tok or shape[1]
 arena, off = pkg.workload.generate(1, n_conv, n_tok)
@@ -124,7 +124,7 @@ if a.what in ("inspect", "inspect_ab", "stream", "inspect_none"):
     if a.what == "stream":
         conv = torch.from_numpy(np.tile(np.arange(n_conv, dtype=np.int32), n_tok)).cuda()
         d_conv = conv.data_ptr()
-elif a.what == "match":
+elif a.what in ("match", "fanout"):
     rng = np.random.default_rng(0x5EED0004)
     ids = [pkg.workload.conversation_id(1, i) for i in range(n_conv)]
     fan = np.maximum(1, (1024.0 / np.arange(1, n_conv + 1) ** 1.1)).astype(np.int64)
@@ -144,6 +144,20 @@ elif a.what == "bridge":
 elif a.what == "ordered":
     op = pkg.OP_ORDERED
 
+if a.what == "fanout":
+    # config 3: the spans the match launch left -> flat (subscriber, record) delivery list
+    db.launch(eng, op, stream, d_conv)
+    stream.synchronize()
+    hit = db.d_hit.cpu().numpy().astype(np.uint32).reshape(-1, 3)
+    pairs = int(hit[:, 1].sum()) + int(sum(bin(int(m)).count("1") for m in np.unique(hit[:, 2])) * 0) + int(np.vectorize(lambda m: bin(int(m)).count("1"))(hit[:, 2]).sum())
+    d_sub = torch.empty(pairs + 16, dtype=torch.int32, device="cuda")
+    d_rec = torch.empty(pairs + 16, dtype=torch.int32, device="cuda")
+    d_roff = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+    ms = timed(lambda: eng.fanout_launch(db.d_hit.data_ptr(), n, d_sub.data_ptr(), d_rec.data_ptr(), pairs + 16, d_roff.data_ptr(), stream.cuda_stream), a.launches)
+    print("fanout: records=%d deliveries=%d  ms mean %.4f min %.4f  %.2f G deliveries/s, %.0f GB/s (12 B read per record + 8 B written per delivery)" % (
+        n, pairs, float(np.mean(ms)), min(ms), pairs / min(ms) / 1e6, (12 * n + 8 * pairs) / min(ms) / 1e6))
+    eng.close()
+    sys.exit(0)
 evs = []
 for _ in range(3 + a.launches):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
