@@ -66,7 +66,11 @@ template <class Src> SSE_HD void go_trim_space(const Src& s, uint32_t& b, uint32
 // ---- walking VALID JSON (the syntax check has run): positions only ----
 template <class Src> SSE_HD uint32_t jv_ws(const Src& s, uint32_t p) { while (is_ws(s.ld8(p))) p++; return p; }
 template <class Src> SSE_HD uint32_t jv_string_end(const Src& s, uint32_t p) {       // p on the opening quote -> past the closing quote
-    for (p++;; p++) { const uint32_t c = s.ld8(p); if (c == '\\') p++; else if (c == '"') return p + 1; }
+    for (p++;;) {                                    // (valid JSON: the closing quote exists; a word at a time between escapes)
+        p = find_byte2(s, p, 0xFFFFFFF0u, '"', '\\');
+        if (s.ld8(p) == '"') return p + 1;
+        p += 2;                                       // backslash + the byte it escapes
+    }
 }
 template <class Src> SSE_HD uint32_t jv_skip(const Src& s, uint32_t p) {             // p on the first byte of a value -> past it
     uint32_t depth = 0;
@@ -202,7 +206,7 @@ template <class Src> SSE_HD uint32_t chunk_line(const Src& s, uint32_t b, uint32
         if (same) return CHUNK_DONE_LINE | CHUNK_ENDS;
     }
     Plan unused;
-    if (parse_general(s, b, e - b, unused, nest) == ST_ERR_SYNTAX) return CHUNK_SKIP;   // whole-document syntax check, as Unmarshal does first
+    if (parse_general(s, b, e - b, unused, nest, true) == ST_ERR_SYNTAX) return CHUNK_SKIP;   // whole-document syntax check, as Unmarshal does first
     chunk_unmarshal(s, b, ev);
     if (ev.too_many) return CHUNK_DATA | CHUNK_TOO_MANY;
     if (ev.type_err) { ev.len = 0; return CHUNK_SKIP; }

@@ -48,25 +48,6 @@ template <class Src> SSE_HD bool wire_uint(const Src& s, uint32_t b, uint32_t e,
     return true;
 }
 
-// First position in [p, e) whose byte is c0 or c1, else e.  Word-wise (aligned 4-byte loads, exact zero-byte test on the
-// lowest match): one load per four bytes on the walk's dependent chain instead of one per byte.  Reads up to 3 bytes past e.
-template <class Src> SSE_HD uint32_t wire_find2(const Src& s, uint32_t p, uint32_t e, uint32_t c0, uint32_t c1) {
-    if (p >= e) return e;
-    uint32_t a = p & ~3u;
-    uint32_t w = s.ld32a(a);
-    const uint32_t before = ~(0xFFFFFFFFu << ((p & 3u) * 8));      // bytes in front of p
-    const uint32_t k0 = c0 * 0x01010101u, k1 = c1 * 0x01010101u;
-    for (;;) {
-        uint32_t x0 = w ^ k0, x1 = w ^ k1;
-        if (a < p) { x0 |= before; x1 |= before; }                  // first word only: what lies in front of p never matches
-        const uint32_t m = (((x0 - 0x01010101u) & ~x0) | ((x1 - 0x01010101u) & ~x1)) & 0x80808080u;
-        if (m) { const uint32_t q = a + first_byte_idx(m); return q < e ? q : e; }
-        a += 4;
-        if (a >= e) return e;
-        w = s.ld32a(a);
-    }
-}
-
 // Walks one connection's bytes [b, e).  emit(k, msg) is called for delivery number k (0-based) in stream order.
 template <class Src, class Emit>
 SSE_HD WireConn wire_walk_nats(const Src& s, uint32_t b, uint32_t e, Emit&& emit) {
@@ -74,7 +55,7 @@ SSE_HD WireConn wire_walk_nats(const Src& s, uint32_t b, uint32_t e, Emit&& emit
     uint32_t p = b;
     for (;;) {
         r.consumed = p - b;
-        const uint32_t q = wire_find2(s, p, e, '\n', '\n');
+        const uint32_t q = find_byte2(s, p, e, '\n', '\n');
         if (q >= e) return r;                                       // no complete control line
         uint32_t le = q;                                            // line = [p, le)
         if (le > p && s.ld8(le - 1) == '\r') le--;
@@ -84,7 +65,7 @@ SSE_HD WireConn wire_walk_nats(const Src& s, uint32_t b, uint32_t e, Emit&& emit
             while (i < le && wire_sp(s.ld8(i))) i++;
             if (i >= le) break;
             fb[nf] = i;
-            i = wire_find2(s, i, le, ' ', '\t');
+            i = find_byte2(s, i, le, ' ', '\t');
             fe[nf++] = i;
         }
         if (nf == 0) { r.status |= WIRE_ST_ERROR; return r; }
@@ -101,7 +82,7 @@ SSE_HD WireConn wire_walk_nats(const Src& s, uint32_t b, uint32_t e, Emit&& emit
                 (is_hmsg && !wire_uint(s, fb[nf - 2], fe[nf - 2], hdr)) || hdr > total || total > 0x7FFFFFFFull) { r.status |= WIRE_ST_ERROR; return r; }
             const uint64_t pend = (uint64_t)q + 1 + total;
             if (pend > e) return r;                                 // payload not complete yet
-            const uint32_t t = wire_find2(s, (uint32_t)pend, e, '\n', '\n');   // nats.go MSG_END: skip to the LF that closes the message
+            const uint32_t t = find_byte2(s, (uint32_t)pend, e, '\n', '\n');   // nats.go MSG_END: skip to the LF that closes the message
             if (t >= e) return r;
             WireMsg m;
             m.payload_off = q + 1 + (uint32_t)hdr; m.payload_len = (uint32_t)(total - hdr);
@@ -126,7 +107,7 @@ SSE_HD WireConn wire_walk_nats(const Src& s, uint32_t b, uint32_t e, Emit&& emit
 // One RESP line "<type><text>CRLF" starting at p: returns the position after the LF, 0 if incomplete, 0xFFFFFFFF on a
 // malformed terminator; [tb, te) is the text.
 template <class Src> SSE_HD uint32_t resp_line(const Src& s, uint32_t p, uint32_t e, uint32_t& tb, uint32_t& te) {
-    const uint32_t q = wire_find2(s, p + 1, e, '\n', '\n');
+    const uint32_t q = find_byte2(s, p + 1, e, '\n', '\n');
     if (q >= e) return 0;
     if (q < p + 2 || s.ld8(q - 1) != '\r') return 0xFFFFFFFFu;
     tb = p + 1; te = q - 1;
