@@ -8,18 +8,22 @@
 //
 // Shape (sm_100a):
 //   * persistent CTAs (grid = SMs x resident CTAs), tiles of TILE records handed out by an
-//     atomic ticket;
+//     atomic ticket, claimed two trips ahead by thread 0 (the next tile's byte range is loaded
+//     during the current tile's decode: two barriers per tile, none at the top);
 //   * a tile's payload bytes arrive in shared memory as ONE TMA bulk copy
-//     (cp.async.bulk ... mbarrier::complete_tx), 16-byte aligned, no register staging;
+//     (cp.async.bulk ... mbarrier::complete_tx), 16-byte aligned, no register staging; the
+//     tile's record offsets (and, in ordered mode's emit pass, its plan words) ride along as
+//     further bulk copies on the same mbarrier;
 //   * one thread per record runs sse_record.cuh (SWAR canonical check / general decoder);
 //   * frame lengths: warp-shuffle scan -> CTA scan; the tile's slice of the arena comes from an
 //     atomic cursor (arrival order, the default) or, in ordered mode, from a counting pass +
-//     one-CTA scan over the tile totals (see "ordered placement" below);
+//     a scan over the tile totals (see "ordered placement" below);
 //   * frames are assembled in a shared-memory staging tile BEFORE the tile's global offset is
 //     needed (the slice comes back from the atomic cursor while the frames are being written),
-//     then leave as ONE TMA bulk store into the tile's 16-byte aligned slice (ordered mode:
-//     coalesced 16-byte vector stores, byte-shifted on the fly to the dense arena's alignment,
-//     plus at most 15 head and 15 tail bytes): HBM sees only full-line traffic.
+//     then leave as ONE TMA bulk store into the tile's 16-byte aligned slice (ordered mode's
+//     emit pass knows the offset up front, stages at that offset modulo 16 and stores the
+//     aligned interior the same way, plus at most 15 head and 15 tail bytes by threads): HBM
+//     sees only full-line traffic.
 //   No tensor cores: nothing here is a contraction.
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -83,10 +87,11 @@ __device__ __forceinline__ void st_relaxed_u64(uint64_t* p, uint64_t v) {
 // earlier tiles' byte counts, i.e. it depends on the decode of every earlier record.  A single-pass decoupled
 // look-back was tried first (round 1, 2.2-2.3 ms per 10 M records): with ~740 persistent CTAs in flight every tile
 // waits for the slowest of hundreds of predecessors, the CTAs fall into lock-step waves and the 5 CTAs per SM stop
-// hiding one another's latencies.  Ordered mode is therefore two passes over the payload with a kernel boundary
-// as the global synchronisation: pass A decodes and records each tile's byte count, a one-CTA scan turns the
-// counts into offsets, pass B decodes again and emits at the known offsets.  The default (arrival-order) mode
-// stays a single pass.
+// hiding one another's latencies (round 2 tried again with a two-level look-back: profiles/r02_ablations.md).  Ordered
+// mode is therefore two passes over the payload with a kernel boundary as the global synchronisation: pass A decodes,
+// records each tile's byte count and leaves a plan word per canonical record, a scan turns the counts into offsets,
+// pass B emits at the known offsets from the plan words (it decodes only what pass A could not plan).  The default
+// (arrival-order) mode stays a single pass.
 constexpr int MODE_ARRIVAL = 0, MODE_ORDERED_COUNT = 1, MODE_ORDERED_EMIT = 2;
 
 // Tile totals -> exclusive prefixes, in place, in two small launches of one CTA per 1024 tiles: block sums first (parked in
