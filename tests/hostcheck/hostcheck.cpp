@@ -204,6 +204,11 @@ extern "C" int hc_encode(const uint8_t* cid, const uint32_t* cid_off, const uint
 
 // ---- wire splitter: the product's per-connection walk on the CPU (test double) ----
 #include "sse_wire.cuh"
+// the word-at-a-time byte search of the wire walkers and the chunk decoder, on its own
+extern "C" uint32_t hc_find_byte2(const uint8_t* buf, uint32_t p, uint32_t e, uint32_t c0, uint32_t c1) {
+    PtrSrc src{buf};
+    return find_byte2(src, p, e, c0, c1);
+}
 struct hc_wire_msg { uint32_t payload_off, payload_len, subj_off, subj_len; uint64_t sid; uint32_t conn, pad; };
 struct hc_wire_conn { uint32_t n_msgs, payload_bytes, consumed, status, pings; };
 extern "C" uint32_t hc_wire_split(uint32_t proto, const uint8_t* buf, const uint32_t* buf_off, uint32_t n_conn, hc_wire_msg* msgs, uint32_t cap,

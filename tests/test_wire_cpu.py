@@ -50,3 +50,27 @@ def test_product_walk_matches_oracle(oracle, proto):
     assert got == msgs
     assert [(oc[c].n_msgs, oc[c].consumed, oc[c].status, oc[c].pings) for c in range(n_conn)] == conns
     assert n > 5000 and sum(1 for x in conns if x[2] & 1) > 50
+
+
+def test_find_byte2_every_alignment_and_neighbour_value():
+    """The SWAR search under the walkers (sse_record.cuh find_byte2) against a byte loop: every start / end alignment, the
+    wanted bytes at every position, and the byte values that trip inexact zero-byte tests (c +- 1, 0x00, 0x01, 0x80, 0xFF)."""
+    import random
+    lib = hc.load()
+    lib.hc_find_byte2.restype = C.c_uint32
+    lib.hc_find_byte2.argtypes = [C.POINTER(C.c_uint8), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+    rng = random.Random(7)
+    for c0, c1 in ((10, 10), (32, 9), (34, 92), (0x80, 0x01)):
+        tricky = [c0, c1, c0 ^ 1, (c0 + 1) & 255, (c0 - 1) & 255, (c1 + 1) & 255, (c1 - 1) & 255, 0, 1, 0x7F, 0x80, 0x81, 0xFF, 65]
+        for trial in range(300):
+            n = 40
+            data = bytes(rng.choice(tricky) if rng.random() < 0.5 else rng.randrange(256) for _ in range(n)) + b"\xff" * 8
+            if trial % 3 == 0:                                   # long runs without a match
+                data = bytes(b if b not in (c0, c1) else 65 for b in data[:n]) + data[n:]
+            buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+            for p in range(0, 9):
+                for e in (p, p + 1, p + 2, p + 3, p + 5, 17, 31, n):
+                    if e < p:
+                        continue
+                    want = next((q for q in range(p, e) if data[q] in (c0, c1)), e)
+                    assert lib.hc_find_byte2(buf, p, e, c0, c1) == want, (c0, c1, data.hex(), p, e)
