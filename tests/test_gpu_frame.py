@@ -252,6 +252,35 @@ def test_oversize_tiles_use_global_path(pkg, eng, oracle):
         assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
 
 
+@pytest.mark.parametrize("op", [8, 8 | 1, 8 | 1 | 128, 0])
+def test_ordered_plan_word_field_limits(pkg, eng, oracle, op):
+    """Ordered mode's counting pass packs a canonical record's plan into 32 bits (start of the sequence literal < 8192, end of
+    the id < 2048).  Go-marshalled records beyond those widths that still fit the shared-memory tile must take the other
+    route (decoded again by the emit pass or its tail) and come out the same."""
+    payloads = []
+    for k in range(128 * 6):
+        if k % 128 == 5:
+            payloads.append(mg.canon("i" * 2100, "t", k, False, 2))            # id ends beyond 2047
+        elif k % 128 == 77:
+            payloads.append(mg.canon("c", "y" * 8200, k, k % 256 == 77, 2))    # sequence literal starts beyond 8191
+        elif k % 128 == 100:
+            payloads.append(mg.canon("j" * 2020, "t", k, False, 2))            # just inside / outside the id limit
+        else:
+            payloads.append(mg.canon("c", "t", k, False, 2))
+    arena, off = oracle.pack(payloads)
+    if op & 128:
+        want_out, want_off, want_subj, want_status = oracle.bridge_pub(arena, off)
+    elif op & 1:
+        want_out, want_off, want_subj, want_status = oracle.bridge(arena, off)
+    else:
+        want_out, want_off, want_status = oracle.adapter(arena, off)
+        want_subj = None
+    out, out_off, status, subj = run_batch(eng, arena, off, None, op)
+    assert np.array_equal(status, want_status) and np.array_equal(out_off, want_off) and np.array_equal(out, want_out)
+    if want_subj is not None:
+        assert np.array_equal(subj, want_subj)
+
+
 @pytest.mark.parametrize("op", [0, 8])
 @pytest.mark.parametrize("config,n_conv,n_tok", [(0, 1000, 512), (1, 10000, 100)])
 def test_baseline_workloads_bit_exact(pkg, eng, oracle, config, n_conv, n_tok, op):
